@@ -1,0 +1,199 @@
+/* svo_c.h - C ABI of the B200-native stereo-VO front end (libsvo.so).
+ *
+ * Drop-in boundary for the pixel work inside the reference's ImageProcessor / FeatureTracker
+ * (EpicDuckPotato/stereo_vo). The reference has no FFI layer of its own: its hot path is five
+ * OpenCV calls inside two C++ classes. Each entry point below replaces one of those call sites
+ * (file:line cited per function); include/stereo_vo/{image_processor,feature_tracker}.hpp keep
+ * the reference's C++ signatures on top of this ABI, INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *  - plain C: POD structs, raw pointers and sizes; no torch / OpenCV / Eigen types.
+ *  - every function returns 0 on success or a negative svo_status; nothing throws across the
+ *    ABI; svo_last_error() gives a human-readable string for the last failure of an engine.
+ *  - caller pointers are never retained past a call: inputs are copied to the device
+ *    (pinned staging + cudaMemcpyAsync), outputs are written to caller-owned arrays.
+ *  - an engine owns one CUDA stream and the device state of `n_seq` independent sequences
+ *    (camera streams). An engine is not thread-safe; distinct engines may be driven from
+ *    different threads. Sequences of one engine are processed together by batched kernels.
+ *  - images are 8-bit grey, row-major, `pitch` bytes per row, size fixed at svo_create().
+ *  - there is no CPU fallback: if no CUDA device is usable every call fails with
+ *    SVO_ERR_CUDA.
+ */
+#ifndef SVO_C_H_
+#define SVO_C_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#if defined(__GNUC__)
+#define SVO_API __attribute__((visibility("default")))
+#else
+#define SVO_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum svo_status {
+    SVO_OK = 0,
+    SVO_ERR_INVALID = -1,      /* bad argument */
+    SVO_ERR_CUDA = -2,         /* CUDA runtime failure (see svo_last_error) */
+    SVO_ERR_CAPACITY = -3,     /* a device buffer overflowed (candidates / features) */
+    SVO_ERR_STATE = -4,        /* call sequence violated (e.g. track before init) */
+    SVO_ERR_NOMEM = -5
+} svo_status;
+
+/* Algorithm constants. svo_default_params() fills the reference's hard-coded values. */
+typedef struct svo_params {
+    int32_t width, height;          /* image size of every frame given to this engine */
+    /* cv::goodFeaturesToTrack(left, out, 300, 0.1, min_feature_distance)  image_processor.cpp:22 */
+    int32_t max_corners;            /* 300 */
+    double quality_level;           /* 0.1 */
+    float min_distance;             /* 30 (vo_node.cpp:34) */
+    int32_t max_candidates;         /* NMS survivor capacity per image; 0 = automatic */
+    /* cv::StereoBM::create(16*3, 21)  image_processor.cpp:174 (+ OpenCV defaults) */
+    int32_t num_disparities;        /* 48 */
+    int32_t sad_window;             /* 21 */
+    int32_t prefilter_cap;          /* 31 */
+    int32_t texture_threshold;      /* 10 */
+    int32_t uniqueness_ratio;       /* 15 */
+    /* cv::calcOpticalFlowPyrLK(..., Size(21,21), 3, {COUNT+EPS,30,0.01}, 0, 1e-2)  feature_tracker.cpp:23-26 */
+    int32_t lk_max_level;           /* 3 (window is fixed at 21x21) */
+    int32_t lk_max_iters;           /* 30 */
+    double lk_epsilon;              /* 0.01 */
+    double lk_min_eig_threshold;    /* 1e-2 */
+    /* FeatureTracker::track_features filter  feature_tracker.cpp:47,53 */
+    float fb_max_error;             /* 2 px forward-backward */
+    float max_parallax;             /* 200 px */
+    int32_t max_features;           /* tracker capacity; 400 = bundle_adjuster.hpp:75 */
+    /* launch tuning (no effect on results) */
+    int32_t lk_warps_per_point;     /* 1, 2 or 4; 0 = default */
+} svo_params;
+
+typedef struct svo_engine svo_engine;   /* opaque */
+
+typedef struct svo_float2 { float x, y; } svo_float2;
+typedef struct svo_float3 { float x, y, z; } svo_float3;
+
+typedef struct svo_track_stats {
+    float av_parallax;      /* feature_tracker.cpp:63 */
+    float percent_lost;     /* feature_tracker.cpp:64 */
+    int32_t n_kept;
+    int32_t n_attempted;
+} svo_track_stats;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+SVO_API void svo_default_params(svo_params* p, int32_t width, int32_t height);
+SVO_API int svo_create(const svo_params* p, int32_t device, int32_t n_seq, svo_engine** out);
+SVO_API void svo_destroy(svo_engine* e);
+SVO_API const char* svo_last_error(const svo_engine* e);   /* e may be NULL: last create() failure */
+SVO_API int svo_get_params(const svo_engine* e, svo_params* out);
+SVO_API int svo_num_levels(const svo_engine* e);            /* pyramid levels actually built */
+/* kernels launched by this engine since creation (bench.py reports the delta per step) */
+SVO_API int64_t svo_kernel_launches(const svo_engine* e);
+/* device-side time of the last svo_step()/stage call's kernels, CUDA events on the engine stream */
+SVO_API float svo_last_gpu_ms(const svo_engine* e);
+/* ms[0] input copies, ms[1] kernels, ms[2] result copy of the last call (CUDA events) */
+SVO_API int svo_last_timing(const svo_engine* e, float ms[3]);
+
+/* ---- stage calls: one reference call site each, single sequence, synchronous ---------- */
+
+/* cv::goodFeaturesToTrack at src/image_processor.cpp:22. Uploads `img` as the current left
+ * frame of `seq` (and builds its pyramid). out_xy holds max_corners entries. */
+SVO_API int svo_good_features_to_track(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pitch,
+                               svo_float2* out_xy, int32_t* out_n);
+
+/* ImageProcessor::triangulate_stereo, src/image_processor.cpp:165-208: StereoBM(48,21) at the
+ * given features + Q reprojection with `pose` (4x4 row-major, camera->world). Outputs hold n
+ * entries; valid_idx[k] is the input index of the k-th valid feature; disp16 is the raw 1/16 px
+ * StereoBM value at EVERY input feature (n entries, -16 = rejected). */
+SVO_API int svo_triangulate_stereo(svo_engine* e, int32_t seq, const uint8_t* left, const uint8_t* right,
+                           int32_t pitch, const svo_float2* feats, int32_t n, const float pose[16],
+                           float focal, float cx, float cy, float baseline,
+                           svo_float3* out_3d, svo_float2* out_valid_2d, int32_t* out_valid_idx,
+                           int16_t* out_disp16, int32_t* out_n_valid);
+
+/* FeatureTracker::init, src/feature_tracker.cpp:3-16 */
+SVO_API int svo_tracker_init(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pitch,
+                     const svo_float2* feats, const uint64_t* ids, int32_t n);
+
+/* FeatureTracker::track_features, src/feature_tracker.cpp:18-67 (LK forward, LK backward when
+ * flow_back, filter, statistics; the tracker then holds the kept set and `img` as last_image) */
+SVO_API int svo_tracker_track(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pitch,
+                      int32_t flow_back, float* av_parallax, float* percent_lost);
+
+/* FeatureTracker::get_tracked_features, src/feature_tracker.cpp:69-72 (max_features entries) */
+SVO_API int svo_tracker_get(svo_engine* e, int32_t seq, svo_float2* feats, uint64_t* ids, int32_t* n);
+
+/* new-vs-tracked dedupe, src/image_processor.cpp:113-128: keep detection i iff no tracked point
+ * within min_distance. out_* hold n_det entries. */
+SVO_API int svo_dedupe(svo_engine* e, int32_t seq, const svo_float2* det, int32_t n_det,
+               const svo_float2* tracked, int32_t n_tracked, float min_distance,
+               svo_float2* out_xy, int32_t* out_keep_idx, int32_t* out_n);
+
+/* taps of the last track call (parity tests): LK outputs before filtering, n_attempted entries */
+SVO_API int svo_tracker_debug(svo_engine* e, int32_t seq, svo_float2* tracked, uint8_t* status1,
+                      svo_float2* reverse, uint8_t* status2, int32_t* kept_idx, int32_t* n_attempted);
+
+/* ---- component taps (parity tests / profiling) ----------------------------------------- */
+/* eig map of cv::cornerMinEigenVal(img, 3, 3) for the current left frame of `seq`; out is
+ * height x width floats, contiguous */
+SVO_API int svo_debug_min_eigen_map(svo_engine* e, int32_t seq, float* out);
+/* pyramid level `level` of the current left frame; out is h_l x w_l bytes, contiguous */
+SVO_API int svo_debug_pyramid_level(svo_engine* e, int32_t seq, int32_t level, uint8_t* out,
+                            int32_t* w, int32_t* h);
+/* sorted NMS candidates of the last detection (x, y), at most cap entries */
+SVO_API int svo_debug_candidates(svo_engine* e, int32_t seq, int32_t* xy, int32_t cap, int32_t* n);
+
+/* ---- fused, batched frame step (the throughput path used by ImageProcessor::process) ---- */
+
+/* Phase A for n listed sequences: upload the stereo pair, build the left pyramid, detect
+ * corners (image_processor.cpp:22) and - for sequences whose tracker is initialised - run
+ * track_features (feature_tracker.cpp:18-67) against the previous frame. Tracking is skipped,
+ * as in the reference, when fewer than 4 corners were found (image_processor.cpp:23-25).
+ * Inputs are HOST pointers: left[i], right[i] for sequence seqs[i].
+ * Outputs (host, caller-owned, may be NULL to skip a copy):
+ *   corners   [n][max_corners]   n_corners [n]
+ *   stats     [n]                (n_attempted == 0 when the tracker was not run)
+ *   tracked   [n][max_features]  tracked_ids [n][max_features]   (kept set, n_kept entries) */
+SVO_API int svo_step(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* left,
+             const uint8_t* const* right, int32_t pitch, svo_float2* corners, int32_t* n_corners,
+             svo_track_stats* stats, svo_float2* tracked, uint64_t* tracked_ids);
+
+/* Same as svo_step but the frames are already resident in device memory (device pointers,
+ * `pitch` bytes per row): the bench's kernel-only leg. */
+SVO_API int svo_step_device(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* d_left,
+                    const uint8_t* const* d_right, int32_t pitch, svo_float2* corners,
+                    int32_t* n_corners, svo_track_stats* stats, svo_float2* tracked,
+                    uint64_t* tracked_ids);
+
+/* Phase B for the sequences that became keyframes (image_processor.cpp:113-142): dedupe the
+ * corners of the current frame against the PnP-inlier tracked points, StereoBM + reprojection of
+ * the remaining new features with `poses[i]` (camera->world, 4x4 row major).
+ *   inliers [n][max_features] with n_inliers[i] valid entries each (0 for the first keyframe)
+ * Outputs per sequence i (stride max_corners):
+ *   new_feats / n_new       detections that survived the dedupe, in order
+ *   valid_2d, pts_3d, valid_idx (index into new_feats), n_valid; disp16 for every new feature */
+SVO_API int svo_keyframe(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* inliers,
+                 const int32_t* n_inliers, const float* poses, float focal, float cx, float cy,
+                 float baseline, svo_float2* new_feats, int32_t* n_new, svo_float2* valid_2d,
+                 svo_float3* pts_3d, int32_t* valid_idx, int16_t* disp16, int32_t* n_valid);
+
+/* FeatureTracker::init against the CURRENT frame of each listed sequence
+ * (image_processor.cpp:51-52,148-162): feats/ids [n][max_features], counts[i] entries. */
+SVO_API int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,
+                    const uint64_t* ids, const int32_t* counts);
+
+/* device allocation helpers for callers that keep frames resident (bench kernel-only leg) */
+SVO_API int svo_device_alloc(svo_engine* e, size_t bytes, void** out);
+SVO_API int svo_device_free(svo_engine* e, void* p);
+SVO_API int svo_device_upload(svo_engine* e, void* dst, const void* src, size_t bytes);
+/* pinned host memory for frame buffers (asynchronous H2D from caller memory) */
+SVO_API int svo_host_alloc(size_t bytes, void** out);
+SVO_API int svo_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVO_C_H_ */

@@ -1,0 +1,390 @@
+"""ctypes binding of include/svo_c.h (libsvo.so). Test / bench harness plumbing only: numpy
+arrays in, numpy arrays out. There is no fallback: if the CUDA library is missing or no GPU is
+usable, loading or engine creation raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsvo.so")
+
+SVO_OK = 0
+ERR_NAMES = {0: "SVO_OK", -1: "SVO_ERR_INVALID", -2: "SVO_ERR_CUDA", -3: "SVO_ERR_CAPACITY",
+             -4: "SVO_ERR_STATE", -5: "SVO_ERR_NOMEM"}
+
+
+class SvoParams(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32),
+        ("max_corners", C.c_int32), ("quality_level", C.c_double), ("min_distance", C.c_float),
+        ("max_candidates", C.c_int32),
+        ("num_disparities", C.c_int32), ("sad_window", C.c_int32), ("prefilter_cap", C.c_int32),
+        ("texture_threshold", C.c_int32), ("uniqueness_ratio", C.c_int32),
+        ("lk_max_level", C.c_int32), ("lk_max_iters", C.c_int32), ("lk_epsilon", C.c_double),
+        ("lk_min_eig_threshold", C.c_double),
+        ("fb_max_error", C.c_float), ("max_parallax", C.c_float), ("max_features", C.c_int32),
+        ("lk_warps_per_point", C.c_int32),
+    ]
+
+
+class SvoTrackStats(C.Structure):
+    _fields_ = [("av_parallax", C.c_float), ("percent_lost", C.c_float),
+                ("n_kept", C.c_int32), ("n_attempted", C.c_int32)]
+
+
+STATS_DTYPE = np.dtype([("av_parallax", np.float32), ("percent_lost", np.float32),
+                        ("n_kept", np.int32), ("n_attempted", np.int32)])
+
+# every symbol include/svo_c.h declares (tests check that the library exports all of them)
+EXPORTS = [
+    "svo_default_params", "svo_create", "svo_destroy", "svo_last_error", "svo_get_params",
+    "svo_num_levels", "svo_kernel_launches", "svo_last_gpu_ms", "svo_last_timing",
+    "svo_good_features_to_track", "svo_triangulate_stereo", "svo_tracker_init",
+    "svo_tracker_track", "svo_tracker_get", "svo_dedupe", "svo_tracker_debug",
+    "svo_debug_min_eigen_map", "svo_debug_pyramid_level", "svo_debug_candidates",
+    "svo_step", "svo_step_device", "svo_keyframe", "svo_tracker_set",
+    "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
+]
+
+_lib = None
+
+
+class SvoError(RuntimeError):
+    pass
+
+
+def load_library(path: Optional[str] = None):
+    """dlopen libsvo.so; raises (never falls back) when it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = path or LIB_PATH
+    if not os.path.exists(p):
+        raise SvoError(f"{p} is missing: build it with `python -m stereo_vo_b200.build` "
+                       "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(p)
+    vp, i32, f32 = C.c_void_p, C.c_int32, C.c_float
+    lib.svo_default_params.argtypes = [C.POINTER(SvoParams), i32, i32]
+    lib.svo_default_params.restype = None
+    lib.svo_create.argtypes = [C.POINTER(SvoParams), i32, i32, C.POINTER(vp)]
+    lib.svo_destroy.argtypes = [vp]
+    lib.svo_destroy.restype = None
+    lib.svo_last_error.argtypes = [vp]
+    lib.svo_last_error.restype = C.c_char_p
+    lib.svo_get_params.argtypes = [vp, C.POINTER(SvoParams)]
+    lib.svo_num_levels.argtypes = [vp]
+    lib.svo_kernel_launches.argtypes = [vp]
+    lib.svo_kernel_launches.restype = C.c_int64
+    lib.svo_last_gpu_ms.argtypes = [vp]
+    lib.svo_last_gpu_ms.restype = f32
+    lib.svo_last_timing.argtypes = [vp, C.POINTER(f32)]
+    lib.svo_good_features_to_track.argtypes = [vp, i32, vp, i32, vp, C.POINTER(i32)]
+    lib.svo_triangulate_stereo.argtypes = [vp, i32, vp, vp, i32, vp, i32, vp, f32, f32, f32, f32,
+                                           vp, vp, vp, vp, C.POINTER(i32)]
+    lib.svo_tracker_init.argtypes = [vp, i32, vp, i32, vp, vp, i32]
+    lib.svo_tracker_track.argtypes = [vp, i32, vp, i32, i32, C.POINTER(f32), C.POINTER(f32)]
+    lib.svo_tracker_get.argtypes = [vp, i32, vp, vp, C.POINTER(i32)]
+    lib.svo_dedupe.argtypes = [vp, i32, vp, i32, vp, i32, f32, vp, vp, C.POINTER(i32)]
+    lib.svo_tracker_debug.argtypes = [vp, i32, vp, vp, vp, vp, vp, C.POINTER(i32)]
+    lib.svo_debug_min_eigen_map.argtypes = [vp, i32, vp]
+    lib.svo_debug_pyramid_level.argtypes = [vp, i32, i32, vp, C.POINTER(i32), C.POINTER(i32)]
+    lib.svo_debug_candidates.argtypes = [vp, i32, vp, i32, C.POINTER(i32)]
+    lib.svo_step.argtypes = [vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp]
+    lib.svo_step_device.argtypes = [vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp]
+    lib.svo_keyframe.argtypes = [vp, i32, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp,
+                                 vp, vp]
+    lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]
+    lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
+    lib.svo_device_free.argtypes = [vp, vp]
+    lib.svo_device_upload.argtypes = [vp, vp, vp, C.c_size_t]
+    lib.svo_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+    lib.svo_host_free.argtypes = [vp]
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def default_params(width: int, height: int) -> SvoParams:
+    p = SvoParams()
+    load_library().svo_default_params(C.byref(p), width, height)
+    return p
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _img(a: np.ndarray) -> np.ndarray:
+    if a.dtype != np.uint8 or a.ndim != 2:
+        raise ValueError("image must be a 2-D uint8 array")
+    if a.strides[1] != 1:
+        a = np.ascontiguousarray(a)
+    return a
+
+
+def pinned_empty(shape, dtype=np.uint8) -> np.ndarray:
+    """numpy view on page-locked host memory (freed when the array is garbage collected)."""
+    lib = load_library()
+    nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = C.c_void_p()
+    if lib.svo_host_alloc(max(nbytes, 1), C.byref(p)) != 0:
+        raise SvoError("svo_host_alloc failed")
+    buf = (C.c_uint8 * max(nbytes, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    _PINNED[id(buf)] = (buf, p)
+    return arr
+
+
+_PINNED: dict = {}
+
+
+class Engine:
+    """One svo_engine: `n_seq` independent stereo sequences on one device / stream."""
+
+    def __init__(self, width: int, height: int, n_seq: int = 1, device: int = 0,
+                 params: Optional[SvoParams] = None, **overrides):
+        self.lib = load_library()
+        p = params or default_params(width, height)
+        p.width, p.height = width, height
+        for k, v in overrides.items():
+            if not hasattr(p, k):
+                raise AttributeError(k)
+            setattr(p, k, v)
+        h = C.c_void_p()
+        rc = self.lib.svo_create(C.byref(p), device, n_seq, C.byref(h))
+        if rc != 0:
+            msg = self.lib.svo_last_error(None)
+            raise SvoError(f"svo_create failed ({ERR_NAMES.get(rc, rc)}): "
+                           f"{msg.decode() if msg else ''}")
+        self.h = h
+        self.params = SvoParams()
+        self.lib.svo_get_params(self.h, C.byref(self.params))
+        self.n_seq = n_seq
+        self.width, self.height = width, height
+        self.max_corners = self.params.max_corners
+        self.max_features = self.params.max_features
+        self.cap = max(self.max_corners, self.max_features)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.svo_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int, what: str):
+        if rc != 0:
+            msg = self.lib.svo_last_error(self.h)
+            raise SvoError(f"{what} failed ({ERR_NAMES.get(rc, rc)}): {msg.decode() if msg else ''}")
+
+    # -- introspection ------------------------------------------------------------------
+    @property
+    def num_levels(self) -> int:
+        return self.lib.svo_num_levels(self.h)
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self.lib.svo_kernel_launches(self.h))
+
+    def last_timing(self):
+        ms = (C.c_float * 3)()
+        self.lib.svo_last_timing(self.h, ms)
+        return float(ms[0]), float(ms[1]), float(ms[2])
+
+    # -- stage calls ----------------------------------------------------------------------
+    def good_features_to_track(self, img: np.ndarray, seq: int = 0) -> np.ndarray:
+        img = _img(img)
+        out = np.zeros((self.max_corners, 2), np.float32)
+        n = C.c_int32()
+        self._check(self.lib.svo_good_features_to_track(self.h, seq, _ptr(img), img.strides[0],
+                                                        _ptr(out), C.byref(n)),
+                    "svo_good_features_to_track")
+        return out[:n.value].copy()
+
+    def triangulate_stereo(self, left, right, feats, pose, focal, cx, cy, baseline, seq: int = 0):
+        left, right = _img(left), _img(right)
+        if left.strides[0] != right.strides[0]:
+            right = np.ascontiguousarray(right)
+            left = np.ascontiguousarray(left)
+        feats = np.ascontiguousarray(feats, np.float32).reshape(-1, 2)
+        n = feats.shape[0]
+        pose = np.ascontiguousarray(pose, np.float32).reshape(16)
+        o3 = np.zeros((max(n, 1), 3), np.float32)
+        o2 = np.zeros((max(n, 1), 2), np.float32)
+        oi = np.zeros(max(n, 1), np.int32)
+        od = np.zeros(max(n, 1), np.int16)
+        nv = C.c_int32()
+        self._check(self.lib.svo_triangulate_stereo(
+            self.h, seq, _ptr(left), _ptr(right), left.strides[0], _ptr(feats), n, _ptr(pose),
+            float(focal), float(cx), float(cy), float(baseline), _ptr(o3), _ptr(o2), _ptr(oi),
+            _ptr(od), C.byref(nv)), "svo_triangulate_stereo")
+        k = nv.value
+        return o3[:k].copy(), o2[:k].copy(), oi[:k].copy(), od[:n].copy()
+
+    def tracker_init(self, img, feats, ids, seq: int = 0):
+        img = _img(img)
+        feats = np.ascontiguousarray(feats, np.float32).reshape(-1, 2)
+        ids = np.ascontiguousarray(ids, np.uint64).reshape(-1)
+        self._check(self.lib.svo_tracker_init(self.h, seq, _ptr(img), img.strides[0], _ptr(feats),
+                                              _ptr(ids), feats.shape[0]), "svo_tracker_init")
+
+    def tracker_track(self, img, flow_back: bool = True, seq: int = 0):
+        img = _img(img)
+        av, lost = C.c_float(), C.c_float()
+        self._check(self.lib.svo_tracker_track(self.h, seq, _ptr(img), img.strides[0],
+                                               1 if flow_back else 0, C.byref(av), C.byref(lost)),
+                    "svo_tracker_track")
+        return np.float32(av.value), np.float32(lost.value)
+
+    def tracker_get(self, seq: int = 0):
+        feats = np.zeros((self.max_features, 2), np.float32)
+        ids = np.zeros(self.max_features, np.uint64)
+        n = C.c_int32()
+        self._check(self.lib.svo_tracker_get(self.h, seq, _ptr(feats), _ptr(ids), C.byref(n)),
+                    "svo_tracker_get")
+        return feats[:n.value].copy(), ids[:n.value].copy()
+
+    def tracker_debug(self, seq: int = 0):
+        mf = self.max_features
+        tracked = np.zeros((mf, 2), np.float32)
+        reverse = np.zeros((mf, 2), np.float32)
+        s1 = np.zeros(mf, np.uint8)
+        s2 = np.zeros(mf, np.uint8)
+        kept = np.zeros(mf, np.int32)
+        n = C.c_int32()
+        self._check(self.lib.svo_tracker_debug(self.h, seq, _ptr(tracked), _ptr(s1), _ptr(reverse),
+                                               _ptr(s2), _ptr(kept), C.byref(n)),
+                    "svo_tracker_debug")
+        k = n.value
+        return dict(tracked=tracked[:k], status1=s1[:k], reverse=reverse[:k], status2=s2[:k],
+                    kept_idx=kept)
+
+    def dedupe(self, det, tracked, min_distance: float, seq: int = 0):
+        det = np.ascontiguousarray(det, np.float32).reshape(-1, 2)
+        tracked = np.ascontiguousarray(tracked, np.float32).reshape(-1, 2)
+        out = np.zeros((max(det.shape[0], 1), 2), np.float32)
+        keep = np.zeros(max(det.shape[0], 1), np.int32)
+        n = C.c_int32()
+        self._check(self.lib.svo_dedupe(self.h, seq, _ptr(det), det.shape[0], _ptr(tracked),
+                                        tracked.shape[0], float(min_distance), _ptr(out),
+                                        _ptr(keep), C.byref(n)), "svo_dedupe")
+        return out[:n.value].copy(), keep[:n.value].copy()
+
+    # -- taps -------------------------------------------------------------------------------
+    def debug_min_eigen_map(self, seq: int = 0) -> np.ndarray:
+        out = np.zeros((self.height, self.width), np.float32)
+        self._check(self.lib.svo_debug_min_eigen_map(self.h, seq, _ptr(out)),
+                    "svo_debug_min_eigen_map")
+        return out
+
+    def debug_pyramid_level(self, level: int, seq: int = 0) -> np.ndarray:
+        w, h = C.c_int32(), C.c_int32()
+        self._check(self.lib.svo_debug_pyramid_level(self.h, seq, level, None, C.byref(w),
+                                                     C.byref(h)), "svo_debug_pyramid_level")
+        out = np.zeros((h.value, w.value), np.uint8)
+        self._check(self.lib.svo_debug_pyramid_level(self.h, seq, level, _ptr(out), C.byref(w),
+                                                     C.byref(h)), "svo_debug_pyramid_level")
+        return out
+
+    def debug_candidates(self, seq: int = 0, cap: int = 1 << 20) -> np.ndarray:
+        n = C.c_int32()
+        self._check(self.lib.svo_debug_candidates(self.h, seq, None, 0, C.byref(n)),
+                    "svo_debug_candidates")
+        m = min(n.value, cap)
+        xy = np.zeros((max(m, 1), 2), np.int32)
+        self._check(self.lib.svo_debug_candidates(self.h, seq, _ptr(xy), m, C.byref(n)),
+                    "svo_debug_candidates")
+        return xy[:m]
+
+    # -- fused batched path ------------------------------------------------------------------
+    def _ptr_array(self, imgs: Sequence[np.ndarray]):
+        arr = (C.c_void_p * len(imgs))()
+        for i, im in enumerate(imgs):
+            arr[i] = im.ctypes.data if isinstance(im, np.ndarray) else int(im)
+        return arr
+
+    def step(self, seqs, left, right, pitch: Optional[int] = None, device: bool = False,
+             want_tracked: bool = True):
+        """svo_step / svo_step_device. `left`/`right`: lists of uint8 images (or raw device
+        pointers when device=True). Returns dict of per-listed-sequence results."""
+        n = len(seqs)
+        seqs_a = np.ascontiguousarray(seqs, np.int32)
+        if not device:
+            left = [_img(a) for a in left]
+            right = [_img(a) for a in right]
+            pitch = left[0].strides[0]
+            for a in list(left) + list(right):
+                if a.strides[0] != pitch:
+                    raise ValueError("all images of a step must share one pitch")
+        lp, rp = self._ptr_array(left), self._ptr_array(right)
+        corners = np.zeros((n, self.max_corners, 2), np.float32)
+        ncorn = np.zeros(n, np.int32)
+        stats = np.zeros(n, STATS_DTYPE)
+        tracked = np.zeros((n, self.max_features, 2), np.float32) if want_tracked else None
+        tids = np.zeros((n, self.max_features), np.uint64) if want_tracked else None
+        fn = self.lib.svo_step_device if device else self.lib.svo_step
+        self._check(fn(self.h, n, _ptr(seqs_a), lp, rp, int(pitch), _ptr(corners), _ptr(ncorn),
+                       _ptr(stats), _ptr(tracked), _ptr(tids)), "svo_step")
+        return dict(corners=corners, n_corners=ncorn, stats=stats, tracked=tracked,
+                    tracked_ids=tids)
+
+    def keyframe(self, seqs, inliers, n_inliers, poses, focal, cx, cy, baseline):
+        n = len(seqs)
+        seqs_a = np.ascontiguousarray(seqs, np.int32)
+        inl = np.zeros((n, self.max_features, 2), np.float32)
+        for i, a in enumerate(inliers):
+            a = np.asarray(a, np.float32).reshape(-1, 2)
+            inl[i, :a.shape[0]] = a
+        ninl = np.ascontiguousarray(n_inliers, np.int32)
+        poses = np.ascontiguousarray(poses, np.float32).reshape(n, 16)
+        mc = self.max_corners
+        new = np.zeros((n, mc, 2), np.float32)
+        nnew = np.zeros(n, np.int32)
+        v2 = np.zeros((n, mc, 2), np.float32)
+        p3 = np.zeros((n, mc, 3), np.float32)
+        vi = np.zeros((n, mc), np.int32)
+        d16 = np.zeros((n, mc), np.int16)
+        nv = np.zeros(n, np.int32)
+        self._check(self.lib.svo_keyframe(self.h, n, _ptr(seqs_a), _ptr(inl), _ptr(ninl),
+                                          _ptr(poses), float(focal), float(cx), float(cy),
+                                          float(baseline), _ptr(new), _ptr(nnew), _ptr(v2),
+                                          _ptr(p3), _ptr(vi), _ptr(d16), _ptr(nv)), "svo_keyframe")
+        return dict(new_feats=new, n_new=nnew, valid_2d=v2, pts_3d=p3, valid_idx=vi, disp16=d16,
+                    n_valid=nv)
+
+    def tracker_set(self, seqs, feats, ids):
+        n = len(seqs)
+        seqs_a = np.ascontiguousarray(seqs, np.int32)
+        f = np.zeros((n, self.max_features, 2), np.float32)
+        d = np.zeros((n, self.max_features), np.uint64)
+        cnt = np.zeros(n, np.int32)
+        for i in range(n):
+            a = np.asarray(feats[i], np.float32).reshape(-1, 2)
+            f[i, :a.shape[0]] = a
+            d[i, :a.shape[0]] = np.asarray(ids[i], np.uint64).reshape(-1)
+            cnt[i] = a.shape[0]
+        self._check(self.lib.svo_tracker_set(self.h, n, _ptr(seqs_a), _ptr(f), _ptr(d), _ptr(cnt)),
+                    "svo_tracker_set")
+
+    # -- device-resident frames (bench kernel-only leg) --------------------------------------
+    def device_alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        self._check(self.lib.svo_device_alloc(self.h, nbytes, C.byref(p)), "svo_device_alloc")
+        return p.value
+
+    def device_free(self, ptr: int):
+        self._check(self.lib.svo_device_free(self.h, C.c_void_p(ptr)), "svo_device_free")
+
+    def device_upload(self, dst: int, src: np.ndarray):
+        src = np.ascontiguousarray(src)
+        self._check(self.lib.svo_device_upload(self.h, C.c_void_p(dst), _ptr(src), src.nbytes),
+                    "svo_device_upload")

@@ -1,0 +1,1005 @@
+// libsvo.so: the C ABI of include/svo_c.h on top of the sm_100a kernels in this directory.
+// One engine = one CUDA stream + the device state of n_seq independent stereo sequences.
+// Host-side responsibilities only: buffer layout, per-call descriptors, H2D/D2H staging,
+// tracker slot bookkeeping (which pyramid slot is FeatureTracker::last_image), error strings.
+// There is no CPU implementation of any stage in here: without a CUDA device every call fails.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "../../include/svo_c.h"
+#include "svo_common.cuh"
+
+namespace {
+
+constexpr int CALL_RING = 8;
+
+struct SeqState {
+    int last_slot = -1;       // pyramid slot that is FeatureTracker::last_image (-1: none)
+    int cur_slot = 0;         // slot of the most recently uploaded left frame
+    bool have_frame = false;
+    bool have_right = false;
+    bool tracker_init = false;
+    int feat_buf = 0;
+    int n_feat = 0;
+    int n_initial = 0;
+    int dbg_attempted = 0;    // n_attempted of the last track call
+};
+
+// header of the packed per-sequence result block of a step
+struct StepHeader {
+    int n_corners;
+    int cand_count;
+    SvoTrackStats stats;
+};
+struct KeyHeader {
+    int n_new;
+    int n_valid;
+};
+
+template <typename T>
+cudaError_t dalloc(T** p, size_t count) {
+    return cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T) + 256);
+}
+
+}  // namespace
+
+struct svo_engine {
+    svo_params p;
+    int device = 0;
+    int n_seq = 0;
+    cudaStream_t st = nullptr;
+    std::string err;
+    SvoPyrLayout lay;
+    size_t seq_stride = 0;
+    size_t right_stride = 0;
+    int pitch0 = 0;
+    int eig_pitch = 0;
+    size_t eig_stride = 0;
+    int max_cand = 0;
+    size_t grid_stride = 0;
+
+    uint8_t* d_pyr = nullptr;
+    uint8_t* d_right = nullptr;
+    float* d_eig = nullptr;
+    unsigned int* d_eig_max = nullptr;
+    unsigned long long* d_cand = nullptr;
+    int* d_cand_count = nullptr;
+    float2* d_corners = nullptr;
+    int* d_ncorners = nullptr;
+    int* d_grid = nullptr;
+    float2* d_feat = nullptr;
+    unsigned long long* d_ids = nullptr;
+    float2* d_initial = nullptr;
+    float2* d_tracked = nullptr;
+    unsigned char* d_status1 = nullptr;
+    float2* d_reverse = nullptr;
+    unsigned char* d_status2 = nullptr;
+    int* d_kept_idx = nullptr;
+    float* d_kept_par = nullptr;
+    SvoTrackStats* d_stats = nullptr;
+    float2* d_inl = nullptr;
+    float2* d_pts = nullptr;      // stereo input points / deduped new features
+    int* d_keep_idx = nullptr;
+    int* d_nnew = nullptr;
+    short* d_disp16 = nullptr;
+    float2* d_valid2d = nullptr;
+    float* d_pts3d = nullptr;
+    int* d_valid_idx = nullptr;
+    int* d_nvalid = nullptr;
+    unsigned char* d_out = nullptr;   // packed result blocks
+    size_t step_block = 0, key_block = 0, out_bytes = 0;
+    int pts_cap = 0;                  // per-sequence capacity of d_pts / stereo outputs
+
+    SvoSeqCall* h_call = nullptr;     // pinned ring [CALL_RING][n_seq]
+    SvoSeqCall* d_call = nullptr;
+    int ring = 0;
+    unsigned char* h_out = nullptr;   // pinned
+    unsigned char* h_in = nullptr;    // pinned small-input staging
+    size_t h_in_bytes = 0;
+
+    std::vector<SeqState> seq;
+    int64_t launches = 0;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    float last_ms[3] = {0, 0, 0};
+};
+
+namespace {
+
+std::string g_create_err;
+
+int fail(svo_engine* e, int code, const char* what, cudaError_t ce = cudaSuccess) {
+    char buf[512];
+    if (ce != cudaSuccess)
+        snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(ce));
+    else
+        snprintf(buf, sizeof buf, "%s", what);
+    if (e) e->err = buf; else g_create_err = buf;
+    return code;
+}
+
+#define ECUDA(e, expr)                                                        \
+    do {                                                                      \
+        cudaError_t _ce = (expr);                                             \
+        if (_ce != cudaSuccess) return fail((e), SVO_ERR_CUDA, #expr, _ce);   \
+    } while (0)
+
+int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// ------------------------------------------------------------------ small glue kernels
+__global__ void reset_kernel(unsigned int* eig_max, int* cand_count, int* n_corners,
+                             const SvoSeqCall* call, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        int s = call[i].seq;
+        eig_max[s] = 0u;
+        cand_count[s] = 0;
+        n_corners[s] = 0;
+    }
+}
+
+// pack the results of one step into a contiguous block per listed sequence (one D2H copy)
+__global__ void pack_step_kernel(unsigned char* out, size_t block, const float2* corners,
+                                 const int* n_corners, const int* cand_count, int max_corners,
+                                 const SvoTrackStats* stats, const float2* feat,
+                                 const unsigned long long* ids, int max_features,
+                                 const SvoSeqCall* call) {
+    const SvoSeqCall cd = call[blockIdx.x];
+    unsigned char* o = out + (size_t)blockIdx.x * block;
+    StepHeader* h = reinterpret_cast<StepHeader*>(o);
+    float2* oc = reinterpret_cast<float2*>(o + sizeof(StepHeader));
+    float2* of = oc + max_corners;
+    unsigned long long* oi = reinterpret_cast<unsigned long long*>(of + max_features);
+    const int nc = n_corners[cd.seq];
+    const SvoTrackStats s = stats[cd.seq];
+    if (threadIdx.x == 0) {
+        h->n_corners = nc;
+        h->cand_count = cand_count[cd.seq];
+        h->stats = s;
+    }
+    for (int i = threadIdx.x; i < nc; i += blockDim.x)
+        oc[i] = corners[(size_t)cd.seq * max_corners + i];
+    if (s.n_attempted >= 0 && (cd.flags & 1)) {
+        // the kept set was compacted into the OTHER feature buffer
+        const size_t fb = ((size_t)cd.seq * 2 + (1 - cd.feat_buf)) * max_features;
+        for (int i = threadIdx.x; i < s.n_kept; i += blockDim.x) {
+            of[i] = feat[fb + i];
+            oi[i] = ids[fb + i];
+        }
+    }
+}
+
+__global__ void pack_key_kernel(unsigned char* out, size_t block, int cap, const float2* pts,
+                                const int* n_new, const float2* valid2d, const float* pts3d,
+                                const int* valid_idx, const short* disp16, const int* n_valid,
+                                const SvoSeqCall* call) {
+    const SvoSeqCall cd = call[blockIdx.x];
+    unsigned char* o = out + (size_t)blockIdx.x * block;
+    KeyHeader* h = reinterpret_cast<KeyHeader*>(o);
+    float2* o_new = reinterpret_cast<float2*>(o + sizeof(KeyHeader));
+    float2* o_v2 = o_new + cap;
+    float* o_3d = reinterpret_cast<float*>(o_v2 + cap);
+    int* o_vi = reinterpret_cast<int*>(o_3d + 3 * (size_t)cap);
+    short* o_d = reinterpret_cast<short*>(o_vi + cap);
+    const size_t b = (size_t)cd.seq * cap;
+    const int nn = n_new ? n_new[cd.seq] : cd.n_pts;
+    const int nv = n_valid[cd.seq];
+    if (threadIdx.x == 0) { h->n_new = nn; h->n_valid = nv; }
+    for (int i = threadIdx.x; i < nn; i += blockDim.x) {
+        o_new[i] = pts[b + i];
+        o_d[i] = disp16[b + i];
+    }
+    for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+        o_v2[i] = valid2d[b + i];
+        o_vi[i] = valid_idx[b + i];
+        o_3d[3 * i + 0] = pts3d[(b + i) * 3 + 0];
+        o_3d[3 * i + 1] = pts3d[(b + i) * 3 + 1];
+        o_3d[3 * i + 2] = pts3d[(b + i) * 3 + 2];
+    }
+}
+
+// the detect kernels of the fused step write n_pts for the stereo stage on the device
+__global__ void set_npts_kernel(SvoSeqCall* call, const int* n_new) {
+    call[blockIdx.x].n_pts = n_new[call[blockIdx.x].seq];
+}
+
+SvoSeqCall* next_call_slot(svo_engine* e) {
+    e->ring = (e->ring + 1) % CALL_RING;
+    return e->h_call + (size_t)e->ring * e->n_seq;
+}
+SvoSeqCall* dev_call_slot(svo_engine* e) { return e->d_call + (size_t)e->ring * e->n_seq; }
+
+int check_seq(svo_engine* e, int seq) {
+    if (!e) return SVO_ERR_INVALID;
+    if (seq < 0 || seq >= e->n_seq) return fail(e, SVO_ERR_INVALID, "sequence index out of range");
+    return SVO_OK;
+}
+
+void fill_call(svo_engine* e, SvoSeqCall& c, int seq) {
+    const SeqState& s = e->seq[seq];
+    memset(&c, 0, sizeof c);
+    c.seq = seq;
+    c.cur_slot = s.cur_slot;
+    c.feat_buf = s.feat_buf;
+    c.n_feat = s.n_feat;
+    c.n_initial = s.n_initial;
+    c.flags = s.tracker_init ? 1 : 0;
+    for (int i = 0; i < 4; ++i) c.pose[i * 5] = 1.f;
+}
+
+// choose the scratch slot for a new left frame (never FeatureTracker::last_image)
+void begin_frame(svo_engine* e, int seq) {
+    SeqState& s = e->seq[seq];
+    s.cur_slot = (s.last_slot == 0) ? 1 : 0;
+    s.have_frame = true;
+}
+
+uint8_t* slot_ptr(svo_engine* e, int seq, int slot) {
+    return e->d_pyr + (size_t)seq * e->seq_stride + (size_t)slot * e->lay.slot_bytes;
+}
+
+cudaError_t upload_left(svo_engine* e, int seq, const uint8_t* img, int pitch, bool device_src) {
+    return cudaMemcpy2DAsync(slot_ptr(e, seq, e->seq[seq].cur_slot) + e->lay.lvl[0].off, e->pitch0,
+                             img, pitch, e->p.width, e->p.height,
+                             device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, e->st);
+}
+cudaError_t upload_right(svo_engine* e, int seq, const uint8_t* img, int pitch, bool device_src) {
+    e->seq[seq].have_right = true;
+    return cudaMemcpy2DAsync(e->d_right + (size_t)seq * e->right_stride, e->pitch0, img, pitch,
+                             e->p.width, e->p.height,
+                             device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, e->st);
+}
+
+cudaError_t push_calls(svo_engine* e, int n) {
+    return cudaMemcpyAsync(dev_call_slot(e), e->h_call + (size_t)e->ring * e->n_seq,
+                           (size_t)n * sizeof(SvoSeqCall), cudaMemcpyHostToDevice, e->st);
+}
+
+// pyramid + detection for the listed sequences (current frames already uploaded)
+cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid) {
+    const SvoSeqCall* dc = dev_call_slot(e);
+    reset_kernel<<<(n + 127) / 128, 128, 0, e->st>>>(e->d_eig_max, e->d_cand_count, e->d_ncorners,
+                                                      dc, n);
+    e->launches += 1;
+    if (with_pyramid) {
+        SVO_CUDA_OK(svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, e->st));
+        e->launches += e->lay.n_levels - 1;
+    }
+    SVO_CUDA_OK(svo_launch_shi_tomasi(e->d_pyr, e->lay, e->seq_stride, e->d_eig, e->eig_pitch,
+                                      e->eig_stride, e->d_eig_max, dc, n, e->st));
+    SVO_CUDA_OK(svo_launch_nms_compact(e->d_eig, e->p.width, e->p.height, e->eig_pitch,
+                                       e->eig_stride, e->d_eig_max, e->p.quality_level, e->d_cand,
+                                       e->max_cand, e->d_cand_count, dc, n, e->st));
+    SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count, dc, n, e->st));
+    SVO_CUDA_OK(svo_launch_greedy_select(e->d_cand, e->max_cand, e->d_cand_count, e->p.width,
+                                         e->p.height, e->p.min_distance, e->p.max_corners,
+                                         e->d_corners, e->d_ncorners, e->d_grid, e->grid_stride, dc,
+                                         n, e->st));
+    e->launches += 3 + svo_sort_launch_count(e->max_cand);
+    return cudaSuccess;
+}
+
+cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_back, bool gated) {
+    const SvoSeqCall* dc = dev_call_slot(e);
+    SvoLkParams lp;
+    lp.max_iters = e->p.lk_max_iters;
+    lp.eps2 = e->p.lk_epsilon * e->p.lk_epsilon;
+    lp.min_eig = e->p.lk_min_eig_threshold;
+    lp.warps_per_point = e->p.lk_warps_per_point;
+    lp.grid_pts = max_feat_in_call;
+    const int* gate = gated ? e->d_ncorners : nullptr;
+    const int mf = e->p.max_features;
+    if (max_feat_in_call > 0) {
+        SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_feat, (size_t)2 * mf,
+                                        1, e->d_tracked, e->d_status1, mf, 0, lp, mf, gate, 4, dc,
+                                        n, e->st));
+        e->launches += 1;
+        if (flow_back) {
+            SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_tracked,
+                                            (size_t)mf, 0, e->d_reverse, e->d_status2, mf, 1, lp,
+                                            mf, gate, 4, dc, n, e->st));
+            e->launches += 1;
+        }
+    }
+    SVO_CUDA_OK(svo_launch_track_filter(e->d_feat, e->d_ids, e->d_initial, (size_t)2 * mf,
+                                        e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, mf,
+                                        flow_back, e->p.fb_max_error, e->p.max_parallax,
+                                        e->d_kept_idx, e->d_kept_par, e->d_stats, mf, gate, 4, dc,
+                                        n, e->st));
+    e->launches += 1;
+    return cudaSuccess;
+}
+
+int finish_timing(svo_engine* e) {
+    float a = 0, b = 0, c = 0;
+    cudaEventElapsedTime(&a, e->ev[0], e->ev[1]);
+    cudaEventElapsedTime(&b, e->ev[1], e->ev[2]);
+    cudaEventElapsedTime(&c, e->ev[2], e->ev[3]);
+    e->last_ms[0] = a; e->last_ms[1] = b; e->last_ms[2] = c;
+    return SVO_OK;
+}
+
+int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* left,
+              const uint8_t* const* right, int pitch, bool device_src, svo_float2* corners,
+              int32_t* n_corners, svo_track_stats* stats, svo_float2* tracked,
+              uint64_t* tracked_ids) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !seqs || !left) return fail(e, SVO_ERR_INVALID, "svo_step: bad arguments");
+    if (pitch < e->p.width) return fail(e, SVO_ERR_INVALID, "svo_step: pitch < width");
+    ECUDA(e, cudaSetDevice(e->device));
+    SvoSeqCall* hc = next_call_slot(e);
+    int max_feat = 0;
+    for (int i = 0; i < n; ++i) {
+        int s = seqs[i];
+        if (s < 0 || s >= e->n_seq) return fail(e, SVO_ERR_INVALID, "svo_step: sequence index out of range");
+        begin_frame(e, s);
+        fill_call(e, hc[i], s);
+        if (e->seq[s].tracker_init && e->seq[s].n_feat > max_feat) max_feat = e->seq[s].n_feat;
+    }
+    ECUDA(e, cudaEventRecord(e->ev[0], e->st));
+    ECUDA(e, push_calls(e, n));
+    for (int i = 0; i < n; ++i) {
+        ECUDA(e, upload_left(e, seqs[i], left[i], pitch, device_src));
+        if (right && right[i]) ECUDA(e, upload_right(e, seqs[i], right[i], pitch, device_src));
+    }
+    ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    ECUDA(e, launch_detect(e, n, true));
+    ECUDA(e, launch_track(e, n, max_feat, 1, true));
+    pack_step_kernel<<<n, 128, 0, e->st>>>(e->d_out, e->step_block, e->d_corners, e->d_ncorners,
+                                           e->d_cand_count, e->p.max_corners, e->d_stats, e->d_feat,
+                                           e->d_ids, e->p.max_features, dev_call_slot(e));
+    e->launches += 1;
+    ECUDA(e, cudaGetLastError());
+    ECUDA(e, cudaEventRecord(e->ev[2], e->st));
+    ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_out, (size_t)n * e->step_block, cudaMemcpyDeviceToHost,
+                             e->st));
+    ECUDA(e, cudaEventRecord(e->ev[3], e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    finish_timing(e);
+    int rc = SVO_OK;
+    const int mc = e->p.max_corners, mf = e->p.max_features;
+    for (int i = 0; i < n; ++i) {
+        const unsigned char* o = e->h_out + (size_t)i * e->step_block;
+        const StepHeader* h = reinterpret_cast<const StepHeader*>(o);
+        const float2* oc = reinterpret_cast<const float2*>(o + sizeof(StepHeader));
+        const float2* of = oc + mc;
+        const unsigned long long* oi = reinterpret_cast<const unsigned long long*>(of + mf);
+        SeqState& s = e->seq[seqs[i]];
+        if (h->cand_count > e->max_cand)
+            rc = fail(e, SVO_ERR_CAPACITY, "NMS candidate buffer overflow: raise max_candidates");
+        if (n_corners) n_corners[i] = h->n_corners;
+        if (corners) memcpy(corners + (size_t)i * mc, oc, (size_t)h->n_corners * sizeof(float2));
+        svo_track_stats st = {0.f, 0.f, 0, 0};
+        if (s.tracker_init && h->stats.n_attempted >= 0) {
+            // FeatureTracker::track_features ran: the tracker now holds the kept set and this
+            // frame as last_image (feature_tracker.cpp:39-41,66)
+            st.av_parallax = h->stats.av_parallax;
+            st.percent_lost = h->stats.percent_lost;
+            st.n_kept = h->stats.n_kept;
+            st.n_attempted = h->stats.n_attempted;
+            s.dbg_attempted = h->stats.n_attempted;
+            s.feat_buf = 1 - s.feat_buf;
+            s.n_feat = h->stats.n_kept;
+            s.last_slot = s.cur_slot;
+            if (tracked) memcpy(tracked + (size_t)i * mf, of, (size_t)st.n_kept * sizeof(float2));
+            if (tracked_ids) memcpy(tracked_ids + (size_t)i * mf, oi, (size_t)st.n_kept * sizeof(uint64_t));
+        }
+        if (stats) stats[i] = st;
+    }
+    return rc;
+}
+
+}  // namespace
+
+// =============================================================================== C ABI
+extern "C" {
+
+void svo_default_params(svo_params* p, int32_t width, int32_t height) {
+    if (!p) return;
+    memset(p, 0, sizeof *p);
+    p->width = width;
+    p->height = height;
+    p->max_corners = 300;
+    p->quality_level = 0.1;
+    p->min_distance = 30.f;
+    p->max_candidates = 0;
+    p->num_disparities = 48;
+    p->sad_window = 21;
+    p->prefilter_cap = 31;
+    p->texture_threshold = 10;
+    p->uniqueness_ratio = 15;
+    p->lk_max_level = 3;
+    p->lk_max_iters = 30;
+    p->lk_epsilon = 0.01;
+    p->lk_min_eig_threshold = 1e-2;
+    p->fb_max_error = 2.f;
+    p->max_parallax = 200.f;
+    p->max_features = 400;
+    p->lk_warps_per_point = 2;
+}
+
+const char* svo_last_error(const svo_engine* e) { return e ? e->err.c_str() : g_create_err.c_str(); }
+
+int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine** out) {
+    if (!pp || !out || n_seq <= 0) return fail(nullptr, SVO_ERR_INVALID, "svo_create: bad arguments");
+    *out = nullptr;
+    svo_params p = *pp;
+    if (p.width < 64 || p.height < 32 || p.width > 16384 || p.height > 16384)
+        return fail(nullptr, SVO_ERR_INVALID, "svo_create: image size out of range (64x32 .. 16384x16384)");
+    if (p.max_corners <= 0 || p.max_features <= 0 || p.max_features < 1)
+        return fail(nullptr, SVO_ERR_INVALID, "svo_create: max_corners / max_features must be positive");
+    if (p.lk_max_level < 0 || p.lk_max_level >= SVO_MAX_LEVELS)
+        return fail(nullptr, SVO_ERR_INVALID, "svo_create: lk_max_level out of range");
+    if (p.num_disparities <= 0 || p.num_disparities % 16 || p.sad_window < 5 || !(p.sad_window & 1) ||
+        p.sad_window > 31 || p.num_disparities > 256)
+        return fail(nullptr, SVO_ERR_INVALID, "svo_create: StereoBM parameters out of range");
+    if (p.lk_warps_per_point != 1 && p.lk_warps_per_point != 4) p.lk_warps_per_point = 2;
+    if ((long long)p.width * p.height >= (1ll << 31))
+        return fail(nullptr, SVO_ERR_INVALID, "svo_create: image too large");
+
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(nullptr, SVO_ERR_CUDA, "svo_create: no CUDA device (this library has no CPU path)", ce);
+    if (device < 0 || device >= ndev) return fail(nullptr, SVO_ERR_INVALID, "svo_create: device index out of range");
+    ce = cudaSetDevice(device);
+    if (ce != cudaSuccess) return fail(nullptr, SVO_ERR_CUDA, "cudaSetDevice", ce);
+
+    svo_engine* e = new svo_engine();
+    e->p = p;
+    e->device = device;
+    e->n_seq = n_seq;
+    e->seq.resize(n_seq);
+
+    // pyramid layout: levels as cv::buildOpticalFlowPyramid keeps them (a level must stay
+    // larger than the 21x21 window)
+    SvoPyrLayout& lay = e->lay;
+    memset(&lay, 0, sizeof lay);
+    int w = p.width, h = p.height;
+    unsigned int off = 0;
+    for (int l = 0; l <= p.lk_max_level; ++l) {
+        if (l > 0) {
+            int nw = (w + 1) / 2, nh = (h + 1) / 2;
+            if (nw <= SVO_LK_WIN || nh <= SVO_LK_WIN) break;
+            w = nw; h = nh;
+        }
+        lay.lvl[l].w = w;
+        lay.lvl[l].h = h;
+        lay.lvl[l].pitch = round_up(w, 128);
+        lay.lvl[l].off = off;
+        off += (unsigned int)lay.lvl[l].pitch * h;
+        off = (off + 255u) & ~255u;
+        lay.n_levels = l + 1;
+    }
+    lay.slot_bytes = off;
+    e->seq_stride = (size_t)2 * off;
+    e->pitch0 = lay.lvl[0].pitch;
+    e->right_stride = ((size_t)e->pitch0 * p.height + 255) & ~(size_t)255;
+    e->eig_pitch = round_up(p.width, 32);
+    e->eig_stride = (size_t)e->eig_pitch * p.height;
+    long long npx = (long long)p.width * p.height;
+    int mc = p.max_candidates;
+    if (mc <= 0) mc = npx <= (1 << 20) ? 16384 : (int)((npx / 16 < (1 << 15)) ? (1 << 15) : npx / 16);
+    if (mc > 16384) mc = svo_sort_capacity_pad(mc);
+    e->max_cand = mc;
+    e->p.max_candidates = mc;
+    e->grid_stride = (size_t)svo_greedy_grid_ints(p.width, p.height, p.min_distance) + 8;
+    e->pts_cap = p.max_corners > p.max_features ? p.max_corners : p.max_features;
+    const int cap = e->pts_cap, mf = p.max_features, mcn = p.max_corners;
+    e->step_block = (sizeof(StepHeader) + (size_t)mcn * 8 + (size_t)mf * 16 + 15) & ~(size_t)15;
+    e->key_block = (sizeof(KeyHeader) + (size_t)cap * (8 + 8 + 12 + 4 + 2) + 15) & ~(size_t)15;
+    size_t blk = e->step_block > e->key_block ? e->step_block : e->key_block;
+    e->out_bytes = blk * n_seq;
+    e->h_in_bytes = (size_t)n_seq * ((size_t)cap * 16 + (size_t)mf * 16) + 4096;
+
+#define CCHK(expr)                                                               \
+    do {                                                                         \
+        cudaError_t _ce = (expr);                                                \
+        if (_ce != cudaSuccess) {                                                \
+            fail(nullptr, _ce == cudaErrorMemoryAllocation ? SVO_ERR_NOMEM : SVO_ERR_CUDA, #expr, _ce); \
+            svo_destroy(e);                                                      \
+            return _ce == cudaErrorMemoryAllocation ? SVO_ERR_NOMEM : SVO_ERR_CUDA; \
+        }                                                                        \
+    } while (0)
+
+    CCHK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
+    for (int i = 0; i < 4; ++i) CCHK(cudaEventCreate(&e->ev[i]));
+    CCHK(svo_sort_init());
+    CCHK(svo_greedy_init());
+    const size_t ns = (size_t)n_seq;
+    CCHK(dalloc(&e->d_pyr, ns * e->seq_stride));
+    CCHK(dalloc(&e->d_right, ns * e->right_stride));
+    CCHK(dalloc(&e->d_eig, ns * e->eig_stride));
+    CCHK(dalloc(&e->d_eig_max, ns));
+    CCHK(dalloc(&e->d_cand, ns * mc));
+    CCHK(dalloc(&e->d_cand_count, ns));
+    CCHK(dalloc(&e->d_corners, ns * mcn));
+    CCHK(dalloc(&e->d_ncorners, ns));
+    CCHK(dalloc(&e->d_grid, ns * e->grid_stride));
+    CCHK(dalloc(&e->d_feat, ns * 2 * mf));
+    CCHK(dalloc(&e->d_ids, ns * 2 * mf));
+    CCHK(dalloc(&e->d_initial, ns * 2 * mf));
+    CCHK(dalloc(&e->d_tracked, ns * mf));
+    CCHK(dalloc(&e->d_status1, ns * mf));
+    CCHK(dalloc(&e->d_reverse, ns * mf));
+    CCHK(dalloc(&e->d_status2, ns * mf));
+    CCHK(dalloc(&e->d_kept_idx, ns * mf));
+    CCHK(dalloc(&e->d_kept_par, ns * mf));
+    CCHK(dalloc(&e->d_stats, ns));
+    CCHK(dalloc(&e->d_inl, ns * mf));
+    CCHK(dalloc(&e->d_pts, ns * cap));
+    CCHK(dalloc(&e->d_keep_idx, ns * cap));
+    CCHK(dalloc(&e->d_nnew, ns));
+    CCHK(dalloc(&e->d_disp16, ns * cap));
+    CCHK(dalloc(&e->d_valid2d, ns * cap));
+    CCHK(dalloc(&e->d_pts3d, ns * cap * 3));
+    CCHK(dalloc(&e->d_valid_idx, ns * cap));
+    CCHK(dalloc(&e->d_nvalid, ns));
+    CCHK(dalloc(&e->d_out, e->out_bytes));
+    CCHK(dalloc(&e->d_call, (size_t)CALL_RING * ns));
+    CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_call), (size_t)CALL_RING * ns * sizeof(SvoSeqCall)));
+    CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_out), e->out_bytes));
+    CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_in), e->h_in_bytes));
+    CCHK(cudaMemsetAsync(e->d_pyr, 0, ns * e->seq_stride, e->st));
+    CCHK(cudaMemsetAsync(e->d_right, 0, ns * e->right_stride, e->st));
+    CCHK(cudaMemsetAsync(e->d_eig, 0, ns * e->eig_stride * sizeof(float), e->st));
+    CCHK(cudaMemsetAsync(e->d_status2, 0, ns * mf, e->st));
+    CCHK(cudaMemsetAsync(e->d_reverse, 0, ns * mf * sizeof(float2), e->st));
+    CCHK(cudaMemsetAsync(e->d_stats, 0, ns * sizeof(SvoTrackStats), e->st));
+    CCHK(cudaStreamSynchronize(e->st));
+#undef CCHK
+    *out = e;
+    return SVO_OK;
+}
+
+void svo_destroy(svo_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->st) cudaStreamSynchronize(e->st);
+    void* dptrs[] = {e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
+                     e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
+                     e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
+                     e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew,
+                     e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
+                     e->d_call};
+    for (void* p : dptrs) if (p) cudaFree(p);
+    if (e->h_call) cudaFreeHost(e->h_call);
+    if (e->h_out) cudaFreeHost(e->h_out);
+    if (e->h_in) cudaFreeHost(e->h_in);
+    for (int i = 0; i < 4; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+    if (e->st) cudaStreamDestroy(e->st);
+    delete e;
+}
+
+int svo_get_params(const svo_engine* e, svo_params* out) {
+    if (!e || !out) return SVO_ERR_INVALID;
+    *out = e->p;
+    return SVO_OK;
+}
+int svo_num_levels(const svo_engine* e) { return e ? e->lay.n_levels : SVO_ERR_INVALID; }
+int64_t svo_kernel_launches(const svo_engine* e) { return e ? e->launches : 0; }
+float svo_last_gpu_ms(const svo_engine* e) { return e ? e->last_ms[1] : 0.f; }
+int svo_last_timing(const svo_engine* e, float ms[3]) {
+    if (!e || !ms) return SVO_ERR_INVALID;
+    ms[0] = e->last_ms[0]; ms[1] = e->last_ms[1]; ms[2] = e->last_ms[2];
+    return SVO_OK;
+}
+
+int svo_step(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* left,
+             const uint8_t* const* right, int32_t pitch, svo_float2* corners, int32_t* n_corners,
+             svo_track_stats* stats, svo_float2* tracked, uint64_t* tracked_ids) {
+    return step_impl(e, n, seqs, left, right, pitch, false, corners, n_corners, stats, tracked,
+                     tracked_ids);
+}
+
+int svo_step_device(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* d_left,
+                    const uint8_t* const* d_right, int32_t pitch, svo_float2* corners,
+                    int32_t* n_corners, svo_track_stats* stats, svo_float2* tracked,
+                    uint64_t* tracked_ids) {
+    return step_impl(e, n, seqs, d_left, d_right, pitch, true, corners, n_corners, stats, tracked,
+                     tracked_ids);
+}
+
+int svo_good_features_to_track(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pitch,
+                               svo_float2* out_xy, int32_t* out_n) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!img || !out_xy || !out_n || pitch < e->p.width) return fail(e, SVO_ERR_INVALID, "svo_good_features_to_track: bad arguments");
+    ECUDA(e, cudaSetDevice(e->device));
+    begin_frame(e, seq);
+    SvoSeqCall* hc = next_call_slot(e);
+    fill_call(e, hc[0], seq);
+    ECUDA(e, push_calls(e, 1));
+    ECUDA(e, upload_left(e, seq, img, pitch, false));
+    ECUDA(e, cudaEventRecord(e->ev[0], e->st));
+    ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    ECUDA(e, launch_detect(e, 1, true));
+    ECUDA(e, cudaEventRecord(e->ev[2], e->st));
+    int hdr[2] = {0, 0};
+    ECUDA(e, cudaMemcpyAsync(&hdr[0], e->d_ncorners + seq, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaMemcpyAsync(&hdr[1], e->d_cand_count + seq, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_corners + (size_t)seq * e->p.max_corners,
+                             (size_t)e->p.max_corners * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[3], e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    finish_timing(e);
+    if (hdr[1] > e->max_cand) return fail(e, SVO_ERR_CAPACITY, "NMS candidate buffer overflow: raise max_candidates");
+    *out_n = hdr[0];
+    memcpy(out_xy, e->h_out, (size_t)hdr[0] * sizeof(float2));
+    return SVO_OK;
+}
+
+static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_float2* inliers,
+                         const int32_t* n_inliers, const float* poses, float focal, float cx,
+                         float cy, float baseline, bool dedupe, const svo_float2* explicit_pts,
+                         const int32_t* n_explicit, svo_float2* new_feats, int32_t* n_new,
+                         svo_float2* valid_2d, svo_float3* pts_3d, int32_t* valid_idx,
+                         int16_t* disp16, int32_t* n_valid) {
+    const int mf = e->p.max_features, cap = e->pts_cap, mcn = e->p.max_corners;
+    ECUDA(e, cudaSetDevice(e->device));
+    SvoSeqCall* hc = next_call_slot(e);
+    float2* h_pts = reinterpret_cast<float2*>(e->h_in);
+    int max_pts = 0;
+    for (int i = 0; i < n; ++i) {
+        int s = seqs[i];
+        if (s < 0 || s >= e->n_seq) return fail(e, SVO_ERR_INVALID, "sequence index out of range");
+        if (!e->seq[s].have_frame || !e->seq[s].have_right)
+            return fail(e, SVO_ERR_STATE, "stereo stage needs an uploaded stereo pair");
+        fill_call(e, hc[i], s);
+        if (poses) memcpy(hc[i].pose, poses + (size_t)i * 16, 16 * sizeof(float));
+        if (dedupe) {
+            int ni = n_inliers ? n_inliers[i] : 0;
+            if (ni < 0 || ni > mf) return fail(e, SVO_ERR_INVALID, "n_inliers out of range");
+            hc[i].n_aux = ni;
+            hc[i].n_pts = 0;
+            if (ni > 0) memcpy(h_pts + (size_t)i * mf, inliers + (size_t)i * mf, (size_t)ni * sizeof(float2));
+            max_pts = mcn;
+        } else {
+            int np = n_explicit[i];
+            if (np < 0 || np > cap) return fail(e, SVO_ERR_CAPACITY, "too many features for the stereo stage");
+            hc[i].n_pts = np;
+            if (np > max_pts) max_pts = np;
+            if (np > 0) memcpy(h_pts + (size_t)i * cap, explicit_pts + (size_t)i * cap, (size_t)np * sizeof(float2));
+        }
+    }
+    ECUDA(e, cudaEventRecord(e->ev[0], e->st));
+    ECUDA(e, push_calls(e, n));
+    SvoSeqCall* dc = dev_call_slot(e);
+    for (int i = 0; i < n; ++i) {
+        int s = seqs[i];
+        if (dedupe) {
+            if (hc[i].n_aux > 0)
+                ECUDA(e, cudaMemcpyAsync(e->d_inl + (size_t)s * mf, h_pts + (size_t)i * mf,
+                                         (size_t)hc[i].n_aux * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+        } else if (hc[i].n_pts > 0) {
+            ECUDA(e, cudaMemcpyAsync(e->d_pts + (size_t)s * cap, h_pts + (size_t)i * cap,
+                                     (size_t)hc[i].n_pts * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+        }
+    }
+    ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    if (dedupe) {
+        ECUDA(e, svo_launch_dedupe(e->d_corners, e->d_ncorners, mcn, e->d_inl, mf, e->p.min_distance,
+                                   e->d_pts, e->d_keep_idx, e->d_nnew, cap, dc, n, e->st));
+        set_npts_kernel<<<n, 1, 0, e->st>>>(dc, e->d_nnew);
+        e->launches += 2;
+    }
+    SvoStereoParams sp = {e->p.num_disparities, e->p.sad_window, e->p.prefilter_cap,
+                          e->p.texture_threshold, e->p.uniqueness_ratio};
+    if (max_pts > 0) {
+        ECUDA(e, svo_launch_stereo_bm_sparse(e->d_pyr, e->lay, e->seq_stride, e->d_right,
+                                             e->right_stride, e->d_pts, cap, e->d_disp16, sp,
+                                             max_pts, dc, n, e->st));
+        e->launches += 1;
+    }
+    ECUDA(e, svo_launch_reproject(e->d_pts, e->d_disp16, cap, focal, cx, cy, baseline, e->d_valid2d,
+                                  e->d_pts3d, e->d_valid_idx, e->d_nvalid, dc, n, e->st));
+    pack_key_kernel<<<n, 128, 0, e->st>>>(e->d_out, e->key_block, cap, e->d_pts,
+                                          dedupe ? e->d_nnew : nullptr, e->d_valid2d, e->d_pts3d,
+                                          e->d_valid_idx, e->d_disp16, e->d_nvalid, dc);
+    e->launches += 2;
+    ECUDA(e, cudaGetLastError());
+    ECUDA(e, cudaEventRecord(e->ev[2], e->st));
+    ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_out, (size_t)n * e->key_block, cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[3], e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    finish_timing(e);
+    for (int i = 0; i < n; ++i) {
+        const unsigned char* o = e->h_out + (size_t)i * e->key_block;
+        const KeyHeader* h = reinterpret_cast<const KeyHeader*>(o);
+        const float2* o_new = reinterpret_cast<const float2*>(o + sizeof(KeyHeader));
+        const float2* o_v2 = o_new + cap;
+        const float* o_3d = reinterpret_cast<const float*>(o_v2 + cap);
+        const int* o_vi = reinterpret_cast<const int*>(o_3d + 3 * (size_t)cap);
+        const short* o_d = reinterpret_cast<const short*>(o_vi + cap);
+        const size_t ob = (size_t)i * (dedupe ? mcn : cap);
+        if (n_new) n_new[i] = h->n_new;
+        if (n_valid) n_valid[i] = h->n_valid;
+        if (new_feats) memcpy(new_feats + ob, o_new, (size_t)h->n_new * sizeof(float2));
+        if (disp16) memcpy(disp16 + ob, o_d, (size_t)h->n_new * sizeof(short));
+        if (valid_2d) memcpy(valid_2d + ob, o_v2, (size_t)h->n_valid * sizeof(float2));
+        if (valid_idx) memcpy(valid_idx + ob, o_vi, (size_t)h->n_valid * sizeof(int));
+        if (pts_3d) memcpy(pts_3d + ob, o_3d, (size_t)h->n_valid * 3 * sizeof(float));
+    }
+    return SVO_OK;
+}
+
+int svo_keyframe(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* inliers,
+                 const int32_t* n_inliers, const float* poses, float focal, float cx, float cy,
+                 float baseline, svo_float2* new_feats, int32_t* n_new, svo_float2* valid_2d,
+                 svo_float3* pts_3d, int32_t* valid_idx, int16_t* disp16, int32_t* n_valid) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !seqs || !poses) return fail(e, SVO_ERR_INVALID, "svo_keyframe: bad arguments");
+    return keyframe_impl(e, n, seqs, inliers, n_inliers, poses, focal, cx, cy, baseline, true,
+                         nullptr, nullptr, new_feats, n_new, valid_2d, pts_3d, valid_idx, disp16,
+                         n_valid);
+}
+
+int svo_triangulate_stereo(svo_engine* e, int32_t seq, const uint8_t* left, const uint8_t* right,
+                           int32_t pitch, const svo_float2* feats, int32_t n, const float pose[16],
+                           float focal, float cx, float cy, float baseline, svo_float3* out_3d,
+                           svo_float2* out_valid_2d, int32_t* out_valid_idx, int16_t* out_disp16,
+                           int32_t* out_n_valid) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!left || !right || (!feats && n > 0) || !pose || n < 0 || pitch < e->p.width)
+        return fail(e, SVO_ERR_INVALID, "svo_triangulate_stereo: bad arguments");
+    if (n > e->pts_cap) return fail(e, SVO_ERR_CAPACITY, "svo_triangulate_stereo: more features than max(max_corners, max_features)");
+    ECUDA(e, cudaSetDevice(e->device));
+    begin_frame(e, seq);
+    ECUDA(e, upload_left(e, seq, left, pitch, false));
+    ECUDA(e, upload_right(e, seq, right, pitch, false));
+    // single-sequence call: element 0 of the [n][cap] arrays
+    int32_t s = seq, nn = n;
+    return keyframe_impl(e, 1, &s, nullptr, nullptr, pose, focal, cx, cy, baseline, false, feats,
+                         &nn, nullptr, nullptr, out_valid_2d, out_3d, out_valid_idx, out_disp16,
+                         out_n_valid);
+}
+
+int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,
+                    const uint64_t* ids, const int32_t* counts) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !seqs || !counts) return fail(e, SVO_ERR_INVALID, "svo_tracker_set: bad arguments");
+    ECUDA(e, cudaSetDevice(e->device));
+    const int mf = e->p.max_features;
+    float2* hf = reinterpret_cast<float2*>(e->h_in);
+    unsigned long long* hi = reinterpret_cast<unsigned long long*>(hf + (size_t)e->n_seq * mf);
+    for (int i = 0; i < n; ++i) {
+        int s = seqs[i];
+        if (s < 0 || s >= e->n_seq) return fail(e, SVO_ERR_INVALID, "sequence index out of range");
+        if (!e->seq[s].have_frame) return fail(e, SVO_ERR_STATE, "svo_tracker_set: no current frame");
+        int c = counts[i];
+        if (c < 0 || c > mf) return fail(e, SVO_ERR_CAPACITY, "svo_tracker_set: more features than max_features");
+        if (c > 0 && (!feats || !ids)) return fail(e, SVO_ERR_INVALID, "svo_tracker_set: null arrays");
+        if (c > 0) {
+            memcpy(hf + (size_t)i * mf, feats + (size_t)i * mf, (size_t)c * sizeof(float2));
+            memcpy(hi + (size_t)i * mf, ids + (size_t)i * mf, (size_t)c * sizeof(uint64_t));
+        }
+    }
+    for (int i = 0; i < n; ++i) {
+        SeqState& s = e->seq[seqs[i]];
+        int c = counts[i];
+        const size_t fb = ((size_t)seqs[i] * 2 + s.feat_buf) * mf;
+        if (c > 0) {
+            ECUDA(e, cudaMemcpyAsync(e->d_feat + fb, hf + (size_t)i * mf, (size_t)c * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+            ECUDA(e, cudaMemcpyAsync(e->d_initial + fb, hf + (size_t)i * mf, (size_t)c * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+            ECUDA(e, cudaMemcpyAsync(e->d_ids + fb, hi + (size_t)i * mf, (size_t)c * sizeof(uint64_t), cudaMemcpyHostToDevice, e->st));
+        }
+        s.n_feat = c;
+        // initial_features is an unordered_map keyed by id: duplicates collapse (feature_tracker.cpp:10-12)
+        int uniq = 0;
+        if (c > 0) {
+            std::vector<uint64_t> v(ids + (size_t)i * mf, ids + (size_t)i * mf + c);
+            std::sort(v.begin(), v.end());
+            uniq = (int)(std::unique(v.begin(), v.end()) - v.begin());
+        }
+        s.n_initial = uniq;
+        s.tracker_init = true;
+        s.last_slot = s.cur_slot;      // last_image = image.clone()  (feature_tracker.cpp:14)
+    }
+    ECUDA(e, cudaStreamSynchronize(e->st));   // h_in is reused by the next call
+    return SVO_OK;
+}
+
+int svo_tracker_init(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pitch,
+                     const svo_float2* feats, const uint64_t* ids, int32_t n) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!img || pitch < e->p.width || n < 0) return fail(e, SVO_ERR_INVALID, "svo_tracker_init: bad arguments");
+    if (n > e->p.max_features) return fail(e, SVO_ERR_CAPACITY, "svo_tracker_init: more features than max_features");
+    ECUDA(e, cudaSetDevice(e->device));
+    begin_frame(e, seq);
+    SvoSeqCall* hc = next_call_slot(e);
+    fill_call(e, hc[0], seq);
+    ECUDA(e, push_calls(e, 1));
+    ECUDA(e, upload_left(e, seq, img, pitch, false));
+    ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), 1, e->st));
+    e->launches += e->lay.n_levels - 1;
+    // single-sequence view of the [n][max_features] arrays
+    int32_t s = seq, c = n;
+    return svo_tracker_set(e, 1, &s, feats, ids, &c);
+}
+
+int svo_tracker_track(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pitch,
+                      int32_t flow_back, float* av_parallax, float* percent_lost) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!img || pitch < e->p.width || !av_parallax || !percent_lost)
+        return fail(e, SVO_ERR_INVALID, "svo_tracker_track: bad arguments");
+    SeqState& s = e->seq[seq];
+    if (!s.tracker_init) return fail(e, SVO_ERR_STATE, "svo_tracker_track: tracker not initialised");
+    ECUDA(e, cudaSetDevice(e->device));
+    begin_frame(e, seq);
+    SvoSeqCall* hc = next_call_slot(e);
+    fill_call(e, hc[0], seq);
+    ECUDA(e, cudaEventRecord(e->ev[0], e->st));
+    ECUDA(e, push_calls(e, 1));
+    ECUDA(e, upload_left(e, seq, img, pitch, false));
+    ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), 1, e->st));
+    e->launches += e->lay.n_levels - 1;
+    ECUDA(e, launch_track(e, 1, s.n_feat, flow_back ? 1 : 0, false));
+    ECUDA(e, cudaEventRecord(e->ev[2], e->st));
+    SvoTrackStats st;
+    ECUDA(e, cudaMemcpyAsync(&st, e->d_stats + seq, sizeof st, cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[3], e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    finish_timing(e);
+    *av_parallax = st.av_parallax;
+    *percent_lost = st.percent_lost;
+    s.dbg_attempted = st.n_attempted;
+    s.feat_buf = 1 - s.feat_buf;
+    s.n_feat = st.n_kept;
+    s.last_slot = s.cur_slot;
+    return SVO_OK;
+}
+
+int svo_tracker_get(svo_engine* e, int32_t seq, svo_float2* feats, uint64_t* ids, int32_t* n) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!n) return fail(e, SVO_ERR_INVALID, "svo_tracker_get: bad arguments");
+    ECUDA(e, cudaSetDevice(e->device));
+    const SeqState& s = e->seq[seq];
+    const size_t fb = ((size_t)seq * 2 + s.feat_buf) * e->p.max_features;
+    *n = s.n_feat;
+    if (s.n_feat > 0) {
+        if (feats) ECUDA(e, cudaMemcpyAsync(feats, e->d_feat + fb, (size_t)s.n_feat * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
+        if (ids) ECUDA(e, cudaMemcpyAsync(ids, e->d_ids + fb, (size_t)s.n_feat * sizeof(uint64_t), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaStreamSynchronize(e->st));
+    }
+    return SVO_OK;
+}
+
+int svo_tracker_debug(svo_engine* e, int32_t seq, svo_float2* tracked, uint8_t* status1,
+                      svo_float2* reverse, uint8_t* status2, int32_t* kept_idx, int32_t* n_attempted) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    ECUDA(e, cudaSetDevice(e->device));
+    const SeqState& s = e->seq[seq];
+    const int na = s.dbg_attempted;
+    const size_t b = (size_t)seq * e->p.max_features;
+    if (n_attempted) *n_attempted = na;
+    if (na > 0) {
+        if (tracked) ECUDA(e, cudaMemcpyAsync(tracked, e->d_tracked + b, (size_t)na * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
+        if (status1) ECUDA(e, cudaMemcpyAsync(status1, e->d_status1 + b, (size_t)na, cudaMemcpyDeviceToHost, e->st));
+        if (reverse) ECUDA(e, cudaMemcpyAsync(reverse, e->d_reverse + b, (size_t)na * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
+        if (status2) ECUDA(e, cudaMemcpyAsync(status2, e->d_status2 + b, (size_t)na, cudaMemcpyDeviceToHost, e->st));
+        if (kept_idx && s.n_feat > 0) ECUDA(e, cudaMemcpyAsync(kept_idx, e->d_kept_idx + b, (size_t)s.n_feat * sizeof(int), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaStreamSynchronize(e->st));
+    }
+    return SVO_OK;
+}
+
+int svo_dedupe(svo_engine* e, int32_t seq, const svo_float2* det, int32_t n_det,
+               const svo_float2* tracked, int32_t n_tracked, float min_distance,
+               svo_float2* out_xy, int32_t* out_keep_idx, int32_t* out_n) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (n_det < 0 || n_tracked < 0 || !out_n || (n_det > 0 && !det) || (n_tracked > 0 && !tracked))
+        return fail(e, SVO_ERR_INVALID, "svo_dedupe: bad arguments");
+    if (n_det > e->pts_cap || n_tracked > e->p.max_features)
+        return fail(e, SVO_ERR_CAPACITY, "svo_dedupe: too many points");
+    ECUDA(e, cudaSetDevice(e->device));
+    const int cap = e->pts_cap, mf = e->p.max_features;
+    SvoSeqCall* hc = next_call_slot(e);
+    fill_call(e, hc[0], seq);
+    hc[0].n_pts = n_det;
+    hc[0].n_aux = n_tracked;
+    ECUDA(e, push_calls(e, 1));
+    // detections go through d_valid2d (scratch), tracked through d_inl
+    if (n_det > 0) ECUDA(e, cudaMemcpyAsync(e->d_valid2d + (size_t)seq * cap, det, (size_t)n_det * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+    if (n_tracked > 0) ECUDA(e, cudaMemcpyAsync(e->d_inl + (size_t)seq * mf, tracked, (size_t)n_tracked * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, svo_launch_dedupe(e->d_valid2d, nullptr, cap, e->d_inl, mf, min_distance, e->d_pts,
+                               e->d_keep_idx, e->d_nnew, cap, dev_call_slot(e), 1, e->st));
+    e->launches += 1;
+    int nn = 0;
+    ECUDA(e, cudaMemcpyAsync(&nn, e->d_nnew + seq, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    *out_n = nn;
+    if (nn > 0) {
+        if (out_xy) ECUDA(e, cudaMemcpyAsync(out_xy, e->d_pts + (size_t)seq * cap, (size_t)nn * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
+        if (out_keep_idx) ECUDA(e, cudaMemcpyAsync(out_keep_idx, e->d_keep_idx + (size_t)seq * cap, (size_t)nn * sizeof(int), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaStreamSynchronize(e->st));
+    }
+    return SVO_OK;
+}
+
+int svo_debug_min_eigen_map(svo_engine* e, int32_t seq, float* out) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!out) return fail(e, SVO_ERR_INVALID, "null output");
+    ECUDA(e, cudaSetDevice(e->device));
+    ECUDA(e, cudaMemcpy2DAsync(out, (size_t)e->p.width * sizeof(float), e->d_eig + (size_t)seq * e->eig_stride,
+                               (size_t)e->eig_pitch * sizeof(float), (size_t)e->p.width * sizeof(float),
+                               e->p.height, cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    return SVO_OK;
+}
+
+int svo_debug_pyramid_level(svo_engine* e, int32_t seq, int32_t level, uint8_t* out, int32_t* w, int32_t* h) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (level < 0 || level >= e->lay.n_levels) return fail(e, SVO_ERR_INVALID, "level out of range");
+    const SvoLevel& lv = e->lay.lvl[level];
+    if (w) *w = lv.w;
+    if (h) *h = lv.h;
+    if (out) {
+        ECUDA(e, cudaSetDevice(e->device));
+        ECUDA(e, cudaMemcpy2DAsync(out, lv.w, slot_ptr(e, seq, e->seq[seq].cur_slot) + lv.off, lv.pitch,
+                                   lv.w, lv.h, cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaStreamSynchronize(e->st));
+    }
+    return SVO_OK;
+}
+
+int svo_debug_candidates(svo_engine* e, int32_t seq, int32_t* xy, int32_t cap, int32_t* n) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!n) return fail(e, SVO_ERR_INVALID, "null output");
+    ECUDA(e, cudaSetDevice(e->device));
+    int cnt = 0;
+    ECUDA(e, cudaMemcpy(&cnt, e->d_cand_count + seq, sizeof(int), cudaMemcpyDeviceToHost));
+    if (cnt > e->max_cand) cnt = e->max_cand;
+    *n = cnt;
+    int m = cnt < cap ? cnt : cap;
+    if (xy && m > 0) {
+        std::vector<unsigned long long> keys(m);
+        ECUDA(e, cudaMemcpy(keys.data(), e->d_cand + (size_t)seq * e->max_cand, (size_t)m * 8, cudaMemcpyDeviceToHost));
+        for (int i = 0; i < m; ++i) {
+            unsigned addr = (unsigned)(keys[i] & 0xffffffffull);
+            xy[2 * i] = (int)(addr % (unsigned)e->p.width);
+            xy[2 * i + 1] = (int)(addr / (unsigned)e->p.width);
+        }
+    }
+    return SVO_OK;
+}
+
+int svo_device_alloc(svo_engine* e, size_t bytes, void** out) {
+    if (!e || !out) return SVO_ERR_INVALID;
+    ECUDA(e, cudaSetDevice(e->device));
+    ECUDA(e, cudaMalloc(out, bytes));
+    return SVO_OK;
+}
+int svo_device_free(svo_engine* e, void* p) {
+    if (!e) return SVO_ERR_INVALID;
+    ECUDA(e, cudaSetDevice(e->device));
+    ECUDA(e, cudaFree(p));
+    return SVO_OK;
+}
+int svo_device_upload(svo_engine* e, void* dst, const void* src, size_t bytes) {
+    if (!e) return SVO_ERR_INVALID;
+    ECUDA(e, cudaSetDevice(e->device));
+    ECUDA(e, cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+    return SVO_OK;
+}
+int svo_host_alloc(size_t bytes, void** out) {
+    if (!out) return SVO_ERR_INVALID;
+    return cudaMallocHost(out, bytes) == cudaSuccess ? SVO_OK : SVO_ERR_NOMEM;
+}
+int svo_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? SVO_OK : SVO_ERR_CUDA; }
+
+}  // extern "C"

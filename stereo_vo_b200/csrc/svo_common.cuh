@@ -1,0 +1,145 @@
+// Shared device/host definitions for the stereo-VO front-end kernels (sm_100a only).
+//
+// Data layout in HBM (all per engine, indexed by sequence `s`):
+//   pyr    u8   [n_seq][2 slots][levels 0..L]   left-image pyramids, pitched rows (pitch % 128 == 0)
+//   right  u8   [n_seq][H * pitch0]             right image of the current frame
+//   eig    f32  [n_seq][H * eig_pitch]          Shi-Tomasi min-eigenvalue map
+//   cand   u64  [n_seq][max_candidates]         (ordered score bits << 32 | y*W+x)
+// Kernels never see host pointers; launchers take raw device pointers + a stream.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SVO_MAX_LEVELS 6
+#define SVO_LK_WIN 21            // reference: cv::Size(21, 21), src/feature_tracker.cpp:24
+
+struct SvoLevel {
+    int w, h, pitch;
+    unsigned int off;            // byte offset of this level inside one pyramid slot
+};
+
+struct SvoPyrLayout {
+    int n_levels;                // levels actually built (<= max_level + 1)
+    SvoLevel lvl[SVO_MAX_LEVELS];
+    unsigned int slot_bytes;     // bytes of one pyramid slot (all levels)
+};
+
+// per-call, per-sequence descriptor (uploaded from pinned memory before the kernels of a call)
+struct SvoSeqCall {
+    int seq;                     // sequence index inside the engine
+    int cur_slot;                // pyramid slot that holds (or receives) the current frame
+    int feat_buf;                // tracker feature buffer holding the input feature set
+    int n_feat;                  // features in that buffer
+    int n_initial;               // initial_features.size() of the reference tracker
+    int n_pts;                   // generic point count of the call (stereo / dedupe)
+    int n_aux;                   // generic secondary count (inliers for dedupe)
+    int flags;
+    float pose[16];              // camera -> world, row major
+};
+
+__host__ __device__ __forceinline__ int svo_reflect101(int i, int n) {
+    // BORDER_REFLECT_101 (gfedcb|abcdefgh|gfedcba) for |overshoot| < n
+    if (i < 0) i = -i;
+    if (i >= n) i = 2 * (n - 1) - i;
+    return i;
+}
+
+// monotone float -> uint key (larger float <=> larger key), and back
+__host__ __device__ __forceinline__ unsigned int svo_float_key(unsigned int bits) {
+    return (bits & 0x80000000u) ? ~bits : (bits | 0x80000000u);
+}
+__host__ __device__ __forceinline__ unsigned int svo_key_float_bits(unsigned int key) {
+    return (key & 0x80000000u) ? (key & 0x7fffffffu) : ~key;
+}
+
+#define SVO_CUDA_OK(expr)                                                   \
+    do {                                                                    \
+        cudaError_t _e = (expr);                                            \
+        if (_e != cudaSuccess) return _e;                                   \
+    } while (0)
+
+// ------------------------------------------------------------------ launchers (one per .cu)
+// Every launcher is asynchronous on `st`; `n_call` sequences are listed in `d_call`.
+
+cudaError_t svo_launch_pyr_down(uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
+                                const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+
+cudaError_t svo_launch_pyr_down_single(const uint8_t* src, int w, int h, int spitch,
+                                       uint8_t* dst, int dpitch, cudaStream_t st);
+
+cudaError_t svo_launch_shi_tomasi(const uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
+                                  float* eig, int eig_pitch, size_t eig_stride,
+                                  unsigned int* eig_max, const SvoSeqCall* d_call, int n_call,
+                                  cudaStream_t st);
+
+cudaError_t svo_launch_nms_compact(const float* eig, int w, int h, int eig_pitch,
+                                   size_t eig_stride, const unsigned int* eig_max, double quality,
+                                   unsigned long long* cand, int max_cand, int* cand_count,
+                                   const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+
+int svo_sort_capacity_pad(int max_cand);
+int svo_sort_launch_count(int max_cand);
+cudaError_t svo_sort_init();
+cudaError_t svo_launch_sort_candidates(unsigned long long* cand, int max_cand,
+                                       const int* cand_count, const SvoSeqCall* d_call, int n_call,
+                                       cudaStream_t st);
+
+int svo_greedy_grid_ints(int w, int h, float min_distance);
+cudaError_t svo_greedy_init();
+cudaError_t svo_launch_greedy_select(const unsigned long long* cand, int max_cand,
+                                     const int* cand_count, int w, int h, float min_distance,
+                                     int max_corners, float2* corners, int* n_corners,
+                                     int* grid_scratch, size_t grid_stride,
+                                     const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+
+struct SvoStereoParams {
+    int ndisp, win, cap, texture, uniq;
+};
+
+cudaError_t svo_launch_stereo_bm_sparse(const uint8_t* pyr, const SvoPyrLayout& lay,
+                                        size_t seq_stride, const uint8_t* right,
+                                        size_t right_stride, const float2* pts, int pts_stride,
+                                        short* disp16, SvoStereoParams sp, int max_pts,
+                                        const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+
+cudaError_t svo_launch_reproject(const float2* pts, const short* disp16, int pts_stride,
+                                 float focal, float cx, float cy, float baseline, float2* valid2d,
+                                 float* pts3d, int* valid_idx, int* n_valid,
+                                 const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+
+cudaError_t svo_launch_dedupe(const float2* det, const int* n_det, int det_stride,
+                              const float2* inl, int inl_stride, float min_distance, float2* out,
+                              int* keep_idx, int* n_out, int out_stride,
+                              const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+
+struct SvoLkParams {
+    int max_iters;
+    double eps2;                 // criteria.epsilon squared (OpenCV squares it in double)
+    double min_eig;              // minEigThreshold (double in the OpenCV signature)
+    int warps_per_point;         // 1, 2 or 4
+    int grid_pts;                // blocks per sequence to launch (0 = max_pts)
+};
+
+// direction 0: prev slot -> cur slot ; direction 1: cur slot -> prev slot
+cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
+                                const float2* in_pts, size_t in_stride, int in_buffered,
+                                float2* out_pts, unsigned char* status, int out_stride,
+                                int direction, SvoLkParams lp, int max_pts, const int* gate,
+                                int gate_min, const SvoSeqCall* d_call, int n_call,
+                                cudaStream_t st);
+
+struct SvoTrackStats {
+    float av_parallax;
+    float percent_lost;
+    int n_kept;
+    int n_attempted;
+};
+
+cudaError_t svo_launch_track_filter(float2* feat, unsigned long long* ids,
+                                    float2* initial, size_t feat_stride,
+                                    const float2* tracked, const unsigned char* status1,
+                                    const float2* reverse, const unsigned char* status2,
+                                    int out_stride, int flow_back, float fb_max, float max_parallax,
+                                    int* kept_idx, float* kept_parallax, SvoTrackStats* stats,
+                                    int max_features, const int* gate, int gate_min,
+                                    const SvoSeqCall* d_call, int n_call, cudaStream_t st);

@@ -1,0 +1,125 @@
+"""GPU parity: pyramid, Shi-Tomasi eig map, NMS candidates and goodFeaturesToTrack corners,
+through the C ABI, against the cv2 oracle (bit-exact; integer / index work)."""
+import cv2
+import numpy as np
+import pytest
+
+from stereo_vo_b200 import synth
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [(1241, 376), (640, 480), (1242, 375), (333, 211)]
+
+
+@pytest.fixture(scope="module")
+def engines(svo_lib):
+    from stereo_vo_b200.capi import Engine
+    cache = {}
+
+    def get(w, h, **kw):
+        key = (w, h, tuple(sorted(kw.items())))
+        if key not in cache:
+            cache[key] = Engine(w, h, n_seq=2, **kw)
+        return cache[key]
+    yield get
+    for e in cache.values():
+        e.close()
+
+
+def _image(w, h, seed):
+    if (w, h) == (1241, 376):
+        return util.frames(seed, 1)[0][0]
+    cam = util.small_camera(w, h)
+    return synth.stereo_frame(seed, 3, cam)[0]
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_pyramid_levels_bit_exact(engines, oracle, w, h):
+    e = engines(w, h)
+    img = _image(w, h, 1)
+    e.good_features_to_track(img)
+    _, pyr = cv2.buildOpticalFlowPyramid(img, (21, 21), 3, withDerivatives=False)
+    assert e.num_levels == len(pyr)
+    ref = img
+    for l in range(e.num_levels):
+        got = e.debug_pyramid_level(l)
+        if l > 0:
+            ref = cv2.pyrDown(ref)
+        assert got.shape == ref.shape
+        assert np.array_equal(got, ref), f"level {l}"
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("seed", [0, 5])
+def test_min_eigen_map_bit_exact(engines, oracle, w, h, seed):
+    e = engines(w, h)
+    img = _image(w, h, seed)
+    e.good_features_to_track(img, seq=1)
+    got = e.debug_min_eigen_map(seq=1)
+    ref = cv2.cornerMinEigenVal(img, 3, ksize=3)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), \
+        f"{(got != ref).sum()} pixels differ, max |d| = {np.abs(got - ref).max()}"
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_good_features_bit_exact(engines, oracle, w, h, seed):
+    e = engines(w, h)
+    img = _image(w, h, seed)
+    got = e.good_features_to_track(img)
+    ref = oracle.detect(img)
+    assert got.shape == ref.shape
+    assert np.array_equal(got, ref)
+
+
+def test_candidates_sorted_like_oracle(engines, oracle):
+    from oracle import restate
+    w, h = 1241, 376
+    e = engines(w, h)
+    img = _image(w, h, 3)
+    e.good_features_to_track(img)
+    got = e.debug_candidates()
+    xs, ys, _ = restate.corner_candidates(cv2.cornerMinEigenVal(img, 3, ksize=3), 0.1)
+    assert got.shape[0] == len(xs)
+    assert np.array_equal(got[:, 0], xs) and np.array_equal(got[:, 1], ys)
+
+
+def test_plateau_ties_and_flat_image(engines, oracle):
+    w, h = 640, 480
+    e = engines(w, h)
+    flat = np.full((h, w), 93, np.uint8)
+    assert e.good_features_to_track(flat).shape[0] == 0          # max == 0 -> no corners
+    assert oracle.detect(flat).shape[0] == 0
+    # blocky image: exact plateaus in the eig map (ties broken by address)
+    rng = np.random.default_rng(7)
+    blocks = rng.integers(0, 256, (h // 8, w // 8)).astype(np.uint8)
+    img = np.kron(blocks, np.ones((8, 8), np.uint8))
+    got = e.good_features_to_track(img)
+    ref = oracle.detect(img)
+    assert np.array_equal(got, ref)
+    stress = util.stress_image(h, w, 11)
+    assert np.array_equal(e.good_features_to_track(stress), oracle.detect(stress))
+
+
+@pytest.mark.parametrize("maxc,q,md", [(50, 0.05, 10.0), (1000, 0.01, 5.0), (300, 0.3, 30.0),
+                                       (200, 0.1, 0.0), (400, 0.02, 7.5)])
+def test_other_detector_parameters(engines, oracle, maxc, q, md):
+    w, h = 640, 480
+    e = engines(w, h, max_corners=maxc, quality_level=q, min_distance=md)
+    img = _image(w, h, 4)
+    got = e.good_features_to_track(img)
+    ref = oracle.detect(img, maxc, q, md)
+    assert np.array_equal(got, ref)
+
+
+def test_two_sequences_independent(engines, oracle):
+    w, h = 1241, 376
+    e = engines(w, h)
+    a, b = _image(w, h, 8), _image(w, h, 9)
+    res = e.step([0, 1], [a, b], [a, b])
+    for i, img in enumerate((a, b)):
+        ref = oracle.detect(img)
+        n = res["n_corners"][i]
+        assert n == ref.shape[0]
+        assert np.array_equal(res["corners"][i, :n], ref)

@@ -1,0 +1,123 @@
+"""GPU parity: pyramidal LK forward/backward + filter/statistics (FeatureTracker) against the
+cv2 oracle. Status, kept indices and ids bit-exact; sub-pixel flow within 0.01 px
+(BASELINE.json north_star tolerance)."""
+import numpy as np
+import pytest
+
+from stereo_vo_b200 import synth
+from tests import util
+
+pytestmark = pytest.mark.gpu
+FLOW_TOL = 0.01
+
+
+@pytest.fixture(scope="module")
+def eng(svo_lib):
+    from stereo_vo_b200.capi import Engine
+    cache = {}
+
+    def get(w, h, **kw):
+        key = (w, h, tuple(sorted(kw.items())))
+        if key not in cache:
+            cache[key] = Engine(w, h, n_seq=1, **kw)
+        return cache[key]
+    yield get
+    for e in cache.values():
+        e.close()
+
+
+def _track_once(e, oracle, prev, nxt, pts, ids):
+    trk = oracle.FeatureTracker()
+    trk.init(prev, pts, ids)
+    av_ref, lost_ref = trk.track_features(nxt, True)
+    e.tracker_init(prev, pts, np.asarray(ids, np.uint64))
+    av, lost = e.tracker_track(nxt, True)
+    dbg = e.tracker_debug()
+    taps = trk.taps
+    assert np.array_equal(dbg["status1"], taps["status1"]), "forward status"
+    ok1 = taps["status1"] > 0
+    assert np.abs(dbg["tracked"][ok1] - taps["tracked"][ok1]).max() <= FLOW_TOL
+    # backward pass starts from OUR forward result; compare where both forward results agree
+    assert np.array_equal(dbg["status2"][ok1], taps["status2"][ok1]), "backward status"
+    ok2 = ok1 & (taps["status2"] > 0)
+    assert np.abs(dbg["reverse"][ok2] - taps["reverse"][ok2]).max() <= 2 * FLOW_TOL
+    feats, fids = e.tracker_get()
+    ref_feats, ref_ids = trk.get_tracked_features()
+    assert list(fids) == list(ref_ids), "kept track ids"
+    assert np.abs(feats - ref_feats).max() <= FLOW_TOL
+    assert np.array_equal(dbg["kept_idx"][:len(ref_ids)], taps["kept_idx"])
+    assert abs(float(av) - float(av_ref)) <= FLOW_TOL
+    assert lost == lost_ref
+    return trk
+
+
+@pytest.mark.parametrize("seed,t", [(0, 0), (1, 7), (2, 20)])
+def test_track_kitti_pair(eng, oracle, seed, t):
+    fr = util.frames(seed, 2, start=t)
+    prev, nxt = fr[0][0], fr[1][0]
+    pts = oracle.detect(prev)
+    e = eng(1241, 376)
+    _track_once(e, oracle, prev, nxt, pts, list(range(100, 100 + len(pts))))
+
+
+def test_track_d435i_pair(eng, oracle):
+    fr = synth.sequence(3, 2, synth.D435I, synth.D435I_MOTION)
+    prev, nxt = fr[0][0], fr[1][0]
+    pts = oracle.detect(prev)
+    e = eng(640, 480)
+    _track_once(e, oracle, prev, nxt, pts, list(range(len(pts))))
+
+
+def test_track_border_points_and_lost(eng, oracle):
+    """points at / beyond the image edge, a large shift that loses tracks, duplicate points"""
+    fr = util.frames(4, 1)
+    prev = fr[0][0]
+    nxt = np.roll(np.roll(prev, -14, axis=1), -9, axis=0)
+    pts = oracle.detect(prev)[:60]
+    edge = np.array([[0, 0], [1240, 375], [3.5, 200.25], [1238.75, 10.5], [620, 0.5],
+                     [620, 374.9], [0.2, 0.3], [1240.0, 0.0], [5, 370], [1230, 5]], np.float32)
+    pts = np.concatenate([pts, edge, pts[:3]], 0)
+    e = eng(1241, 376)
+    _track_once(e, oracle, prev, nxt, pts, list(range(len(pts))))
+
+
+def test_track_flat_image_all_lost(eng, oracle):
+    prev = np.full((376, 1241), 120, np.uint8)
+    nxt = prev.copy()
+    pts = np.array([[100, 100], [600, 200], [1200, 300]], np.float32)
+    trk = oracle.FeatureTracker()
+    trk.init(prev, pts, [0, 1, 2])
+    av_ref, lost_ref = trk.track_features(nxt, True)
+    e = eng(1241, 376)
+    e.tracker_init(prev, pts, np.arange(3, dtype=np.uint64))
+    av, lost = e.tracker_track(nxt, True)
+    assert len(trk.feature_ids) == 0 and e.tracker_get()[0].shape[0] == 0
+    assert av == av_ref and lost == lost_ref == np.float32(1.0)
+
+
+def test_track_multi_frame_chain(eng, oracle):
+    """four consecutive frames: the tracker state (kept set, ids, initial positions) carries over"""
+    fr = util.frames(5, 5)
+    pts = oracle.detect(fr[0][0])
+    ids = list(range(len(pts)))
+    trk = oracle.FeatureTracker()
+    trk.init(fr[0][0], pts, ids)
+    e = eng(1241, 376)
+    e.tracker_init(fr[0][0], pts, np.asarray(ids, np.uint64))
+    for t in range(1, 5):
+        av_ref, lost_ref = trk.track_features(fr[t][0], True)
+        av, lost = e.tracker_track(fr[t][0], True)
+        feats, fids = e.tracker_get()
+        assert list(fids) == list(trk.feature_ids), f"frame {t}"
+        assert np.abs(feats - trk.feature_set).max() <= FLOW_TOL * t
+        assert abs(float(av) - float(av_ref)) <= FLOW_TOL * t
+        assert lost == lost_ref
+
+
+@pytest.mark.parametrize("warps", [1, 4])
+def test_track_other_block_shapes(eng, oracle, warps):
+    fr = util.frames(6, 2)
+    prev, nxt = fr[0][0], fr[1][0]
+    pts = oracle.detect(prev)
+    e = eng(1241, 376, lk_warps_per_point=warps)
+    _track_once(e, oracle, prev, nxt, pts, list(range(len(pts))))

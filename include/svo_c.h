@@ -97,6 +97,17 @@ SVO_API float svo_last_gpu_ms(const svo_engine* e);
 /* ms[0] input copies, ms[1] kernels, ms[2] result copy of the last call (CUDA events) */
 SVO_API int svo_last_timing(const svo_engine* e, float ms[3]);
 
+/* per-kernel profiling: when on, every kernel group of a call is bracketed by CUDA events on
+ * the engine stream; totals (ms, launches of the group) accumulate per slot until reset by the
+ * next svo_set_profiling() call. Slot names: svo_profile_name(0 .. svo_profile_slots()-1). */
+SVO_API int svo_set_profiling(svo_engine* e, int32_t on);
+SVO_API int svo_profile_slots(void);
+SVO_API const char* svo_profile_name(int32_t slot);
+SVO_API int svo_get_profile(const svo_engine* e, double* ms, int64_t* counts);
+/* device-side stopwatch on the engine stream (CUDA events): begin synchronises first */
+SVO_API int svo_timer_begin(svo_engine* e);
+SVO_API int svo_timer_end(svo_engine* e, float* ms);
+
 /* ---- stage calls: one reference call site each, single sequence, synchronous ---------- */
 
 /* cv::goodFeaturesToTrack at src/image_processor.cpp:22. Uploads `img` as the current left

@@ -49,6 +49,8 @@ EXPORTS = [
     "svo_debug_min_eigen_map", "svo_debug_pyramid_level", "svo_debug_candidates",
     "svo_step", "svo_step_device", "svo_keyframe", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
+    "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
+    "svo_timer_begin", "svo_timer_end",
 ]
 
 _lib = None
@@ -104,6 +106,13 @@ def load_library(path: Optional[str] = None):
     lib.svo_device_upload.argtypes = [vp, vp, vp, C.c_size_t]
     lib.svo_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
     lib.svo_host_free.argtypes = [vp]
+    lib.svo_set_profiling.argtypes = [vp, i32]
+    lib.svo_profile_slots.argtypes = []
+    lib.svo_profile_name.argtypes = [i32]
+    lib.svo_profile_name.restype = C.c_char_p
+    lib.svo_get_profile.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    lib.svo_timer_begin.argtypes = [vp]
+    lib.svo_timer_end.argtypes = [vp, C.POINTER(f32)]
     if path is None:
         _lib = lib
     return lib
@@ -199,6 +208,25 @@ class Engine:
         ms = (C.c_float * 3)()
         self.lib.svo_last_timing(self.h, ms)
         return float(ms[0]), float(ms[1]), float(ms[2])
+
+    def set_profiling(self, on: bool):
+        self._check(self.lib.svo_set_profiling(self.h, 1 if on else 0), "svo_set_profiling")
+
+    def get_profile(self) -> dict:
+        n = self.lib.svo_profile_slots()
+        ms = (C.c_double * n)()
+        cnt = (C.c_int64 * n)()
+        self._check(self.lib.svo_get_profile(self.h, ms, cnt), "svo_get_profile")
+        return {self.lib.svo_profile_name(i).decode(): (float(ms[i]), int(cnt[i]))
+                for i in range(n)}
+
+    def timer_begin(self):
+        self._check(self.lib.svo_timer_begin(self.h), "svo_timer_begin")
+
+    def timer_end(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.svo_timer_end(self.h, C.byref(ms)), "svo_timer_end")
+        return float(ms.value)
 
     # -- stage calls ----------------------------------------------------------------------
     def good_features_to_track(self, img: np.ndarray, seq: int = 0) -> np.ndarray:

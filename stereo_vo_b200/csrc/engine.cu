@@ -15,6 +15,14 @@
 #include "../../include/svo_c.h"
 #include "svo_common.cuh"
 
+#define SVO_PROF_SLOTS 12
+static const char* const kProfNames[SVO_PROF_SLOTS] = {
+    "pyr_down_u8", "shi_tomasi_score", "nms_threshold_compact", "sort_candidates",
+    "greedy_min_distance", "lk_track_fwd", "lk_track_bwd", "track_filter_compact",
+    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q"};
+enum { P_PYR, P_SCORE, P_NMS, P_SORT, P_GREEDY, P_LKF, P_LKB, P_FILTER, P_PACK, P_DEDUPE,
+       P_STEREO, P_REPROJ };
+
 namespace {
 
 constexpr int CALL_RING = 8;
@@ -105,6 +113,14 @@ struct svo_engine {
 
     std::vector<SeqState> seq;
     int64_t launches = 0;
+    // optional per-kernel profiling (CUDA events on the engine stream)
+    bool profiling = false;
+    std::vector<cudaEvent_t> prof_ev;      // pool, pairs
+    std::vector<int> prof_slot;            // slot id per pair in flight
+    int prof_used = 0;
+    double prof_ms[SVO_PROF_SLOTS] = {0};
+    int64_t prof_count[SVO_PROF_SLOTS] = {0};
+    cudaEvent_t timer_ev[2] = {nullptr, nullptr};
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     float last_ms[3] = {0, 0, 0};
 };
@@ -130,6 +146,40 @@ int fail(svo_engine* e, int code, const char* what, cudaError_t ce = cudaSuccess
     } while (0)
 
 int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// profiling scope: records an event pair around a kernel group when profiling is on
+struct ProfScope {
+    svo_engine* e;
+    int idx = -1;
+    ProfScope(svo_engine* eng, int slot) : e(eng) {
+        if (!e->profiling) return;
+        if ((size_t)(e->prof_used + 1) * 2 > e->prof_ev.size()) {
+            cudaEvent_t a, b;
+            if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+            e->prof_ev.push_back(a);
+            e->prof_ev.push_back(b);
+            e->prof_slot.push_back(0);
+        }
+        idx = e->prof_used++;
+        e->prof_slot[idx] = slot;
+        cudaEventRecord(e->prof_ev[2 * idx], e->st);
+    }
+    ~ProfScope() {
+        if (idx >= 0) cudaEventRecord(e->prof_ev[2 * idx + 1], e->st);
+    }
+};
+
+// after a stream synchronize: fold the finished event pairs into the per-kernel totals
+void prof_collect(svo_engine* e) {
+    for (int i = 0; i < e->prof_used; ++i) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e->prof_ev[2 * i], e->prof_ev[2 * i + 1]) == cudaSuccess) {
+            e->prof_ms[e->prof_slot[i]] += ms;
+            e->prof_count[e->prof_slot[i]] += 1;
+        }
+    }
+    e->prof_used = 0;
+}
 
 // ------------------------------------------------------------------ small glue kernels
 __global__ void reset_kernel(unsigned int* eig_max, int* cand_count, int* n_corners,
@@ -267,19 +317,33 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid) {
                                                       dc, n);
     e->launches += 1;
     if (with_pyramid) {
+        ProfScope ps(e, P_PYR);
         SVO_CUDA_OK(svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, e->st));
         e->launches += e->lay.n_levels - 1;
     }
-    SVO_CUDA_OK(svo_launch_shi_tomasi(e->d_pyr, e->lay, e->seq_stride, e->d_eig, e->eig_pitch,
-                                      e->eig_stride, e->d_eig_max, dc, n, e->st));
-    SVO_CUDA_OK(svo_launch_nms_compact(e->d_eig, e->p.width, e->p.height, e->eig_pitch,
-                                       e->eig_stride, e->d_eig_max, e->p.quality_level, e->d_cand,
-                                       e->max_cand, e->d_cand_count, dc, n, e->st));
-    SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count, dc, n, e->st));
-    SVO_CUDA_OK(svo_launch_greedy_select(e->d_cand, e->max_cand, e->d_cand_count, e->p.width,
-                                         e->p.height, e->p.min_distance, e->p.max_corners,
-                                         e->d_corners, e->d_ncorners, e->d_grid, e->grid_stride, dc,
-                                         n, e->st));
+    {
+        ProfScope ps(e, P_SCORE);
+        SVO_CUDA_OK(svo_launch_shi_tomasi(e->d_pyr, e->lay, e->seq_stride, e->d_eig, e->eig_pitch,
+                                          e->eig_stride, e->d_eig_max, dc, n, e->st));
+    }
+    {
+        ProfScope ps(e, P_NMS);
+        SVO_CUDA_OK(svo_launch_nms_compact(e->d_eig, e->p.width, e->p.height, e->eig_pitch,
+                                           e->eig_stride, e->d_eig_max, e->p.quality_level,
+                                           e->d_cand, e->max_cand, e->d_cand_count, dc, n, e->st));
+    }
+    {
+        ProfScope ps(e, P_SORT);
+        SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count, dc, n,
+                                               e->st));
+    }
+    {
+        ProfScope ps(e, P_GREEDY);
+        SVO_CUDA_OK(svo_launch_greedy_select(e->d_cand, e->max_cand, e->d_cand_count, e->p.width,
+                                             e->p.height, e->p.min_distance, e->p.max_corners,
+                                             e->d_corners, e->d_ncorners, e->d_grid,
+                                             e->grid_stride, dc, n, e->st));
+    }
     e->launches += 3 + svo_sort_launch_count(e->max_cand);
     return cudaSuccess;
 }
@@ -295,17 +359,22 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
     const int* gate = gated ? e->d_ncorners : nullptr;
     const int mf = e->p.max_features;
     if (max_feat_in_call > 0) {
-        SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_feat, (size_t)2 * mf,
-                                        1, e->d_tracked, e->d_status1, mf, 0, lp, mf, gate, 4, dc,
-                                        n, e->st));
+        {
+            ProfScope ps(e, P_LKF);
+            SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_feat,
+                                            (size_t)2 * mf, 1, e->d_tracked, e->d_status1, mf, 0,
+                                            lp, mf, gate, 4, dc, n, e->st));
+        }
         e->launches += 1;
         if (flow_back) {
+            ProfScope ps(e, P_LKB);
             SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_tracked,
                                             (size_t)mf, 0, e->d_reverse, e->d_status2, mf, 1, lp,
                                             mf, gate, 4, dc, n, e->st));
             e->launches += 1;
         }
     }
+    ProfScope psf(e, P_FILTER);
     SVO_CUDA_OK(svo_launch_track_filter(e->d_feat, e->d_ids, e->d_initial, (size_t)2 * mf,
                                         e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, mf,
                                         flow_back, e->p.fb_max_error, e->p.max_parallax,
@@ -321,6 +390,7 @@ int finish_timing(svo_engine* e) {
     cudaEventElapsedTime(&b, e->ev[1], e->ev[2]);
     cudaEventElapsedTime(&c, e->ev[2], e->ev[3]);
     e->last_ms[0] = a; e->last_ms[1] = b; e->last_ms[2] = c;
+    if (e->profiling) prof_collect(e);
     return SVO_OK;
 }
 
@@ -350,9 +420,13 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     ECUDA(e, launch_detect(e, n, true));
     ECUDA(e, launch_track(e, n, max_feat, 1, true));
-    pack_step_kernel<<<n, 128, 0, e->st>>>(e->d_out, e->step_block, e->d_corners, e->d_ncorners,
-                                           e->d_cand_count, e->p.max_corners, e->d_stats, e->d_feat,
-                                           e->d_ids, e->p.max_features, dev_call_slot(e));
+    {
+        ProfScope ps(e, P_PACK);
+        pack_step_kernel<<<n, 128, 0, e->st>>>(e->d_out, e->step_block, e->d_corners,
+                                               e->d_ncorners, e->d_cand_count, e->p.max_corners,
+                                               e->d_stats, e->d_feat, e->d_ids, e->p.max_features,
+                                               dev_call_slot(e));
+    }
     e->launches += 1;
     ECUDA(e, cudaGetLastError());
     ECUDA(e, cudaEventRecord(e->ev[2], e->st));
@@ -509,6 +583,7 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
 
     CCHK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (int i = 0; i < 4; ++i) CCHK(cudaEventCreate(&e->ev[i]));
+    for (int i = 0; i < 2; ++i) CCHK(cudaEventCreate(&e->timer_ev[i]));
     CCHK(svo_sort_init());
     CCHK(svo_greedy_init());
     const size_t ns = (size_t)n_seq;
@@ -572,6 +647,8 @@ void svo_destroy(svo_engine* e) {
     if (e->h_out) cudaFreeHost(e->h_out);
     if (e->h_in) cudaFreeHost(e->h_in);
     for (int i = 0; i < 4; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
+    for (int i = 0; i < 2; ++i) if (e->timer_ev[i]) cudaEventDestroy(e->timer_ev[i]);
+    for (cudaEvent_t ev : e->prof_ev) cudaEventDestroy(ev);
     if (e->st) cudaStreamDestroy(e->st);
     delete e;
 }
@@ -587,6 +664,39 @@ float svo_last_gpu_ms(const svo_engine* e) { return e ? e->last_ms[1] : 0.f; }
 int svo_last_timing(const svo_engine* e, float ms[3]) {
     if (!e || !ms) return SVO_ERR_INVALID;
     ms[0] = e->last_ms[0]; ms[1] = e->last_ms[1]; ms[2] = e->last_ms[2];
+    return SVO_OK;
+}
+
+int svo_set_profiling(svo_engine* e, int32_t on) {
+    if (!e) return SVO_ERR_INVALID;
+    cudaStreamSynchronize(e->st);
+    e->profiling = on != 0;
+    e->prof_used = 0;
+    for (int i = 0; i < SVO_PROF_SLOTS; ++i) { e->prof_ms[i] = 0; e->prof_count[i] = 0; }
+    return SVO_OK;
+}
+int svo_profile_slots(void) { return SVO_PROF_SLOTS; }
+const char* svo_profile_name(int32_t slot) {
+    return (slot >= 0 && slot < SVO_PROF_SLOTS) ? kProfNames[slot] : "";
+}
+int svo_get_profile(const svo_engine* e, double* ms, int64_t* counts) {
+    if (!e || !ms || !counts) return SVO_ERR_INVALID;
+    for (int i = 0; i < SVO_PROF_SLOTS; ++i) { ms[i] = e->prof_ms[i]; counts[i] = e->prof_count[i]; }
+    return SVO_OK;
+}
+int svo_timer_begin(svo_engine* e) {
+    if (!e) return SVO_ERR_INVALID;
+    ECUDA(e, cudaSetDevice(e->device));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, cudaEventRecord(e->timer_ev[0], e->st));
+    return SVO_OK;
+}
+int svo_timer_end(svo_engine* e, float* ms) {
+    if (!e || !ms) return SVO_ERR_INVALID;
+    ECUDA(e, cudaSetDevice(e->device));
+    ECUDA(e, cudaEventRecord(e->timer_ev[1], e->st));
+    ECUDA(e, cudaEventSynchronize(e->timer_ev[1]));
+    ECUDA(e, cudaEventElapsedTime(ms, e->timer_ev[0], e->timer_ev[1]));
     return SVO_OK;
 }
 
@@ -683,6 +793,7 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
     }
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     if (dedupe) {
+        ProfScope ps(e, P_DEDUPE);
         ECUDA(e, svo_launch_dedupe(e->d_corners, e->d_ncorners, mcn, e->d_inl, mf, e->p.min_distance,
                                    e->d_pts, e->d_keep_idx, e->d_nnew, cap, dc, n, e->st));
         set_npts_kernel<<<n, 1, 0, e->st>>>(dc, e->d_nnew);
@@ -691,13 +802,18 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
     SvoStereoParams sp = {e->p.num_disparities, e->p.sad_window, e->p.prefilter_cap,
                           e->p.texture_threshold, e->p.uniqueness_ratio};
     if (max_pts > 0) {
+        ProfScope ps(e, P_STEREO);
         ECUDA(e, svo_launch_stereo_bm_sparse(e->d_pyr, e->lay, e->seq_stride, e->d_right,
                                              e->right_stride, e->d_pts, cap, e->d_disp16, sp,
                                              max_pts, dc, n, e->st));
         e->launches += 1;
     }
-    ECUDA(e, svo_launch_reproject(e->d_pts, e->d_disp16, cap, focal, cx, cy, baseline, e->d_valid2d,
-                                  e->d_pts3d, e->d_valid_idx, e->d_nvalid, dc, n, e->st));
+    {
+        ProfScope ps(e, P_REPROJ);
+        ECUDA(e, svo_launch_reproject(e->d_pts, e->d_disp16, cap, focal, cx, cy, baseline,
+                                      e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, dc, n,
+                                      e->st));
+    }
     pack_key_kernel<<<n, 128, 0, e->st>>>(e->d_out, e->key_block, cap, e->d_pts,
                                           dedupe ? e->d_nnew : nullptr, e->d_valid2d, e->d_pts3d,
                                           e->d_valid_idx, e->d_disp16, e->d_nvalid, dc);

@@ -211,7 +211,7 @@ def run_ours(args, rank, world, local_rank):
 
     K, Wm = args.steps, args.warmup
     dev = run_leg(True, K, Wm, profile=True)
-    e2e = run_leg(False, K, Wm, profile=False)
+    e2e = dev if args.skip_e2e else run_leg(False, K, Wm, profile=False)
 
     def reduce_max(x):
         if dist is None:
@@ -261,7 +261,7 @@ def run_ours(args, rank, world, local_rank):
                         "peak_source": peak_src,
                         "algorithmic_bytes_per_launch": ALGO_BYTES[hbm_dom] * S,
                         "dominant_kernel_of_step": dom}
-        cpu = cpu_baseline(sample_frames=args.cpu_frames)
+        cpu = None if args.skip_cpu_baseline else cpu_baseline(sample_frames=args.cpu_frames)
         in_bytes = S * 2 * H * W
         eng_tmp_block = 16 + 24 + 300 * 8 + 400 * 16
         line = {
@@ -389,13 +389,15 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=300)
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--seqs-per-gpu", type=int, default=64)
     ap.add_argument("--textures", type=int, default=8)
     ap.add_argument("--frames", type=int, default=12)
-    ap.add_argument("--cpu-frames", type=int, default=160)
+    ap.add_argument("--cpu-frames", type=int, default=960)
+    ap.add_argument("--skip-cpu-baseline", action="store_true", help="profiling runs only")
+    ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only")
     ap.add_argument("--ref-frames", type=int, default=16)
     args = ap.parse_args()
     rank = _env_int("RANK", 0)

@@ -74,6 +74,8 @@ struct svo_engine {
 
     uint8_t* d_pyr = nullptr;
     uint8_t* d_right = nullptr;
+    uint8_t* d_stage = nullptr;       // [n_seq][2] contiguous (unpitched) H2D landing buffers
+    size_t stage_img = 0;             // bytes of one staged image (width*height rounded to 256)
     float* d_eig = nullptr;
     unsigned int* d_eig_max = nullptr;
     unsigned long long* d_cand = nullptr;
@@ -193,6 +195,42 @@ __global__ void reset_kernel(unsigned int* eig_max, int* cand_count, int* n_corn
     }
 }
 
+// ingest: copy the (unpitched, arbitrarily aligned) source rows of the current stereo pair into
+// the pitched device images (pyramid level 0 of the current slot, right image). A thread moves
+// 16 output bytes: five aligned 32-bit loads, funnel shifts, one 128-bit store.
+__global__ void __launch_bounds__(256)
+ingest_kernel(uint8_t* pyr, SvoPyrLayout lay, size_t seq_stride, uint8_t* right,
+              size_t right_stride, const SvoSeqCall* __restrict__ call) {
+    const SvoSeqCall cd = call[blockIdx.z];
+    const int W = lay.lvl[0].w, H = lay.lvl[0].h, dpitch = lay.lvl[0].pitch;
+    const int y = blockIdx.y * blockDim.y + threadIdx.y;
+    const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    if (y >= H || x0 >= W) return;
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+        const uint8_t* src = which == 0 ? cd.src_left : cd.src_right;
+        if (!src) continue;
+        uint8_t* dst = which == 0
+            ? pyr + (size_t)cd.seq * seq_stride + (size_t)cd.cur_slot * lay.slot_bytes + lay.lvl[0].off
+            : right + (size_t)cd.seq * right_stride;
+        const uint8_t* p = src + (size_t)y * cd.src_pitch + x0;
+        const int valid = min(16, W - x0);
+        const unsigned mis = (unsigned)((uintptr_t)p & 3u);
+        const unsigned int* pa = reinterpret_cast<const unsigned int*>(p - mis);
+        const int nwords = (int)((mis + valid + 3) >> 2);      // aligned words holding valid bytes
+        unsigned int w[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) w[k] = (k < nwords) ? __ldg(pa + k) : 0u;
+        const unsigned sh = mis * 8;
+        uint4 o;
+        o.x = __funnelshift_r(w[0], w[1], sh);
+        o.y = __funnelshift_r(w[1], w[2], sh);
+        o.z = __funnelshift_r(w[2], w[3], sh);
+        o.w = __funnelshift_r(w[3], w[4], sh);
+        *reinterpret_cast<uint4*>(dst + (size_t)y * dpitch + x0) = o;
+    }
+}
+
 // pack the results of one step into a contiguous block per listed sequence (one D2H copy)
 __global__ void pack_step_kernel(unsigned char* out, size_t block, const float2* corners,
                                  const int* n_corners, const int* cand_count, int max_corners,
@@ -293,16 +331,41 @@ uint8_t* slot_ptr(svo_engine* e, int seq, int slot) {
     return e->d_pyr + (size_t)seq * e->seq_stride + (size_t)slot * e->lay.slot_bytes;
 }
 
-cudaError_t upload_left(svo_engine* e, int seq, const uint8_t* img, int pitch, bool device_src) {
-    return cudaMemcpy2DAsync(slot_ptr(e, seq, e->seq[seq].cur_slot) + e->lay.lvl[0].off, e->pitch0,
-                             img, pitch, e->p.width, e->p.height,
-                             device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, e->st);
+// stage one image of the current stereo pair and record its device source in the descriptor
+cudaError_t upload_image(svo_engine* e, SvoSeqCall& c, int which, const uint8_t* img, int pitch,
+                         bool device_src) {
+    const uint8_t* src = img;
+    if (!device_src) {
+        uint8_t* stage = e->d_stage + ((size_t)c.seq * 2 + which) * e->stage_img;
+        const int W = e->p.width, H = e->p.height;
+        cudaError_t ce = (pitch == W)
+            ? cudaMemcpyAsync(stage, img, (size_t)W * H, cudaMemcpyHostToDevice, e->st)
+            : cudaMemcpy2DAsync(stage, W, img, pitch, W, H, cudaMemcpyHostToDevice, e->st);
+        if (ce != cudaSuccess) return ce;
+        src = stage;
+        pitch = W;
+    }
+    if (which == 0) c.src_left = src; else { c.src_right = src; e->seq[c.seq].have_right = true; }
+    c.src_pitch = pitch;
+    return cudaSuccess;
 }
-cudaError_t upload_right(svo_engine* e, int seq, const uint8_t* img, int pitch, bool device_src) {
-    e->seq[seq].have_right = true;
-    return cudaMemcpy2DAsync(e->d_right + (size_t)seq * e->right_stride, e->pitch0, img, pitch,
-                             e->p.width, e->p.height,
-                             device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, e->st);
+cudaError_t upload_left(svo_engine* e, SvoSeqCall& c, const uint8_t* img, int pitch, bool dev) {
+    return upload_image(e, c, 0, img, pitch, dev);
+}
+cudaError_t upload_right(svo_engine* e, SvoSeqCall& c, const uint8_t* img, int pitch, bool dev) {
+    return upload_image(e, c, 1, img, pitch, dev);
+}
+
+// descriptors -> device, then the ingest kernel moves the staged pairs into the pitched images
+cudaError_t push_calls(svo_engine* e, int n);
+cudaError_t push_and_ingest(svo_engine* e, int n) {
+    SVO_CUDA_OK(push_calls(e, n));
+    dim3 blk(128, 2);
+    dim3 grid((e->p.width + 2047) / 2048, (e->p.height + 1) / 2, n);
+    ingest_kernel<<<grid, blk, 0, e->st>>>(e->d_pyr, e->lay, e->seq_stride, e->d_right,
+                                           e->right_stride, e->d_call + (size_t)e->ring * e->n_seq);
+    e->launches += 1;
+    return cudaGetLastError();
 }
 
 cudaError_t push_calls(svo_engine* e, int n) {
@@ -412,12 +475,12 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
         if (e->seq[s].tracker_init && e->seq[s].n_feat > max_feat) max_feat = e->seq[s].n_feat;
     }
     ECUDA(e, cudaEventRecord(e->ev[0], e->st));
-    ECUDA(e, push_calls(e, n));
     for (int i = 0; i < n; ++i) {
-        ECUDA(e, upload_left(e, seqs[i], left[i], pitch, device_src));
-        if (right && right[i]) ECUDA(e, upload_right(e, seqs[i], right[i], pitch, device_src));
+        ECUDA(e, upload_left(e, hc[i], left[i], pitch, device_src));
+        if (right && right[i]) ECUDA(e, upload_right(e, hc[i], right[i], pitch, device_src));
     }
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    ECUDA(e, push_and_ingest(e, n));
     ECUDA(e, launch_detect(e, n, true));
     ECUDA(e, launch_track(e, n, max_feat, 1, true));
     {
@@ -589,6 +652,8 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     const size_t ns = (size_t)n_seq;
     CCHK(dalloc(&e->d_pyr, ns * e->seq_stride));
     CCHK(dalloc(&e->d_right, ns * e->right_stride));
+    e->stage_img = ((size_t)p.width * p.height + 255) & ~(size_t)255;
+    CCHK(dalloc(&e->d_stage, ns * 2 * e->stage_img));
     CCHK(dalloc(&e->d_eig, ns * e->eig_stride));
     CCHK(dalloc(&e->d_eig_max, ns));
     CCHK(dalloc(&e->d_cand, ns * mc));
@@ -636,7 +701,7 @@ void svo_destroy(svo_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->st) cudaStreamSynchronize(e->st);
-    void* dptrs[] = {e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
+    void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
                      e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew,
@@ -724,10 +789,10 @@ int svo_good_features_to_track(svo_engine* e, int32_t seq, const uint8_t* img, i
     begin_frame(e, seq);
     SvoSeqCall* hc = next_call_slot(e);
     fill_call(e, hc[0], seq);
-    ECUDA(e, push_calls(e, 1));
-    ECUDA(e, upload_left(e, seq, img, pitch, false));
+    ECUDA(e, upload_left(e, hc[0], img, pitch, false));
     ECUDA(e, cudaEventRecord(e->ev[0], e->st));
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    ECUDA(e, push_and_ingest(e, 1));
     ECUDA(e, launch_detect(e, 1, true));
     ECUDA(e, cudaEventRecord(e->ev[2], e->st));
     int hdr[2] = {0, 0};
@@ -867,8 +932,13 @@ int svo_triangulate_stereo(svo_engine* e, int32_t seq, const uint8_t* left, cons
     if (n > e->pts_cap) return fail(e, SVO_ERR_CAPACITY, "svo_triangulate_stereo: more features than max(max_corners, max_features)");
     ECUDA(e, cudaSetDevice(e->device));
     begin_frame(e, seq);
-    ECUDA(e, upload_left(e, seq, left, pitch, false));
-    ECUDA(e, upload_right(e, seq, right, pitch, false));
+    {
+        SvoSeqCall* hc = next_call_slot(e);
+        fill_call(e, hc[0], seq);
+        ECUDA(e, upload_left(e, hc[0], left, pitch, false));
+        ECUDA(e, upload_right(e, hc[0], right, pitch, false));
+        ECUDA(e, push_and_ingest(e, 1));
+    }
     // single-sequence call: element 0 of the [n][cap] arrays
     int32_t s = seq, nn = n;
     return keyframe_impl(e, 1, &s, nullptr, nullptr, pose, focal, cx, cy, baseline, false, feats,
@@ -931,8 +1001,8 @@ int svo_tracker_init(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pit
     begin_frame(e, seq);
     SvoSeqCall* hc = next_call_slot(e);
     fill_call(e, hc[0], seq);
-    ECUDA(e, push_calls(e, 1));
-    ECUDA(e, upload_left(e, seq, img, pitch, false));
+    ECUDA(e, upload_left(e, hc[0], img, pitch, false));
+    ECUDA(e, push_and_ingest(e, 1));
     ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), 1, e->st));
     e->launches += e->lay.n_levels - 1;
     // single-sequence view of the [n][max_features] arrays
@@ -953,9 +1023,9 @@ int svo_tracker_track(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pi
     SvoSeqCall* hc = next_call_slot(e);
     fill_call(e, hc[0], seq);
     ECUDA(e, cudaEventRecord(e->ev[0], e->st));
-    ECUDA(e, push_calls(e, 1));
-    ECUDA(e, upload_left(e, seq, img, pitch, false));
+    ECUDA(e, upload_left(e, hc[0], img, pitch, false));
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    ECUDA(e, push_and_ingest(e, 1));
     ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), 1, e->st));
     e->launches += e->lay.n_levels - 1;
     ECUDA(e, launch_track(e, 1, s.n_feat, flow_back ? 1 : 0, false));

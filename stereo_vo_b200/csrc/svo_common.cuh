@@ -35,6 +35,12 @@ struct SvoSeqCall {
     int n_aux;                   // generic secondary count (inliers for dedupe)
     int flags;
     float pose[16];              // camera -> world, row major
+    // source of the current stereo pair for the ingest kernel (device pointers: either the
+    // engine's contiguous H2D staging buffer or caller-owned device memory), rows src_pitch apart
+    const uint8_t* src_left;
+    const uint8_t* src_right;
+    int src_pitch;
+    int pad_;
 };
 
 __host__ __device__ __forceinline__ int svo_reflect101(int i, int n) {

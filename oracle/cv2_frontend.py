@@ -218,7 +218,14 @@ class BundleAdjusterBookkeeping:
 
 
 def solve_pnp(world, pts2d, cam_matrix, rvec, tvec):
-    """src/image_processor.cpp:75-92."""
+    """src/image_processor.cpp:75-92.
+
+    The extrinsic guess is handed over as fresh float64 arrays: with cv2 4.13 a float32 (3,1)
+    in/out rvec/tvec (what the reference's CV_32F zeros at :54-55 become in Python) makes
+    solvePnPRansac return garbage in ~3 % of calls (uninitialised read inside the binding;
+    reproduced single-threaded). The values of the guess are unchanged by the widening."""
+    rvec = np.array(rvec, np.float64).reshape(3, 1).copy()
+    tvec = np.array(tvec, np.float64).reshape(3, 1).copy()
     ok, rvec, tvec, inliers = cv2.solvePnPRansac(
         world.reshape(-1, 1, 3).astype(np.float32), pts2d.reshape(-1, 1, 2).astype(np.float32),
         cam_matrix, np.zeros((4, 1), np.float32), rvec, tvec, True, 100, 8.0, 0.99)

@@ -103,6 +103,10 @@ def pose_inverse(rmat: np.ndarray, tvec: np.ndarray) -> np.ndarray:
 def opencv_pnp(world, pts2d, cam_matrix, rvec, tvec):
     """src/image_processor.cpp:75-92: host-side consumer, exactly the reference's call."""
     import cv2
+    # float64 copies of the guess: cv2 4.13 mis-handles float32 in/out rvec/tvec (garbage poses
+    # in ~3 % of calls); the guess values are unchanged
+    rvec = np.array(rvec, np.float64).reshape(3, 1).copy()
+    tvec = np.array(tvec, np.float64).reshape(3, 1).copy()
     _ok, rvec, tvec, inliers = cv2.solvePnPRansac(
         world.reshape(-1, 1, 3).astype(np.float32), pts2d.reshape(-1, 1, 2).astype(np.float32),
         cam_matrix, np.zeros((4, 1), np.float32), rvec, tvec, True, 100, 8.0, 0.99)

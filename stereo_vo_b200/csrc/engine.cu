@@ -426,14 +426,14 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
             ProfScope ps(e, P_LKF);
             SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_feat,
                                             (size_t)2 * mf, 1, e->d_tracked, e->d_status1, mf, 0,
-                                            lp, mf, gate, 4, dc, n, e->st));
+                                            lp, mf, gate, 4, nullptr, dc, n, e->st));
         }
         e->launches += 1;
         if (flow_back) {
             ProfScope ps(e, P_LKB);
             SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_tracked,
                                             (size_t)mf, 0, e->d_reverse, e->d_status2, mf, 1, lp,
-                                            mf, gate, 4, dc, n, e->st));
+                                            mf, gate, 4, e->d_status1, dc, n, e->st));
             e->launches += 1;
         }
     }

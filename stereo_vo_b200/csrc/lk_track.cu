@@ -3,27 +3,37 @@
 // src/feature_tracker.cpp:23-26 (forward) and :32-35 (backward); arithmetic pinned in
 // oracle/restate.py:lk_track.
 //
-// One block of NW warps per key-point, walking pyramid levels top -> 0 like LKTrackerInvoker:
-//   * the 24x24 raw patch of I around the window is staged in shared memory (reflect-101, the
-//     21-px border OpenCV keeps around each level), unnormalised Scharr derivatives are built
-//     on the fly for the 22x22 integer grid (zero outside the image, as OpenCV's constant
-//     border on the derivative image), then each thread interpolates its share of the 441
-//     window pixels with the 14-bit fixed-point bilinear weights (I*32, Ix, Iy as int16 range);
+// One block of 64 threads per key-point, walking pyramid levels top -> 0 like LKTrackerInvoker.
+// Thread (wy, run) owns 7 horizontally adjacent pixels of window row wy (21 rows x 3 runs = 63
+// threads), so neighbouring taps are shared in registers.
+//   * the 24x24 raw patch of I is staged in shared memory: with aligned 32-bit loads when it
+//     lies inside the image (the common case), byte-wise with reflect-101 at the border;
+//   * interior windows: B = w00*I + w01*I(x+1) + w10*I(y+1) + w11*I(x+1,y+1) is built once on a
+//     23x23 grid (exact integers). The interpolated patch is (B + 2^8) >> 9 and, because the
+//     unnormalised Scharr operator is linear, the interpolated derivatives OpenCV takes from
+//     its int16 derivative image are exactly (Scharr(B) + 2^13) >> 14 - no derivative image is
+//     ever materialised;
+//   * windows touching the image border keep OpenCV's semantics literally: Scharr of the
+//     reflect-101 image on the 22x22 integer grid, ZERO outside the image, then interpolation;
 //   * A11/A12/A22 and, per iteration, b1/b2 are EXACT integer window sums (per-thread int32,
-//     warp REDUX on 16-bit halves, int64 across warps) converted once to f32 - cv2 accumulates
-//     in f32 SIMD lanes, the two agree to <= 1e-4 px (tolerance 0.01 px, BASELINE.json);
-//   * a 28x28 region of J is staged per level and re-staged only when the window leaves it, so
-//     an iteration is shared-memory + integer work only; all threads carry the scalar
-//     Gauss-Newton state redundantly, so control flow is uniform and needs no broadcast.
+//     warp REDUX on 16-bit halves, int64 across the two warps) converted once to f32 - cv2
+//     accumulates in f32 SIMD lanes, the two agree to <= 1e-4 px (tolerance 0.01 px);
+//   * a 28x28 region of J is staged per level (aligned words when interior) and re-staged only
+//     when the window leaves it, so an iteration is shared-memory + integer work only; all
+//     threads carry the scalar Gauss-Newton state redundantly: uniform control flow.
 // Issue/shared-memory bound (<= 400 points x 4 levels x <= 30 iterations), not HBM-bound.
 #include "svo_common.cuh"
 
 namespace {
 
 constexpr int WIN = SVO_LK_WIN;            // 21
-constexpr int WIN2 = WIN * WIN;            // 441
+constexpr int NT = 64;                     // threads per key-point
+constexpr int RUN = 7;                     // window pixels per thread
 constexpr int IP = WIN + 3;                // raw I patch edge (24)
-constexpr int DG = WIN + 1;                // derivative grid edge (22)
+constexpr int SP = 32;                     // byte pitch of the staged I / J rows
+constexpr int BG = WIN + 2;                // B grid edge (23)
+constexpr int BP = 25;                     // int pitch of the B grid
+constexpr int DG = WIN + 1;                // derivative grid edge, border path (22)
 constexpr int JM = 3;                      // margin of the staged J region
 constexpr int JR = WIN + 1 + 2 * JM;       // staged J region edge (28)
 constexpr unsigned FULL = 0xffffffffu;
@@ -49,45 +59,83 @@ __device__ __forceinline__ void lk_weights(float a, float b, int& w00, int& w01,
     w11 = 16384 - w00 - w01 - w10;
 }
 
-template <int NW>
-__global__ void __launch_bounds__(NW * 32)
-lk_track_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_stride,
+// stage an n_rows x (4 * n_words) byte region whose first wanted byte is (x0, y0): aligned
+// 32-bit loads when the region lies inside the image (returns x0 & 3, the byte offset of x0 in
+// a staged row), byte-wise reflect-101 otherwise (returns 0). n_cols wanted bytes per row.
+template <int N_ROWS, int N_COLS>
+__device__ __forceinline__ int stage_region(const uint8_t* __restrict__ img, int w, int h,
+                                            int pitch, int x0, int y0, unsigned* s_words,
+                                            int tid) {
+    constexpr int NW = (N_COLS + 3 + 3) / 4;          // words covering any alignment
+    static_assert(NW * 4 <= SP, "staged row too wide");
+    if (x0 >= 0 && y0 >= 0 && x0 + N_COLS <= w && y0 + N_ROWS <= h) {
+        const int off = x0 & 3;
+        const uint8_t* base = img + (size_t)y0 * pitch + (x0 - off);
+        for (int i = tid; i < N_ROWS * NW; i += NT) {
+            int r = i / NW, c = i - r * NW;
+            s_words[r * (SP / 4) + c] =
+                __ldg(reinterpret_cast<const unsigned*>(base + (size_t)r * pitch) + c);
+        }
+        return off;
+    }
+    unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_words);
+    for (int i = tid; i < N_ROWS * N_COLS; i += NT) {
+        int r = i / N_COLS, c = i - r * N_COLS;
+        int gy = clamp_reflect(y0 + r, h), gx = clamp_reflect(x0 + c, w);
+        s_bytes[r * SP + c] = img[(size_t)gy * pitch + gx];
+    }
+    return 0;
+}
+
+__global__ void __launch_bounds__(NT)
+lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrLayout lay,
+                size_t seq_stride,
                 const float2* __restrict__ in_pts, size_t in_stride, int in_buffered,
                 float2* __restrict__ out_pts, unsigned char* __restrict__ status, int out_stride,
                 int direction, int max_iters, double eps2, double min_eig_thr, int max_pts,
                 const int* __restrict__ gate, int gate_min,
+                const unsigned char* __restrict__ skip_status,
                 const SvoSeqCall* __restrict__ call) {
-    constexpr int NT = NW * 32;
-    constexpr int NPT = (WIN2 + NT - 1) / NT;
+    __shared__ __align__(16) unsigned s_Iw[IP * (SP / 4)];
+    __shared__ __align__(16) unsigned s_Jw[JR * (SP / 4)];
+    __shared__ __align__(16) int s_B[BG * BP];       // border path: s_dx / s_dy alias this
+    __shared__ long long s_red[2][2][3];
 
-    __shared__ unsigned char s_I[IP][IP];
-    __shared__ short s_dx[DG][DG];
-    __shared__ short s_dy[DG][DG];
-    __shared__ unsigned char s_J[JR][JR];
-    __shared__ long long s_red[2][NW][3];
-
-    const SvoSeqCall cd = call[blockIdx.y];
+    const SvoSeqCall* cp = call + blockIdx.y;
+    const int seq = cp->seq;
     const int pi = blockIdx.x;
-    if (pi >= cd.n_feat || (cd.flags & 1) == 0) return;
-    if (gate && gate[cd.seq] < gate_min) return;   // < 4 corners: the reference returns first
+    if (pi >= cp->n_feat || (cp->flags & 1) == 0) return;
+    if (gate && gate[seq] < gate_min) return;      // < 4 corners: the reference returns first
     const int tid = threadIdx.x;
     const int wrp = tid >> 5;
 
-    const uint8_t* seq_base = pyr + (size_t)cd.seq * seq_stride;
-    const int slot_i = direction == 0 ? (1 - cd.cur_slot) : cd.cur_slot;
+    const float2 pt = in_pts[(size_t)seq * in_stride +
+                             (in_buffered ? (size_t)cp->feat_buf * max_pts : 0) + pi];
+    if (skip_status && skip_status[(size_t)seq * out_stride + pi] == 0) {
+        // backward pass of a point the forward pass lost: the reference tracks it anyway
+        // (feature_tracker.cpp:32-35) but never looks at the result (:45-47)
+        if (tid == 0) {
+            out_pts[(size_t)seq * out_stride + pi] = pt;
+            status[(size_t)seq * out_stride + pi] = 0;
+        }
+        return;
+    }
+
+    const int cur_slot = cp->cur_slot;
+    const uint8_t* seq_base = pyr + (size_t)seq * seq_stride;
+    const int slot_i = direction == 0 ? (1 - cur_slot) : cur_slot;
     const uint8_t* __restrict__ pyrI = seq_base + (size_t)slot_i * lay.slot_bytes;
     const uint8_t* __restrict__ pyrJ = seq_base + (size_t)(1 - slot_i) * lay.slot_bytes;
 
-    const float2 pt =
-        in_pts[(size_t)cd.seq * in_stride + (in_buffered ? (size_t)cd.feat_buf * max_pts : 0) + pi];
-
-    // window pixels owned by this thread
-    int wofs[NPT];                           // wy * 32 + wx, or -1
-#pragma unroll
-    for (int t = 0; t < NPT; ++t) {
-        int k = tid + t * NT;
-        wofs[t] = (k < WIN2) ? ((k / WIN) << 5 | (k % WIN)) : -1;
-    }
+    // window pixels owned by this thread: row wy, columns wx0 .. wx0 + 6 (thread 63 idles)
+    const bool has_px = tid < WIN * 3;
+    const int wy = min(tid / 3, WIN - 1);
+    const int wx0 = (tid - (tid / 3) * 3) * RUN;
+    const unsigned char* s_Ib = reinterpret_cast<const unsigned char*>(s_Iw);
+    const unsigned char* s_Jb = reinterpret_cast<const unsigned char*>(s_Jw);
+    short* s_dx = reinterpret_cast<short*>(s_B);
+    short* s_dy = s_dx + DG * DG;
+    static_assert(2 * DG * DG * sizeof(short) <= sizeof(int) * BG * BP, "alias too small");
 
     const float half = 10.f;                 // (winSize - 1) * 0.5
     const float FLT_SCALE = 1.f / (float)(1 << 20);
@@ -117,67 +165,94 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_st
                    w10, w11);
 
         __syncthreads();                     // previous level's readers are done with smem
-        for (int i = tid; i < IP * IP; i += NT) {
-            int r = i / IP, c = i - r * IP;
-            int gy = clamp_reflect(ipy - 1 + r, h), gx = clamp_reflect(ipx - 1 + c, w);
-            s_I[r][c] = I[(size_t)gy * pitch + gx];
-        }
-        __syncthreads();
-        for (int i = tid; i < DG * DG; i += NT) {
-            int r = i / DG, c = i - r * DG;
-            int gy = ipy + r, gx = ipx + c;
-            int vx = 0, vy = 0;
-            if (gx >= 0 && gx < w && gy >= 0 && gy < h) {
-                // s_I[r + 1][c + 1] is pixel (gy, gx)
-                int a0 = s_I[r][c], a1 = s_I[r][c + 1], a2 = s_I[r][c + 2];
-                int b0 = s_I[r + 1][c], b2 = s_I[r + 1][c + 2];
-                int c0 = s_I[r + 2][c], c1 = s_I[r + 2][c + 1], c2 = s_I[r + 2][c + 2];
-                int t0l = 3 * (a0 + c0) + 10 * b0, t0r = 3 * (a2 + c2) + 10 * b2;
-                int t1l = c0 - a0, t1c = c1 - a1, t1r = c2 - a2;
-                vx = t0r - t0l;
-                vy = 3 * (t1l + t1r) + 10 * t1c;
-            }
-            s_dx[r][c] = (short)vx;
-            s_dy[r][c] = (short)vy;
-        }
+        const int offI = stage_region<IP, IP>(I, w, h, pitch, ipx - 1, ipy - 1, s_Iw, tid);
         __syncthreads();
 
-        int ival[NPT], ixv[NPT], iyv[NPT];
+        int ival[RUN], ixv[RUN], iyv[RUN];
+        // every corner of every window pixel inside the image <=> no zero-border derivative
+        const bool grid_inside = ipx >= 0 && ipy >= 0 && ipx + WIN < w && ipy + WIN < h;
+        if (grid_inside) {
+            if (tid < 2 * BG) {              // B grid: thread = (row, half row)
+                const int r = tid >> 1, c0 = (tid & 1) * 12, n = (tid & 1) ? 11 : 12;
+                const unsigned char* p0 = s_Ib + r * SP + offI + c0;
+                const unsigned char* p1 = p0 + SP;
+                int a = p0[0], b = p1[0];
+                int* o = s_B + r * BP + c0;
+#pragma unroll
+                for (int k = 0; k < 12; ++k) {
+                    if (k < n) {
+                        int a1 = p0[k + 1], b1 = p1[k + 1];
+                        o[k] = a * w00 + a1 * w01 + b * w10 + b1 * w11;
+                        a = a1; b = b1;
+                    }
+                }
+            }
+            __syncthreads();
+            const int* bp = s_B + wy * BP + wx0;
+            int t0[RUN + 2], t1[RUN + 2];
+#pragma unroll
+            for (int c = 0; c < RUN + 2; ++c) {
+                int b0 = bp[c], b1 = bp[BP + c], b2 = bp[2 * BP + c];
+                t0[c] = 3 * (b0 + b2) + 10 * b1;
+                t1[c] = b2 - b0;
+                if (c >= 1 && c <= RUN) ival[c - 1] = (b1 + 256) >> 9;
+            }
+#pragma unroll
+            for (int t = 0; t < RUN; ++t) {
+                ixv[t] = (t0[t + 2] - t0[t] + 8192) >> 14;
+                iyv[t] = (3 * (t1[t] + t1[t + 2]) + 10 * t1[t + 1] + 8192) >> 14;
+            }
+        } else {
+            // border path: derivative image semantics of OpenCV (zero outside the image)
+            for (int i = tid; i < DG * DG; i += NT) {
+                int r = i / DG, c = i - r * DG;
+                int gy = ipy + r, gx = ipx + c;
+                int vx = 0, vy = 0;
+                if (gx >= 0 && gx < w && gy >= 0 && gy < h) {
+                    const unsigned char* q = s_Ib + r * SP + c;      // pixel (gy-1, gx-1)
+                    int a0 = q[0], a1 = q[1], a2 = q[2];
+                    int b0 = q[SP], b2 = q[SP + 2];
+                    int c0 = q[2 * SP], c1 = q[2 * SP + 1], c2 = q[2 * SP + 2];
+                    int t0l = 3 * (a0 + c0) + 10 * b0, t0r = 3 * (a2 + c2) + 10 * b2;
+                    int t1l = c0 - a0, t1c = c1 - a1, t1r = c2 - a2;
+                    vx = t0r - t0l;
+                    vy = 3 * (t1l + t1r) + 10 * t1c;
+                }
+                s_dx[i] = (short)vx;
+                s_dy[i] = (short)vy;
+            }
+            __syncthreads();
+#pragma unroll
+            for (int t = 0; t < RUN; ++t) {
+                const int wx = wx0 + t;
+                const unsigned char* q = s_Ib + (wy + 1) * SP + wx + 1;
+                ival[t] = (q[0] * w00 + q[1] * w01 + q[SP] * w10 + q[SP + 1] * w11 + 256) >> 9;
+                const short* dx = s_dx + wy * DG + wx;
+                const short* dy = s_dy + wy * DG + wx;
+                ixv[t] = (dx[0] * w00 + dx[1] * w01 + dx[DG] * w10 + dx[DG + 1] * w11 + 8192) >> 14;
+                iyv[t] = (dy[0] * w00 + dy[1] * w01 + dy[DG] * w10 + dy[DG + 1] * w11 + 8192) >> 14;
+            }
+        }
         int sa11 = 0, sa12 = 0, sa22 = 0;
 #pragma unroll
-        for (int t = 0; t < NPT; ++t) {
-            ival[t] = ixv[t] = iyv[t] = 0;
-            if (wofs[t] >= 0) {
-                int wy = wofs[t] >> 5, wx = wofs[t] & 31;
-                ival[t] = (s_I[wy + 1][wx + 1] * w00 + s_I[wy + 1][wx + 2] * w01 +
-                           s_I[wy + 2][wx + 1] * w10 + s_I[wy + 2][wx + 2] * w11 + 256) >> 9;
-                ixv[t] = (s_dx[wy][wx] * w00 + s_dx[wy][wx + 1] * w01 + s_dx[wy + 1][wx] * w10 +
-                          s_dx[wy + 1][wx + 1] * w11 + 8192) >> 14;
-                iyv[t] = (s_dy[wy][wx] * w00 + s_dy[wy][wx + 1] * w01 + s_dy[wy + 1][wx] * w10 +
-                          s_dy[wy + 1][wx + 1] * w11 + 8192) >> 14;
-                sa11 += ixv[t] * ixv[t];
-                sa12 += ixv[t] * iyv[t];
-                sa22 += iyv[t] * iyv[t];
-            }
+        for (int t = 0; t < RUN; ++t) {
+            if (!has_px) ixv[t] = iyv[t] = 0;
+            sa11 += ixv[t] * ixv[t];
+            sa12 += ixv[t] * iyv[t];
+            sa22 += iyv[t] * iyv[t];
         }
         long long iA11 = warp_sum_exact(sa11), iA12 = warp_sum_exact(sa12),
                   iA22 = warp_sum_exact(sa22);
-        if (NW > 1) {
-            if ((tid & 31) == 0) {
-                s_red[red_par][wrp][0] = iA11;
-                s_red[red_par][wrp][1] = iA12;
-                s_red[red_par][wrp][2] = iA22;
-            }
-            __syncthreads();
-            iA11 = iA12 = iA22 = 0;
-#pragma unroll
-            for (int q = 0; q < NW; ++q) {
-                iA11 += s_red[red_par][q][0];
-                iA12 += s_red[red_par][q][1];
-                iA22 += s_red[red_par][q][2];
-            }
-            red_par ^= 1;
+        if ((tid & 31) == 0) {
+            s_red[red_par][wrp][0] = iA11;
+            s_red[red_par][wrp][1] = iA12;
+            s_red[red_par][wrp][2] = iA22;
         }
+        __syncthreads();
+        iA11 = s_red[red_par][0][0] + s_red[red_par][1][0];
+        iA12 = s_red[red_par][0][1] + s_red[red_par][1][1];
+        iA22 = s_red[red_par][0][2] + s_red[red_par][1][2];
+        red_par ^= 1;
         const float A11 = __fmul_rn(__ll2float_rn(iA11), FLT_SCALE);
         const float A12 = __fmul_rn(__ll2float_rn(iA12), FLT_SCALE);
         const float A22 = __fmul_rn(__ll2float_rn(iA22), FLT_SCALE);
@@ -195,6 +270,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_st
         float2 np = make_float2(__fsub_rn(nextPt.x, half), __fsub_rn(nextPt.y, half));
         float2 prevDelta = make_float2(0.f, 0.f);
         int jx0 = -(1 << 30), jy0 = -(1 << 30);      // staged J origin (none yet)
+        int offJ = 0;
         for (int j = 0; j < max_iters; ++j) {
             const int inx = (int)floorf(np.x), iny = (int)floorf(np.y);
             if (inx < -WIN || inx >= w || iny < -WIN || iny >= h) {
@@ -208,41 +284,34 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_st
                 __syncthreads();
                 jx0 = inx - JM;
                 jy0 = iny - JM;
-                for (int i = tid; i < JR * JR; i += NT) {
-                    int r = i / JR, c = i - r * JR;
-                    int gy = clamp_reflect(jy0 + r, h), gx = clamp_reflect(jx0 + c, w);
-                    s_J[r][c] = J[(size_t)gy * pitch + gx];
-                }
+                offJ = stage_region<JR, JR>(J, w, h, pitch, jx0, jy0, s_Jw, tid);
                 __syncthreads();
                 ox = oy = JM;
             }
             int sb1 = 0, sb2 = 0;
+            {
+                const unsigned char* j0 = s_Jb + (wy + oy) * SP + offJ + wx0 + ox;
+                const unsigned char* j1 = j0 + SP;
+                int a = j0[0], b = j1[0];
 #pragma unroll
-            for (int t = 0; t < NPT; ++t) {
-                if (wofs[t] >= 0) {
-                    int wy = (wofs[t] >> 5) + oy, wx = (wofs[t] & 31) + ox;
-                    int jv = (s_J[wy][wx] * w00 + s_J[wy][wx + 1] * w01 + s_J[wy + 1][wx] * w10 +
-                              s_J[wy + 1][wx + 1] * w11 + 256) >> 9;
+                for (int t = 0; t < RUN; ++t) {
+                    int a1 = j0[t + 1], b1 = j1[t + 1];
+                    int jv = (a * w00 + a1 * w01 + b * w10 + b1 * w11 + 256) >> 9;
                     int diff = jv - ival[t];
                     sb1 += diff * ixv[t];
                     sb2 += diff * iyv[t];
+                    a = a1; b = b1;
                 }
             }
             long long ib1 = warp_sum_exact(sb1), ib2 = warp_sum_exact(sb2);
-            if (NW > 1) {
-                if ((tid & 31) == 0) {
-                    s_red[red_par][wrp][0] = ib1;
-                    s_red[red_par][wrp][1] = ib2;
-                }
-                __syncthreads();
-                ib1 = ib2 = 0;
-#pragma unroll
-                for (int q = 0; q < NW; ++q) {
-                    ib1 += s_red[red_par][q][0];
-                    ib2 += s_red[red_par][q][1];
-                }
-                red_par ^= 1;
+            if ((tid & 31) == 0) {
+                s_red[red_par][wrp][0] = ib1;
+                s_red[red_par][wrp][1] = ib2;
             }
+            __syncthreads();
+            ib1 = s_red[red_par][0][0] + s_red[red_par][1][0];
+            ib2 = s_red[red_par][0][1] + s_red[red_par][1][1];
+            red_par ^= 1;
             const float b1 = __fmul_rn(__ll2float_rn(ib1), FLT_SCALE);
             const float b2 = __fmul_rn(__ll2float_rn(ib2), FLT_SCALE);
             float2 delta;
@@ -270,8 +339,8 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_st
         if (inx < -WIN || inx >= l0.w || iny < -WIN || iny >= l0.h) ok = false;
     }
     if (tid == 0) {
-        out_pts[(size_t)cd.seq * out_stride + pi] = nextPt;
-        status[(size_t)cd.seq * out_stride + pi] = ok ? 1 : 0;
+        out_pts[(size_t)seq * out_stride + pi] = nextPt;
+        status[(size_t)seq * out_stride + pi] = ok ? 1 : 0;
     }
 }
 
@@ -281,24 +350,13 @@ cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, siz
                                 const float2* in_pts, size_t in_stride, int in_buffered,
                                 float2* out_pts, unsigned char* status, int out_stride,
                                 int direction, SvoLkParams lp, int max_pts, const int* gate,
-                                int gate_min, const SvoSeqCall* d_call, int n_call,
-                                cudaStream_t st) {
+                                int gate_min, const unsigned char* skip_status,
+                                const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
     if (max_pts <= 0 || n_call <= 0) return cudaSuccess;
     dim3 grid(lp.grid_pts > 0 ? lp.grid_pts : max_pts, n_call);
-    if (lp.warps_per_point == 1)
-        lk_track_kernel<1><<<grid, 32, 0, st>>>(pyr, lay, seq_stride, in_pts, in_stride,
-                                                in_buffered, out_pts, status, out_stride,
-                                                direction, lp.max_iters, lp.eps2, lp.min_eig,
-                                                max_pts, gate, gate_min, d_call);
-    else if (lp.warps_per_point == 4)
-        lk_track_kernel<4><<<grid, 128, 0, st>>>(pyr, lay, seq_stride, in_pts, in_stride,
-                                                 in_buffered, out_pts, status, out_stride,
-                                                 direction, lp.max_iters, lp.eps2, lp.min_eig,
-                                                 max_pts, gate, gate_min, d_call);
-    else
-        lk_track_kernel<2><<<grid, 64, 0, st>>>(pyr, lay, seq_stride, in_pts, in_stride,
-                                                in_buffered, out_pts, status, out_stride,
-                                                direction, lp.max_iters, lp.eps2, lp.min_eig,
-                                                max_pts, gate, gate_min, d_call);
+    lk_track_kernel<<<grid, NT, 0, st>>>(pyr, lay, seq_stride, in_pts, in_stride, in_buffered,
+                                         out_pts, status, out_stride, direction, lp.max_iters,
+                                         lp.eps2, lp.min_eig, max_pts, gate, gate_min,
+                                         skip_status, d_call);
     return cudaGetLastError();
 }

@@ -122,7 +122,7 @@ struct SvoLkParams {
     int max_iters;
     double eps2;                 // criteria.epsilon squared (OpenCV squares it in double)
     double min_eig;              // minEigThreshold (double in the OpenCV signature)
-    int warps_per_point;         // 1, 2 or 4
+    int warps_per_point;         // accepted for ABI compatibility; the kernel uses 2 warps
     int grid_pts;                // blocks per sequence to launch (0 = max_pts)
 };
 
@@ -131,8 +131,8 @@ cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, siz
                                 const float2* in_pts, size_t in_stride, int in_buffered,
                                 float2* out_pts, unsigned char* status, int out_stride,
                                 int direction, SvoLkParams lp, int max_pts, const int* gate,
-                                int gate_min, const SvoSeqCall* d_call, int n_call,
-                                cudaStream_t st);
+                                int gate_min, const unsigned char* skip_status,
+                                const SvoSeqCall* d_call, int n_call, cudaStream_t st);
 
 struct SvoTrackStats {
     float av_parallax;

@@ -68,7 +68,10 @@ typedef struct svo_params {
     float max_parallax;             /* 200 px */
     int32_t max_features;           /* tracker capacity; 400 = bundle_adjuster.hpp:75 */
     /* launch tuning (no effect on results) */
-    int32_t lk_warps_per_point;     /* 1, 2 or 4; 0 = default */
+    int32_t lk_warps_per_point;     /* accepted for compatibility; the kernel uses 2 warps */
+    /* debug: also store the cv::cornerMinEigenVal map (read by svo_debug_min_eigen_map); the
+     * product path never materialises it */
+    int32_t keep_eig_map;           /* 0 */
 } svo_params;
 
 typedef struct svo_engine svo_engine;   /* opaque */
@@ -149,7 +152,8 @@ SVO_API int svo_tracker_debug(svo_engine* e, int32_t seq, svo_float2* tracked, u
 
 /* ---- component taps (parity tests / profiling) ----------------------------------------- */
 /* eig map of cv::cornerMinEigenVal(img, 3, 3) for the current left frame of `seq`; out is
- * height x width floats, contiguous */
+ * height x width floats, contiguous. SVO_ERR_STATE unless the engine keeps the map
+ * (svo_params.keep_eig_map) */
 SVO_API int svo_debug_min_eigen_map(svo_engine* e, int32_t seq, float* out);
 /* pyramid level `level` of the current left frame; out is h_l x w_l bytes, contiguous */
 SVO_API int svo_debug_pyramid_level(svo_engine* e, int32_t seq, int32_t level, uint8_t* out,

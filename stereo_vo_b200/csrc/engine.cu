@@ -17,10 +17,10 @@
 
 #define SVO_PROF_SLOTS 12
 static const char* const kProfNames[SVO_PROF_SLOTS] = {
-    "pyr_down_u8", "shi_tomasi_score", "nms_threshold_compact", "sort_candidates",
+    "pyr_down_u8", "corner_score_nms", "ingest", "sort_candidates",
     "greedy_min_distance", "lk_track_fwd", "lk_track_bwd", "track_filter_compact",
     "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q"};
-enum { P_PYR, P_SCORE, P_NMS, P_SORT, P_GREEDY, P_LKF, P_LKB, P_FILTER, P_PACK, P_DEDUPE,
+enum { P_PYR, P_SCORE, P_INGEST, P_SORT, P_GREEDY, P_LKF, P_LKB, P_FILTER, P_PACK, P_DEDUPE,
        P_STEREO, P_REPROJ };
 
 namespace {
@@ -80,6 +80,9 @@ struct svo_engine {
     unsigned int* d_eig_max = nullptr;
     unsigned long long* d_cand = nullptr;
     int* d_cand_count = nullptr;
+    unsigned long long* d_strips = nullptr;   // [n_seq][n_strips][strip_cap]
+    int* d_strip_count = nullptr;
+    int n_strips = 0, strip_cap = 0;
     float2* d_corners = nullptr;
     int* d_ncorners = nullptr;
     int* d_grid = nullptr;
@@ -362,6 +365,7 @@ cudaError_t push_and_ingest(svo_engine* e, int n) {
     SVO_CUDA_OK(push_calls(e, n));
     dim3 blk(128, 2);
     dim3 grid((e->p.width + 2047) / 2048, (e->p.height + 1) / 2, n);
+    ProfScope ps(e, P_INGEST);
     ingest_kernel<<<grid, blk, 0, e->st>>>(e->d_pyr, e->lay, e->seq_stride, e->d_right,
                                            e->right_stride, e->d_call + (size_t)e->ring * e->n_seq);
     e->launches += 1;
@@ -386,19 +390,17 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid) {
     }
     {
         ProfScope ps(e, P_SCORE);
-        SVO_CUDA_OK(svo_launch_shi_tomasi(e->d_pyr, e->lay, e->seq_stride, e->d_eig, e->eig_pitch,
-                                          e->eig_stride, e->d_eig_max, dc, n, e->st));
-    }
-    {
-        ProfScope ps(e, P_NMS);
-        SVO_CUDA_OK(svo_launch_nms_compact(e->d_eig, e->p.width, e->p.height, e->eig_pitch,
-                                           e->eig_stride, e->d_eig_max, e->p.quality_level,
-                                           e->d_cand, e->max_cand, e->d_cand_count, dc, n, e->st));
+        SVO_CUDA_OK(svo_launch_corner_score_nms(e->d_pyr, e->lay, e->seq_stride, e->d_eig,
+                                                e->eig_pitch, e->eig_stride, e->d_eig_max,
+                                                e->p.quality_level, e->d_strips, e->n_strips,
+                                                e->strip_cap, e->d_strip_count, dc, n, e->st));
     }
     {
         ProfScope ps(e, P_SORT);
-        SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count, dc, n,
-                                               e->st));
+        SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count,
+                                               e->d_strips, e->n_strips, e->strip_cap,
+                                               e->d_strip_count, e->d_eig_max,
+                                               e->p.quality_level, dc, n, e->st));
     }
     {
         ProfScope ps(e, P_GREEDY);
@@ -407,7 +409,7 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid) {
                                              e->d_corners, e->d_ncorners, e->d_grid,
                                              e->grid_stride, dc, n, e->st));
     }
-    e->launches += 3 + svo_sort_launch_count(e->max_cand);
+    e->launches += 2 + svo_sort_launch_count(e->max_cand);
     return cudaSuccess;
 }
 
@@ -558,6 +560,7 @@ void svo_default_params(svo_params* p, int32_t width, int32_t height) {
     p->max_parallax = 200.f;
     p->max_features = 400;
     p->lk_warps_per_point = 2;
+    p->keep_eig_map = 0;
 }
 
 const char* svo_last_error(const svo_engine* e) { return e ? e->err.c_str() : g_create_err.c_str(); }
@@ -654,7 +657,11 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_right, ns * e->right_stride));
     e->stage_img = ((size_t)p.width * p.height + 255) & ~(size_t)255;
     CCHK(dalloc(&e->d_stage, ns * 2 * e->stage_img));
-    CCHK(dalloc(&e->d_eig, ns * e->eig_stride));
+    if (p.keep_eig_map) CCHK(dalloc(&e->d_eig, ns * e->eig_stride));
+    e->n_strips = svo_corner_strips(p.width);
+    e->strip_cap = svo_corner_strip_cap(p.height);
+    CCHK(dalloc(&e->d_strips, ns * e->n_strips * (size_t)e->strip_cap));
+    CCHK(dalloc(&e->d_strip_count, ns * e->n_strips));
     CCHK(dalloc(&e->d_eig_max, ns));
     CCHK(dalloc(&e->d_cand, ns * mc));
     CCHK(dalloc(&e->d_cand_count, ns));
@@ -687,7 +694,7 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_in), e->h_in_bytes));
     CCHK(cudaMemsetAsync(e->d_pyr, 0, ns * e->seq_stride, e->st));
     CCHK(cudaMemsetAsync(e->d_right, 0, ns * e->right_stride, e->st));
-    CCHK(cudaMemsetAsync(e->d_eig, 0, ns * e->eig_stride * sizeof(float), e->st));
+    if (e->d_eig) CCHK(cudaMemsetAsync(e->d_eig, 0, ns * e->eig_stride * sizeof(float), e->st));
     CCHK(cudaMemsetAsync(e->d_status2, 0, ns * mf, e->st));
     CCHK(cudaMemsetAsync(e->d_reverse, 0, ns * mf * sizeof(float2), e->st));
     CCHK(cudaMemsetAsync(e->d_stats, 0, ns * sizeof(SvoTrackStats), e->st));
@@ -702,7 +709,7 @@ void svo_destroy(svo_engine* e) {
     cudaSetDevice(e->device);
     if (e->st) cudaStreamSynchronize(e->st);
     void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
-                     e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
+                     e->d_strips, e->d_strip_count, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
@@ -1118,6 +1125,7 @@ int svo_debug_min_eigen_map(svo_engine* e, int32_t seq, float* out) {
     int rc = check_seq(e, seq);
     if (rc) return rc;
     if (!out) return fail(e, SVO_ERR_INVALID, "null output");
+    if (!e->d_eig) return fail(e, SVO_ERR_STATE, "eig map not kept: create the engine with keep_eig_map = 1");
     ECUDA(e, cudaSetDevice(e->device));
     ECUDA(e, cudaMemcpy2DAsync(out, (size_t)e->p.width * sizeof(float), e->d_eig + (size_t)seq * e->eig_stride,
                                (size_t)e->eig_pitch * sizeof(float), (size_t)e->p.width * sizeof(float),

@@ -33,16 +33,57 @@ __device__ __forceinline__ void bitonic_step_smem(unsigned long long* s, int cou
     }
 }
 
+// Single-block path: gather the per-strip candidate lists of corner_score_nms, apply the exact
+// quality threshold (step 6: thr = (float)((double)max * quality), keep eig > thr), sort.
 __global__ void __launch_bounds__(SORT_THREADS)
 sort_small_kernel(unsigned long long* __restrict__ cand, int max_cand,
-                  const int* __restrict__ cand_count, const SvoSeqCall* __restrict__ call) {
+                  int* __restrict__ cand_count, const unsigned long long* __restrict__ strips,
+                  int n_strips, int strip_cap, const int* __restrict__ strip_count,
+                  const unsigned int* __restrict__ eig_max, double quality,
+                  const SvoSeqCall* __restrict__ call) {
     extern __shared__ unsigned long long s_keys[];
+    __shared__ int s_n, s_over;
     const int seq = call[blockIdx.x].seq;
     unsigned long long* keys = cand + (size_t)seq * max_cand;
-    const int n = min(cand_count[seq], max_cand);
-    if (n <= 1) return;
+    if (threadIdx.x == 0) { s_n = 0; s_over = 0; }
+    __syncthreads();
+    const unsigned mk = eig_max[seq];
+    const float maxv = mk ? __uint_as_float(svo_key_float_bits(mk)) : 0.f;
+    const float thr = (float)((double)maxv * quality);
+    const int lane = threadIdx.x & 31;
+    for (int st = 0; st < n_strips; ++st) {
+        const int raw = strip_count[seq * n_strips + st];
+        const int cnt = min(raw, strip_cap);
+        if (raw > strip_cap && threadIdx.x == 0) s_over = 1;
+        const unsigned long long* src = strips + ((size_t)seq * n_strips + st) * (size_t)strip_cap;
+        for (int i0 = 0; i0 < cnt; i0 += SORT_THREADS) {
+            const int i = i0 + threadIdx.x;
+            unsigned long long key = 0;
+            bool keep = false;
+            if (i < cnt) {
+                key = src[i];
+                float e = __uint_as_float(svo_key_float_bits((unsigned)(key >> 32)));
+                keep = (e > thr) && (e != 0.f);
+            }
+            unsigned bal = __ballot_sync(0xffffffffu, keep);
+            if (bal) {
+                int base = 0;
+                if (lane == 0) base = atomicAdd(&s_n, __popc(bal));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (keep) {
+                    int idx = base + __popc(bal & ((1u << lane) - 1u));
+                    if (idx < max_cand) s_keys[idx] = key;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int total = s_n;
+    if (threadIdx.x == 0) cand_count[seq] = s_over ? (1 << 30) : total;   // > max_cand: overflow
+    const int n = min(total, max_cand);
+    if (n == 0) return;
     const int npad = next_pow2(n);
-    for (int i = threadIdx.x; i < npad; i += blockDim.x) s_keys[i] = (i < n) ? keys[i] : 0ull;
+    for (int i = n + threadIdx.x; i < npad; i += blockDim.x) s_keys[i] = 0ull;
     __syncthreads();
     for (int k = 2; k <= npad; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
@@ -132,7 +173,7 @@ int svo_sort_capacity_pad(int max_cand) {
 int svo_sort_launch_count(int max_cand) {
     if (max_cand <= SORT_SMEM_MAX) return 1;
     const int cap_pad = svo_sort_capacity_pad(max_cand);
-    int c = 1;
+    int c = 2;                                  // filter + tile sort
     for (int k = SORT_TILE * 2; k <= cap_pad; k <<= 1) {
         for (int j = k >> 1; j >= SORT_TILE; j >>= 1) ++c;
         ++c;
@@ -152,18 +193,24 @@ cudaError_t svo_sort_init() {
     return cudaSuccess;
 }
 
-cudaError_t svo_launch_sort_candidates(unsigned long long* cand, int max_cand,
-                                       const int* cand_count, const SvoSeqCall* d_call, int n_call,
-                                       cudaStream_t st) {
+cudaError_t svo_launch_sort_candidates(unsigned long long* cand, int max_cand, int* cand_count,
+                                       const unsigned long long* strips, int n_strips,
+                                       int strip_cap, const int* strip_count,
+                                       const unsigned int* eig_max, double quality,
+                                       const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
     if (max_cand <= SORT_SMEM_MAX) {
         int p = 2;
         while (p < max_cand) p <<= 1;
-        sort_small_kernel<<<n_call, SORT_THREADS, (size_t)p * 8, st>>>(cand, max_cand, cand_count,
-                                                                       d_call);
+        sort_small_kernel<<<n_call, SORT_THREADS, (size_t)p * 8, st>>>(
+            cand, max_cand, cand_count, strips, n_strips, strip_cap, strip_count, eig_max,
+            quality, d_call);
         return cudaGetLastError();
     }
     const int cap_pad = svo_sort_capacity_pad(max_cand);
     const int tiles = cap_pad / SORT_TILE;
+    SVO_CUDA_OK(svo_launch_filter_candidates(strips, n_strips, strip_cap, strip_count, eig_max,
+                                             quality, cand, cap_pad, max_cand, cand_count, d_call,
+                                             n_call, st));
     sort_tile_kernel<<<dim3(tiles, n_call), SORT_THREADS, SORT_TILE * 8, st>>>(
         cand, cap_pad, cand_count, max_cand, d_call);
     for (int k = SORT_TILE * 2; k <= cap_pad; k <<= 1) {

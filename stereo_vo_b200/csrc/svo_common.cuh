@@ -3,8 +3,9 @@
 // Data layout in HBM (all per engine, indexed by sequence `s`):
 //   pyr    u8   [n_seq][2 slots][levels 0..L]   left-image pyramids, pitched rows (pitch % 128 == 0)
 //   right  u8   [n_seq][H * pitch0]             right image of the current frame
-//   eig    f32  [n_seq][H * eig_pitch]          Shi-Tomasi min-eigenvalue map
-//   cand   u64  [n_seq][max_candidates]         (ordered score bits << 32 | y*W+x)
+//   eig    f32  [n_seq][H * eig_pitch]          Shi-Tomasi min-eigenvalue map (debug tap only)
+//   strips u64  [n_seq][n_strips][strip_cap]    local maxima above the running threshold
+//   cand   u64  [n_seq][max_candidates]         (ordered score bits << 32 | y*W+x), sorted
 // Kernels never see host pointers; launchers take raw device pointers + a stream.
 #pragma once
 #include <cuda_runtime.h>
@@ -73,22 +74,30 @@ cudaError_t svo_launch_pyr_down(uint8_t* pyr, const SvoPyrLayout& lay, size_t se
 cudaError_t svo_launch_pyr_down_single(const uint8_t* src, int w, int h, int spitch,
                                        uint8_t* dst, int dpitch, cudaStream_t st);
 
-cudaError_t svo_launch_shi_tomasi(const uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
-                                  float* eig, int eig_pitch, size_t eig_stride,
-                                  unsigned int* eig_max, const SvoSeqCall* d_call, int n_call,
-                                  cudaStream_t st);
-
-cudaError_t svo_launch_nms_compact(const float* eig, int w, int h, int eig_pitch,
-                                   size_t eig_stride, const unsigned int* eig_max, double quality,
-                                   unsigned long long* cand, int max_cand, int* cand_count,
-                                   const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+// fused Shi-Tomasi score + 3x3 NMS: per-strip candidate lists (corner_score.cu)
+int svo_corner_strips(int w);
+int svo_corner_strip_cap(int h);
+cudaError_t svo_launch_corner_score_nms(const uint8_t* pyr, const SvoPyrLayout& lay,
+                                        size_t seq_stride, float* eig, int eig_pitch,
+                                        size_t eig_stride, unsigned int* eig_max, double quality,
+                                        unsigned long long* strips, int n_strips, int strip_cap,
+                                        int* strip_count, const SvoSeqCall* d_call, int n_call,
+                                        cudaStream_t st);
+cudaError_t svo_launch_filter_candidates(const unsigned long long* strips, int n_strips,
+                                         int strip_cap, const int* strip_count,
+                                         const unsigned int* eig_max, double quality,
+                                         unsigned long long* cand, int cand_stride, int max_cand,
+                                         int* cand_count, const SvoSeqCall* d_call, int n_call,
+                                         cudaStream_t st);
 
 int svo_sort_capacity_pad(int max_cand);
 int svo_sort_launch_count(int max_cand);
 cudaError_t svo_sort_init();
-cudaError_t svo_launch_sort_candidates(unsigned long long* cand, int max_cand,
-                                       const int* cand_count, const SvoSeqCall* d_call, int n_call,
-                                       cudaStream_t st);
+cudaError_t svo_launch_sort_candidates(unsigned long long* cand, int max_cand, int* cand_count,
+                                       const unsigned long long* strips, int n_strips,
+                                       int strip_cap, const int* strip_count,
+                                       const unsigned int* eig_max, double quality,
+                                       const SvoSeqCall* d_call, int n_call, cudaStream_t st);
 
 int svo_greedy_grid_ints(int w, int h, float min_distance);
 cudaError_t svo_greedy_init();

@@ -53,7 +53,7 @@ def test_pyramid_levels_bit_exact(engines, oracle, w, h):
 @pytest.mark.parametrize("w,h", SIZES)
 @pytest.mark.parametrize("seed", [0, 5])
 def test_min_eigen_map_bit_exact(engines, oracle, w, h, seed):
-    e = engines(w, h)
+    e = engines(w, h, keep_eig_map=1)
     img = _image(w, h, seed)
     e.good_features_to_track(img, seq=1)
     got = e.debug_min_eigen_map(seq=1)

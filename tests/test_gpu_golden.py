@@ -23,7 +23,7 @@ def test_gpu_reproduces_golden(svo_lib, name):
     assert np.array_equal(d16, extra["probe_disp16"])
     e.close()
 
-    e = Engine(cam.width, cam.height, n_seq=1)
+    e = Engine(cam.width, cam.height, n_seq=1, keep_eig_map=1)
     gpu = frontend.ImageProcessor(e, frontend.camera_matrix(f, cx, cy), frontend.BundleAdjuster(), b,
                                   teacher=recs)
     for t, (l, r) in enumerate(frames):

@@ -37,9 +37,11 @@ W, H = 1241, 376
 N_PIX = W * H
 # algorithmic bytes per image of the HBM-bound kernels (DESIGN.md / SURVEY.md 8d)
 ALGO_BYTES = {
-    "shi_tomasi_score": 5 * N_PIX,             # u8 read + f32 eig write
-    "nms_threshold_compact": 4 * N_PIX,        # one read of the f32 map (+ 8 B per candidate)
+    # fused Shi-Tomasi score + 3x3 NMS: the u8 image is read once, the f32 eig map is never
+    # written (SURVEY.md 8d "fused" variant), + 8 B per local maximum (~1e4 per image, ignored)
+    "corner_score_nms": N_PIX,
     "pyr_down_u8": 612598 + 153314,            # 3 levels: bytes read + bytes written
+    "ingest": 4 * N_PIX,                       # left+right: staged copy read + pitched image written
 }
 
 
@@ -131,6 +133,8 @@ def run_ours(args, rank, world, local_rank):
     from stereo_vo_b200 import build
     if build.needs_build():
         build.build_lib()
+    if build.host_needs_build():
+        build.build_host_lib()
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: the front end has no CPU path")
     torch.cuda.set_device(local_rank)
@@ -156,62 +160,76 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def run_leg(device_resident: bool, steps: int, warmup: int, profile: bool):
-        eng = capi.Engine(W, H, n_seq=S, device=local_rank)
-        fe = frontend.BatchFrontEnd(eng, cam, pose_fn)
+    def run_leg(device_resident: bool, steps: int, warmup: int, profile: bool, groups: int):
+        import ctypes as C
+        from stereo_vo_b200 import hostapi
+        batch = hostapi.Batch(W, H, S, groups, cam, device=local_rank)
         pitch = W
         dptr = None
         if device_resident:
-            dptr = eng.device_alloc(frames.nbytes)
-            eng.device_upload(dptr, frames)
+            dptr = batch.device_alloc(frames.nbytes)
+            batch.device_upload(dptr, frames)
         img_bytes = H * W
-
-        def inputs(step):
-            ls, rs = [], []
+        base = dptr if device_resident else frames.ctypes.data
+        period = 2 * n_frames - 2
+        # pointer arrays and keyframe poses for every phase of the (periodic) frame schedule
+        sched = []
+        for k in range(period):
+            ls, rs, ps = [], [], []
             for slot in range(S):
-                tex, t = frame_index(step, slot, n_tex, n_frames)
-                if device_resident:
-                    off = ((tex * n_frames + t) * 2) * img_bytes
-                    ls.append(dptr + off)
-                    rs.append(dptr + off + img_bytes)
-                else:
-                    ls.append(frames[tex, t, 0])
-                    rs.append(frames[tex, t, 1])
-            return ls, rs
+                tex, t = frame_index(k, slot, n_tex, n_frames)
+                off = ((tex * n_frames + t) * 2) * img_bytes
+                ls.append(base + off)
+                rs.append(base + off + img_bytes)
+                ps.append(pose_fn(slot, k))
+            poses = np.ascontiguousarray(np.stack(ps).reshape(S, 16), np.float32)
+            sched.append(((C.c_void_p * S)(*ls), (C.c_void_p * S)(*rs), poses,
+                          poses.ctypes.data_as(C.c_void_p)))
+
+        def one(k):
+            lp, rp, _poses, pz = sched[k % period]
+            if device_resident or not args.prefetch:
+                return batch.step_raw(lp, rp, pitch, device_resident, pz)
+            nlp, nrp, _p, _z = sched[(k + 1) % period]
+            return batch.step_raw(lp, rp, pitch, False, pz, nlp, nrp)
 
         for k in range(warmup):
-            ls, rs = inputs(k)
-            fe.step(ls, rs, pitch=pitch, device=device_resident)
-        kf0, launches0 = fe.keyframes, eng.kernel_launches
+            one(k)
+        launches0 = batch.kernel_launches
         if profile:
-            eng.set_profiling(True)
+            batch.set_profiling(True)
         sampler = ClockSampler(local_rank)
         barrier()
         sampler.start()
-        eng.timer_begin()
+        batch.timer_begin()
         t0 = time.perf_counter()
-        tracked = corners = 0
+        tracked = corners = keyframes = 0
         for k in range(warmup, warmup + steps):
-            ls, rs = inputs(k)
-            res, _ = fe.step(ls, rs, pitch=pitch, device=device_resident)
-            tracked += int(res["stats"]["n_kept"].sum())
-            corners += int(res["n_corners"].sum())
-        ev_ms = eng.timer_end()
+            sm = one(k)
+            tracked += sm.tracked
+            corners += sm.corners
+            keyframes += sm.keyframes
+        ev_ms = batch.timer_end()
         barrier()
         wall_ms = (time.perf_counter() - t0) * 1e3
         clocks = sampler.stop()
-        prof = eng.get_profile() if profile else {}
+        prof = batch.get_profile() if profile else {}
         out = dict(ms=max(ev_ms, 0.0), wall_ms=wall_ms, clocks=clocks, prof=prof,
-                   launches=eng.kernel_launches - launches0, keyframes=fe.keyframes - kf0,
+                   launches=batch.kernel_launches - launches0, keyframes=keyframes,
                    tracked=tracked, corners=corners)
         if dptr is not None:
-            eng.device_free(dptr)
-        eng.close()
+            batch.device_free(dptr)
+        batch.close()
         return out
 
     K, Wm = args.steps, args.warmup
-    dev = run_leg(True, K, Wm, profile=True)
-    e2e = dev if args.skip_e2e else run_leg(False, K, Wm, profile=False)
+    dev = run_leg(True, K, Wm, profile=False, groups=args.groups)
+    e2e = dev if args.skip_e2e else run_leg(False, K, Wm, profile=False, groups=args.groups)
+    # per-kernel durations: a separate pass with ONE engine group, so every kernel is timed
+    # alone on the device (with several groups kernels of different streams overlap and their
+    # event-bracketed durations include each other)
+    Kp = max(1, min(K, args.profile_steps))
+    prof_leg = run_leg(True, Kp, Wm, profile=True, groups=1)
 
     def reduce_max(x):
         if dist is None:
@@ -237,21 +255,22 @@ def run_ours(args, rank, world, local_rank):
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else \
             "fallback 6650 GB/s (B200_PROFILING.md)"
-        prof = dev["prof"]
+        prof = prof_leg["prof"]
         kernels = {}
         step_kernel_ms = sum(ms for ms, _ in prof.values())
         for name, (ms, cnt) in prof.items():
             if cnt == 0:
                 continue
-            ent = {"ms_per_step": ms / K, "share": ms / step_kernel_ms if step_kernel_ms else None}
+            ent = {"ms_per_step": ms / Kp, "share": ms / step_kernel_ms if step_kernel_ms else None}
             if name in ALGO_BYTES:
                 gbs = ALGO_BYTES[name] * S * cnt / (ms * 1e-3) / 1e9
                 ent.update(algo_gbs=gbs, frac_of_hbm=gbs / peak)
             kernels[name] = ent
         dom = max(prof.items(), key=lambda kv: kv[1][0])[0] if prof else None
-        # roofline of the dominant HBM-side kernel of the step (shi_tomasi_score unless the
-        # profile says another HBM kernel is bigger)
-        hbm_dom = max((n for n in ALGO_BYTES if n in kernels),
+        # roofline of the dominant kernel among those whose interface is HBM traffic (whole-image
+        # passes); lk_track / stereo / sort / greedy work on <= 400 points per frame and are
+        # issue/latency-bound (profiles/: SM issue and L1 figures from ncu)
+        hbm_dom = max((n for n in ("corner_score_nms", "pyr_down_u8") if n in kernels),
                       key=lambda n: kernels[n]["ms_per_step"], default=None)
         roofline = None
         if hbm_dom:
@@ -272,9 +291,14 @@ def run_ours(args, rank, world, local_rank):
             "config": {"workload": f"{S} independent KITTI-shaped (1241x376) synthetic stereo "
                                    "sequences per GPU, kitti00 params (BASELINE configs[3] shape)",
                        "seqs_per_gpu": S, "frames_per_step": S * world,
-                       "parallelism": f"{world} independent replicas x {S} sequences, no collective",
-                       "l2": "working set per step (inputs 60 MB + eig maps 120 MB + pyramids) "
-                             "exceeds the 126 MB L2; no flush needed",
+                       "parallelism": f"{world} GPU(s) x {S} sequences in {args.groups} engine groups "
+                                      "(one CUDA stream + host worker each), no collective",
+                       "host": "C++ svo::BatchFrontEnd via svo_batch_step (libsvo_host.so); e2e leg "
+                               + ("prefetches" if args.prefetch else "does not prefetch")
+                               + " the next step's frames (svo_prefetch)",
+                       "l2": "inputs larger than L2: every step reads 64 new stereo pairs (60 MB "
+                             "staged + 60 MB pitched copies + 2 x 51 MB pyramid slots in flight "
+                             "> 126 MB L2); no flush between steps",
                        "keyframes_per_step": dev["keyframes"] / K,
                        "tracked_per_frame": dev["tracked"] / (S * K),
                        "corners_per_frame": dev["corners"] / (S * K),
@@ -399,6 +423,12 @@ def main():
     ap.add_argument("--skip-cpu-baseline", action="store_true", help="profiling runs only")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only")
     ap.add_argument("--ref-frames", type=int, default=16)
+    ap.add_argument("--profile-steps", type=int, default=60,
+                    help="steps of the separate single-group pass that times every kernel alone")
+    ap.add_argument("--groups", type=int, default=4,
+                    help="engine groups (CUDA streams + host workers) the sequences of a GPU are split into")
+    ap.add_argument("--no-prefetch", dest="prefetch", action="store_false",
+                    help="e2e leg: do not copy the next step's frames ahead")
     args = ap.parse_args()
     rank = _env_int("RANK", 0)
     world = _env_int("WORLD_SIZE", 1)

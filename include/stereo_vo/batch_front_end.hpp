@@ -1,0 +1,143 @@
+// batch_front_end.hpp - throughput driver for many independent stereo sequences on one GPU
+// (BASELINE configs[3]: 64 KITTI-shaped sequences sharded over 1/2/4/8 B200).
+//
+// The reference processes one camera stream per vo_node process, single-threaded
+// (src/vo_node.cpp:139-227). Here S sequences of one GPU are split into G groups; every group
+// owns one svo_engine (one CUDA stream, batched kernels over its sequences) and one host worker
+// thread that runs the per-frame control flow of ImageProcessor::process for its sequences:
+//   svo_step -> keyframe decision (src/image_processor.cpp:23-25,63-65) -> svo_keyframe ->
+//   id assignment (src/bundle_adjuster.cpp:98-116) -> svo_tracker_set.
+// Groups run concurrently, so the host work and the launch-latency-bound small kernels of one
+// group overlap the heavy kernels of the others, and (host frames) the H2D copies of the next
+// step overlap the kernels of the current one (svo_prefetch). Sequences never interact: there
+// is no collective, on one GPU or across GPUs.
+//
+// PnP-RANSAC is a host consumer outside the accelerated path: in this driver
+// a keyframe keeps every tracked feature as inlier and takes the camera->world pose the caller
+// supplies for that frame (teacher forcing; the facade ImageProcessor is the closed-loop form).
+#pragma once
+#include <condition_variable>
+#include <cstdint>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "svo_c.h"
+
+namespace svo {
+
+struct BatchOptions {
+    svo_params params;            // svo_default_params() + overrides; width/height required
+    int device = 0;
+    int n_seq = 1;
+    int n_groups = 1;
+    float focal = 0.f, cx = 0.f, cy = 0.f, baseline = 0.f;
+    float parallax_thresh = 20.f; // src/vo_node.cpp:35
+};
+
+enum BatchDecision : int32_t { BATCH_TOO_FEW = 1, BATCH_FIRST = 2, BATCH_SKIP = 3, BATCH_KEYFRAME = 4 };
+
+struct BatchSummary {             // totals over all sequences of one step
+    int64_t frames = 0, keyframes = 0, corners = 0, tracked = 0, new_points = 0;
+};
+
+class BatchFrontEnd {
+  public:
+    explicit BatchFrontEnd(const BatchOptions& opt);
+    ~BatchFrontEnd();
+    BatchFrontEnd(const BatchFrontEnd&) = delete;
+    BatchFrontEnd& operator=(const BatchFrontEnd&) = delete;
+
+    // One frame of every sequence. left/right: n_seq image pointers (host memory, or device
+    // memory when on_device), `pitch` bytes per row. poses: n_seq x 16 floats (row-major
+    // camera->world, used only by sequences that become keyframes) or nullptr for identity.
+    // next_left/next_right: optional host frames of the following step, copied ahead while
+    // this step computes. Throws std::runtime_error on a C-ABI failure.
+    BatchSummary step(const uint8_t* const* left, const uint8_t* const* right, int pitch,
+                      bool on_device, const float* poses, const uint8_t* const* next_left = nullptr,
+                      const uint8_t* const* next_right = nullptr);
+
+    int n_seq() const { return opt_.n_seq; }
+    int n_groups() const { return (int)groups_.size(); }
+    int max_corners() const { return opt_.params.max_corners; }
+    int max_features() const { return opt_.params.max_features; }
+
+    // results of the last step for sequence s
+    int32_t decision(int s) const { return seq_[s].decision; }
+    int32_t n_corners(int s) const { return seq_[s].n_corners; }
+    const svo_float2* corners(int s) const;
+    const svo_track_stats& stats(int s) const { return seq_[s].stats; }
+    // tracker set after the step (what FeatureTracker holds): points, ids, count
+    int32_t tracker_count(int s) const { return seq_[s].n_tracker; }
+    const svo_float2* tracker_points(int s) const;
+    const uint64_t* tracker_ids(int s) const;
+    // keyframe outputs of the step (valid when decision is FIRST or KEYFRAME)
+    int32_t n_new(int s) const { return seq_[s].n_new; }
+    const svo_float2* new_2d(int s) const;
+    const svo_float3* new_3d(int s) const;
+
+    int64_t kernel_launches() const;
+    // device-side stopwatch over all groups: begin() synchronises every engine stream and
+    // starts a CUDA-event timer on each; end() returns the longest elapsed time (ms)
+    void timer_begin();
+    float timer_end();
+    void set_profiling(bool on);
+    // sums over groups, indexed by svo_profile_name() slot
+    void get_profile(std::vector<double>& ms, std::vector<int64_t>& counts) const;
+    svo_engine* engine(int group) const { return groups_[group]->e; }
+
+  private:
+    struct SeqState {
+        int group = 0, local = 0;          // engine and index inside it
+        bool have_kf = false;
+        uint64_t next_id = 0;
+        int32_t decision = 0, n_corners = 0, n_tracker = 0, n_new = 0;
+        svo_track_stats stats{};
+    };
+    struct Group {
+        svo_engine* e = nullptr;
+        std::vector<int> seqs;             // global sequence indices, local order
+        std::thread worker;
+        BatchSummary sum;
+        std::string error;
+        // scratch (all sized for the group's sequences)
+        std::vector<int32_t> local_ids, kf_local, n_inl, n_newv, n_valid, counts, n_corn;
+        std::vector<const uint8_t*> lp, rp, nlp, nrp;
+        std::vector<svo_track_stats> stats;
+        std::vector<svo_float2> corners, tracked, inl, new_feats, valid_2d, feats;
+        std::vector<svo_float3> pts_3d;
+        std::vector<uint64_t> tracked_ids, ids;
+        std::vector<int32_t> valid_idx;
+        std::vector<int16_t> disp16;
+        std::vector<float> poses;
+    };
+    struct Job {
+        const uint8_t* const* left = nullptr;
+        const uint8_t* const* right = nullptr;
+        const uint8_t* const* next_left = nullptr;
+        const uint8_t* const* next_right = nullptr;
+        const float* poses = nullptr;
+        int pitch = 0;
+        bool on_device = false;
+    };
+    void run_group(Group& g);
+    void worker_loop(Group* g);
+
+    BatchOptions opt_;
+    std::vector<std::unique_ptr<Group>> groups_;
+    std::vector<SeqState> seq_;
+    // per-sequence result storage (global index)
+    std::vector<svo_float2> corners_, tracker_pts_, new_2d_;
+    std::vector<svo_float3> new_3d_;
+    std::vector<uint64_t> tracker_ids_;
+    Job job_;
+    std::mutex mu_;
+    std::condition_variable cv_start_, cv_done_;
+    uint64_t generation_ = 0;
+    int pending_ = 0;
+    bool stop_ = false;
+};
+
+}  // namespace svo

@@ -176,6 +176,17 @@ SVO_API int svo_step(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_
              const uint8_t* const* right, int32_t pitch, svo_float2* corners, int32_t* n_corners,
              svo_track_stats* stats, svo_float2* tracked, uint64_t* tracked_ids);
 
+/* Optional hint: start copying the stereo pairs of an UPCOMING svo_step() to the device now,
+ * on a second stream, so the transfer overlaps the kernels of the step in flight (the
+ * reference's vo_node keeps up to 5 queued StereoPairs, src/vo_node.cpp:36,73, so the next pair
+ * is known ahead). Returns at once. A later svo_step() whose n, seqs, left, right and pitch are
+ * identical consumes the staged frames instead of copying again; the host buffers must stay
+ * unchanged until that step returns. At most two announcements may be pending (two staging
+ * sets); a step for other frames than the oldest announcement copies normally, and an
+ * announcement passed over twice is dropped. No effect on results. */
+SVO_API int svo_prefetch(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* left,
+                 const uint8_t* const* right, int32_t pitch);
+
 /* Same as svo_step but the frames are already resident in device memory (device pointers,
  * `pitch` bytes per row): the bench's kernel-only leg. */
 SVO_API int svo_step_device(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* d_left,

@@ -1,0 +1,101 @@
+/* svo_host_c.h - C entry points of libsvo_host.so: the C++ host layer that sits on top of the
+ * CUDA library (include/svo_c.h) exposed to non-C++ callers (the Python parity tests, bench.py).
+ *
+ *   svo_vo_*     one stereo sequence driven through the reference-shaped C++ classes
+ *                (include/stereo_vo/image_processor.hpp: ImageProcessor::process over
+ *                FeatureTracker + BundleAdjuster bookkeeping) - the headless stand-in for the
+ *                vo_node main loop, src/vo_node.cpp:112-119,141-144.
+ *   svo_batch_*  many independent sequences per GPU (include/stereo_vo/batch_front_end.hpp).
+ *   svo_camera_from_yaml   the camera YAML semantics of src/vo_node.cpp:82-98.
+ *
+ * Same conventions as svo_c.h: POD only, 0 on success / negative svo_status, nothing throws
+ * across the boundary, *_last_error() returns the message of the last failure.
+ */
+#ifndef SVO_HOST_C_H_
+#define SVO_HOST_C_H_
+
+#include "svo_c.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* flat `key: value` YAML of config/ *.yaml -> the four numbers, narrowed to float */
+SVO_API int svo_camera_from_yaml(const char* yaml_text, float* focal, float* cx, float* cy,
+                                 float* baseline, float* frame_rate);
+
+/* ---- single sequence through ImageProcessor::process --------------------------------- */
+typedef struct svo_vo svo_vo;
+
+/* Host PnP step (src/image_processor.cpp:75-92) supplied by the caller when the library is
+ * built without OpenCV: n world points (xyz) and image points (xy), K row-major 3x3;
+ * rvec/tvec: extrinsic guess in, solution out; rmat: row-major 3x3 rotation out; inliers:
+ * room for n indices. Return 0 on success. */
+typedef int (*svo_pnp_fn)(void* user, int32_t n, const float* world_xyz, const float* image_xy,
+                          const float* K, double* rvec, double* tvec, double* rmat,
+                          int32_t* inliers, int32_t* n_inliers);
+
+enum { SVO_VO_NONE = 0, SVO_VO_TOO_FEW = 1, SVO_VO_FIRST = 2, SVO_VO_SKIP = 3, SVO_VO_KEYFRAME = 4 };
+
+/* what process() did with the last pair; pointers stay valid until the next svo_vo_process() */
+typedef struct svo_vo_record {
+    int32_t decision;
+    int32_t n_detected;      const svo_float2* detected;
+    float av_parallax, percent_lost;
+    int32_t n_tracked;       const svo_float2* tracked;       const uint64_t* tracked_ids;
+    int32_t n_inliers;       const int32_t* inliers;
+    float hmat[16];
+    int32_t n_new_features;  const svo_float2* new_features;  const int16_t* disp16;
+    int32_t n_new;           const int32_t* valid_idx;        const svo_float2* new_2d;
+                             const svo_float3* new_3d;        const uint64_t* new_ids;
+    int32_t n_tracker;       const svo_float2* tracker_pts;   const uint64_t* tracker_ids;
+} svo_vo_record;
+
+/* vo_node's construction sequence (src/vo_node.cpp:104-119): K from focal/cx/cy (float),
+ * BundleAdjuster(window 5), FeatureTracker, ImageProcessor(K, ..., baseline, 30, 20) */
+SVO_API int svo_vo_create(float focal, float cx, float cy, float baseline,
+                          float min_feature_distance, float parallax_thresh, int32_t device,
+                          svo_vo** out);
+SVO_API void svo_vo_destroy(svo_vo* v);
+SVO_API int svo_vo_set_pnp(svo_vo* v, svo_pnp_fn fn, void* user);
+SVO_API int svo_vo_process(svo_vo* v, const uint8_t* left, const uint8_t* right, int32_t width,
+                           int32_t height, int32_t pitch, double t);
+SVO_API int svo_vo_last_record(svo_vo* v, svo_vo_record* out);
+SVO_API const char* svo_vo_last_error(const svo_vo* v);
+
+/* ---- many sequences per GPU ----------------------------------------------------------- */
+typedef struct svo_batch svo_batch;
+
+typedef struct svo_batch_summary {
+    int64_t frames, keyframes, corners, tracked, new_points;
+} svo_batch_summary;
+
+SVO_API int svo_batch_create(const svo_params* p, int32_t device, int32_t n_seq, int32_t n_groups,
+                             float focal, float cx, float cy, float baseline,
+                             float parallax_thresh, svo_batch** out);
+SVO_API void svo_batch_destroy(svo_batch* b);
+SVO_API const char* svo_batch_last_error(const svo_batch* b);   /* b may be NULL (create) */
+/* one frame of every sequence; see svo::BatchFrontEnd::step. left/right/next_*: n_seq pointers
+ * (next_* may be NULL), poses: n_seq x 16 floats or NULL, summary may be NULL */
+SVO_API int svo_batch_step(svo_batch* b, const uint8_t* const* left, const uint8_t* const* right,
+                           int32_t pitch, int32_t on_device, const float* poses,
+                           const uint8_t* const* next_left, const uint8_t* const* next_right,
+                           svo_batch_summary* summary);
+/* per-sequence results of the last step. Arrays: corners [max_corners], tracker_pts /
+ * tracker_ids [max_features], new_2d / new_3d [max_corners]; any may be NULL */
+SVO_API int svo_batch_get(svo_batch* b, int32_t seq, int32_t* decision, int32_t* n_corners,
+                          svo_float2* corners, svo_track_stats* stats, int32_t* n_tracker,
+                          svo_float2* tracker_pts, uint64_t* tracker_ids, int32_t* n_new,
+                          svo_float2* new_2d, svo_float3* new_3d);
+SVO_API int64_t svo_batch_kernel_launches(const svo_batch* b);
+SVO_API int svo_batch_timer_begin(svo_batch* b);
+SVO_API int svo_batch_timer_end(svo_batch* b, float* ms);
+SVO_API int svo_batch_set_profiling(svo_batch* b, int32_t on);
+SVO_API int svo_batch_get_profile(const svo_batch* b, double* ms, int64_t* counts);
+/* engine of group g (device allocation helpers, debugging) */
+SVO_API svo_engine* svo_batch_engine(svo_batch* b, int32_t group);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SVO_HOST_C_H_ */

@@ -20,6 +20,14 @@ NVCC_FLAGS = ["-O3", "-std=c++17", "--fmad=false", "-gencode", "arch=compute_100
               "--threads", "0"]
 
 
+HOST_LIB = os.path.join(HERE, "libsvo_host.so")
+HOST_DIR = os.path.join(HERE, "host")
+INCLUDE = os.path.join(HERE, "..", "include")
+HOST_SOURCES = ["bundle_adjuster.cpp", "camera_config.cpp", "feature_tracker.cpp",
+                "image_processor.cpp", "batch_front_end.cpp", "host_c.cpp"]
+CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wextra", "-pthread"]
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
         if cand and (os.path.isabs(cand) and os.path.exists(cand) or not os.path.isabs(cand)):
@@ -34,6 +42,41 @@ def needs_build() -> bool:
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)]
     deps.append(os.path.join(HERE, "..", "include", "svo_c.h"))
     return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def host_needs_build() -> bool:
+    if not os.path.exists(HOST_LIB):
+        return True
+    t = os.path.getmtime(HOST_LIB)
+    deps = [os.path.join(HOST_DIR, f) for f in os.listdir(HOST_DIR)]
+    for root, _d, files in os.walk(INCLUDE):
+        deps += [os.path.join(root, f) for f in files]
+    deps.append(LIB)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build_host_lib(force: bool = False) -> str:
+    """g++ -> stereo_vo_b200/libsvo_host.so: the C++ host layer (ImageProcessor / FeatureTracker
+    facade, BundleAdjuster bookkeeping, BatchFrontEnd, YAML reader) linked against libsvo.so."""
+    if not force and not host_needs_build():
+        return HOST_LIB
+    cxx = os.environ.get("CXX", "g++")
+    cmd = [cxx, *CXX_FLAGS, "-shared", "-I", INCLUDE,
+           *[os.path.join(HOST_DIR, f) for f in HOST_SOURCES], "-o", HOST_LIB,
+           "-L", HERE, "-l:libsvo.so", "-Wl,-rpath,$ORIGIN"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    text = r.stdout.decode(errors="replace")
+    if r.returncode != 0:
+        sys.stderr.write(f"[build] libsvo_host.so FAILED\n{text}\n")
+        raise RuntimeError("g++ failed")
+    if text.strip():
+        sys.stderr.write(f"[build] libsvo_host.so\n{text}\n")
+    return HOST_LIB
+
+
+def build_all(force: bool = False) -> None:
+    build_lib(force=force)
+    build_host_lib(force=force)
 
 
 def build_lib(force: bool = False, verbose: bool = False) -> str:
@@ -68,3 +111,4 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
 
 if __name__ == "__main__":
     print(build_lib(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host_lib(force="--force" in sys.argv))

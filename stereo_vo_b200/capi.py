@@ -47,7 +47,7 @@ EXPORTS = [
     "svo_good_features_to_track", "svo_triangulate_stereo", "svo_tracker_init",
     "svo_tracker_track", "svo_tracker_get", "svo_dedupe", "svo_tracker_debug",
     "svo_debug_min_eigen_map", "svo_debug_pyramid_level", "svo_debug_candidates",
-    "svo_step", "svo_step_device", "svo_keyframe", "svo_tracker_set",
+    "svo_step", "svo_prefetch", "svo_step_device", "svo_keyframe", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
     "svo_timer_begin", "svo_timer_end",
@@ -98,6 +98,7 @@ def load_library(path: Optional[str] = None):
     lib.svo_debug_candidates.argtypes = [vp, i32, vp, i32, C.POINTER(i32)]
     lib.svo_step.argtypes = [vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp]
     lib.svo_step_device.argtypes = [vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp]
+    lib.svo_prefetch.argtypes = [vp, i32, vp, vp, vp, i32]
     lib.svo_keyframe.argtypes = [vp, i32, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp,
                                  vp, vp]
     lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]
@@ -364,6 +365,16 @@ class Engine:
                        _ptr(stats), _ptr(tracked), _ptr(tids)), "svo_step")
         return dict(corners=corners, n_corners=ncorn, stats=stats, tracked=tracked,
                     tracked_ids=tids)
+
+    def prefetch(self, seqs, left, right):
+        """svo_prefetch: announce the host frames of an upcoming step() (same arrays)."""
+        seqs_a = np.ascontiguousarray(seqs, np.int32)
+        left = [_img(a) for a in left]
+        right = [_img(a) for a in right]
+        pitch = left[0].strides[0]
+        lp, rp = self._ptr_array(left), self._ptr_array(right)
+        self._check(self.lib.svo_prefetch(self.h, len(seqs), _ptr(seqs_a), lp, rp, int(pitch)),
+                    "svo_prefetch")
 
     def keyframe(self, seqs, inliers, n_inliers, poses, focal, cx, cy, baseline):
         n = len(seqs)

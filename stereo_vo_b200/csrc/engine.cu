@@ -74,8 +74,23 @@ struct svo_engine {
 
     uint8_t* d_pyr = nullptr;
     uint8_t* d_right = nullptr;
-    uint8_t* d_stage = nullptr;       // [n_seq][2] contiguous (unpitched) H2D landing buffers
+    uint8_t* d_stage = nullptr;       // [2 sets][n_seq][2] contiguous (unpitched) H2D landing buffers
     size_t stage_img = 0;             // bytes of one staged image (width*height rounded to 256)
+    size_t stage_set = 0;             // bytes of one staging set
+    // svo_prefetch(): stereo pairs of upcoming steps copied ahead on a second stream while the
+    // kernels of the current step run (FIFO, one entry per staging set)
+    struct Prefetch {
+        bool valid = false;
+        int set = 0, n = 0, pitch = 0;
+        std::vector<int32_t> seqs;
+        std::vector<const uint8_t*> left, right;
+        cudaEvent_t done = nullptr;
+        int skipped = 0;              // steps that passed this entry over (other frames)
+    };
+    Prefetch pf[2];
+    int pf_head = 0, pf_count = 0;    // oldest pending entry, number pending
+    int cur_set = 0;                  // staging set of the uploads of the current call
+    cudaStream_t st_copy = nullptr;
     float* d_eig = nullptr;
     unsigned int* d_eig_max = nullptr;
     unsigned long long* d_cand = nullptr;
@@ -334,12 +349,18 @@ uint8_t* slot_ptr(svo_engine* e, int seq, int slot) {
     return e->d_pyr + (size_t)seq * e->seq_stride + (size_t)slot * e->lay.slot_bytes;
 }
 
+void prefetch_discard(svo_engine* e);
+
 // stage one image of the current stereo pair and record its device source in the descriptor
 cudaError_t upload_image(svo_engine* e, SvoSeqCall& c, int which, const uint8_t* img, int pitch,
                          bool device_src) {
     const uint8_t* src = img;
     if (!device_src) {
-        uint8_t* stage = e->d_stage + ((size_t)c.seq * 2 + which) * e->stage_img;
+        // never land in a staging set that holds announced (prefetched) frames
+        if (e->pf_count == 2) prefetch_discard(e);
+        if (e->pf_count == 1) e->cur_set = 1 - e->pf[e->pf_head].set;
+        uint8_t* stage = e->d_stage + (size_t)e->cur_set * e->stage_set +
+                         ((size_t)c.seq * 2 + which) * e->stage_img;
         const int W = e->p.width, H = e->p.height;
         cudaError_t ce = (pitch == W)
             ? cudaMemcpyAsync(stage, img, (size_t)W * H, cudaMemcpyHostToDevice, e->st)
@@ -459,6 +480,54 @@ int finish_timing(svo_engine* e) {
     return SVO_OK;
 }
 
+// drop every pending prefetch (the caller asked for different frames than it announced)
+void prefetch_discard(svo_engine* e) {
+    if (e->pf_count == 0) return;
+    cudaStreamSynchronize(e->st_copy);
+    for (auto& p : e->pf) p.valid = false;
+    e->pf_count = 0;
+    e->pf_head = 0;
+}
+
+// If the oldest pending prefetch announced exactly these frames: make the engine stream wait
+// for its copies, point the descriptors at that staging set and return true.
+bool prefetch_consume(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* left,
+                      const uint8_t* const* right, int pitch, SvoSeqCall* hc) {
+    if (e->pf_count == 0) return false;
+    svo_engine::Prefetch& p = e->pf[e->pf_head];
+    bool same = p.valid && p.n == n && p.pitch == pitch;
+    for (int i = 0; same && i < n; ++i)
+        same = p.seqs[i] == seqs[i] && p.left[i] == left[i] &&
+               p.right[i] == (right ? right[i] : nullptr);
+    if (!same) {
+        // a step for other frames than announced: keep a single announced entry for the step
+        // after this one (the usual "prefetch k+1, then step k" order of a first step), drop
+        // everything if it is passed over twice or both staging sets are taken
+        if (e->pf_count == 2 || ++p.skipped > 1) prefetch_discard(e);
+        return false;
+    }
+    if (cudaStreamWaitEvent(e->st, p.done, 0) != cudaSuccess) {
+        prefetch_discard(e);
+        return false;
+    }
+    const int W = e->p.width;
+    for (int i = 0; i < n; ++i) {
+        uint8_t* base = e->d_stage + (size_t)p.set * e->stage_set +
+                        (size_t)seqs[i] * 2 * e->stage_img;
+        hc[i].src_left = base;
+        hc[i].src_pitch = W;
+        if (p.right[i]) {
+            hc[i].src_right = base + e->stage_img;
+            e->seq[seqs[i]].have_right = true;
+        }
+    }
+    p.valid = false;
+    e->cur_set = p.set;
+    e->pf_head ^= 1;
+    e->pf_count -= 1;
+    return true;
+}
+
 int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* left,
               const uint8_t* const* right, int pitch, bool device_src, svo_float2* corners,
               int32_t* n_corners, svo_track_stats* stats, svo_float2* tracked,
@@ -477,9 +546,15 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
         if (e->seq[s].tracker_init && e->seq[s].n_feat > max_feat) max_feat = e->seq[s].n_feat;
     }
     ECUDA(e, cudaEventRecord(e->ev[0], e->st));
-    for (int i = 0; i < n; ++i) {
-        ECUDA(e, upload_left(e, hc[i], left[i], pitch, device_src));
-        if (right && right[i]) ECUDA(e, upload_right(e, hc[i], right[i], pitch, device_src));
+    if (device_src || !prefetch_consume(e, n, seqs, left, right, pitch, hc)) {
+        if (!device_src) {
+            // the staging set no pending prefetch occupies
+            e->cur_set = e->pf_count ? 1 - e->pf[e->pf_head].set : 0;
+        }
+        for (int i = 0; i < n; ++i) {
+            ECUDA(e, upload_left(e, hc[i], left[i], pitch, device_src));
+            if (right && right[i]) ECUDA(e, upload_right(e, hc[i], right[i], pitch, device_src));
+        }
     }
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     ECUDA(e, push_and_ingest(e, n));
@@ -648,6 +723,8 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     } while (0)
 
     CCHK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
+    CCHK(cudaStreamCreateWithFlags(&e->st_copy, cudaStreamNonBlocking));
+    for (auto& pfe : e->pf) CCHK(cudaEventCreateWithFlags(&pfe.done, cudaEventDisableTiming));
     for (int i = 0; i < 4; ++i) CCHK(cudaEventCreate(&e->ev[i]));
     for (int i = 0; i < 2; ++i) CCHK(cudaEventCreate(&e->timer_ev[i]));
     CCHK(svo_sort_init());
@@ -656,7 +733,8 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_pyr, ns * e->seq_stride));
     CCHK(dalloc(&e->d_right, ns * e->right_stride));
     e->stage_img = ((size_t)p.width * p.height + 255) & ~(size_t)255;
-    CCHK(dalloc(&e->d_stage, ns * 2 * e->stage_img));
+    e->stage_set = ns * 2 * e->stage_img;
+    CCHK(dalloc(&e->d_stage, 2 * e->stage_set));
     if (p.keep_eig_map) CCHK(dalloc(&e->d_eig, ns * e->eig_stride));
     e->n_strips = svo_corner_strips(p.width);
     e->strip_cap = svo_corner_strip_cap(p.height);
@@ -708,6 +786,7 @@ void svo_destroy(svo_engine* e) {
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->st) cudaStreamSynchronize(e->st);
+    if (e->st_copy) cudaStreamSynchronize(e->st_copy);
     void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
                      e->d_strips, e->d_strip_count, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
@@ -721,6 +800,8 @@ void svo_destroy(svo_engine* e) {
     for (int i = 0; i < 4; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; ++i) if (e->timer_ev[i]) cudaEventDestroy(e->timer_ev[i]);
     for (cudaEvent_t ev : e->prof_ev) cudaEventDestroy(ev);
+    for (auto& pfe : e->pf) if (pfe.done) cudaEventDestroy(pfe.done);
+    if (e->st_copy) cudaStreamDestroy(e->st_copy);
     if (e->st) cudaStreamDestroy(e->st);
     delete e;
 }
@@ -777,6 +858,44 @@ int svo_step(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const
              svo_track_stats* stats, svo_float2* tracked, uint64_t* tracked_ids) {
     return step_impl(e, n, seqs, left, right, pitch, false, corners, n_corners, stats, tracked,
                      tracked_ids);
+}
+
+int svo_prefetch(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* left,
+                 const uint8_t* const* right, int32_t pitch) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !seqs || !left) return fail(e, SVO_ERR_INVALID, "svo_prefetch: bad arguments");
+    if (pitch < e->p.width) return fail(e, SVO_ERR_INVALID, "svo_prefetch: pitch < width");
+    if (e->pf_count >= 2) return fail(e, SVO_ERR_STATE, "svo_prefetch: two prefetches already pending");
+    ECUDA(e, cudaSetDevice(e->device));
+    // the set the other pending entry (if any) does not use; with none pending, not the set of
+    // the step that may still be running its ingest kernel
+    int set = e->pf_count ? 1 - e->pf[e->pf_head].set : 1 - e->cur_set;
+    svo_engine::Prefetch& p = e->pf[e->pf_head ^ (e->pf_count ? 1 : 0)];
+    p.seqs.assign(seqs, seqs + n);
+    p.left.assign(left, left + n);
+    p.right.assign((size_t)n, nullptr);
+    const int W = e->p.width, H = e->p.height;
+    for (int i = 0; i < n; ++i) {
+        if (seqs[i] < 0 || seqs[i] >= e->n_seq) return fail(e, SVO_ERR_INVALID, "svo_prefetch: sequence index out of range");
+        if (right) p.right[i] = right[i];
+        for (int which = 0; which < 2; ++which) {
+            const uint8_t* img = which ? p.right[i] : p.left[i];
+            if (!img) continue;
+            uint8_t* stage = e->d_stage + (size_t)set * e->stage_set +
+                             ((size_t)seqs[i] * 2 + which) * e->stage_img;
+            ECUDA(e, pitch == W
+                ? cudaMemcpyAsync(stage, img, (size_t)W * H, cudaMemcpyHostToDevice, e->st_copy)
+                : cudaMemcpy2DAsync(stage, W, img, pitch, W, H, cudaMemcpyHostToDevice, e->st_copy));
+        }
+    }
+    ECUDA(e, cudaEventRecord(p.done, e->st_copy));
+    p.valid = true;
+    p.skipped = 0;
+    p.set = set;
+    p.n = n;
+    p.pitch = pitch;
+    e->pf_count += 1;
+    return SVO_OK;
 }
 
 int svo_step_device(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* d_left,

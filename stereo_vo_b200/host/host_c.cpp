@@ -1,0 +1,265 @@
+// C entry points of libsvo_host.so (include/svo_host_c.h): thin, exception-tight wrappers
+// around the C++ host layer.
+#include "svo_host_c.h"
+
+#include <cstring>
+#include <exception>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "stereo_vo/batch_front_end.hpp"
+#include "stereo_vo/camera_info.hpp"
+#include "stereo_vo/image_processor.hpp"
+
+namespace {
+thread_local std::string g_create_error;
+
+template <typename F>
+int guarded(std::string& err, F&& f) {
+    try {
+        f();
+        return SVO_OK;
+    } catch (const std::invalid_argument& ex) {
+        err = ex.what();
+        return SVO_ERR_INVALID;
+    } catch (const std::logic_error& ex) {
+        err = ex.what();
+        return SVO_ERR_STATE;
+    } catch (const std::bad_alloc&) {
+        err = "out of host memory";
+        return SVO_ERR_NOMEM;
+    } catch (const std::exception& ex) {
+        err = ex.what();
+        return SVO_ERR_CUDA;
+    } catch (...) {
+        err = "unknown exception";
+        return SVO_ERR_CUDA;
+    }
+}
+}  // namespace
+
+struct svo_vo {
+    std::shared_ptr<BundleAdjuster> adjuster;
+    std::shared_ptr<FeatureTracker> tracker;
+    std::unique_ptr<ImageProcessor> processor;
+    std::string error;
+    // flat copies of the last record (size_t ids widened to uint64_t)
+    std::vector<uint64_t> tracked_ids, new_ids, tracker_ids;
+    std::vector<int32_t> inliers, valid_idx;
+};
+
+struct svo_batch {
+    std::unique_ptr<svo::BatchFrontEnd> fe;
+    std::string error;
+};
+
+extern "C" {
+
+int svo_camera_from_yaml(const char* yaml_text, float* focal, float* cx, float* cy,
+                         float* baseline, float* frame_rate) {
+    if (!yaml_text) return SVO_ERR_INVALID;
+    return guarded(g_create_error, [&] {
+        svo::CameraConfig c = svo::parse_camera_yaml(yaml_text);
+        if (focal) *focal = c.focal_length;
+        if (cx) *cx = c.cx;
+        if (cy) *cy = c.cy;
+        if (baseline) *baseline = c.baseline;
+        if (frame_rate) *frame_rate = c.frame_rate;
+    });
+}
+
+int svo_vo_create(float focal, float cx, float cy, float baseline, float min_feature_distance,
+                  float parallax_thresh, int32_t device, svo_vo** out) {
+    if (!out) return SVO_ERR_INVALID;
+    *out = nullptr;
+    return guarded(g_create_error, [&] {
+        auto v = std::make_unique<svo_vo>();
+        cv::Mat K = cv::Mat::eye(3, 3, CV_32F);                      // src/vo_node.cpp:104-108
+        K.at<float>(0, 0) = focal; K.at<float>(0, 2) = cx;
+        K.at<float>(1, 1) = focal; K.at<float>(1, 2) = cy;
+        CameraInfo info;                                             // :110
+        info.focal = focal; info.cx = cx; info.cy = cy; info.baseline = baseline;
+        v->adjuster = std::make_shared<BundleAdjuster>(5, info);     // window 5, vo_node.cpp:36
+        v->tracker = std::make_shared<FeatureTracker>(device);
+        v->processor = std::make_unique<ImageProcessor>(K, v->tracker, v->adjuster, baseline,
+                                                        min_feature_distance, parallax_thresh);
+        *out = v.release();
+    });
+}
+
+void svo_vo_destroy(svo_vo* v) { delete v; }
+
+const char* svo_vo_last_error(const svo_vo* v) { return v ? v->error.c_str() : g_create_error.c_str(); }
+
+int svo_vo_set_pnp(svo_vo* v, svo_pnp_fn fn, void* user) {
+    if (!v || !fn) return SVO_ERR_INVALID;
+    v->processor->set_pnp_solver(
+        [fn, user](const std::vector<cv::Point3f>& world, const std::vector<cv::Point2f>& image,
+                   const cv::Mat& K, cv::Mat& rvec, cv::Mat& tvec, double rmat[9],
+                   std::vector<int>& inliers) {
+            const int32_t n = (int32_t)world.size();
+            float k[9];
+            for (int i = 0; i < 9; ++i) k[i] = K.at<float>(i / 3, i % 3);
+            double rv[3], tv[3];
+            for (int i = 0; i < 3; ++i) {
+                rv[i] = rvec.empty() ? 0.0 : rvec.at<double>(i);
+                tv[i] = tvec.empty() ? 0.0 : tvec.at<double>(i);
+            }
+            std::vector<int32_t> inl((size_t)n + 1);
+            int32_t n_inl = 0;
+            static_assert(sizeof(cv::Point3f) == 12 && sizeof(cv::Point2f) == 8, "packed points");
+            int rc = fn(user, n, reinterpret_cast<const float*>(world.data()),
+                        reinterpret_cast<const float*>(image.data()), k, rv, tv, rmat, inl.data(),
+                        &n_inl);
+            if (rc != 0) return false;
+            rvec = cv::Mat::zeros(3, 1, CV_64F);
+            tvec = cv::Mat::zeros(3, 1, CV_64F);
+            for (int i = 0; i < 3; ++i) { rvec.at<double>(i) = rv[i]; tvec.at<double>(i) = tv[i]; }
+            inliers.assign(inl.begin(), inl.begin() + n_inl);
+            return true;
+        });
+    return SVO_OK;
+}
+
+int svo_vo_process(svo_vo* v, const uint8_t* left, const uint8_t* right, int32_t width,
+                   int32_t height, int32_t pitch, double t) {
+    if (!v || !left || !right || width <= 0 || height <= 0 || pitch < width) return SVO_ERR_INVALID;
+    return guarded(v->error, [&] {
+        // owned copies, like the cv_bridge::toCvCopy images vo_node queues (vo_node.cpp:70-73):
+        // the Keyframe keeps a shallow reference to the left image past this call
+        cv::Mat l = cv::Mat(height, width, CV_8UC1, const_cast<uint8_t*>(left), (size_t)pitch).clone();
+        cv::Mat r = cv::Mat(height, width, CV_8UC1, const_cast<uint8_t*>(right), (size_t)pitch).clone();
+        v->processor->process(StereoPair(l, r, t));
+    });
+}
+
+int svo_vo_last_record(svo_vo* v, svo_vo_record* out) {
+    if (!v || !out) return SVO_ERR_INVALID;
+    const svo::FrameRecord& r = v->processor->last_record();
+    std::memset(out, 0, sizeof *out);
+    auto f2 = [](const std::vector<cv::Point2f>& a) { return reinterpret_cast<const svo_float2*>(a.data()); };
+    v->tracked_ids.assign(r.tracked_ids.begin(), r.tracked_ids.end());
+    v->new_ids.assign(r.new_ids.begin(), r.new_ids.end());
+    v->tracker_ids.assign(r.tracker_ids.begin(), r.tracker_ids.end());
+    v->inliers.assign(r.inliers.begin(), r.inliers.end());
+    v->valid_idx.assign(r.valid_idx.begin(), r.valid_idx.end());
+    out->decision = (int32_t)r.decision;
+    out->n_detected = (int32_t)r.detected.size();
+    out->detected = f2(r.detected);
+    out->av_parallax = r.av_parallax;
+    out->percent_lost = r.percent_lost;
+    out->n_tracked = (int32_t)r.tracked.size();
+    out->tracked = f2(r.tracked);
+    out->tracked_ids = v->tracked_ids.data();
+    out->n_inliers = (int32_t)r.inliers.size();
+    out->inliers = v->inliers.data();
+    std::memcpy(out->hmat, r.hmat, sizeof out->hmat);
+    out->n_new_features = (int32_t)r.new_features.size();
+    out->new_features = f2(r.new_features);
+    out->disp16 = r.disp16.data();
+    out->n_new = (int32_t)r.new_2d.size();
+    out->valid_idx = v->valid_idx.data();
+    out->new_2d = f2(r.new_2d);
+    out->new_3d = reinterpret_cast<const svo_float3*>(r.new_3d.data());
+    out->new_ids = v->new_ids.data();
+    out->n_tracker = (int32_t)r.tracker_pts.size();
+    out->tracker_pts = f2(r.tracker_pts);
+    out->tracker_ids = v->tracker_ids.data();
+    return SVO_OK;
+}
+
+// ------------------------------------------------------------------------------- batch
+int svo_batch_create(const svo_params* p, int32_t device, int32_t n_seq, int32_t n_groups,
+                     float focal, float cx, float cy, float baseline, float parallax_thresh,
+                     svo_batch** out) {
+    if (!p || !out) return SVO_ERR_INVALID;
+    *out = nullptr;
+    return guarded(g_create_error, [&] {
+        svo::BatchOptions o;
+        o.params = *p;
+        o.device = device;
+        o.n_seq = n_seq;
+        o.n_groups = n_groups;
+        o.focal = focal; o.cx = cx; o.cy = cy; o.baseline = baseline;
+        o.parallax_thresh = parallax_thresh;
+        auto b = std::make_unique<svo_batch>();
+        b->fe = std::make_unique<svo::BatchFrontEnd>(o);
+        *out = b.release();
+    });
+}
+
+void svo_batch_destroy(svo_batch* b) { delete b; }
+
+const char* svo_batch_last_error(const svo_batch* b) { return b ? b->error.c_str() : g_create_error.c_str(); }
+
+int svo_batch_step(svo_batch* b, const uint8_t* const* left, const uint8_t* const* right,
+                   int32_t pitch, int32_t on_device, const float* poses,
+                   const uint8_t* const* next_left, const uint8_t* const* next_right,
+                   svo_batch_summary* summary) {
+    if (!b || !left) return SVO_ERR_INVALID;
+    return guarded(b->error, [&] {
+        svo::BatchSummary s = b->fe->step(left, right, pitch, on_device != 0, poses, next_left, next_right);
+        if (summary) {
+            summary->frames = s.frames; summary->keyframes = s.keyframes;
+            summary->corners = s.corners; summary->tracked = s.tracked;
+            summary->new_points = s.new_points;
+        }
+    });
+}
+
+int svo_batch_get(svo_batch* b, int32_t seq, int32_t* decision, int32_t* n_corners,
+                  svo_float2* corners, svo_track_stats* stats, int32_t* n_tracker,
+                  svo_float2* tracker_pts, uint64_t* tracker_ids, int32_t* n_new,
+                  svo_float2* new_2d, svo_float3* new_3d) {
+    if (!b || seq < 0 || seq >= b->fe->n_seq()) return SVO_ERR_INVALID;
+    const svo::BatchFrontEnd& fe = *b->fe;
+    if (decision) *decision = fe.decision(seq);
+    if (n_corners) *n_corners = fe.n_corners(seq);
+    if (corners) std::memcpy(corners, fe.corners(seq), (size_t)fe.n_corners(seq) * sizeof(svo_float2));
+    if (stats) *stats = fe.stats(seq);
+    if (n_tracker) *n_tracker = fe.tracker_count(seq);
+    if (tracker_pts) std::memcpy(tracker_pts, fe.tracker_points(seq), (size_t)fe.tracker_count(seq) * sizeof(svo_float2));
+    if (tracker_ids) std::memcpy(tracker_ids, fe.tracker_ids(seq), (size_t)fe.tracker_count(seq) * sizeof(uint64_t));
+    if (n_new) *n_new = fe.n_new(seq);
+    if (new_2d) std::memcpy(new_2d, fe.new_2d(seq), (size_t)fe.n_new(seq) * sizeof(svo_float2));
+    if (new_3d) std::memcpy(new_3d, fe.new_3d(seq), (size_t)fe.n_new(seq) * sizeof(svo_float3));
+    return SVO_OK;
+}
+
+int64_t svo_batch_kernel_launches(const svo_batch* b) { return b ? b->fe->kernel_launches() : 0; }
+
+int svo_batch_timer_begin(svo_batch* b) {
+    if (!b) return SVO_ERR_INVALID;
+    b->fe->timer_begin();
+    return SVO_OK;
+}
+
+int svo_batch_timer_end(svo_batch* b, float* ms) {
+    if (!b || !ms) return SVO_ERR_INVALID;
+    *ms = b->fe->timer_end();
+    return SVO_OK;
+}
+
+int svo_batch_set_profiling(svo_batch* b, int32_t on) {
+    if (!b) return SVO_ERR_INVALID;
+    b->fe->set_profiling(on != 0);
+    return SVO_OK;
+}
+
+int svo_batch_get_profile(const svo_batch* b, double* ms, int64_t* counts) {
+    if (!b || !ms || !counts) return SVO_ERR_INVALID;
+    std::vector<double> m;
+    std::vector<int64_t> c;
+    b->fe->get_profile(m, c);
+    std::memcpy(ms, m.data(), m.size() * sizeof(double));
+    std::memcpy(counts, c.data(), c.size() * sizeof(int64_t));
+    return SVO_OK;
+}
+
+svo_engine* svo_batch_engine(svo_batch* b, int32_t group) {
+    if (!b || group < 0 || group >= b->fe->n_groups()) return nullptr;
+    return b->fe->engine(group);
+}
+
+}  // extern "C"

@@ -1,0 +1,344 @@
+"""ctypes binding of libsvo_host.so (include/svo_host_c.h): the C++ host layer - the
+reference-shaped ImageProcessor / FeatureTracker facade and the multi-sequence BatchFrontEnd -
+for the Python parity tests and bench.py. No computation happens in this file."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+from typing import Callable, Optional
+
+import numpy as np
+
+from . import capi
+from .capi import STATS_DTYPE, SvoError, SvoParams
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+HOST_LIB_PATH = os.path.join(HERE, "libsvo_host.so")
+HEADER = os.path.join(HERE, "..", "include", "svo_host_c.h")
+
+DECISIONS = {0: None, 1: "too_few", 2: "first", 3: "skip", 4: "keyframe"}
+
+PNP_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_float),
+                     C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                     C.POINTER(C.c_double), C.POINTER(C.c_int32), C.POINTER(C.c_int32))
+
+
+class VoRecord(C.Structure):
+    _fields_ = [
+        ("decision", C.c_int32),
+        ("n_detected", C.c_int32), ("detected", C.c_void_p),
+        ("av_parallax", C.c_float), ("percent_lost", C.c_float),
+        ("n_tracked", C.c_int32), ("tracked", C.c_void_p), ("tracked_ids", C.c_void_p),
+        ("n_inliers", C.c_int32), ("inliers", C.c_void_p),
+        ("hmat", C.c_float * 16),
+        ("n_new_features", C.c_int32), ("new_features", C.c_void_p), ("disp16", C.c_void_p),
+        ("n_new", C.c_int32), ("valid_idx", C.c_void_p), ("new_2d", C.c_void_p),
+        ("new_3d", C.c_void_p), ("new_ids", C.c_void_p),
+        ("n_tracker", C.c_int32), ("tracker_pts", C.c_void_p), ("tracker_ids", C.c_void_p),
+    ]
+
+
+class BatchSummary(C.Structure):
+    _fields_ = [("frames", C.c_int64), ("keyframes", C.c_int64), ("corners", C.c_int64),
+                ("tracked", C.c_int64), ("new_points", C.c_int64)]
+
+
+def declared_symbols():
+    """Every SVO_API function svo_host_c.h declares."""
+    with open(HEADER) as fh:
+        text = fh.read()
+    return re.findall(r"SVO_API\s+[\w\s\*]+?\b(svo_\w+)\s*\(", text)
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libsvo_host.so (which pulls in libsvo.so); raises when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(HOST_LIB_PATH):
+        raise SvoError(f"{HOST_LIB_PATH} is missing: build it with `python -m stereo_vo_b200.build`")
+    capi.load_library()
+    lib = C.CDLL(HOST_LIB_PATH)
+    vp, i32, f32 = C.c_void_p, C.c_int32, C.c_float
+    pf = C.POINTER(f32)
+    lib.svo_camera_from_yaml.argtypes = [C.c_char_p, pf, pf, pf, pf, pf]
+    lib.svo_vo_create.argtypes = [f32, f32, f32, f32, f32, f32, i32, C.POINTER(vp)]
+    lib.svo_vo_destroy.argtypes = [vp]
+    lib.svo_vo_destroy.restype = None
+    lib.svo_vo_set_pnp.argtypes = [vp, PNP_FN, vp]
+    lib.svo_vo_process.argtypes = [vp, vp, vp, i32, i32, i32, C.c_double]
+    lib.svo_vo_last_record.argtypes = [vp, C.POINTER(VoRecord)]
+    lib.svo_vo_last_error.argtypes = [vp]
+    lib.svo_vo_last_error.restype = C.c_char_p
+    lib.svo_batch_create.argtypes = [C.POINTER(SvoParams), i32, i32, i32, f32, f32, f32, f32, f32,
+                                     C.POINTER(vp)]
+    lib.svo_batch_destroy.argtypes = [vp]
+    lib.svo_batch_destroy.restype = None
+    lib.svo_batch_last_error.argtypes = [vp]
+    lib.svo_batch_last_error.restype = C.c_char_p
+    lib.svo_batch_step.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, C.POINTER(BatchSummary)]
+    lib.svo_batch_get.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), vp, vp, C.POINTER(i32),
+                                  vp, vp, C.POINTER(i32), vp, vp]
+    lib.svo_batch_kernel_launches.argtypes = [vp]
+    lib.svo_batch_kernel_launches.restype = C.c_int64
+    lib.svo_batch_timer_begin.argtypes = [vp]
+    lib.svo_batch_timer_end.argtypes = [vp, pf]
+    lib.svo_batch_set_profiling.argtypes = [vp, i32]
+    lib.svo_batch_get_profile.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    lib.svo_batch_engine.argtypes = [vp, i32]
+    lib.svo_batch_engine.restype = vp
+    _lib = lib
+    return lib
+
+
+def camera_from_yaml(text: str):
+    """(focal, cx, cy, baseline, frame_rate) as the float32 values vo_node would hold."""
+    lib = load_library()
+    v = [C.c_float() for _ in range(5)]
+    rc = lib.svo_camera_from_yaml(text.encode(), *[C.byref(x) for x in v])
+    if rc != 0:
+        raise SvoError(f"svo_camera_from_yaml failed ({rc}): "
+                       f"{lib.svo_vo_last_error(None).decode(errors='replace')}")
+    return tuple(np.float32(x.value) for x in v)
+
+
+def _arr(ptr, n, dtype, cols=None):
+    if not ptr or n <= 0:
+        shape = (0,) if cols is None else (0, cols)
+        return np.zeros(shape, dtype)
+    count = n * (cols or 1)
+    buf = (C.c_char * (count * np.dtype(dtype).itemsize)).from_address(ptr)
+    a = np.frombuffer(buf, dtype=dtype, count=count).copy()
+    return a if cols is None else a.reshape(n, cols)
+
+
+class VoSequence:
+    """One stereo sequence through the C++ ImageProcessor facade (svo_vo_*)."""
+
+    def __init__(self, focal, cx, cy, baseline, min_feature_distance=30.0, parallax_thresh=20.0,
+                 device=0, pnp: Optional[Callable] = None):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.svo_vo_create(float(focal), float(cx), float(cy), float(baseline),
+                                    float(min_feature_distance), float(parallax_thresh), device,
+                                    C.byref(h))
+        if rc != 0:
+            raise SvoError(f"svo_vo_create failed ({rc})")
+        self.h = h
+        self._cb = None
+        self.log = []
+        if pnp is not None:
+            self.set_pnp(pnp)
+
+    def set_pnp(self, fn: Callable):
+        """fn(world (n,3) f32, image (n,2) f32, K (3,3) f32, rvec (3,) f64, tvec (3,) f64) ->
+        (rvec, tvec, rmat (3,3), inlier indices)."""
+        def trampoline(_user, n, world, image, k, rvec, tvec, rmat, inliers, n_inl):
+            try:
+                w = np.ctypeslib.as_array(world, shape=(n, 3)).copy()
+                im = np.ctypeslib.as_array(image, shape=(n, 2)).copy()
+                kk = np.ctypeslib.as_array(k, shape=(3, 3)).copy()
+                rv = np.ctypeslib.as_array(rvec, shape=(3,)).copy()
+                tv = np.ctypeslib.as_array(tvec, shape=(3,)).copy()
+                rv2, tv2, rm, inl = fn(w, im, kk, rv, tv)
+                rv2 = np.asarray(rv2, np.float64).reshape(3)
+                tv2 = np.asarray(tv2, np.float64).reshape(3)
+                rm = np.asarray(rm, np.float64).reshape(9)
+                inl = np.asarray(inl, np.int32).reshape(-1)
+                for i in range(3):
+                    rvec[i] = rv2[i]
+                    tvec[i] = tv2[i]
+                for i in range(9):
+                    rmat[i] = rm[i]
+                for i, v in enumerate(inl):
+                    inliers[i] = int(v)
+                n_inl[0] = len(inl)
+                return 0
+            except Exception:                              # never unwind through the C++ frames
+                import traceback
+                traceback.print_exc()
+                return -1
+        self._cb = PNP_FN(trampoline)
+        rc = self.lib.svo_vo_set_pnp(self.h, self._cb, None)
+        if rc != 0:
+            raise SvoError("svo_vo_set_pnp failed")
+
+    def process(self, left: np.ndarray, right: np.ndarray, t: float = 0.0) -> dict:
+        left = np.ascontiguousarray(left, np.uint8)
+        right = np.ascontiguousarray(right, np.uint8)
+        hgt, wid = left.shape
+        rc = self.lib.svo_vo_process(self.h, left.ctypes.data, right.ctypes.data, wid, hgt,
+                                     left.strides[0], float(t))
+        if rc != 0:
+            raise SvoError(f"svo_vo_process failed ({rc}): "
+                           f"{self.lib.svo_vo_last_error(self.h).decode(errors='replace')}")
+        r = VoRecord()
+        self.lib.svo_vo_last_record(self.h, C.byref(r))
+        rec = dict(
+            decision=DECISIONS[r.decision],
+            detected=_arr(r.detected, r.n_detected, np.float32, 2),
+            av_parallax=np.float32(r.av_parallax), percent_lost=np.float32(r.percent_lost),
+            tracked_pts=_arr(r.tracked, r.n_tracked, np.float32, 2),
+            tracked_ids=[int(i) for i in _arr(r.tracked_ids, r.n_tracked, np.uint64)],
+            inliers=_arr(r.inliers, r.n_inliers, np.int32),
+            hmat=np.array(list(r.hmat), np.float32).reshape(4, 4),
+            new_features=_arr(r.new_features, r.n_new_features, np.float32, 2),
+            disp16=_arr(r.disp16, r.n_new_features, np.int16),
+            valid_idx=_arr(r.valid_idx, r.n_new, np.int32),
+            new2d=_arr(r.new_2d, r.n_new, np.float32, 2),
+            new3d=_arr(r.new_3d, r.n_new, np.float32, 3),
+            new_ids=[int(i) for i in _arr(r.new_ids, r.n_new, np.uint64)],
+            tracker_pts=_arr(r.tracker_pts, r.n_tracker, np.float32, 2),
+            tracker_ids=[int(i) for i in _arr(r.tracker_ids, r.n_tracker, np.uint64)],
+        )
+        self.log.append(rec)
+        return rec
+
+    def close(self):
+        if self.h:
+            self.lib.svo_vo_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Batch:
+    """Many independent sequences on one GPU through svo::BatchFrontEnd (svo_batch_*)."""
+
+    def __init__(self, width, height, n_seq, n_groups, cam, device=0, parallax_thresh=20.0,
+                 params: Optional[SvoParams] = None):
+        self.lib = load_library()
+        p = params or capi.default_params(width, height)
+        self.params = p
+        f, cx, cy, b = cam.f32()
+        h = C.c_void_p()
+        rc = self.lib.svo_batch_create(C.byref(p), device, n_seq, n_groups, float(f), float(cx),
+                                       float(cy), float(b), float(parallax_thresh), C.byref(h))
+        if rc != 0:
+            raise SvoError(f"svo_batch_create failed ({rc}): "
+                           f"{self.lib.svo_batch_last_error(None).decode(errors='replace')}")
+        self.h = h
+        self.n_seq = n_seq
+        self.n_groups = max(1, min(n_groups, n_seq))
+        self.max_corners, self.max_features = p.max_corners, p.max_features
+        self._keep = None
+
+    @staticmethod
+    def _ptrs(items, device):
+        if items is None:
+            return None, None
+        if device:
+            arr = (C.c_void_p * len(items))(*[int(x) for x in items])
+            return arr, None
+        keep = [np.ascontiguousarray(a) if a.strides[1] != 1 else a for a in items]
+        arr = (C.c_void_p * len(keep))(*[a.ctypes.data for a in keep])
+        return arr, keep
+
+    def step(self, left, right, pitch, device=False, poses=None, next_left=None, next_right=None):
+        lp, k1 = self._ptrs(left, device)
+        rp, k2 = self._ptrs(right, device)
+        nlp, k3 = self._ptrs(next_left, False) if not device else (None, None)
+        nrp, k4 = self._ptrs(next_right, False) if not device else (None, None)
+        self._keep = (k1, k2, k3, k4)      # prefetched host frames must outlive this call
+        pz = None
+        if poses is not None:
+            poses = np.ascontiguousarray(poses, np.float32).reshape(self.n_seq, 16)
+            pz = poses.ctypes.data_as(C.c_void_p)
+        s = BatchSummary()
+        rc = self.lib.svo_batch_step(self.h, lp, rp, int(pitch), 1 if device else 0, pz, nlp, nrp,
+                                     C.byref(s))
+        if rc != 0:
+            raise SvoError(f"svo_batch_step failed ({rc}): "
+                           f"{self.lib.svo_batch_last_error(self.h).decode(errors='replace')}")
+        return dict(frames=s.frames, keyframes=s.keyframes, corners=s.corners, tracked=s.tracked,
+                    new_points=s.new_points)
+
+    def step_raw(self, lp, rp, pitch, device, poses_ptr=None, nlp=None, nrp=None) -> BatchSummary:
+        """svo_batch_step on prebuilt ctypes pointer arrays (bench inner loop)."""
+        s = BatchSummary()
+        rc = self.lib.svo_batch_step(self.h, lp, rp, int(pitch), 1 if device else 0, poses_ptr,
+                                     nlp, nrp, C.byref(s))
+        if rc != 0:
+            raise SvoError(f"svo_batch_step failed ({rc}): "
+                           f"{self.lib.svo_batch_last_error(self.h).decode(errors='replace')}")
+        return s
+
+    # device-resident frames (bench kernel-only leg): allocations through group 0's engine
+    def device_alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        rc = capi.load_library().svo_device_alloc(self.engine_handle(0), nbytes, C.byref(p))
+        if rc != 0:
+            raise SvoError(f"svo_device_alloc failed ({rc})")
+        return p.value
+
+    def device_upload(self, dst: int, src: np.ndarray):
+        src = np.ascontiguousarray(src)
+        rc = capi.load_library().svo_device_upload(self.engine_handle(0), C.c_void_p(dst),
+                                                   src.ctypes.data_as(C.c_void_p), src.nbytes)
+        if rc != 0:
+            raise SvoError(f"svo_device_upload failed ({rc})")
+
+    def device_free(self, ptr: int):
+        capi.load_library().svo_device_free(self.engine_handle(0), C.c_void_p(ptr))
+
+    def get(self, seq: int) -> dict:
+        dec, nc, nt, nn = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        corners = np.zeros((self.max_corners, 2), np.float32)
+        stats = np.zeros(1, STATS_DTYPE)
+        tp = np.zeros((self.max_features, 2), np.float32)
+        ti = np.zeros(self.max_features, np.uint64)
+        n2 = np.zeros((self.max_corners, 2), np.float32)
+        n3 = np.zeros((self.max_corners, 3), np.float32)
+        rc = self.lib.svo_batch_get(self.h, seq, C.byref(dec), C.byref(nc), corners.ctypes.data,
+                                    stats.ctypes.data, C.byref(nt), tp.ctypes.data, ti.ctypes.data,
+                                    C.byref(nn), n2.ctypes.data, n3.ctypes.data)
+        if rc != 0:
+            raise SvoError(f"svo_batch_get failed ({rc})")
+        return dict(decision=DECISIONS[dec.value], corners=corners[:nc.value], stats=stats[0],
+                    tracker_pts=tp[:nt.value], tracker_ids=ti[:nt.value], new2d=n2[:nn.value],
+                    new3d=n3[:nn.value])
+
+    @property
+    def kernel_launches(self) -> int:
+        return int(self.lib.svo_batch_kernel_launches(self.h))
+
+    def timer_begin(self):
+        self.lib.svo_batch_timer_begin(self.h)
+
+    def timer_end(self) -> float:
+        ms = C.c_float()
+        self.lib.svo_batch_timer_end(self.h, C.byref(ms))
+        return float(ms.value)
+
+    def set_profiling(self, on: bool):
+        self.lib.svo_batch_set_profiling(self.h, 1 if on else 0)
+
+    def get_profile(self) -> dict:
+        lib = capi.load_library()
+        n = lib.svo_profile_slots()
+        ms = (C.c_double * n)()
+        cnt = (C.c_int64 * n)()
+        self.lib.svo_batch_get_profile(self.h, ms, cnt)
+        return {lib.svo_profile_name(i).decode(): (ms[i], cnt[i]) for i in range(n)}
+
+    def engine_handle(self, group: int = 0):
+        return self.lib.svo_batch_engine(self.h, group)
+
+    def close(self):
+        if self.h:
+            self.lib.svo_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

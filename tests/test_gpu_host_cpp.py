@@ -1,0 +1,179 @@
+"""GPU parity of the C++ host layer (libsvo_host.so): the reference-shaped ImageProcessor /
+FeatureTracker facade (include/stereo_vo/*.hpp, reference src/image_processor.cpp:18-163) against
+the cv2 oracle, and the multi-sequence BatchFrontEnd against the single-engine Python driver."""
+import numpy as np
+import pytest
+
+from stereo_vo_b200 import synth
+from tests import util
+from tests.test_gpu_pipeline import _compare
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def host_lib(svo_lib):
+    from stereo_vo_b200 import build, hostapi
+    if build.host_needs_build():
+        build.build_host_lib()
+    return hostapi.load_library()
+
+
+def _teacher_pnp(log, counter):
+    """Replay the oracle's PnP decisions (inliers, rvec, tvec) for the frame being processed."""
+    import cv2
+
+    def pnp(world, image, K, rvec, tvec):
+        tr = log[counter["t"]]
+        assert tr["decision"] == "keyframe", "teacher log out of step with the facade"
+        rmat, _ = cv2.Rodrigues(np.asarray(tr["rvec"], np.float64))
+        return tr["rvec"], tr["tvec"], rmat, tr["inliers"]
+    return pnp
+
+
+@pytest.mark.parametrize("cam,motion,seed,n", [
+    (synth.KITTI00, synth.KITTI_MOTION, 0, 14),
+    (synth.D435I, synth.D435I_MOTION, 1, 10),
+])
+def test_cpp_facade_teacher_forced(host_lib, oracle, cam, motion, seed, n):
+    from stereo_vo_b200 import hostapi
+    fr = synth.sequence(seed, n, cam, motion)
+    ref = oracle.make_pipeline(cam)
+    for l, r in fr:
+        ref.process(l, r)
+    f, cx, cy, b = cam.f32()
+    counter = {"t": 0}
+    vo = hostapi.VoSequence(f, cx, cy, b, pnp=_teacher_pnp(ref.log, counter))
+    for t, (l, r) in enumerate(fr):
+        counter["t"] = t
+        vo.process(l, r, t * 0.1)
+    kf = _compare(ref.log, vo.log)
+    assert kf >= 2
+    for t, (a, g) in enumerate(zip(ref.log, vo.log)):
+        if a["decision"] == "keyframe":
+            assert np.array_equal(a["inliers"], g["inliers"])
+            assert np.abs(a["hmat"] - g["hmat"]).max() <= 1e-6 * max(1.0, np.abs(a["hmat"]).max())
+            # tracked part: sub-pixel flow tolerance; new part: integer corners, exact
+            assert a["tracker_pts"].shape == g["tracker_pts"].shape
+            assert np.abs(a["tracker_pts"] - g["tracker_pts"]).max() <= 0.01 * (1 + t)
+            nn = len(a["new_ids"])
+            assert np.array_equal(a["tracker_pts"][len(a["tracker_pts"]) - nn:],
+                                  g["tracker_pts"][len(g["tracker_pts"]) - nn:])
+    vo.close()
+
+
+def test_cpp_facade_closed_loop(host_lib, oracle):
+    """PnP through the callback on the facade's own tracks (cv2.solvePnPRansac with the
+    reference's arguments): the pose must stay on the synthetic ground truth."""
+    from stereo_vo_b200 import hostapi
+    cam = synth.KITTI00
+    fr = util.frames(0, 12)
+    f, cx, cy, b = cam.f32()
+
+    def pnp(world, image, K, rvec, tvec):
+        rv, tv, rmat, inl = oracle.solve_pnp(world, image, K, rvec, tvec)
+        return rv, tv, rmat, inl
+    vo = hostapi.VoSequence(f, cx, cy, b, pnp=pnp)
+    for t, (l, r) in enumerate(fr):
+        vo.process(l, r, t * 0.1)
+    kfs = [(t, r) for t, r in enumerate(vo.log) if r["decision"] == "keyframe"]
+    assert len(kfs) >= 2
+    for t, r in kfs:
+        gt = np.array(synth.ground_truth(t))
+        assert np.abs(r["hmat"][:3, 3] - gt).max() < 0.05, (t, r["hmat"][:3, 3], gt)
+    vo.close()
+
+
+def test_cpp_facade_needs_a_pnp_solver(host_lib):
+    """Built without OpenCV there is no default PnP: the first frame that needs one fails
+    loudly instead of guessing a pose."""
+    from stereo_vo_b200 import hostapi
+    from stereo_vo_b200.capi import SvoError
+    cam = synth.KITTI00
+    fr = util.frames(0, 12)
+    f, cx, cy, b = cam.f32()
+    vo = hostapi.VoSequence(f, cx, cy, b)
+    with pytest.raises(SvoError, match="PnP"):
+        for l, r in fr:
+            vo.process(l, r)
+    vo.close()
+
+
+@pytest.mark.parametrize("groups,prefetch", [(1, False), (2, True), (3, True)])
+def test_cpp_batch_matches_python_driver(host_lib, oracle, groups, prefetch):
+    """svo::BatchFrontEnd (G engine groups, worker threads, prefetched uploads) == the
+    single-engine Python driver, sequence by sequence and frame by frame."""
+    from stereo_vo_b200 import frontend, hostapi
+    from stereo_vo_b200.capi import Engine
+    cam = synth.KITTI00
+    n_seq, n_fr = 5, 7
+    seqs = [util.frames(s % 3, n_fr, start=2 * (s // 3)) for s in range(n_seq)]
+
+    def pose_fn(s, t):
+        p = np.eye(4, dtype=np.float32)
+        p[:3, 3] = synth.ground_truth(t)
+        return p
+    e = Engine(cam.width, cam.height, n_seq=n_seq)
+    py = frontend.BatchFrontEnd(e, cam, pose_fn)
+    cb = hostapi.Batch(cam.width, cam.height, n_seq, groups, cam)
+    assert cb.n_groups == groups
+    total_kf = 0
+    for t in range(n_fr):
+        left = [seqs[s][t][0] for s in range(n_seq)]
+        right = [seqs[s][t][1] for s in range(n_seq)]
+        nl = nr = None
+        if prefetch and t + 1 < n_fr:
+            nl = [seqs[s][t + 1][0] for s in range(n_seq)]
+            nr = [seqs[s][t + 1][1] for s in range(n_seq)]
+        res, kfs = py.step(left, right)
+        poses = np.stack([pose_fn(s, t) for s in range(n_seq)])
+        summ = cb.step(left, right, left[0].strides[0], poses=poses, next_left=nl, next_right=nr)
+        assert summ["frames"] == n_seq and summ["keyframes"] == len(kfs)
+        total_kf += len(kfs)
+        for s in range(n_seq):
+            g = cb.get(s)
+            n = int(res["n_corners"][s])
+            assert np.array_equal(g["corners"], res["corners"][s, :n]), (t, s)
+            assert (g["decision"] in ("first", "keyframe")) == (s in kfs), (t, s, g["decision"])
+            if g["decision"] == "skip":
+                k = int(res["stats"][s]["n_kept"])
+                assert g["stats"].tobytes() == res["stats"][s].tobytes()
+                assert np.array_equal(g["tracker_pts"], res["tracked"][s, :k])
+                assert np.array_equal(g["tracker_ids"], res["tracked_ids"][s, :k])
+    assert total_kf >= n_seq + 2
+    # the two drivers end with identical tracker sets on the device
+    for s in range(n_seq):
+        pts, ids = e.tracker_get(s)
+        g = cb.get(s)
+        assert np.array_equal(g["tracker_pts"], pts) and np.array_equal(g["tracker_ids"], ids)
+    cb.close()
+    e.close()
+
+
+def test_prefetch_is_transparent(svo_lib, oracle):
+    """svo_prefetch announced / not announced / announced for other frames: same results."""
+    from stereo_vo_b200.capi import Engine
+    cam = synth.KITTI00
+    fr = util.frames(1, 5)
+    outs = []
+    for mode in ("none", "announce", "wrong"):
+        e = Engine(cam.width, cam.height, n_seq=1)
+        rec = []
+        for t, (l, r) in enumerate(fr):
+            if mode == "announce" and t + 1 < len(fr):
+                e.prefetch([0], [fr[t + 1][0]], [fr[t + 1][1]])
+            if mode == "wrong" and t + 2 < len(fr):
+                e.prefetch([0], [fr[t + 2][0]], [fr[t + 2][1]])
+            res = e.step([0], [l], [r])
+            n = int(res["n_corners"][0])
+            rec.append(res["corners"][0, :n].copy())
+            if t == 0:
+                e.tracker_set([0], [res["corners"][0, :n]], [np.arange(n, dtype=np.uint64)])
+            else:
+                rec.append(res["tracked"][0, :int(res["stats"][0]["n_kept"])].copy())
+        outs.append(rec)
+        e.close()
+    for other in outs[1:]:
+        assert len(other) == len(outs[0])
+        for a, b in zip(outs[0], other):
+            assert np.array_equal(a, b)

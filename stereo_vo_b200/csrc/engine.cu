@@ -351,6 +351,26 @@ uint8_t* slot_ptr(svo_engine* e, int seq, int slot) {
 
 void prefetch_discard(svo_engine* e);
 
+// H2D of one stereo pair into staging set `set` on stream `st` (one copy when the pair is
+// contiguous in host memory, else one per image)
+cudaError_t stage_pair(svo_engine* e, cudaStream_t st, int set, int seq, const uint8_t* left,
+                       const uint8_t* right, int pitch) {
+    const int W = e->p.width, H = e->p.height;
+    uint8_t* base = e->d_stage + (size_t)set * e->stage_set + (size_t)seq * 2 * e->stage_img;
+    if (pitch == W && right == left + (size_t)W * H)
+        return cudaMemcpyAsync(base, left, (size_t)2 * W * H, cudaMemcpyHostToDevice, st);
+    for (int which = 0; which < 2; ++which) {
+        const uint8_t* img = which ? right : left;
+        if (!img) continue;
+        uint8_t* dst = base + (size_t)which * e->stage_img;
+        cudaError_t ce = (pitch == W)
+            ? cudaMemcpyAsync(dst, img, (size_t)W * H, cudaMemcpyHostToDevice, st)
+            : cudaMemcpy2DAsync(dst, W, img, pitch, W, H, cudaMemcpyHostToDevice, st);
+        if (ce != cudaSuccess) return ce;
+    }
+    return cudaSuccess;
+}
+
 // stage one image of the current stereo pair and record its device source in the descriptor
 cudaError_t upload_image(svo_engine* e, SvoSeqCall& c, int which, const uint8_t* img, int pitch,
                          bool device_src) {
@@ -552,8 +572,21 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
             e->cur_set = e->pf_count ? 1 - e->pf[e->pf_head].set : 0;
         }
         for (int i = 0; i < n; ++i) {
-            ECUDA(e, upload_left(e, hc[i], left[i], pitch, device_src));
-            if (right && right[i]) ECUDA(e, upload_right(e, hc[i], right[i], pitch, device_src));
+            if (device_src) {
+                ECUDA(e, upload_left(e, hc[i], left[i], pitch, true));
+                if (right && right[i]) ECUDA(e, upload_right(e, hc[i], right[i], pitch, true));
+                continue;
+            }
+            const uint8_t* r = right ? right[i] : nullptr;
+            ECUDA(e, stage_pair(e, e->st, e->cur_set, seqs[i], left[i], r, pitch));
+            uint8_t* base = e->d_stage + (size_t)e->cur_set * e->stage_set +
+                            (size_t)seqs[i] * 2 * e->stage_img;
+            hc[i].src_left = base;
+            hc[i].src_pitch = e->p.width;
+            if (r) {
+                hc[i].src_right = base + e->stage_img;
+                e->seq[seqs[i]].have_right = true;
+            }
         }
     }
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
@@ -732,7 +765,9 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     const size_t ns = (size_t)n_seq;
     CCHK(dalloc(&e->d_pyr, ns * e->seq_stride));
     CCHK(dalloc(&e->d_right, ns * e->right_stride));
-    e->stage_img = ((size_t)p.width * p.height + 255) & ~(size_t)255;
+    // exact stride: a host pair stored back to back (right == left + W*H) lands with ONE copy;
+    // the ingest kernel reads the staged images with aligned words + funnel shifts
+    e->stage_img = (size_t)p.width * p.height;
     e->stage_set = ns * 2 * e->stage_img;
     CCHK(dalloc(&e->d_stage, 2 * e->stage_set));
     if (p.keep_eig_map) CCHK(dalloc(&e->d_eig, ns * e->eig_stride));
@@ -874,19 +909,10 @@ int svo_prefetch(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* c
     p.seqs.assign(seqs, seqs + n);
     p.left.assign(left, left + n);
     p.right.assign((size_t)n, nullptr);
-    const int W = e->p.width, H = e->p.height;
     for (int i = 0; i < n; ++i) {
         if (seqs[i] < 0 || seqs[i] >= e->n_seq) return fail(e, SVO_ERR_INVALID, "svo_prefetch: sequence index out of range");
         if (right) p.right[i] = right[i];
-        for (int which = 0; which < 2; ++which) {
-            const uint8_t* img = which ? p.right[i] : p.left[i];
-            if (!img) continue;
-            uint8_t* stage = e->d_stage + (size_t)set * e->stage_set +
-                             ((size_t)seqs[i] * 2 + which) * e->stage_img;
-            ECUDA(e, pitch == W
-                ? cudaMemcpyAsync(stage, img, (size_t)W * H, cudaMemcpyHostToDevice, e->st_copy)
-                : cudaMemcpy2DAsync(stage, W, img, pitch, W, H, cudaMemcpyHostToDevice, e->st_copy));
-        }
+        ECUDA(e, stage_pair(e, e->st_copy, set, seqs[i], p.left[i], p.right[i], pitch));
     }
     ECUDA(e, cudaEventRecord(p.done, e->st_copy));
     p.valid = true;

@@ -3,115 +3,140 @@
 // oracle/restate.py:pyr_down). dst size ((w+1)/2, (h+1)/2); separable [1 4 6 4 1] with
 // BORDER_REFLECT_101; out = (sum + 128) >> 8. Pure integer, bit-exact.
 //
-// HBM-bound: algorithmic bytes = w*h (read) + ow*oh (write). A block produces a 128x8 output
-// tile: the (2*8+3) x (256+32) source footprint is staged into shared memory with 128-bit
-// loads (rows reflected at staging time, columns reflected when the taps are read), the
-// horizontal pass leaves 16-bit partial sums in shared memory, the vertical pass writes packed
-// uchar4 words (a warp stores 128 contiguous bytes).
+// HBM-bound: algorithmic bytes = w*h (read) + ow*oh (write). Register-only design, no shared
+// memory and no barrier:
+//   * a thread owns 4 adjacent output columns and ROWS output rows; a warp therefore
+//     reads 256 contiguous source bytes per source row (aligned 32/64-bit loads) and stores 128
+//     contiguous output bytes per output row;
+//   * horizontal pass: the five taps of an output are one dp4a with weights (1,4,6,4) on the
+//     word that starts two pixels left of the centre plus one dp4a that picks the fifth byte -
+//     8 dp4a + 2 byte permutes per 4 outputs and source row;
+//   * the 12-bit horizontal sums of two neighbouring outputs share one 32-bit register (16-bit
+//     lanes); the vertical pass P0 + P4 + 4(P1 + P3) + 6 P2 + 128 cannot carry between lanes
+//     (<= 255*256 + 128 < 2^16), so it runs on both lanes at once;
+//   * a thread filters its 2*ROWS+3 source rows up front (all loads in flight together), then
+//     runs the vertical pass; rows outside the image are fetched through reflect-101 indices,
+//     columns outside the image by per-thread byte-permute / weight constants (no edge path).
 #include "svo_common.cuh"
 
 namespace {
 
-constexpr int TW = 128;                  // output tile width
-constexpr int TH = 8;                    // output tile height
-constexpr int SROWS = 2 * TH + 3;        // source rows needed: 2*oy-2 .. 2*(oy+TH-1)+2
-constexpr int SCOLS = 2 * TW + 32;       // staged source columns: [2*ox0-16, 2*ox0+2*TW+16)
-constexpr int NTHREADS = 256;
+constexpr int BANDS = 4;                 // row bands per block (threadIdx.y)
+constexpr unsigned W_1464 = 0x04060401u; // byte0..3 weights 1,4,6,4
 
-__device__ __forceinline__ void pyr_down_tile(const uint8_t* __restrict__ src, int w, int h,
-                                              int spitch, uint8_t* __restrict__ dst, int ow,
-                                              int oh, int dpitch, int ox0, int oy0) {
-    __shared__ __align__(16) uint8_t s_src[SROWS][SCOLS];
-    __shared__ __align__(16) unsigned short s_h[SROWS][TW];
+// Per-thread constants of the horizontal pass. Column reflect-101 never needs a second code
+// path: on the left only output 0 reads columns -2,-1 (= columns 2,1: a different byte
+// permute of the same word); on the right only the LAST output column has taps outside the
+// image (centre c = w-1 for odd w: taps c+1,c+2 fold onto c-1,c-2; c = w-2 for even w: tap c+2
+// folds onto c), which is a different weight vector for that one output.
+struct ColSetup {
+    unsigned wgt[4];                     // dp4a weights of bytes c-2 .. c+1 per output
+    unsigned fifth[4];                   // dp4a weights that pick byte c+2 (0: folded / unused)
+    unsigned sel0;                       // byte permute building bytes x0-2 .. x0+1
+    int off_m;                           // byte offset of the word left of x0 (clamped at 0)
+};
 
-    const int tid = threadIdx.x;
-    const int sx0 = 2 * ox0 - 16;        // multiple of 16 (ox0 % 128 == 0)
-    const int sy0 = 2 * oy0 - 2;
-    // ---- stage: SROWS x (SCOLS/16) chunks of 16 bytes
-    constexpr int CHUNKS = SCOLS / 16;
-    for (int i = tid; i < SROWS * CHUNKS; i += NTHREADS) {
-        int r = i / CHUNKS, c = i - r * CHUNKS;
-        int gy = svo_reflect101(sy0 + r, h);
-        gy = min(max(gy, 0), h - 1);         // rows feeding outputs >= oh only (never stored)
-        int gx = sx0 + c * 16;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (gx >= 0 && gx + 16 <= spitch)   // pitch is a multiple of 16; pad bytes are never used
-            v = *reinterpret_cast<const uint4*>(src + (size_t)gy * spitch + gx);
-        *reinterpret_cast<uint4*>(&s_src[r][c * 16]) = v;
-    }
-    __syncthreads();
-    // ---- horizontal pass: s_h[r][ox] = I[2x-2] + 4 I[2x-1] + 6 I[2x] + 4 I[2x+1] + I[2x+2]
-    for (int i = tid; i < SROWS * TW; i += NTHREADS) {
-        int r = i / TW, ox = i - r * TW;
-        int gx = 2 * (ox0 + ox);
-        int v = 0;
-        if (ox0 + ox < ow) {
-            int x0 = svo_reflect101(gx - 2, w) - sx0;
-            int x1 = svo_reflect101(gx - 1, w) - sx0;
-            int x2 = gx - sx0;
-            int x3 = svo_reflect101(gx + 1, w) - sx0;
-            int x4 = svo_reflect101(gx + 2, w) - sx0;
-            const uint8_t* row = s_src[r];
-            v = row[x0] + row[x4] + 4 * (row[x1] + row[x3]) + 6 * row[x2];
-        }
-        s_h[r][ox] = (unsigned short)v;
-    }
-    __syncthreads();
-    // ---- vertical pass: 4 outputs per thread, one uchar4 store
-    {
-        int oyl = tid / (TW / 4);            // 0..7
-        int oxl = (tid - oyl * (TW / 4)) * 4;
-        int oy = oy0 + oyl;
-        if (oy < oh) {
-            unsigned int packed = 0;
+__device__ __forceinline__ ColSetup col_setup(int w, int ow, int ox) {
+    ColSetup cs;
+    const unsigned f[4] = {0x00010000u, 0x00000001u, 0x00010000u, 0x00000001u};
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                int r = 2 * oyl;
-                int v = s_h[r][oxl + k] + s_h[r + 4][oxl + k] +
-                        4 * (s_h[r + 1][oxl + k] + s_h[r + 3][oxl + k]) + 6 * s_h[r + 2][oxl + k];
-                packed |= (unsigned int)((v + 128) >> 8) << (8 * k);
-            }
-            int ox = ox0 + oxl;
-            if (ox < ow)                      // dpitch % 4 == 0, so a whole word always fits
-                *reinterpret_cast<unsigned int*>(dst + (size_t)oy * dpitch + ox) = packed;
-        }
+    for (int k = 0; k < 4; ++k) {
+        const bool last = (ox + k == ow - 1);
+        cs.wgt[k] = !last ? W_1464 : ((w & 1) ? 0x00060802u : 0x04070401u);
+        cs.fifth[k] = !last ? f[k] : 0u;
     }
+    cs.sel0 = (ox == 0) ? 0x5412u : 0x5432u;   // (I2, I1, I0, I1) at the left border
+    cs.off_m = (ox == 0) ? 0 : 2 * ox - 4;
+    return cs;
 }
 
-__global__ void __launch_bounds__(NTHREADS)
-pyr_down_u8_kernel(uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_stride, int level,
-                   const SvoSeqCall* __restrict__ call) {
-    const SvoSeqCall c = call[blockIdx.z];
-    uint8_t* slot = pyr + (size_t)c.seq * seq_stride + (size_t)c.cur_slot * lay.slot_bytes;
+struct HRow {
+    unsigned a, b;                       // (h0 | h1 << 16), (h2 | h3 << 16)
+};
+
+// horizontally filtered source row for output columns ox..ox+3 (ox % 4 == 0); `row` points at
+// column 0 of the source row. Words may extend past column w-1 (into the row padding or the next
+// row, always inside the allocation): those bytes only ever meet zero weights.
+__device__ __forceinline__ HRow filter_row(const uint8_t* __restrict__ row, int x0,
+                                           const ColSetup& cs) {
+    const unsigned wm = __ldg(reinterpret_cast<const unsigned*>(row + cs.off_m));
+    const uint2 c = __ldg(reinterpret_cast<const uint2*>(row + x0));
+    const unsigned w2 = __ldg(reinterpret_cast<const unsigned*>(row + x0 + 8));
+    const unsigned w0 = c.x, w1 = c.y;
+    const unsigned m0 = __byte_perm(wm, w0, cs.sel0);  // bytes x0-2 .. x0+1 (off_m == 0: wm == w0)
+    const unsigned m2 = __byte_perm(w0, w1, 0x5432);   // bytes x0+2 .. x0+5
+    unsigned h0 = __dp4a(m0, cs.wgt[0], 0u);
+    unsigned h1 = __dp4a(w0, cs.wgt[1], 0u);
+    unsigned h2 = __dp4a(m2, cs.wgt[2], 0u);
+    unsigned h3 = __dp4a(w1, cs.wgt[3], 0u);
+    h0 = __dp4a(w0, cs.fifth[0], h0);                  // + I[x0+2]
+    h1 = __dp4a(w1, cs.fifth[1], h1);                  // + I[x0+4]
+    h2 = __dp4a(w1, cs.fifth[2], h2);                  // + I[x0+6]
+    h3 = __dp4a(w2, cs.fifth[3], h3);                  // + I[x0+8]
+    HRow r;
+    r.a = h0 | (h1 << 16);
+    r.b = h2 | (h3 << 16);
+    return r;
+}
+
+__device__ __forceinline__ unsigned vertical(unsigned p0, unsigned p1, unsigned p2, unsigned p3,
+                                             unsigned p4) {
+    // both 16-bit lanes at once; no carry crosses bit 16 (see header)
+    const unsigned v = p0 + p4 + 4u * (p1 + p3) + 6u * p2 + 0x00800080u;
+    return (v >> 8) & 0x00ff00ffu;
+}
+
+template <int ROWS>
+__global__ void __launch_bounds__(32 * BANDS)
+pyr_down_u8_kernel(uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrLayout lay,
+                   size_t seq_stride, int level, const SvoSeqCall* __restrict__ call) {
+    const SvoSeqCall* c = call + blockIdx.z;
+    uint8_t* slot = pyr + (size_t)c->seq * seq_stride + (size_t)c->cur_slot * lay.slot_bytes;
     const SvoLevel s = lay.lvl[level];
     const SvoLevel d = lay.lvl[level + 1];
-    pyr_down_tile(slot + s.off, s.w, s.h, s.pitch, slot + d.off, d.w, d.h, d.pitch,
-                  blockIdx.x * TW, blockIdx.y * TH);
-}
-
-__global__ void __launch_bounds__(NTHREADS)
-pyr_down_u8_single_kernel(const uint8_t* __restrict__ src, int w, int h, int spitch,
-                          uint8_t* __restrict__ dst, int dpitch) {
-    pyr_down_tile(src, w, h, spitch, dst, (w + 1) / 2, (h + 1) / 2, dpitch, blockIdx.x * TW,
-                  blockIdx.y * TH);
+    const int ox = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int oy0 = (blockIdx.y * BANDS + threadIdx.y) * ROWS;
+    if (ox >= d.w || oy0 >= d.h) return;
+    const uint8_t* __restrict__ src = slot + s.off;
+    uint8_t* __restrict__ dst = slot + d.off;
+    const int h = s.h, spitch = s.pitch, x0 = 2 * ox;
+    const ColSetup cs = col_setup(s.w, d.w, ox);
+    auto srow = [&](int y) {                 // reflect-101 on rows, clamped for unused rows
+        int yr = abs(y);
+        yr = (yr >= h) ? 2 * h - 2 - yr : yr;
+        yr = min(max(yr, 0), h - 1);
+        return filter_row(src + (size_t)yr * spitch, x0, cs);
+    };
+    HRow r[2 * ROWS + 3];
+#pragma unroll
+    for (int i = 0; i < 2 * ROWS + 3; ++i) r[i] = srow(2 * oy0 - 2 + i);
+#pragma unroll
+    for (int j = 0; j < ROWS; ++j) {
+        const int oy = oy0 + j;
+        const unsigned lo = vertical(r[2 * j].a, r[2 * j + 1].a, r[2 * j + 2].a, r[2 * j + 3].a,
+                                     r[2 * j + 4].a);
+        const unsigned hi = vertical(r[2 * j].b, r[2 * j + 1].b, r[2 * j + 2].b, r[2 * j + 3].b,
+                                     r[2 * j + 4].b);
+        // dpitch % 4 == 0, so a whole word always fits (pad bytes are never read as pixels)
+        if (oy < d.h)
+            *reinterpret_cast<unsigned*>(dst + (size_t)oy * d.pitch + ox) =
+                __byte_perm(lo, hi, 0x6420);
+    }
 }
 
 }  // namespace
 
 cudaError_t svo_launch_pyr_down(uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
                                 const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
+    // fewer rows per thread on the small levels: the grid, not the row overlap, is what counts
     for (int l = 0; l + 1 < lay.n_levels; ++l) {
         const SvoLevel& d = lay.lvl[l + 1];
-        dim3 grid((d.w + TW - 1) / TW, (d.h + TH - 1) / TH, n_call);
-        pyr_down_u8_kernel<<<grid, NTHREADS, 0, st>>>(pyr, lay, seq_stride, l, d_call);
+        const int rows = (l == 0) ? 8 : (l == 1) ? 4 : 2;
+        dim3 block(32, BANDS);
+        dim3 grid((d.w + 127) / 128, (d.h + rows * BANDS - 1) / (rows * BANDS), n_call);
+        if (rows == 8) pyr_down_u8_kernel<8><<<grid, block, 0, st>>>(pyr, lay, seq_stride, l, d_call);
+        else if (rows == 4) pyr_down_u8_kernel<4><<<grid, block, 0, st>>>(pyr, lay, seq_stride, l, d_call);
+        else pyr_down_u8_kernel<2><<<grid, block, 0, st>>>(pyr, lay, seq_stride, l, d_call);
     }
-    return cudaGetLastError();
-}
-
-cudaError_t svo_launch_pyr_down_single(const uint8_t* src, int w, int h, int spitch,
-                                       uint8_t* dst, int dpitch, cudaStream_t st) {
-    int ow = (w + 1) / 2, oh = (h + 1) / 2;
-    dim3 grid((ow + TW - 1) / TW, (oh + TH - 1) / TH, 1);
-    pyr_down_u8_single_kernel<<<grid, NTHREADS, 0, st>>>(src, w, h, spitch, dst, dpitch);
     return cudaGetLastError();
 }

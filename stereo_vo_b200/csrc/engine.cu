@@ -124,7 +124,14 @@ struct svo_engine {
     size_t step_block = 0, key_block = 0, out_bytes = 0;
     int pts_cap = 0;                  // per-sequence capacity of d_pts / stereo outputs
 
-    SvoSeqCall* h_call = nullptr;     // pinned ring [CALL_RING][n_seq]
+    SvoSeqCall* h_call = nullptr;     // pinned + device-mapped ring [CALL_RING][n_seq]
+    // small host->device inputs (descriptors, inlier / feature lists) are PULLED by a kernel
+    // straight out of mapped pinned memory instead of going through cudaMemcpyAsync: the H2D
+    // copy engine is a FIFO shared by all streams, and a 30 MB svo_prefetch() queued on it
+    // would hold a 7 KB descriptor copy - and every kernel behind it - back for ~0.5 ms
+    struct PullSeg { const void* src; void* dst; unsigned int bytes; unsigned int pad; };
+    PullSeg* h_pull = nullptr;        // pinned + mapped segment lists
+    int pull_used = 0, pull_cap = 0;
     SvoSeqCall* d_call = nullptr;
     int ring = 0;
     unsigned char* h_out = nullptr;   // pinned
@@ -402,6 +409,7 @@ cudaError_t upload_right(svo_engine* e, SvoSeqCall& c, const uint8_t* img, int p
 
 // descriptors -> device, then the ingest kernel moves the staged pairs into the pitched images
 cudaError_t push_calls(svo_engine* e, int n);
+struct PullList;
 cudaError_t push_and_ingest(svo_engine* e, int n) {
     SVO_CUDA_OK(push_calls(e, n));
     dim3 blk(128, 2);
@@ -413,9 +421,55 @@ cudaError_t push_and_ingest(svo_engine* e, int n) {
     return cudaGetLastError();
 }
 
+static_assert(sizeof(SvoSeqCall) % 8 == 0, "descriptors are pulled in 8-byte words");
+
+// one block per segment: 8-byte words read from mapped host memory (ld.cv: never served from a
+// stale cache line - the host rewrites these buffers between calls) and written to the device
+__global__ void __launch_bounds__(128)
+pull_kernel(const svo_engine::PullSeg* __restrict__ segs) {
+    const svo_engine::PullSeg* sp = segs + blockIdx.x;
+    const uint2* src = reinterpret_cast<const uint2*>(__ldcv(reinterpret_cast<const unsigned long long*>(&sp->src)));
+    uint2* dst = reinterpret_cast<uint2*>(__ldcv(reinterpret_cast<const unsigned long long*>(&sp->dst)));
+    const unsigned n = __ldcv(&sp->bytes) >> 3;
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) dst[i] = __ldcv(src + i);
+}
+
+// segment lists live in a ring of the pinned h_pull array; every API call is synchronous, so a
+// list is consumed before its slots come round again
+struct PullList {
+    svo_engine* e;
+    int first, count;
+    explicit PullList(svo_engine* eng) : e(eng), first(eng->pull_used), count(0) {
+        if (first + 4 * eng->n_seq + 8 > eng->pull_cap) first = eng->pull_used = 0;
+    }
+    // src must lie in mapped pinned memory (h_call / h_in), bytes % 8 == 0
+    void add(void* dst, const void* src, size_t bytes) {
+        if (bytes == 0) return;
+        svo_engine::PullSeg& sg = e->h_pull[first + count++];
+        sg.src = src; sg.dst = dst; sg.bytes = (unsigned)bytes; sg.pad = 0;
+    }
+    cudaError_t launch() {
+        e->pull_used = first + count;
+        if (count == 0) return cudaSuccess;
+        if (e->pf_count == 0) {
+            // no bulk prefetch queued on the copy engine: plain DMA has the lower latency
+            for (int i = 0; i < count; ++i) {
+                const svo_engine::PullSeg& sg = e->h_pull[first + i];
+                cudaError_t ce = cudaMemcpyAsync(sg.dst, sg.src, sg.bytes, cudaMemcpyHostToDevice, e->st);
+                if (ce != cudaSuccess) return ce;
+            }
+            return cudaSuccess;
+        }
+        pull_kernel<<<count, 128, 0, e->st>>>(e->h_pull + first);
+        e->launches += 1;
+        return cudaGetLastError();
+    }
+};
+
 cudaError_t push_calls(svo_engine* e, int n) {
-    return cudaMemcpyAsync(dev_call_slot(e), e->h_call + (size_t)e->ring * e->n_seq,
-                           (size_t)n * sizeof(SvoSeqCall), cudaMemcpyHostToDevice, e->st);
+    PullList pl(e);
+    pl.add(dev_call_slot(e), e->h_call + (size_t)e->ring * e->n_seq, (size_t)n * sizeof(SvoSeqCall));
+    return pl.launch();
 }
 
 // pyramid + detection for the listed sequences (current frames already uploaded)
@@ -681,7 +735,7 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
         return fail(nullptr, SVO_ERR_INVALID, "svo_create: image size out of range (64x32 .. 16384x16384)");
     if (p.max_corners <= 0 || p.max_features <= 0 || p.max_features < 1)
         return fail(nullptr, SVO_ERR_INVALID, "svo_create: max_corners / max_features must be positive");
-    if (p.lk_max_level < 0 || p.lk_max_level >= SVO_MAX_LEVELS)
+    if (p.lk_max_level < 0 || p.lk_max_level > 3)      // lk_track pre-stages <= 4 levels
         return fail(nullptr, SVO_ERR_INVALID, "svo_create: lk_max_level out of range");
     if (p.num_disparities <= 0 || p.num_disparities % 16 || p.sad_window < 5 || !(p.sad_window & 1) ||
         p.sad_window > 31 || p.num_disparities > 256)
@@ -802,9 +856,15 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_nvalid, ns));
     CCHK(dalloc(&e->d_out, e->out_bytes));
     CCHK(dalloc(&e->d_call, (size_t)CALL_RING * ns));
-    CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_call), (size_t)CALL_RING * ns * sizeof(SvoSeqCall)));
+    // cudaHostAllocMapped: with unified addressing the device uses the same pointers
+    CCHK(cudaHostAlloc(reinterpret_cast<void**>(&e->h_call), (size_t)CALL_RING * ns * sizeof(SvoSeqCall),
+                       cudaHostAllocMapped | cudaHostAllocPortable));
+    e->pull_cap = 16 * n_seq + 64;
+    CCHK(cudaHostAlloc(reinterpret_cast<void**>(&e->h_pull), (size_t)e->pull_cap * sizeof(svo_engine::PullSeg),
+                       cudaHostAllocMapped | cudaHostAllocPortable));
     CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_out), e->out_bytes));
-    CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_in), e->h_in_bytes));
+    CCHK(cudaHostAlloc(reinterpret_cast<void**>(&e->h_in), e->h_in_bytes,
+                       cudaHostAllocMapped | cudaHostAllocPortable));
     CCHK(cudaMemsetAsync(e->d_pyr, 0, ns * e->seq_stride, e->st));
     CCHK(cudaMemsetAsync(e->d_right, 0, ns * e->right_stride, e->st));
     if (e->d_eig) CCHK(cudaMemsetAsync(e->d_eig, 0, ns * e->eig_stride * sizeof(float), e->st));
@@ -830,6 +890,7 @@ void svo_destroy(svo_engine* e) {
                      e->d_call};
     for (void* p : dptrs) if (p) cudaFree(p);
     if (e->h_call) cudaFreeHost(e->h_call);
+    if (e->h_pull) cudaFreeHost(e->h_pull);
     if (e->h_out) cudaFreeHost(e->h_out);
     if (e->h_in) cudaFreeHost(e->h_in);
     for (int i = 0; i < 4; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
@@ -995,18 +1056,18 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
         }
     }
     ECUDA(e, cudaEventRecord(e->ev[0], e->st));
-    ECUDA(e, push_calls(e, n));
     SvoSeqCall* dc = dev_call_slot(e);
-    for (int i = 0; i < n; ++i) {
-        int s = seqs[i];
-        if (dedupe) {
-            if (hc[i].n_aux > 0)
-                ECUDA(e, cudaMemcpyAsync(e->d_inl + (size_t)s * mf, h_pts + (size_t)i * mf,
-                                         (size_t)hc[i].n_aux * sizeof(float2), cudaMemcpyHostToDevice, e->st));
-        } else if (hc[i].n_pts > 0) {
-            ECUDA(e, cudaMemcpyAsync(e->d_pts + (size_t)s * cap, h_pts + (size_t)i * cap,
-                                     (size_t)hc[i].n_pts * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+    {
+        PullList pl(e);
+        pl.add(dc, hc, (size_t)n * sizeof(SvoSeqCall));
+        for (int i = 0; i < n; ++i) {
+            int s = seqs[i];
+            if (dedupe)
+                pl.add(e->d_inl + (size_t)s * mf, h_pts + (size_t)i * mf, (size_t)hc[i].n_aux * sizeof(float2));
+            else
+                pl.add(e->d_pts + (size_t)s * cap, h_pts + (size_t)i * cap, (size_t)hc[i].n_pts * sizeof(float2));
         }
+        ECUDA(e, pl.launch());
     }
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     if (dedupe) {
@@ -1118,15 +1179,14 @@ int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_flo
             memcpy(hi + (size_t)i * mf, ids + (size_t)i * mf, (size_t)c * sizeof(uint64_t));
         }
     }
+    PullList pl(e);
     for (int i = 0; i < n; ++i) {
         SeqState& s = e->seq[seqs[i]];
         int c = counts[i];
         const size_t fb = ((size_t)seqs[i] * 2 + s.feat_buf) * mf;
-        if (c > 0) {
-            ECUDA(e, cudaMemcpyAsync(e->d_feat + fb, hf + (size_t)i * mf, (size_t)c * sizeof(float2), cudaMemcpyHostToDevice, e->st));
-            ECUDA(e, cudaMemcpyAsync(e->d_initial + fb, hf + (size_t)i * mf, (size_t)c * sizeof(float2), cudaMemcpyHostToDevice, e->st));
-            ECUDA(e, cudaMemcpyAsync(e->d_ids + fb, hi + (size_t)i * mf, (size_t)c * sizeof(uint64_t), cudaMemcpyHostToDevice, e->st));
-        }
+        pl.add(e->d_feat + fb, hf + (size_t)i * mf, (size_t)c * sizeof(float2));
+        pl.add(e->d_initial + fb, hf + (size_t)i * mf, (size_t)c * sizeof(float2));
+        pl.add(e->d_ids + fb, hi + (size_t)i * mf, (size_t)c * sizeof(uint64_t));
         s.n_feat = c;
         // initial_features is an unordered_map keyed by id: duplicates collapse (feature_tracker.cpp:10-12)
         int uniq = 0;
@@ -1139,6 +1199,7 @@ int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_flo
         s.tracker_init = true;
         s.last_slot = s.cur_slot;      // last_image = image.clone()  (feature_tracker.cpp:14)
     }
+    ECUDA(e, pl.launch());
     ECUDA(e, cudaStreamSynchronize(e->st));   // h_in is reused by the next call
     return SVO_OK;
 }

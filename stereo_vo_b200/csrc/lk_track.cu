@@ -37,6 +37,7 @@ constexpr int DG = WIN + 1;                // derivative grid edge, border path 
 constexpr int JM = 3;                      // margin of the staged J region
 constexpr int JR = WIN + 1 + 2 * JM;       // staged J region edge (28)
 constexpr unsigned FULL = 0xffffffffu;
+constexpr int LK_LEVELS = 4;               // levels pre-staged (reference: maxLevel 3)
 
 __device__ __forceinline__ long long warp_sum_exact(int v) {
     int lo = __reduce_add_sync(FULL, v & 0xffff);
@@ -59,32 +60,64 @@ __device__ __forceinline__ void lk_weights(float a, float b, int& w00, int& w01,
     w11 = 16384 - w00 - w01 - w10;
 }
 
-// stage an n_rows x (4 * n_words) byte region whose first wanted byte is (x0, y0): aligned
-// 32-bit loads when the region lies inside the image (returns x0 & 3, the byte offset of x0 in
-// a staged row), byte-wise reflect-101 otherwise (returns 0). n_cols wanted bytes per row.
+// Staging of an N_ROWS x N_COLS byte region whose first wanted byte is (x0, y0) into shared
+// rows of SP bytes. Column range inside the image (the common case, also for windows that
+// stick out above/below: rows are fetched through reflect-101 indices): aligned 32-bit loads;
+// region_load() only ISSUES them (into registers), region_store() writes them to shared memory,
+// so several regions can be in flight at once. Returns x0 & 3 (byte offset of x0 in a staged
+// row). Column range crossing the image border: byte-wise reflect-101, done at once; returns 0.
+template <int N_ROWS, int N_COLS>
+struct Region {
+    static constexpr int NW = (N_COLS + 3 + 3) / 4;          // words covering any alignment
+    static constexpr int NLD = (N_ROWS * NW + NT - 1) / NT;  // words per thread
+    static_assert(NW * 4 <= SP, "staged row too wide");
+    unsigned v[NLD];
+    bool words;
+
+    __device__ __forceinline__ int load(const uint8_t* __restrict__ img, int w, int h, int pitch,
+                                        int x0, int y0, unsigned* s_words, int tid) {
+        words = (x0 >= 0 && x0 + N_COLS <= w);
+        if (words) {
+            const int off = x0 & 3;
+            const uint8_t* base = img + (x0 - off);
+#pragma unroll
+            for (int k = 0; k < NLD; ++k) {
+                const int i = tid + k * NT;
+                const int r = min(i / NW, N_ROWS - 1), c = i - (i / NW) * NW;
+                const int gy = clamp_reflect(y0 + r, h);
+                v[k] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)gy * pitch) + c);
+            }
+            return off;
+        }
+        unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_words);
+        for (int i = tid; i < N_ROWS * N_COLS; i += NT) {
+            int r = i / N_COLS, c = i - r * N_COLS;
+            int gy = clamp_reflect(y0 + r, h), gx = clamp_reflect(x0 + c, w);
+            s_bytes[r * SP + c] = img[(size_t)gy * pitch + gx];
+        }
+        return 0;
+    }
+    __device__ __forceinline__ void store(unsigned* s_words, int tid) const {
+        if (!words) return;
+#pragma unroll
+        for (int k = 0; k < NLD; ++k) {
+            const int i = tid + k * NT;
+            if (i < N_ROWS * NW) {
+                const int r = i / NW, c = i - r * NW;
+                s_words[r * (SP / 4) + c] = v[k];
+            }
+        }
+    }
+};
+
 template <int N_ROWS, int N_COLS>
 __device__ __forceinline__ int stage_region(const uint8_t* __restrict__ img, int w, int h,
                                             int pitch, int x0, int y0, unsigned* s_words,
                                             int tid) {
-    constexpr int NW = (N_COLS + 3 + 3) / 4;          // words covering any alignment
-    static_assert(NW * 4 <= SP, "staged row too wide");
-    if (x0 >= 0 && y0 >= 0 && x0 + N_COLS <= w && y0 + N_ROWS <= h) {
-        const int off = x0 & 3;
-        const uint8_t* base = img + (size_t)y0 * pitch + (x0 - off);
-        for (int i = tid; i < N_ROWS * NW; i += NT) {
-            int r = i / NW, c = i - r * NW;
-            s_words[r * (SP / 4) + c] =
-                __ldg(reinterpret_cast<const unsigned*>(base + (size_t)r * pitch) + c);
-        }
-        return off;
-    }
-    unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_words);
-    for (int i = tid; i < N_ROWS * N_COLS; i += NT) {
-        int r = i / N_COLS, c = i - r * N_COLS;
-        int gy = clamp_reflect(y0 + r, h), gx = clamp_reflect(x0 + c, w);
-        s_bytes[r * SP + c] = img[(size_t)gy * pitch + gx];
-    }
-    return 0;
+    Region<N_ROWS, N_COLS> rg;
+    const int off = rg.load(img, w, h, pitch, x0, y0, s_words, tid);
+    rg.store(s_words, tid);
+    return off;
 }
 
 __global__ void __launch_bounds__(NT)
@@ -96,8 +129,12 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 const int* __restrict__ gate, int gate_min,
                 const unsigned char* __restrict__ skip_status,
                 const SvoSeqCall* __restrict__ call) {
-    __shared__ __align__(16) unsigned s_Iw[IP * (SP / 4)];
-    __shared__ __align__(16) unsigned s_Jw[JR * (SP / 4)];
+    // I patch and J region of EVERY level are fetched up front (their positions are known
+    // before any iteration: pt / 2^l, zero-flow guess for J), so a point pays the global-memory
+    // latency once instead of once or twice per level; J is re-staged only when the window
+    // leaves the +-JM margin of its level's region
+    __shared__ __align__(16) unsigned s_Iall[LK_LEVELS][IP * (SP / 4)];
+    __shared__ __align__(16) unsigned s_Jall[LK_LEVELS][JR * (SP / 4)];
     __shared__ __align__(16) int s_B[BG * BP];       // border path: s_dx / s_dy alias this
     __shared__ long long s_red[2][2][3];
 
@@ -131,21 +168,49 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     const bool has_px = tid < WIN * 3;
     const int wy = min(tid / 3, WIN - 1);
     const int wx0 = (tid - (tid / 3) * 3) * RUN;
-    const unsigned char* s_Ib = reinterpret_cast<const unsigned char*>(s_Iw);
-    const unsigned char* s_Jb = reinterpret_cast<const unsigned char*>(s_Jw);
     short* s_dx = reinterpret_cast<short*>(s_B);
     short* s_dy = s_dx + DG * DG;
     static_assert(2 * DG * DG * sizeof(short) <= sizeof(int) * BG * BP, "alias too small");
 
     const float half = 10.f;                 // (winSize - 1) * 0.5
     const float FLT_SCALE = 1.f / (float)(1 << 20);
+
+    // ---- fetch the I patch and the zero-flow J region of every level (loads of all levels in
+    // flight together), then one barrier
+    unsigned offs = 0;                       // 2 bits per (level, I/J): byte offset in a staged row
+    {
+        Region<IP, IP> rI[LK_LEVELS];
+        Region<JR, JR> rJ[LK_LEVELS];
+#pragma unroll
+        for (int l = 0; l < LK_LEVELS; ++l) {
+            rI[l].words = rJ[l].words = false;
+            if (l < lay.n_levels) {
+                const SvoLevel lv = lay.lvl[l];
+                const float inv = 1.f / (float)(1 << l);
+                const int ipx = (int)floorf(__fsub_rn(__fmul_rn(pt.x, inv), half));
+                const int ipy = (int)floorf(__fsub_rn(__fmul_rn(pt.y, inv), half));
+                if (!(ipx < -WIN || ipx >= lv.w || ipy < -WIN || ipy >= lv.h)) {
+                    const int oi = rI[l].load(pyrI + lv.off, lv.w, lv.h, lv.pitch, ipx - 1,
+                                              ipy - 1, s_Iall[l], tid);
+                    const int oj = rJ[l].load(pyrJ + lv.off, lv.w, lv.h, lv.pitch, ipx - JM,
+                                              ipy - JM, s_Jall[l], tid);
+                    offs |= (unsigned)(oi | (oj << 2)) << (4 * l);
+                }
+            }
+        }
+#pragma unroll
+        for (int l = 0; l < LK_LEVELS; ++l) {
+            rI[l].store(s_Iall[l], tid);
+            rJ[l].store(s_Jall[l], tid);
+        }
+    }
+    __syncthreads();
     float2 nextPt = make_float2(0.f, 0.f);   // the value OpenCV keeps in nextPts[ptidx]
     bool ok = true;
     int red_par = 0;
 
     for (int l = lay.n_levels - 1; l >= 0; --l) {
         const SvoLevel lv = lay.lvl[l];
-        const uint8_t* __restrict__ I = pyrI + lv.off;
         const uint8_t* __restrict__ J = pyrJ + lv.off;
         const int w = lv.w, h = lv.h, pitch = lv.pitch;
         const float inv = 1.f / (float)(1 << l);
@@ -164,9 +229,11 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         lk_weights(__fsub_rn(prevPt.x, (float)ipx), __fsub_rn(prevPt.y, (float)ipy), w00, w01,
                    w10, w11);
 
-        __syncthreads();                     // previous level's readers are done with smem
-        const int offI = stage_region<IP, IP>(I, w, h, pitch, ipx - 1, ipy - 1, s_Iw, tid);
-        __syncthreads();
+        const int offI = (offs >> (4 * l)) & 3;      // staged before the loop
+        const unsigned char* s_Ib = reinterpret_cast<const unsigned char*>(s_Iall[l]);
+        unsigned* s_Jw = s_Jall[l];
+        const unsigned char* s_Jb = reinterpret_cast<const unsigned char*>(s_Jw);
+        __syncthreads();                     // previous level's readers are done with s_B
 
         int ival[RUN], ixv[RUN], iyv[RUN];
         // every corner of every window pixel inside the image <=> no zero-border derivative
@@ -209,7 +276,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 int gy = ipy + r, gx = ipx + c;
                 int vx = 0, vy = 0;
                 if (gx >= 0 && gx < w && gy >= 0 && gy < h) {
-                    const unsigned char* q = s_Ib + r * SP + c;      // pixel (gy-1, gx-1)
+                    const unsigned char* q = s_Ib + r * SP + offI + c;   // pixel (gy-1, gx-1)
                     int a0 = q[0], a1 = q[1], a2 = q[2];
                     int b0 = q[SP], b2 = q[SP + 2];
                     int c0 = q[2 * SP], c1 = q[2 * SP + 1], c2 = q[2 * SP + 2];
@@ -225,7 +292,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
 #pragma unroll
             for (int t = 0; t < RUN; ++t) {
                 const int wx = wx0 + t;
-                const unsigned char* q = s_Ib + (wy + 1) * SP + wx + 1;
+                const unsigned char* q = s_Ib + (wy + 1) * SP + offI + wx + 1;
                 ival[t] = (q[0] * w00 + q[1] * w01 + q[SP] * w10 + q[SP + 1] * w11 + 256) >> 9;
                 const short* dx = s_dx + wy * DG + wx;
                 const short* dy = s_dy + wy * DG + wx;
@@ -269,8 +336,8 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
 
         float2 np = make_float2(__fsub_rn(nextPt.x, half), __fsub_rn(nextPt.y, half));
         float2 prevDelta = make_float2(0.f, 0.f);
-        int jx0 = -(1 << 30), jy0 = -(1 << 30);      // staged J origin (none yet)
-        int offJ = 0;
+        int jx0 = ipx - JM, jy0 = ipy - JM;          // origin of the pre-staged J region
+        int offJ = (offs >> (4 * l + 2)) & 3;
         for (int j = 0; j < max_iters; ++j) {
             const int inx = (int)floorf(np.x), iny = (int)floorf(np.y);
             if (inx < -WIN || inx >= w || iny < -WIN || iny >= h) {

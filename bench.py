@@ -140,6 +140,10 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
+        # NCCL_DEBUG=VERSION makes NCCL print its version banner on stdout, next to the one JSON
+        # line the driver parses
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         import torch.distributed as dist_mod
         dist = dist_mod
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -363,7 +367,7 @@ def cpu_baseline(sample_frames: int = 120):
             "sample": f"{n_proc} processes x {each} synthetic KITTI-shaped frames, cv2 "
                       f"{_cv2_version()} oracle (oracle/cv2_frontend.py: the reference's own "
                       "OpenCV calls), 1 OpenCV thread each, default optimized mode; "
-                      f"{wall:.1f} s of CPU work"}
+                      f"{wall:.1f} s wall = {wall * n_proc:.0f} core-seconds of CPU work"}
 
 
 def _cv2_version():
@@ -419,7 +423,7 @@ def main():
     ap.add_argument("--seqs-per-gpu", type=int, default=64)
     ap.add_argument("--textures", type=int, default=8)
     ap.add_argument("--frames", type=int, default=12)
-    ap.add_argument("--cpu-frames", type=int, default=960)
+    ap.add_argument("--cpu-frames", type=int, default=2400)
     ap.add_argument("--skip-cpu-baseline", action="store_true", help="profiling runs only")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only")
     ap.add_argument("--ref-frames", type=int, default=16)

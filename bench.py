@@ -41,8 +41,8 @@ ALGO_BYTES = {
     # written (SURVEY.md 8d "fused" variant), + 8 B per local maximum (~1e4 per image, ignored)
     "corner_score_nms": N_PIX,
     "pyr_down_u8": 612598 + 153314,            # 3 levels: bytes read + bytes written
-    "ingest": 4 * N_PIX,                       # left+right: staged copy read + pitched image written
 }
+INGEST_BYTES_PER_IMAGE = 2 * N_PIX             # staged copy read + pitched image written
 
 
 def _env_int(name, default):
@@ -190,12 +190,15 @@ def run_ours(args, rank, world, local_rank):
             sched.append(((C.c_void_p * S)(*ls), (C.c_void_p * S)(*rs), poses,
                           poses.ctypes.data_as(C.c_void_p)))
 
-        def one(k):
+        def args_of(k):
             lp, rp, _poses, pz = sched[k % period]
             if device_resident or not args.prefetch:
-                return batch.step_raw(lp, rp, pitch, device_resident, pz)
+                return (lp, rp, pitch, device_resident, pz)
             nlp, nrp, _p, _z = sched[(k + 1) % period]
-            return batch.step_raw(lp, rp, pitch, False, pz, nlp, nrp)
+            return (lp, rp, pitch, False, pz, nlp, nrp)
+
+        def one(k):
+            return batch.step_raw(*args_of(k))
 
         for k in range(warmup):
             one(k)
@@ -208,11 +211,24 @@ def run_ours(args, rank, world, local_rank):
         batch.timer_begin()
         t0 = time.perf_counter()
         tracked = corners = keyframes = 0
-        for k in range(warmup, warmup + steps):
-            sm = one(k)
-            tracked += sm.tracked
-            corners += sm.corners
-            keyframes += sm.keyframes
+        first, last = warmup, warmup + steps
+        if args.pipeline and not profile:
+            # two steps in flight (svo_batch_submit / svo_batch_wait): engine groups run free of
+            # each other, the tail of step k overlaps the heavy kernels of step k+1
+            batch.submit_raw(*args_of(first))
+            for k in range(first, last):
+                if k + 1 < last:
+                    batch.submit_raw(*args_of(k + 1))
+                sm = batch.wait()
+                tracked += sm.tracked
+                corners += sm.corners
+                keyframes += sm.keyframes
+        else:
+            for k in range(first, last):
+                sm = one(k)
+                tracked += sm.tracked
+                corners += sm.corners
+                keyframes += sm.keyframes
         ev_ms = batch.timer_end()
         barrier()
         wall_ms = (time.perf_counter() - t0) * 1e3
@@ -269,6 +285,11 @@ def run_ours(args, rank, world, local_rank):
             if name in ALGO_BYTES:
                 gbs = ALGO_BYTES[name] * S * cnt / (ms * 1e-3) / 1e9
                 ent.update(algo_gbs=gbs, frac_of_hbm=gbs / peak)
+            elif name == "ingest":
+                # every left image + the right image of every keyframe (svo_set_right)
+                images = S * Kp + prof_leg["keyframes"]
+                gbs = INGEST_BYTES_PER_IMAGE * images / (ms * 1e-3) / 1e9
+                ent.update(algo_gbs=gbs, frac_of_hbm=gbs / peak)
             kernels[name] = ent
         dom = max(prof.items(), key=lambda kv: kv[1][0])[0] if prof else None
         # roofline of the dominant kernel among those whose interface is HBM traffic (whole-image
@@ -285,7 +306,8 @@ def run_ours(args, rank, world, local_rank):
                         "algorithmic_bytes_per_launch": ALGO_BYTES[hbm_dom] * S,
                         "dominant_kernel_of_step": dom}
         cpu = None if args.skip_cpu_baseline else cpu_baseline(sample_frames=args.cpu_frames)
-        in_bytes = S * 2 * H * W
+        # every left image + the right image of the frames that became keyframes
+        in_bytes = int(S * H * W + e2e["keyframes"] / K * H * W)
         eng_tmp_block = 16 + 24 + 300 * 8 + 400 * 16
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
@@ -297,7 +319,10 @@ def run_ours(args, rank, world, local_rank):
                        "seqs_per_gpu": S, "frames_per_step": S * world,
                        "parallelism": f"{world} GPU(s) x {S} sequences in {args.groups} engine groups "
                                       "(one CUDA stream + host worker each), no collective",
-                       "host": "C++ svo::BatchFrontEnd via svo_batch_step (libsvo_host.so); e2e leg "
+                       "host": "C++ svo::BatchFrontEnd (libsvo_host.so) via "
+                               + ("svo_batch_submit/wait, 2 steps in flight" if args.pipeline
+                                  else "svo_batch_step")
+                               + "; right images uploaded for keyframes only; e2e leg "
                                + ("prefetches" if args.prefetch else "does not prefetch")
                                + " the next step's frames (svo_prefetch)",
                        "l2": "inputs larger than L2: every step reads 64 new stereo pairs (60 MB "
@@ -431,6 +456,8 @@ def main():
                     help="steps of the separate single-group pass that times every kernel alone")
     ap.add_argument("--groups", type=int, default=4,
                     help="engine groups (CUDA streams + host workers) the sequences of a GPU are split into")
+    ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",
+                    help="one synchronous svo_batch_step per step instead of two steps in flight")
     ap.add_argument("--no-prefetch", dest="prefetch", action="store_false",
                     help="e2e leg: do not copy the next step's frames ahead")
     args = ap.parse_args()

@@ -59,22 +59,36 @@ class BatchFrontEnd {
                       bool on_device, const float* poses, const uint8_t* const* next_left = nullptr,
                       const uint8_t* const* next_right = nullptr);
 
+    // Pipelined form: submit() queues one frame of every sequence and returns at once, wait()
+    // blocks until the OLDEST submitted step is complete and makes its results current. Up to
+    // kPipeDepth steps may be in flight. Groups then run free of each other: while one group is
+    // in the latency-bound tail of step k (keyframe stage, tracker re-init, host bookkeeping),
+    // others already run the heavy kernels of step k+1. The pointer arrays are copied at
+    // submit(); the IMAGES must stay unchanged until the matching wait() returns (and, for
+    // next_left/next_right, until the step that consumes them has been waited for).
+    static constexpr int kPipeDepth = 2;
+    void submit(const uint8_t* const* left, const uint8_t* const* right, int pitch, bool on_device,
+                const float* poses, const uint8_t* const* next_left = nullptr,
+                const uint8_t* const* next_right = nullptr);
+    BatchSummary wait();
+    int in_flight() const { return (int)(n_submitted_ - n_waited_); }
+
     int n_seq() const { return opt_.n_seq; }
     int n_groups() const { return (int)groups_.size(); }
     int max_corners() const { return opt_.params.max_corners; }
     int max_features() const { return opt_.params.max_features; }
 
-    // results of the last step for sequence s
-    int32_t decision(int s) const { return seq_[s].decision; }
-    int32_t n_corners(int s) const { return seq_[s].n_corners; }
+    // results of the last completed (step() / wait()) step for sequence s
+    int32_t decision(int s) const { return res(s).decision; }
+    int32_t n_corners(int s) const { return res(s).n_corners; }
     const svo_float2* corners(int s) const;
-    const svo_track_stats& stats(int s) const { return seq_[s].stats; }
+    const svo_track_stats& stats(int s) const { return res(s).stats; }
     // tracker set after the step (what FeatureTracker holds): points, ids, count
-    int32_t tracker_count(int s) const { return seq_[s].n_tracker; }
+    int32_t tracker_count(int s) const { return res(s).n_tracker; }
     const svo_float2* tracker_points(int s) const;
     const uint64_t* tracker_ids(int s) const;
     // keyframe outputs of the step (valid when decision is FIRST or KEYFRAME)
-    int32_t n_new(int s) const { return seq_[s].n_new; }
+    int32_t n_new(int s) const { return res(s).n_new; }
     const svo_float2* new_2d(int s) const;
     const svo_float3* new_3d(int s) const;
 
@@ -89,19 +103,22 @@ class BatchFrontEnd {
     svo_engine* engine(int group) const { return groups_[group]->e; }
 
   private:
+    struct SeqResult {                     // per pipeline slot
+        int32_t decision = 0, n_corners = 0, n_tracker = 0, n_new = 0;
+        svo_track_stats stats{};
+    };
     struct SeqState {
         int group = 0, local = 0;          // engine and index inside it
         bool have_kf = false;
         uint64_t next_id = 0;
-        int32_t decision = 0, n_corners = 0, n_tracker = 0, n_new = 0;
-        svo_track_stats stats{};
+        int32_t n_tracker = 0;             // tracker set size carried from step to step
+        SeqResult res[kPipeDepth];
     };
     struct Group {
         svo_engine* e = nullptr;
         std::vector<int> seqs;             // global sequence indices, local order
         std::thread worker;
-        BatchSummary sum;
-        std::string error;
+        uint64_t done = 0;                 // steps this group has completed
         // scratch (all sized for the group's sequences)
         std::vector<int32_t> local_ids, kf_local, n_inl, n_newv, n_valid, counts, n_corn;
         std::vector<const uint8_t*> lp, rp, nlp, nrp;
@@ -112,31 +129,37 @@ class BatchFrontEnd {
         std::vector<int32_t> valid_idx;
         std::vector<int16_t> disp16;
         std::vector<float> poses;
+        double phase_ms[12] = {0};         // SVO_BATCH_TRACE=1: accumulated per-phase times
+        int64_t phase_calls = 0;
     };
-    struct Job {
-        const uint8_t* const* left = nullptr;
-        const uint8_t* const* right = nullptr;
-        const uint8_t* const* next_left = nullptr;
-        const uint8_t* const* next_right = nullptr;
-        const float* poses = nullptr;
+    struct Job {                           // one submitted step (pointer arrays owned)
+        std::vector<const uint8_t*> left, right, next_left, next_right;
+        std::vector<float> poses;
+        bool has_right = false, has_next = false, has_next_right = false, has_poses = false;
         int pitch = 0;
         bool on_device = false;
+        std::vector<BatchSummary> sum;     // per group
+        std::vector<std::string> error;    // per group
+        int pending = 0;                   // groups still working on it
     };
-    void run_group(Group& g);
-    void worker_loop(Group* g);
+    void run_group(Group& g, Job& job, int slot, int gi);
+    void worker_loop(Group* g, int gi);
+    const SeqResult& res(int s) const { return seq_[s].res[cur_slot_]; }
 
     BatchOptions opt_;
+    bool trace_ = false;           // SVO_BATCH_TRACE=1: per-phase host/device times on stderr
+    bool lazy_right_ = true;       // upload right images for keyframes only (SVO_BATCH_LAZY_RIGHT=0: always)
     std::vector<std::unique_ptr<Group>> groups_;
     std::vector<SeqState> seq_;
-    // per-sequence result storage (global index)
-    std::vector<svo_float2> corners_, tracker_pts_, new_2d_;
-    std::vector<svo_float3> new_3d_;
-    std::vector<uint64_t> tracker_ids_;
-    Job job_;
+    // per-sequence result storage (global index), one set per pipeline slot
+    std::vector<svo_float2> corners_[kPipeDepth], tracker_pts_[kPipeDepth], new_2d_[kPipeDepth];
+    std::vector<svo_float3> new_3d_[kPipeDepth];
+    std::vector<uint64_t> tracker_ids_[kPipeDepth];
+    Job jobs_[kPipeDepth];
     std::mutex mu_;
     std::condition_variable cv_start_, cv_done_;
-    uint64_t generation_ = 0;
-    int pending_ = 0;
+    uint64_t n_submitted_ = 0, n_waited_ = 0;
+    int cur_slot_ = 0;                     // slot of the last step handed back by wait()
     bool stop_ = false;
 };
 

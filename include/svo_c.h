@@ -194,6 +194,16 @@ SVO_API int svo_step_device(svo_engine* e, int32_t n, const int32_t* seqs, const
                     int32_t* n_corners, svo_track_stats* stats, svo_float2* tracked,
                     uint64_t* tracked_ids);
 
+/* Right image of the CURRENT frame for the listed sequences, for callers that gave svo_step()
+ * no right images (right == NULL): the reference only ever reads the right image inside
+ * triangulate_stereo, i.e. on keyframes (src/image_processor.cpp:34-39,137-142), so a caller
+ * that knows the keyframe decision can skip ~3/4 of the right-image uploads. right[i] are host
+ * pointers (device pointers when on_device), `pitch` bytes per row. Asynchronous: returns once
+ * the copies are queued; the host images must stay unchanged until the next svo_keyframe() /
+ * svo_triangulate_stereo() of the engine returns. */
+SVO_API int svo_set_right(svo_engine* e, int32_t n, const int32_t* seqs,
+                          const uint8_t* const* right, int32_t pitch, int32_t on_device);
+
 /* Phase B for the sequences that became keyframes (image_processor.cpp:113-142): dedupe the
  * corners of the current frame against the PnP-inlier tracked points, StereoBM + reprojection of
  * the remaining new features with `poses[i]` (camera->world, 4x4 row major).

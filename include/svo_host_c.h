@@ -81,6 +81,16 @@ SVO_API int svo_batch_step(svo_batch* b, const uint8_t* const* left, const uint8
                            int32_t pitch, int32_t on_device, const float* poses,
                            const uint8_t* const* next_left, const uint8_t* const* next_right,
                            svo_batch_summary* summary);
+/* Pipelined form of svo_batch_step (svo::BatchFrontEnd::submit / wait): submit queues one frame
+ * of every sequence and returns at once; wait blocks until the OLDEST submitted step is complete,
+ * fills `summary` and makes that step the one svo_batch_get reads. At most 2 steps in flight
+ * (SVO_ERR_STATE otherwise). Pointer arrays are copied at submit; the images must stay unchanged
+ * until the matching wait returns. */
+SVO_API int svo_batch_submit(svo_batch* b, const uint8_t* const* left, const uint8_t* const* right,
+                             int32_t pitch, int32_t on_device, const float* poses,
+                             const uint8_t* const* next_left, const uint8_t* const* next_right);
+SVO_API int svo_batch_wait(svo_batch* b, svo_batch_summary* summary);
+
 /* per-sequence results of the last step. Arrays: corners [max_corners], tracker_pts /
  * tracker_ids [max_features], new_2d / new_3d [max_corners]; any may be NULL */
 SVO_API int svo_batch_get(svo_batch* b, int32_t seq, int32_t* decision, int32_t* n_corners,

@@ -350,6 +350,7 @@ void begin_frame(svo_engine* e, int seq) {
     SeqState& s = e->seq[seq];
     s.cur_slot = (s.last_slot == 0) ? 1 : 0;
     s.have_frame = true;
+    s.have_right = false;     // set again by the upload of this frame's right image
 }
 
 uint8_t* slot_ptr(svo_engine* e, int seq, int slot) {
@@ -1157,6 +1158,30 @@ int svo_triangulate_stereo(svo_engine* e, int32_t seq, const uint8_t* left, cons
     return keyframe_impl(e, 1, &s, nullptr, nullptr, pose, focal, cx, cy, baseline, false, feats,
                          &nn, nullptr, nullptr, out_valid_2d, out_3d, out_valid_idx, out_disp16,
                          out_n_valid);
+}
+
+int svo_set_right(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* right,
+                  int32_t pitch, int32_t on_device) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !seqs || !right) return fail(e, SVO_ERR_INVALID, "svo_set_right: bad arguments");
+    if (pitch < e->p.width) return fail(e, SVO_ERR_INVALID, "svo_set_right: pitch < width");
+    ECUDA(e, cudaSetDevice(e->device));
+    if (!on_device) {
+        // land in a staging set no announced (prefetched) frames occupy
+        if (e->pf_count == 2) prefetch_discard(e);
+        if (e->pf_count == 1) e->cur_set = 1 - e->pf[e->pf_head].set;
+    }
+    SvoSeqCall* hc = next_call_slot(e);
+    for (int i = 0; i < n; ++i) {
+        const int s = seqs[i];
+        if (s < 0 || s >= e->n_seq) return fail(e, SVO_ERR_INVALID, "svo_set_right: sequence index out of range");
+        if (!right[i]) return fail(e, SVO_ERR_INVALID, "svo_set_right: null image");
+        if (!e->seq[s].have_frame) return fail(e, SVO_ERR_STATE, "svo_set_right: no current left frame");
+        fill_call(e, hc[i], s);
+        ECUDA(e, upload_right(e, hc[i], right[i], pitch, on_device != 0));
+    }
+    ECUDA(e, push_and_ingest(e, n));      // asynchronous: ordered before the next call's kernels
+    return SVO_OK;
 }
 
 int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,

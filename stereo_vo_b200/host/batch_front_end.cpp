@@ -3,6 +3,9 @@
 #include "stereo_vo/batch_front_end.hpp"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 
@@ -16,15 +19,21 @@ std::string engine_error(svo_engine* e, const char* what, int rc) {
 }  // namespace
 
 BatchFrontEnd::BatchFrontEnd(const BatchOptions& opt) : opt_(opt) {
+    if (const char* v = std::getenv("SVO_BATCH_LAZY_RIGHT")) lazy_right_ = std::atoi(v) != 0;
+    if (const char* v = std::getenv("SVO_BATCH_TRACE")) trace_ = std::atoi(v) != 0;
     if (opt.n_seq <= 0) throw std::invalid_argument("BatchFrontEnd: n_seq must be positive");
     const int G = std::max(1, std::min(opt.n_groups, opt.n_seq));
     const int mc = opt.params.max_corners, mf = opt.params.max_features;
     seq_.resize((size_t)opt.n_seq);
-    corners_.resize((size_t)opt.n_seq * mc);
-    tracker_pts_.resize((size_t)opt.n_seq * mf);
-    tracker_ids_.resize((size_t)opt.n_seq * mf);
-    new_2d_.resize((size_t)opt.n_seq * mc);
-    new_3d_.resize((size_t)opt.n_seq * mc);
+    for (int p = 0; p < kPipeDepth; ++p) {
+        corners_[p].resize((size_t)opt.n_seq * mc);
+        tracker_pts_[p].resize((size_t)opt.n_seq * mf);
+        tracker_ids_[p].resize((size_t)opt.n_seq * mf);
+        new_2d_[p].resize((size_t)opt.n_seq * mc);
+        new_3d_[p].resize((size_t)opt.n_seq * mc);
+        jobs_[p].sum.resize((size_t)G);
+        jobs_[p].error.resize((size_t)G);
+    }
     // contiguous blocks of sequences per group (sizes differ by at most one)
     int s0 = 0;
     for (int g = 0; g < G; ++g) {
@@ -55,8 +64,8 @@ BatchFrontEnd::BatchFrontEnd(const BatchOptions& opt) : opt_(opt) {
         for (int i = 0; i < cnt; ++i) grp->local_ids[(size_t)i] = i;
         groups_.push_back(std::move(grp));
     }
-    if (G > 1)
-        for (auto& g : groups_) g->worker = std::thread(&BatchFrontEnd::worker_loop, this, g.get());
+    int gi = 0;
+    for (auto& g : groups_) g->worker = std::thread(&BatchFrontEnd::worker_loop, this, g.get(), gi++);
 }
 
 BatchFrontEnd::~BatchFrontEnd() {
@@ -65,110 +74,166 @@ BatchFrontEnd::~BatchFrontEnd() {
         stop_ = true;
     }
     cv_start_.notify_all();
+    int gi = 0;
     for (auto& g : groups_) {
         if (g->worker.joinable()) g->worker.join();
+        if (trace_ && g->phase_calls) {
+            const double c = (double)g->phase_calls;
+            std::fprintf(stderr,
+                         "[svo batch] group %d (%zu seqs, %ld steps) host ms/step: prefetch %.3f "
+                         "step %.3f set_right %.3f keyframe %.3f bookkeeping %.3f tracker_set %.3f | "
+                         "device ms/step: step copy-in %.3f kernels %.3f copy-out %.3f ; keyframe "
+                         "copy-in %.3f kernels %.3f copy-out %.3f\n",
+                         gi, g->seqs.size(), (long)g->phase_calls, g->phase_ms[0] / c,
+                         g->phase_ms[1] / c, g->phase_ms[2] / c, g->phase_ms[3] / c,
+                         g->phase_ms[4] / c, g->phase_ms[5] / c, g->phase_ms[6] / c,
+                         g->phase_ms[7] / c, g->phase_ms[8] / c, g->phase_ms[9] / c,
+                         g->phase_ms[10] / c, g->phase_ms[11] / c);
+        }
+        ++gi;
         if (g->e) svo_destroy(g->e);
     }
 }
 
-void BatchFrontEnd::worker_loop(Group* g) {
-    uint64_t seen = 0;
+void BatchFrontEnd::worker_loop(Group* g, int gi) {
     for (;;) {
+        uint64_t job_no;
         {
             std::unique_lock<std::mutex> lk(mu_);
-            cv_start_.wait(lk, [&] { return stop_ || generation_ != seen; });
+            cv_start_.wait(lk, [&] { return stop_ || n_submitted_ > g->done; });
             if (stop_) return;
-            seen = generation_;
+            job_no = g->done;
         }
+        const int slot = (int)(job_no % kPipeDepth);
+        Job& job = jobs_[slot];
         try {
-            run_group(*g);
+            run_group(*g, job, slot, gi);
         } catch (const std::exception& ex) {
-            g->error = ex.what();
+            job.error[(size_t)gi] = ex.what();
         }
         {
             std::lock_guard<std::mutex> lk(mu_);
-            --pending_;
+            g->done = job_no + 1;
+            --job.pending;
         }
-        cv_done_.notify_one();
+        cv_done_.notify_all();
     }
 }
 
+namespace {
+inline double now_ms() {
+    return std::chrono::duration<double, std::milli>(
+               std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+}  // namespace
+
 // One frame for the sequences of one group: the body of ImageProcessor::process, batched.
-void BatchFrontEnd::run_group(Group& g) {
-    const Job& job = job_;
+void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
+    double t_mark = trace_ ? now_ms() : 0.0;
+    auto lap = [&](int slot) {          // host wall time per phase (SVO_BATCH_TRACE=1)
+        if (!trace_) return;
+        const double t = now_ms();
+        g.phase_ms[slot] += t - t_mark;
+        t_mark = t;
+    };
+    g.phase_calls += 1;
     svo_engine* e = g.e;
+    BatchSummary& sum = job.sum[(size_t)gi];
+    sum = BatchSummary();
+    job.error[(size_t)gi].clear();
     const int n = (int)g.seqs.size();
     const int mc = opt_.params.max_corners, mf = opt_.params.max_features;
-    g.sum = BatchSummary();
-    g.error.clear();
     for (int i = 0; i < n; ++i) {
         const int s = g.seqs[(size_t)i];
         g.lp[(size_t)i] = job.left[s];
-        g.rp[(size_t)i] = job.right ? job.right[s] : nullptr;
+        g.rp[(size_t)i] = job.has_right ? job.right[s] : nullptr;
     }
+    // The right image is only read by the stereo stage of a keyframe
+    // (src/image_processor.cpp:34-39,137-142): with lazy_right_ it is uploaded for the sequences
+    // that became keyframes only (svo_set_right), ~1/4 of the frames on KITTI-like motion.
+    const bool lazy = lazy_right_ && job.has_right;
     int rc;
-    if (!job.on_device && job.next_left) {
+    if (!job.on_device && job.has_next) {
         // announce the next step's frames first: their copies run on the engine's copy stream
-        // underneath the kernels launched below
+        // underneath the kernels launched below. (All groups start a step together, so these
+        // bulk copies have drained from the shared H2D engine long before any group reaches its
+        // keyframe stage and queues right images behind them.)
         for (int i = 0; i < n; ++i) {
             const int s = g.seqs[(size_t)i];
             g.nlp[(size_t)i] = job.next_left[s];
-            g.nrp[(size_t)i] = job.next_right ? job.next_right[s] : nullptr;
+            g.nrp[(size_t)i] = (!lazy && job.has_next_right) ? job.next_right[s] : nullptr;
         }
-        rc = svo_prefetch(e, n, g.local_ids.data(), g.nlp.data(), g.nrp.data(), job.pitch);
+        rc = svo_prefetch(e, n, g.local_ids.data(), g.nlp.data(), lazy ? nullptr : g.nrp.data(),
+                          job.pitch);
         if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_prefetch", rc));
     }
+    lap(0);
     rc = job.on_device
-        ? svo_step_device(e, n, g.local_ids.data(), g.lp.data(), g.rp.data(), job.pitch,
-                          g.corners.data(), g.n_corn.data(), g.stats.data(), g.tracked.data(),
-                          g.tracked_ids.data())
-        : svo_step(e, n, g.local_ids.data(), g.lp.data(), g.rp.data(), job.pitch, g.corners.data(),
-                   g.n_corn.data(), g.stats.data(), g.tracked.data(), g.tracked_ids.data());
+        ? svo_step_device(e, n, g.local_ids.data(), g.lp.data(), lazy ? nullptr : g.rp.data(),
+                          job.pitch, g.corners.data(), g.n_corn.data(), g.stats.data(),
+                          g.tracked.data(), g.tracked_ids.data())
+        : svo_step(e, n, g.local_ids.data(), g.lp.data(), lazy ? nullptr : g.rp.data(), job.pitch,
+                   g.corners.data(), g.n_corn.data(), g.stats.data(), g.tracked.data(),
+                   g.tracked_ids.data());
     if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_step", rc));
+    lap(1);
+    if (trace_) {
+        float ms[3];
+        svo_last_timing(e, ms);
+        g.phase_ms[6] += ms[0]; g.phase_ms[7] += ms[1]; g.phase_ms[8] += ms[2];
+    }
 
     // ---- keyframe decision per sequence (src/image_processor.cpp:23-30,63-65)
     int nk = 0;
     for (int i = 0; i < n; ++i) {
         const int s = g.seqs[(size_t)i];
         SeqState& st = seq_[(size_t)s];
-        st.n_corners = g.n_corn[(size_t)i];
-        st.stats = g.stats[(size_t)i];
-        st.n_new = 0;
-        std::memcpy(&corners_[(size_t)s * mc], &g.corners[(size_t)i * mc],
-                    (size_t)st.n_corners * sizeof(svo_float2));
-        g.sum.frames += 1;
-        g.sum.corners += st.n_corners;
-        if (st.n_corners < 4) {
-            st.decision = BATCH_TOO_FEW;
+        SeqResult& rs = st.res[slot];
+        rs.n_corners = g.n_corn[(size_t)i];
+        rs.stats = g.stats[(size_t)i];
+        rs.n_new = 0;
+        rs.n_tracker = st.n_tracker;
+        std::memcpy(&corners_[slot][(size_t)s * mc], &g.corners[(size_t)i * mc],
+                    (size_t)rs.n_corners * sizeof(svo_float2));
+        sum.frames += 1;
+        sum.corners += rs.n_corners;
+        if (rs.n_corners < 4) {
+            rs.decision = BATCH_TOO_FEW;
             continue;
         }
         int n_inl = 0;
         if (st.have_kf) {
-            const svo_track_stats& ts = st.stats;
-            st.n_tracker = ts.n_kept;
-            std::memcpy(&tracker_pts_[(size_t)s * mf], &g.tracked[(size_t)i * mf],
+            const svo_track_stats& ts = rs.stats;
+            st.n_tracker = rs.n_tracker = ts.n_kept;
+            std::memcpy(&tracker_pts_[slot][(size_t)s * mf], &g.tracked[(size_t)i * mf],
                         (size_t)ts.n_kept * sizeof(svo_float2));
-            std::memcpy(&tracker_ids_[(size_t)s * mf], &g.tracked_ids[(size_t)i * mf],
+            std::memcpy(&tracker_ids_[slot][(size_t)s * mf], &g.tracked_ids[(size_t)i * mf],
                         (size_t)ts.n_kept * sizeof(uint64_t));
-            g.sum.tracked += ts.n_kept;
+            sum.tracked += ts.n_kept;
             if (ts.av_parallax <= opt_.parallax_thresh && ts.percent_lost < 0.4) {
-                st.decision = BATCH_SKIP;
+                rs.decision = BATCH_SKIP;
                 continue;
             }
-            st.decision = BATCH_KEYFRAME;
+            rs.decision = BATCH_KEYFRAME;
             n_inl = ts.n_kept;             // every kept track is an inlier (no host PnP here)
             std::memcpy(&g.inl[(size_t)nk * mf], &g.tracked[(size_t)i * mf],
                         (size_t)n_inl * sizeof(svo_float2));
         } else {
-            st.decision = BATCH_FIRST;
+            rs.decision = BATCH_FIRST;
         }
         g.kf_local[(size_t)nk] = i;
         g.n_inl[(size_t)nk] = n_inl;
         float* pose = &g.poses[(size_t)nk * 16];
-        if (job.poses) std::memcpy(pose, job.poses + (size_t)s * 16, 16 * sizeof(float));
+        if (job.has_poses) std::memcpy(pose, job.poses.data() + (size_t)s * 16, 16 * sizeof(float));
         else for (int k = 0; k < 16; ++k) pose[k] = (k % 5 == 0) ? 1.f : 0.f;
         ++nk;
     }
+    if (lazy && nk > 0) {
+        for (int k = 0; k < nk; ++k) g.nrp[(size_t)k] = g.rp[(size_t)g.kf_local[(size_t)k]];
+        rc = svo_set_right(e, nk, g.kf_local.data(), g.nrp.data(), job.pitch, job.on_device ? 1 : 0);
+        if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_set_right", rc));
+    }
+    lap(2);
     if (nk == 0) return;
 
     // ---- dedupe + StereoBM + reprojection for the new keyframes (:113-142)
@@ -177,6 +242,12 @@ void BatchFrontEnd::run_group(Group& g) {
                       g.n_newv.data(), g.valid_2d.data(), g.pts_3d.data(), g.valid_idx.data(),
                       g.disp16.data(), g.n_valid.data());
     if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_keyframe", rc));
+    lap(3);
+    if (trace_) {
+        float ms[3];
+        svo_last_timing(e, ms);
+        g.phase_ms[9] += ms[0]; g.phase_ms[10] += ms[1]; g.phase_ms[11] += ms[2];
+    }
 
     // ---- BundleAdjuster::add_keyframe bookkeeping (ids are a running counter, SURVEY.md B7;
     // new features are clipped to the 400-feature limit) + FeatureTracker::init (:148-162)
@@ -194,53 +265,83 @@ void BatchFrontEnd::run_group(Group& g) {
         for (int j = 0; j < nv; ++j) id[n_inl + j] = st.next_id++;
         g.counts[(size_t)k] = n_inl + nv;
         st.have_kf = true;
-        st.n_new = nv;
-        st.n_tracker = n_inl + nv;
-        std::memcpy(&new_2d_[(size_t)s * mc], &g.valid_2d[(size_t)k * mc], (size_t)nv * sizeof(svo_float2));
-        std::memcpy(&new_3d_[(size_t)s * mc], &g.pts_3d[(size_t)k * mc], (size_t)nv * sizeof(svo_float3));
-        std::memcpy(&tracker_pts_[(size_t)s * mf], f, (size_t)(n_inl + nv) * sizeof(svo_float2));
-        std::memcpy(&tracker_ids_[(size_t)s * mf], id, (size_t)(n_inl + nv) * sizeof(uint64_t));
-        g.sum.keyframes += 1;
-        g.sum.new_points += nv;
+        SeqResult& rs = st.res[slot];
+        rs.n_new = nv;
+        st.n_tracker = rs.n_tracker = n_inl + nv;
+        std::memcpy(&new_2d_[slot][(size_t)s * mc], &g.valid_2d[(size_t)k * mc], (size_t)nv * sizeof(svo_float2));
+        std::memcpy(&new_3d_[slot][(size_t)s * mc], &g.pts_3d[(size_t)k * mc], (size_t)nv * sizeof(svo_float3));
+        std::memcpy(&tracker_pts_[slot][(size_t)s * mf], f, (size_t)(n_inl + nv) * sizeof(svo_float2));
+        std::memcpy(&tracker_ids_[slot][(size_t)s * mf], id, (size_t)(n_inl + nv) * sizeof(uint64_t));
+        sum.keyframes += 1;
+        sum.new_points += nv;
     }
+    lap(4);
     rc = svo_tracker_set(e, nk, g.kf_local.data(), g.feats.data(), g.ids.data(), g.counts.data());
     if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_tracker_set", rc));
+    lap(5);
+}
+
+void BatchFrontEnd::submit(const uint8_t* const* left, const uint8_t* const* right, int pitch,
+                           bool on_device, const float* poses, const uint8_t* const* next_left,
+                           const uint8_t* const* next_right) {
+    if (!left) throw std::invalid_argument("BatchFrontEnd::submit: left is null");
+    if (in_flight() >= kPipeDepth)
+        throw std::logic_error("BatchFrontEnd::submit: pipeline full, call wait() first");
+    const size_t n = (size_t)opt_.n_seq;
+    Job& job = jobs_[n_submitted_ % kPipeDepth];
+    job.left.assign(left, left + n);
+    job.has_right = right != nullptr;
+    if (right) job.right.assign(right, right + n);
+    job.has_next = next_left != nullptr;
+    if (next_left) job.next_left.assign(next_left, next_left + n);
+    job.has_next_right = next_left != nullptr && next_right != nullptr;
+    if (job.has_next_right) job.next_right.assign(next_right, next_right + n);
+    job.has_poses = poses != nullptr;
+    if (poses) job.poses.assign(poses, poses + n * 16);
+    job.pitch = pitch;
+    job.on_device = on_device;
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        job.pending = (int)groups_.size();
+        ++n_submitted_;
+    }
+    cv_start_.notify_all();
+}
+
+BatchSummary BatchFrontEnd::wait() {
+    if (in_flight() == 0) throw std::logic_error("BatchFrontEnd::wait: nothing submitted");
+    const int slot = (int)(n_waited_ % kPipeDepth);
+    Job& job = jobs_[slot];
+    {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_done_.wait(lk, [&] { return job.pending == 0; });
+    }
+    ++n_waited_;
+    cur_slot_ = slot;
+    BatchSummary total;
+    for (size_t g = 0; g < groups_.size(); ++g) {
+        if (!job.error[g].empty()) throw std::runtime_error(job.error[g]);
+        const BatchSummary& sm = job.sum[g];
+        total.frames += sm.frames; total.keyframes += sm.keyframes; total.corners += sm.corners;
+        total.tracked += sm.tracked; total.new_points += sm.new_points;
+    }
+    return total;
 }
 
 BatchSummary BatchFrontEnd::step(const uint8_t* const* left, const uint8_t* const* right, int pitch,
                                  bool on_device, const float* poses,
                                  const uint8_t* const* next_left,
                                  const uint8_t* const* next_right) {
-    if (!left) throw std::invalid_argument("BatchFrontEnd::step: left is null");
-    job_.left = left; job_.right = right; job_.pitch = pitch; job_.on_device = on_device;
-    job_.poses = poses; job_.next_left = next_left; job_.next_right = next_right;
-    if (groups_.size() == 1) {
-        run_group(*groups_[0]);
-    } else {
-        {
-            std::lock_guard<std::mutex> lk(mu_);
-            pending_ = (int)groups_.size();
-            ++generation_;
-        }
-        cv_start_.notify_all();
-        std::unique_lock<std::mutex> lk(mu_);
-        cv_done_.wait(lk, [&] { return pending_ == 0; });
-    }
-    BatchSummary total;
-    for (auto& g : groups_) {
-        if (!g->error.empty()) throw std::runtime_error(g->error);
-        total.frames += g->sum.frames; total.keyframes += g->sum.keyframes;
-        total.corners += g->sum.corners; total.tracked += g->sum.tracked;
-        total.new_points += g->sum.new_points;
-    }
-    return total;
+    while (in_flight() > 0) wait();      // a synchronous step never overtakes queued ones
+    submit(left, right, pitch, on_device, poses, next_left, next_right);
+    return wait();
 }
 
-const svo_float2* BatchFrontEnd::corners(int s) const { return &corners_[(size_t)s * opt_.params.max_corners]; }
-const svo_float2* BatchFrontEnd::tracker_points(int s) const { return &tracker_pts_[(size_t)s * opt_.params.max_features]; }
-const uint64_t* BatchFrontEnd::tracker_ids(int s) const { return &tracker_ids_[(size_t)s * opt_.params.max_features]; }
-const svo_float2* BatchFrontEnd::new_2d(int s) const { return &new_2d_[(size_t)s * opt_.params.max_corners]; }
-const svo_float3* BatchFrontEnd::new_3d(int s) const { return &new_3d_[(size_t)s * opt_.params.max_corners]; }
+const svo_float2* BatchFrontEnd::corners(int s) const { return &corners_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
+const svo_float2* BatchFrontEnd::tracker_points(int s) const { return &tracker_pts_[cur_slot_][(size_t)s * opt_.params.max_features]; }
+const uint64_t* BatchFrontEnd::tracker_ids(int s) const { return &tracker_ids_[cur_slot_][(size_t)s * opt_.params.max_features]; }
+const svo_float2* BatchFrontEnd::new_2d(int s) const { return &new_2d_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
+const svo_float3* BatchFrontEnd::new_3d(int s) const { return &new_3d_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
 
 int64_t BatchFrontEnd::kernel_launches() const {
     int64_t n = 0;

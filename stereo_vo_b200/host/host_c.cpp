@@ -208,6 +208,27 @@ int svo_batch_step(svo_batch* b, const uint8_t* const* left, const uint8_t* cons
     });
 }
 
+int svo_batch_submit(svo_batch* b, const uint8_t* const* left, const uint8_t* const* right,
+                     int32_t pitch, int32_t on_device, const float* poses,
+                     const uint8_t* const* next_left, const uint8_t* const* next_right) {
+    if (!b || !left) return SVO_ERR_INVALID;
+    return guarded(b->error, [&] {
+        b->fe->submit(left, right, pitch, on_device != 0, poses, next_left, next_right);
+    });
+}
+
+int svo_batch_wait(svo_batch* b, svo_batch_summary* summary) {
+    if (!b) return SVO_ERR_INVALID;
+    return guarded(b->error, [&] {
+        svo::BatchSummary s = b->fe->wait();
+        if (summary) {
+            summary->frames = s.frames; summary->keyframes = s.keyframes;
+            summary->corners = s.corners; summary->tracked = s.tracked;
+            summary->new_points = s.new_points;
+        }
+    });
+}
+
 int svo_batch_get(svo_batch* b, int32_t seq, int32_t* decision, int32_t* n_corners,
                   svo_float2* corners, svo_track_stats* stats, int32_t* n_tracker,
                   svo_float2* tracker_pts, uint64_t* tracker_ids, int32_t* n_new,

@@ -81,6 +81,8 @@ def load_library():
     lib.svo_batch_last_error.argtypes = [vp]
     lib.svo_batch_last_error.restype = C.c_char_p
     lib.svo_batch_step.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp, C.POINTER(BatchSummary)]
+    lib.svo_batch_submit.argtypes = [vp, vp, vp, i32, i32, vp, vp, vp]
+    lib.svo_batch_wait.argtypes = [vp, C.POINTER(BatchSummary)]
     lib.svo_batch_get.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), vp, vp, C.POINTER(i32),
                                   vp, vp, C.POINTER(i32), vp, vp]
     lib.svo_batch_kernel_launches.argtypes = [vp]
@@ -270,6 +272,36 @@ class Batch:
             raise SvoError(f"svo_batch_step failed ({rc}): "
                            f"{self.lib.svo_batch_last_error(self.h).decode(errors='replace')}")
         return s
+
+    def submit_raw(self, lp, rp, pitch, device, poses_ptr=None, nlp=None, nrp=None):
+        """svo_batch_submit on prebuilt ctypes pointer arrays (at most 2 steps in flight)."""
+        rc = self.lib.svo_batch_submit(self.h, lp, rp, int(pitch), 1 if device else 0, poses_ptr,
+                                       nlp, nrp)
+        if rc != 0:
+            raise SvoError(f"svo_batch_submit failed ({rc}): "
+                           f"{self.lib.svo_batch_last_error(self.h).decode(errors='replace')}")
+
+    def wait(self) -> BatchSummary:
+        s = BatchSummary()
+        rc = self.lib.svo_batch_wait(self.h, C.byref(s))
+        if rc != 0:
+            raise SvoError(f"svo_batch_wait failed ({rc}): "
+                           f"{self.lib.svo_batch_last_error(self.h).decode(errors='replace')}")
+        return s
+
+    def submit(self, left, right, pitch, device=False, poses=None, next_left=None, next_right=None):
+        """Pipelined step: returns at once; call wait() for the results (oldest first). The
+        image arrays are kept alive until two more submits have gone by."""
+        lp, k1 = self._ptrs(left, device)
+        rp, k2 = self._ptrs(right, device)
+        nlp, k3 = self._ptrs(next_left, False) if not device else (None, None)
+        nrp, k4 = self._ptrs(next_right, False) if not device else (None, None)
+        pz = None
+        if poses is not None:
+            poses = np.ascontiguousarray(poses, np.float32).reshape(self.n_seq, 16)
+            pz = poses.ctypes.data_as(C.c_void_p)
+        self._pipe_keep = (getattr(self, "_pipe_keep", []) + [(k1, k2, k3, k4, poses)])[-4:]
+        self.submit_raw(lp, rp, pitch, device, pz, nlp, nrp)
 
     # device-resident frames (bench kernel-only leg): allocations through group 0's engine
     def device_alloc(self, nbytes: int) -> int:

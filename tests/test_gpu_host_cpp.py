@@ -177,3 +177,53 @@ def test_prefetch_is_transparent(svo_lib, oracle):
         assert len(other) == len(outs[0])
         for a, b in zip(outs[0], other):
             assert np.array_equal(a, b)
+
+
+def test_cpp_batch_pipelined_matches_synchronous(host_lib, oracle):
+    """submit()/wait() with two steps in flight (groups drifting apart, prefetch active, right
+    images uploaded lazily) returns, step by step, exactly what synchronous step() returns."""
+    from stereo_vo_b200 import hostapi
+    cam = synth.KITTI00
+    n_seq, n_fr = 6, 8
+    seqs = [util.frames(s % 3, n_fr, start=3 * (s // 3)) for s in range(n_seq)]
+    poses = [np.stack([np.eye(4, dtype=np.float32) for _ in range(n_seq)]) for _ in range(n_fr)]
+    for t in range(n_fr):
+        poses[t][:, :3, 3] = synth.ground_truth(t)
+
+    def frames_of(t):
+        return [seqs[s][t][0] for s in range(n_seq)], [seqs[s][t][1] for s in range(n_seq)]
+
+    def snapshot(b):
+        return [b.get(s) for s in range(n_seq)]
+
+    ref = hostapi.Batch(cam.width, cam.height, n_seq, 1, cam)
+    want = []
+    for t in range(n_fr):
+        l, r = frames_of(t)
+        sm = ref.step(l, r, l[0].strides[0], poses=poses[t])
+        want.append((sm, snapshot(ref)))
+    ref.close()
+
+    pipe = hostapi.Batch(cam.width, cam.height, n_seq, 3, cam)
+    got = []
+    l, r = frames_of(0)
+    nl, nr = frames_of(1)
+    pipe.submit(l, r, l[0].strides[0], poses=poses[0], next_left=nl, next_right=nr)
+    for t in range(n_fr):
+        if t + 1 < n_fr:
+            l, r = frames_of(t + 1)
+            nl, nr = frames_of(t + 2) if t + 2 < n_fr else (None, None)
+            pipe.submit(l, r, l[0].strides[0], poses=poses[t + 1], next_left=nl, next_right=nr)
+        s = pipe.wait()
+        got.append((dict(frames=s.frames, keyframes=s.keyframes, corners=s.corners,
+                         tracked=s.tracked, new_points=s.new_points), snapshot(pipe)))
+    pipe.close()
+    assert sum(w[0]["keyframes"] for w in want) >= n_seq + 2
+    for t, ((sa, ra), (sb, rb)) in enumerate(zip(want, got)):
+        assert sa == sb, (t, sa, sb)
+        for s in range(n_seq):
+            a, b = ra[s], rb[s]
+            assert a["decision"] == b["decision"], (t, s)
+            for key in ("corners", "tracker_pts", "tracker_ids", "new2d", "new3d"):
+                assert np.array_equal(a[key], b[key]), (t, s, key)
+            assert a["stats"].tobytes() == b["stats"].tobytes()

@@ -148,6 +148,7 @@ class BatchFrontEnd {
 
     BatchOptions opt_;
     bool trace_ = false;           // SVO_BATCH_TRACE=1: per-phase host/device times on stderr
+    bool zero_copy_right_ = true;  // keyframe right images read in place from mapped pinned memory
     bool lazy_right_ = true;       // upload right images for keyframes only (SVO_BATCH_LAZY_RIGHT=0: always)
     std::vector<std::unique_ptr<Group>> groups_;
     std::vector<SeqState> seq_;

@@ -201,6 +201,11 @@ SVO_API int svo_step_device(svo_engine* e, int32_t n, const int32_t* seqs, const
  * pointers (device pointers when on_device), `pitch` bytes per row. Asynchronous: returns once
  * the copies are queued; the host images must stay unchanged until the next svo_keyframe() /
  * svo_triangulate_stereo() of the engine returns. */
+/* 1 when kernels can read `p` directly (device memory, or pinned host memory mapped at the same
+ * address, e.g. from svo_host_alloc): such images may be passed with on_device = 1, and are then
+ * fetched by the ingest kernel itself - for pinned HOST memory that is a zero-copy read over
+ * PCIe which does not queue behind bulk copies on the H2D copy engine. */
+SVO_API int svo_device_can_read(const void* p);
 SVO_API int svo_set_right(svo_engine* e, int32_t n, const int32_t* seqs,
                           const uint8_t* const* right, int32_t pitch, int32_t on_device);
 

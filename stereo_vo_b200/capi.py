@@ -47,7 +47,7 @@ EXPORTS = [
     "svo_good_features_to_track", "svo_triangulate_stereo", "svo_tracker_init",
     "svo_tracker_track", "svo_tracker_get", "svo_dedupe", "svo_tracker_debug",
     "svo_debug_min_eigen_map", "svo_debug_pyramid_level", "svo_debug_candidates",
-    "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_keyframe", "svo_tracker_set",
+    "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
     "svo_timer_begin", "svo_timer_end",
@@ -100,6 +100,7 @@ def load_library(path: Optional[str] = None):
     lib.svo_step_device.argtypes = [vp, i32, vp, vp, vp, i32, vp, vp, vp, vp, vp]
     lib.svo_prefetch.argtypes = [vp, i32, vp, vp, vp, i32]
     lib.svo_set_right.argtypes = [vp, i32, vp, vp, i32, i32]
+    lib.svo_device_can_read.argtypes = [vp]
     lib.svo_keyframe.argtypes = [vp, i32, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp,
                                  vp, vp]
     lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]

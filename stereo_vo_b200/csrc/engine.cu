@@ -1160,6 +1160,19 @@ int svo_triangulate_stereo(svo_engine* e, int32_t seq, const uint8_t* left, cons
                          out_n_valid);
 }
 
+int svo_device_can_read(const void* p) {
+    if (!p) return 0;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) return 1;
+    // pinned host memory is mapped into the device address space under unified addressing;
+    // kernels can only use it through the same pointer value
+    return (a.type == cudaMemoryTypeHost && a.devicePointer == p) ? 1 : 0;
+}
+
 int svo_set_right(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* right,
                   int32_t pitch, int32_t on_device) {
     if (!e) return SVO_ERR_INVALID;
@@ -1423,7 +1436,9 @@ int svo_device_upload(svo_engine* e, void* dst, const void* src, size_t bytes) {
 }
 int svo_host_alloc(size_t bytes, void** out) {
     if (!out) return SVO_ERR_INVALID;
-    return cudaMallocHost(out, bytes) == cudaSuccess ? SVO_OK : SVO_ERR_NOMEM;
+    // mapped + portable: kernels of any device may read the buffer in place (svo_device_can_read)
+    return cudaHostAlloc(out, bytes, cudaHostAllocMapped | cudaHostAllocPortable) == cudaSuccess
+               ? SVO_OK : SVO_ERR_NOMEM;
 }
 int svo_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? SVO_OK : SVO_ERR_CUDA; }
 

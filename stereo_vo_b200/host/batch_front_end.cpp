@@ -21,6 +21,7 @@ std::string engine_error(svo_engine* e, const char* what, int rc) {
 BatchFrontEnd::BatchFrontEnd(const BatchOptions& opt) : opt_(opt) {
     if (const char* v = std::getenv("SVO_BATCH_LAZY_RIGHT")) lazy_right_ = std::atoi(v) != 0;
     if (const char* v = std::getenv("SVO_BATCH_TRACE")) trace_ = std::atoi(v) != 0;
+    if (const char* v = std::getenv("SVO_BATCH_ZERO_COPY_RIGHT")) zero_copy_right_ = std::atoi(v) != 0;
     if (opt.n_seq <= 0) throw std::invalid_argument("BatchFrontEnd: n_seq must be positive");
     const int G = std::max(1, std::min(opt.n_groups, opt.n_seq));
     const int mc = opt.params.max_corners, mf = opt.params.max_features;
@@ -229,8 +230,16 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         ++nk;
     }
     if (lazy && nk > 0) {
+        // pinned, device-mapped host frames are read by the ingest kernel itself (zero-copy over
+        // PCIe): a DMA copy would queue behind the bulk prefetches of every group on the one H2D
+        // copy engine and hold the keyframe stage back
+        bool direct = job.on_device;
         for (int k = 0; k < nk; ++k) g.nrp[(size_t)k] = g.rp[(size_t)g.kf_local[(size_t)k]];
-        rc = svo_set_right(e, nk, g.kf_local.data(), g.nrp.data(), job.pitch, job.on_device ? 1 : 0);
+        if (!direct && zero_copy_right_) {
+            direct = true;
+            for (int k = 0; k < nk && direct; ++k) direct = svo_device_can_read(g.nrp[(size_t)k]) != 0;
+        }
+        rc = svo_set_right(e, nk, g.kf_local.data(), g.nrp.data(), job.pitch, direct ? 1 : 0);
         if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_set_right", rc));
     }
     lap(2);

@@ -210,7 +210,7 @@ def run_ours(args, rank, world, local_rank):
         sampler.start()
         batch.timer_begin()
         t0 = time.perf_counter()
-        tracked = corners = keyframes = 0
+        tracked = corners = keyframes = rights = 0
         first, last = warmup, warmup + steps
         if args.pipeline and not profile:
             # two steps in flight (svo_batch_submit / svo_batch_wait): engine groups run free of
@@ -223,12 +223,14 @@ def run_ours(args, rank, world, local_rank):
                 tracked += sm.tracked
                 corners += sm.corners
                 keyframes += sm.keyframes
+                rights += sm.right_images
         else:
             for k in range(first, last):
                 sm = one(k)
                 tracked += sm.tracked
                 corners += sm.corners
                 keyframes += sm.keyframes
+                rights += sm.right_images
         ev_ms = batch.timer_end()
         barrier()
         wall_ms = (time.perf_counter() - t0) * 1e3
@@ -236,7 +238,7 @@ def run_ours(args, rank, world, local_rank):
         prof = batch.get_profile() if profile else {}
         out = dict(ms=max(ev_ms, 0.0), wall_ms=wall_ms, clocks=clocks, prof=prof,
                    launches=batch.kernel_launches - launches0, keyframes=keyframes,
-                   tracked=tracked, corners=corners)
+                   tracked=tracked, corners=corners, rights=rights)
         if dptr is not None:
             batch.device_free(dptr)
         batch.close()
@@ -324,8 +326,9 @@ def run_ours(args, rank, world, local_rank):
                         "algorithmic_bytes_per_launch": ALGO_BYTES[hbm_dom] * S,
                         "dominant_kernel_of_step": dom}
         cpu = None if args.skip_cpu_baseline else cpu_baseline(sample_frames=args.cpu_frames)
-        # every left image + the right image of the frames that became keyframes
-        in_bytes = int(S * H * W + e2e["keyframes"] / K * H * W)
+        # every left image + the right images actually transferred (predicted keyframes and
+        # keyframes fetched on demand; counted by the driver)
+        in_bytes = int(S * H * W + e2e["rights"] / K * H * W)
         eng_tmp_block = 16 + 24 + 300 * 8 + 400 * 16
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,

@@ -41,6 +41,7 @@ enum BatchDecision : int32_t { BATCH_TOO_FEW = 1, BATCH_FIRST = 2, BATCH_SKIP = 
 
 struct BatchSummary {             // totals over all sequences of one step
     int64_t frames = 0, keyframes = 0, corners = 0, tracked = 0, new_points = 0;
+    int64_t right_images = 0;     // right images transferred (all, or predicted + on demand)
 };
 
 class BatchFrontEnd {
@@ -112,6 +113,7 @@ class BatchFrontEnd {
         bool have_kf = false;
         uint64_t next_id = 0;
         int32_t n_tracker = 0;             // tracker set size carried from step to step
+        float par_last = 0.f, par_rate = 8.f;   // keyframe predictor: last av_parallax, growth/step
         SeqResult res[kPipeDepth];
     };
     struct Group {
@@ -121,7 +123,11 @@ class BatchFrontEnd {
         uint64_t done = 0;                 // steps this group has completed
         // scratch (all sized for the group's sequences)
         std::vector<int32_t> local_ids, kf_local, n_inl, n_newv, n_valid, counts, n_corn;
-        std::vector<const uint8_t*> lp, rp, nlp, nrp;
+        std::vector<const uint8_t*> lp, rp, nlp, nrp, srp;
+        std::vector<int32_t> miss_local;
+        std::vector<char> pred_cur, pred_next;   // right image travels with this / the next step
+        bool have_pred = false;
+        int64_t pred_sent = 0, pred_hits = 0, pred_miss = 0;
         std::vector<svo_track_stats> stats;
         std::vector<svo_float2> corners, tracked, inl, new_feats, valid_2d, feats;
         std::vector<svo_float3> pts_3d;

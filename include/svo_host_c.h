@@ -68,6 +68,7 @@ typedef struct svo_batch svo_batch;
 
 typedef struct svo_batch_summary {
     int64_t frames, keyframes, corners, tracked, new_points;
+    int64_t right_images;    /* right images transferred with / for this step */
 } svo_batch_summary;
 
 SVO_API int svo_batch_create(const svo_params* p, int32_t device, int32_t n_seq, int32_t n_groups,

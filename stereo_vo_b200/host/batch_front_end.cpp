@@ -56,6 +56,8 @@ BatchFrontEnd::BatchFrontEnd(const BatchOptions& opt) : opt_(opt) {
         grp->local_ids.resize(n); grp->kf_local.resize(n); grp->n_inl.resize(n);
         grp->n_newv.resize(n); grp->n_valid.resize(n); grp->counts.resize(n); grp->n_corn.resize(n);
         grp->lp.resize(n); grp->rp.resize(n); grp->nlp.resize(n); grp->nrp.resize(n);
+        grp->srp.resize(n); grp->miss_local.resize(n);
+        grp->pred_cur.assign(n, 0); grp->pred_next.assign(n, 0);
         grp->stats.resize(n);
         grp->corners.resize(n * mc); grp->new_feats.resize(n * mc); grp->valid_2d.resize(n * mc);
         grp->pts_3d.resize(n * mc); grp->valid_idx.resize(n * mc); grp->disp16.resize(n * mc);
@@ -84,12 +86,14 @@ BatchFrontEnd::~BatchFrontEnd() {
                          "[svo batch] group %d (%zu seqs, %ld steps) host ms/step: prefetch %.3f "
                          "step %.3f set_right %.3f keyframe %.3f bookkeeping %.3f tracker_set %.3f | "
                          "device ms/step: step copy-in %.3f kernels %.3f copy-out %.3f ; keyframe "
-                         "copy-in %.3f kernels %.3f copy-out %.3f\n",
+                         "copy-in %.3f kernels %.3f copy-out %.3f | right images: %ld sent ahead, %ld "
+                         "keyframes predicted, %ld fetched on demand\n",
                          gi, g->seqs.size(), (long)g->phase_calls, g->phase_ms[0] / c,
                          g->phase_ms[1] / c, g->phase_ms[2] / c, g->phase_ms[3] / c,
                          g->phase_ms[4] / c, g->phase_ms[5] / c, g->phase_ms[6] / c,
                          g->phase_ms[7] / c, g->phase_ms[8] / c, g->phase_ms[9] / c,
-                         g->phase_ms[10] / c, g->phase_ms[11] / c);
+                         g->phase_ms[10] / c, g->phase_ms[11] / c, (long)g->pred_sent,
+                         (long)g->pred_hits, (long)g->pred_miss);
         }
         ++gi;
         if (g->e) svo_destroy(g->e);
@@ -150,32 +154,58 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         g.rp[(size_t)i] = job.has_right ? job.right[s] : nullptr;
     }
     // The right image is only read by the stereo stage of a keyframe
-    // (src/image_processor.cpp:34-39,137-142): with lazy_right_ it is uploaded for the sequences
-    // that became keyframes only (svo_set_right), ~1/4 of the frames on KITTI-like motion.
+    // (src/image_processor.cpp:34-39,137-142). With lazy_right_ it travels with the step only for
+    // the sequences PREDICTED to become keyframes (parallax extrapolated from the last steps:
+    // a correct guess keeps the transfer off this group's critical chain); a keyframe that was
+    // not predicted fetches its right image on demand (svo_set_right), a wrong guess costs one
+    // idle image copy. Results never depend on the prediction.
     const bool lazy = lazy_right_ && job.has_right;
+    auto predict = [&](const SeqState& st, int steps_ahead) {
+        if (!st.have_kf) return steps_ahead == 1;                     // the bootstrap keyframe
+        const float margin = 0.85f * opt_.parallax_thresh;
+        const float p1 = st.par_last + st.par_rate;                   // next step
+        if (steps_ahead == 1) return p1 > margin;
+        if (p1 > opt_.parallax_thresh) return st.par_rate > margin;   // keyframe resets parallax
+        return st.par_last + 2.f * st.par_rate > margin;
+    };
+    if (lazy) {
+        // right images that travel with THIS step: what the previous job announced, else a
+        // fresh one-step prediction
+        if (!g.have_pred) {
+            for (int i = 0; i < n; ++i) g.pred_cur[(size_t)i] = predict(seq_[(size_t)g.seqs[(size_t)i]], 1);
+        } else {
+            g.pred_cur = g.pred_next;
+        }
+        g.have_pred = false;
+        for (int i = 0; i < n; ++i)
+            g.srp[(size_t)i] = g.pred_cur[(size_t)i] ? g.rp[(size_t)i] : nullptr;
+    }
+    const uint8_t* const* step_right = lazy ? g.srp.data() : g.rp.data();
     int rc;
     if (!job.on_device && job.has_next) {
         // announce the next step's frames first: their copies run on the engine's copy stream
-        // underneath the kernels launched below. (All groups start a step together, so these
-        // bulk copies have drained from the shared H2D engine long before any group reaches its
-        // keyframe stage and queues right images behind them.)
+        // underneath the kernels launched below
         for (int i = 0; i < n; ++i) {
             const int s = g.seqs[(size_t)i];
             g.nlp[(size_t)i] = job.next_left[s];
-            g.nrp[(size_t)i] = (!lazy && job.has_next_right) ? job.next_right[s] : nullptr;
+            bool want_right = job.has_next_right;
+            if (lazy && want_right) {
+                want_right = predict(seq_[(size_t)s], 2);
+                g.pred_next[(size_t)i] = want_right;
+            }
+            g.nrp[(size_t)i] = want_right ? job.next_right[s] : nullptr;
         }
-        rc = svo_prefetch(e, n, g.local_ids.data(), g.nlp.data(), lazy ? nullptr : g.nrp.data(),
-                          job.pitch);
+        if (lazy && job.has_next_right) g.have_pred = true;
+        rc = svo_prefetch(e, n, g.local_ids.data(), g.nlp.data(), g.nrp.data(), job.pitch);
         if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_prefetch", rc));
     }
     lap(0);
     rc = job.on_device
-        ? svo_step_device(e, n, g.local_ids.data(), g.lp.data(), lazy ? nullptr : g.rp.data(),
-                          job.pitch, g.corners.data(), g.n_corn.data(), g.stats.data(),
-                          g.tracked.data(), g.tracked_ids.data())
-        : svo_step(e, n, g.local_ids.data(), g.lp.data(), lazy ? nullptr : g.rp.data(), job.pitch,
-                   g.corners.data(), g.n_corn.data(), g.stats.data(), g.tracked.data(),
-                   g.tracked_ids.data());
+        ? svo_step_device(e, n, g.local_ids.data(), g.lp.data(), step_right, job.pitch,
+                          g.corners.data(), g.n_corn.data(), g.stats.data(), g.tracked.data(),
+                          g.tracked_ids.data())
+        : svo_step(e, n, g.local_ids.data(), g.lp.data(), step_right, job.pitch, g.corners.data(),
+                   g.n_corn.data(), g.stats.data(), g.tracked.data(), g.tracked_ids.data());
     if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_step", rc));
     lap(1);
     if (trace_) {
@@ -211,11 +241,17 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
             std::memcpy(&tracker_ids_[slot][(size_t)s * mf], &g.tracked_ids[(size_t)i * mf],
                         (size_t)ts.n_kept * sizeof(uint64_t));
             sum.tracked += ts.n_kept;
+            // parallax model of the keyframe predictor (finite values only)
+            if (ts.av_parallax == ts.av_parallax) {
+                st.par_rate = 0.5f * st.par_rate + 0.5f * std::max(0.f, ts.av_parallax - st.par_last);
+                st.par_last = ts.av_parallax;
+            }
             if (ts.av_parallax <= opt_.parallax_thresh && ts.percent_lost < 0.4) {
                 rs.decision = BATCH_SKIP;
                 continue;
             }
             rs.decision = BATCH_KEYFRAME;
+            st.par_last = 0.f;             // the tracker restarts from this frame
             n_inl = ts.n_kept;             // every kept track is an inlier (no host PnP here)
             std::memcpy(&g.inl[(size_t)nk * mf], &g.tracked[(size_t)i * mf],
                         (size_t)n_inl * sizeof(svo_float2));
@@ -230,17 +266,36 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         ++nk;
     }
     if (lazy && nk > 0) {
-        // pinned, device-mapped host frames are read by the ingest kernel itself (zero-copy over
-        // PCIe): a DMA copy would queue behind the bulk prefetches of every group on the one H2D
-        // copy engine and hold the keyframe stage back
-        bool direct = job.on_device;
-        for (int k = 0; k < nk; ++k) g.nrp[(size_t)k] = g.rp[(size_t)g.kf_local[(size_t)k]];
-        if (!direct && zero_copy_right_) {
-            direct = true;
-            for (int k = 0; k < nk && direct; ++k) direct = svo_device_can_read(g.nrp[(size_t)k]) != 0;
+        // keyframes the predictor missed: fetch their right image now. Pinned, device-mapped
+        // host frames are read by the ingest kernel itself (zero-copy over PCIe): a DMA copy
+        // would queue behind the bulk prefetches of every group on the one H2D copy engine
+        int nm = 0;
+        for (int k = 0; k < nk; ++k) {
+            const int i = g.kf_local[(size_t)k];
+            if (g.pred_cur[(size_t)i]) { g.pred_hits += 1; continue; }
+            g.miss_local[(size_t)nm] = i;
+            g.nrp[(size_t)nm] = g.rp[(size_t)i];
+            ++nm;
         }
-        rc = svo_set_right(e, nk, g.kf_local.data(), g.nrp.data(), job.pitch, direct ? 1 : 0);
-        if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_set_right", rc));
+        g.pred_miss += nm;
+        sum.right_images += nm;
+        if (nm > 0) {
+            bool direct = job.on_device;
+            if (!direct && zero_copy_right_) {
+                direct = true;
+                for (int k = 0; k < nm && direct; ++k) direct = svo_device_can_read(g.nrp[(size_t)k]) != 0;
+            }
+            rc = svo_set_right(e, nm, g.miss_local.data(), g.nrp.data(), job.pitch, direct ? 1 : 0);
+            if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_set_right", rc));
+        }
+    }
+    if (lazy) {
+        for (int i = 0; i < n; ++i) {
+            g.pred_sent += g.pred_cur[(size_t)i] ? 1 : 0;
+            sum.right_images += g.pred_cur[(size_t)i] ? 1 : 0;
+        }
+    } else if (job.has_right) {
+        sum.right_images += n;
     }
     lap(2);
     if (nk == 0) return;
@@ -333,6 +388,7 @@ BatchSummary BatchFrontEnd::wait() {
         const BatchSummary& sm = job.sum[g];
         total.frames += sm.frames; total.keyframes += sm.keyframes; total.corners += sm.corners;
         total.tracked += sm.tracked; total.new_points += sm.new_points;
+        total.right_images += sm.right_images;
     }
     return total;
 }

@@ -204,6 +204,7 @@ int svo_batch_step(svo_batch* b, const uint8_t* const* left, const uint8_t* cons
             summary->frames = s.frames; summary->keyframes = s.keyframes;
             summary->corners = s.corners; summary->tracked = s.tracked;
             summary->new_points = s.new_points;
+            summary->right_images = s.right_images;
         }
     });
 }
@@ -225,6 +226,7 @@ int svo_batch_wait(svo_batch* b, svo_batch_summary* summary) {
             summary->frames = s.frames; summary->keyframes = s.keyframes;
             summary->corners = s.corners; summary->tracked = s.tracked;
             summary->new_points = s.new_points;
+            summary->right_images = s.right_images;
         }
     });
 }

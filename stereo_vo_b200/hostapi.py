@@ -41,7 +41,7 @@ class VoRecord(C.Structure):
 
 class BatchSummary(C.Structure):
     _fields_ = [("frames", C.c_int64), ("keyframes", C.c_int64), ("corners", C.c_int64),
-                ("tracked", C.c_int64), ("new_points", C.c_int64)]
+                ("tracked", C.c_int64), ("new_points", C.c_int64), ("right_images", C.c_int64)]
 
 
 def declared_symbols():

@@ -115,6 +115,7 @@ struct svo_engine {
     float2* d_pts = nullptr;      // stereo input points / deduped new features
     int* d_keep_idx = nullptr;
     int* d_nnew = nullptr;
+    unsigned* d_ticket = nullptr;     // dedupe: blocks of a sequence that have finished (0 between calls)
     short* d_disp16 = nullptr;
     float2* d_valid2d = nullptr;
     float* d_pts3d = nullptr;
@@ -137,6 +138,8 @@ struct svo_engine {
     unsigned char* h_out = nullptr;   // pinned
     unsigned char* h_in = nullptr;    // pinned small-input staging
     size_t h_in_bytes = 0;
+    unsigned char* h_trk = nullptr;   // staging of svo_tracker_set alone (that call does not wait)
+    cudaEvent_t ev_trk = nullptr;     // recorded once the device has read h_trk
 
     std::vector<SeqState> seq;
     int64_t launches = 0;
@@ -316,11 +319,6 @@ __global__ void pack_key_kernel(unsigned char* out, size_t block, int cap, const
     }
 }
 
-// the detect kernels of the fused step write n_pts for the stereo stage on the device
-__global__ void set_npts_kernel(SvoSeqCall* call, const int* n_new) {
-    call[blockIdx.x].n_pts = n_new[call[blockIdx.x].seq];
-}
-
 SvoSeqCall* next_call_slot(svo_engine* e) {
     e->ring = (e->ring + 1) % CALL_RING;
     return e->h_call + (size_t)e->ring * e->n_seq;
@@ -435,8 +433,8 @@ pull_kernel(const svo_engine::PullSeg* __restrict__ segs) {
     for (unsigned i = threadIdx.x; i < n; i += blockDim.x) dst[i] = __ldcv(src + i);
 }
 
-// segment lists live in a ring of the pinned h_pull array; every API call is synchronous, so a
-// list is consumed before its slots come round again
+// segment lists live in a ring of the pinned h_pull array (room for four lists); every API call
+// but svo_tracker_set waits for the stream, so a list is consumed before its slots come round
 struct PullList {
     svo_engine* e;
     int first, count;
@@ -850,6 +848,8 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_pts, ns * cap));
     CCHK(dalloc(&e->d_keep_idx, ns * cap));
     CCHK(dalloc(&e->d_nnew, ns));
+    CCHK(dalloc(&e->d_ticket, ns));
+    CCHK(cudaMemsetAsync(e->d_ticket, 0, ns * sizeof(unsigned), e->st));
     CCHK(dalloc(&e->d_disp16, ns * cap));
     CCHK(dalloc(&e->d_valid2d, ns * cap));
     CCHK(dalloc(&e->d_pts3d, ns * cap * 3));
@@ -866,6 +866,9 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(cudaMallocHost(reinterpret_cast<void**>(&e->h_out), e->out_bytes));
     CCHK(cudaHostAlloc(reinterpret_cast<void**>(&e->h_in), e->h_in_bytes,
                        cudaHostAllocMapped | cudaHostAllocPortable));
+    CCHK(cudaHostAlloc(reinterpret_cast<void**>(&e->h_trk), ns * mf * 16 + 64,
+                       cudaHostAllocMapped | cudaHostAllocPortable));
+    CCHK(cudaEventCreateWithFlags(&e->ev_trk, cudaEventDisableTiming));
     CCHK(cudaMemsetAsync(e->d_pyr, 0, ns * e->seq_stride, e->st));
     CCHK(cudaMemsetAsync(e->d_right, 0, ns * e->right_stride, e->st));
     if (e->d_eig) CCHK(cudaMemsetAsync(e->d_eig, 0, ns * e->eig_stride * sizeof(float), e->st));
@@ -886,7 +889,7 @@ void svo_destroy(svo_engine* e) {
     void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
                      e->d_strips, e->d_strip_count, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
-                     e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew,
+                     e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
                      e->d_call};
     for (void* p : dptrs) if (p) cudaFree(p);
@@ -894,6 +897,8 @@ void svo_destroy(svo_engine* e) {
     if (e->h_pull) cudaFreeHost(e->h_pull);
     if (e->h_out) cudaFreeHost(e->h_out);
     if (e->h_in) cudaFreeHost(e->h_in);
+    if (e->h_trk) cudaFreeHost(e->h_trk);
+    if (e->ev_trk) cudaEventDestroy(e->ev_trk);
     for (int i = 0; i < 4; ++i) if (e->ev[i]) cudaEventDestroy(e->ev[i]);
     for (int i = 0; i < 2; ++i) if (e->timer_ev[i]) cudaEventDestroy(e->timer_ev[i]);
     for (cudaEvent_t ev : e->prof_ev) cudaEventDestroy(ev);
@@ -1074,9 +1079,8 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
     if (dedupe) {
         ProfScope ps(e, P_DEDUPE);
         ECUDA(e, svo_launch_dedupe(e->d_corners, e->d_ncorners, mcn, e->d_inl, mf, e->p.min_distance,
-                                   e->d_pts, e->d_keep_idx, e->d_nnew, cap, dc, n, e->st));
-        set_npts_kernel<<<n, 1, 0, e->st>>>(dc, e->d_nnew);
-        e->launches += 2;
+                                   e->d_pts, e->d_keep_idx, e->d_nnew, cap, dc, e->d_ticket, n, e->st));
+        e->launches += 1;
     }
     SvoStereoParams sp = {e->p.num_disparities, e->p.sad_window, e->p.prefilter_cap,
                           e->p.texture_threshold, e->p.uniqueness_ratio};
@@ -1203,7 +1207,11 @@ int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_flo
     if (n <= 0 || n > e->n_seq || !seqs || !counts) return fail(e, SVO_ERR_INVALID, "svo_tracker_set: bad arguments");
     ECUDA(e, cudaSetDevice(e->device));
     const int mf = e->p.max_features;
-    float2* hf = reinterpret_cast<float2*>(e->h_in);
+    // The call does not wait for the device: the feature lists are staged in a buffer of their
+    // own and every later call on this engine is ordered behind the copy on the engine stream.
+    // Only a second svo_tracker_set has to wait until the first one's staging has been read.
+    ECUDA(e, cudaEventSynchronize(e->ev_trk));
+    float2* hf = reinterpret_cast<float2*>(e->h_trk);
     unsigned long long* hi = reinterpret_cast<unsigned long long*>(hf + (size_t)e->n_seq * mf);
     for (int i = 0; i < n; ++i) {
         int s = seqs[i];
@@ -1238,7 +1246,7 @@ int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_flo
         s.last_slot = s.cur_slot;      // last_image = image.clone()  (feature_tracker.cpp:14)
     }
     ECUDA(e, pl.launch());
-    ECUDA(e, cudaStreamSynchronize(e->st));   // h_in is reused by the next call
+    ECUDA(e, cudaEventRecord(e->ev_trk, e->st));
     return SVO_OK;
 }
 
@@ -1351,7 +1359,7 @@ int svo_dedupe(svo_engine* e, int32_t seq, const svo_float2* det, int32_t n_det,
     if (n_det > 0) ECUDA(e, cudaMemcpyAsync(e->d_valid2d + (size_t)seq * cap, det, (size_t)n_det * sizeof(float2), cudaMemcpyHostToDevice, e->st));
     if (n_tracked > 0) ECUDA(e, cudaMemcpyAsync(e->d_inl + (size_t)seq * mf, tracked, (size_t)n_tracked * sizeof(float2), cudaMemcpyHostToDevice, e->st));
     ECUDA(e, svo_launch_dedupe(e->d_valid2d, nullptr, cap, e->d_inl, mf, min_distance, e->d_pts,
-                               e->d_keep_idx, e->d_nnew, cap, dev_call_slot(e), 1, e->st));
+                               e->d_keep_idx, e->d_nnew, cap, dev_call_slot(e), e->d_ticket, 1, e->st));
     e->launches += 1;
     int nn = 0;
     ECUDA(e, cudaMemcpyAsync(&nn, e->d_nnew + seq, sizeof(int), cudaMemcpyDeviceToHost, e->st));

@@ -216,31 +216,73 @@ reproject_kernel(const float2* __restrict__ pts, const short* __restrict__ disp1
     if (threadIdx.x == 0) n_valid[cd.seq] = written;
 }
 
+// dist < md with dist = sqrt_rn(d2) is a threshold test on d2 itself (sqrt_rn is monotonic):
+// the smallest float t with sqrt_rn(t) >= md. Found by walking a few ulps around md*md.
+__device__ __forceinline__ float dist2_threshold(float md) {
+    if (!(md > 0.f)) return 0.f;                      // dist >= 0: nothing is closer than md
+    float t = __fmul_rn(md, md);
+    for (int k = 0; k < 8 && t > 0.f; ++k) {
+        const float lo = __int_as_float(__float_as_int(t) - 1);
+        if (__fsqrt_rn(lo) >= md) t = lo; else break;
+    }
+    for (int k = 0; k < 8 && __fsqrt_rn(t) < md; ++k) t = __int_as_float(__float_as_int(t) + 1);
+    return t;
+}
+
+constexpr int DD_BLOCKS = 4;      // blocks per sequence
+constexpr int DD_TILE = 1024;     // tracked points staged per pass
+
+// New detections closer than min_distance to a tracked inlier are dropped, order kept
+// (src/image_processor.cpp:118-131). DD_BLOCKS blocks of a sequence test a quarter of the
+// detections each against the tracked points (staged in shared memory) and leave a flag per
+// detection in keep_idx; the block that finishes last compacts. `ticket` is zero between calls.
 __global__ void __launch_bounds__(RP_THREADS)
 dedupe_kernel(const float2* __restrict__ det, const int* __restrict__ n_det, int det_stride,
               const float2* __restrict__ inl, int inl_stride, float min_distance,
-              float2* __restrict__ out, int* __restrict__ keep_idx, int* __restrict__ n_out,
-              int out_stride, const SvoSeqCall* __restrict__ call) {
+              float2* __restrict__ out, int* keep_idx, int* __restrict__ n_out,
+              int out_stride, SvoSeqCall* call, unsigned* ticket) {
+    __shared__ float2 s_q[DD_TILE];
     __shared__ int s_w[RP_THREADS / 32];
+    __shared__ bool s_last;
     const SvoSeqCall cd = call[blockIdx.x];
     const float2* d = det + (size_t)cd.seq * det_stride;
     const float2* q = inl + (size_t)cd.seq * inl_stride;
     const int nd = n_det ? n_det[cd.seq] : cd.n_pts;
     const int ni = cd.n_aux;
     const size_t ob = (size_t)cd.seq * out_stride;
-    int written = 0;
-    for (int i0 = 0; i0 < nd; i0 += RP_THREADS) {
+    const float thr = dist2_threshold(min_distance);
+    const int per = (nd + DD_BLOCKS - 1) / DD_BLOCKS;
+    const int i_beg = blockIdx.y * per, i_end = min(nd, i_beg + per);
+    for (int i0 = i_beg; i0 < i_end; i0 += RP_THREADS) {
         const int i = i0 + threadIdx.x;
-        bool keep = i < nd;
-        float2 p = make_float2(0.f, 0.f);
-        if (keep) {
-            p = d[i];
-            for (int j = 0; j < ni; ++j) {
-                float dx = __fsub_rn(p.x, q[j].x), dy = __fsub_rn(p.y, q[j].y);
-                float dist = __fsqrt_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)));
-                if (dist < min_distance) { keep = false; break; }
+        const float2 p = (i < i_end) ? d[i] : make_float2(0.f, 0.f);
+        bool near = false;
+        for (int j0 = 0; j0 < ni; j0 += DD_TILE) {
+            const int nj = min(DD_TILE, ni - j0);
+            __syncthreads();
+            for (int j = threadIdx.x; j < nj; j += RP_THREADS) s_q[j] = q[j0 + j];
+            __syncthreads();
+#pragma unroll 8
+            for (int j = 0; j < nj; ++j) {
+                const float2 t = s_q[j];
+                const float dx = __fsub_rn(p.x, t.x), dy = __fsub_rn(p.y, t.y);
+                near |= __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < thr;
             }
         }
+        if (i < i_end) keep_idx[ob + i] = near ? 0 : 1;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(ticket + cd.seq, 1u) == DD_BLOCKS - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    int written = 0;
+    for (int i0 = 0; i0 < nd; i0 += RP_THREADS) {
+        // flags of this chunk are read before any slot (<= i) of it is written: in place is safe
+        const int i = i0 + threadIdx.x;
+        const bool keep = i < nd && __ldcg(keep_idx + ob + i) != 0;
+        const float2 p = keep ? d[i] : make_float2(0.f, 0.f);
         int total;
         int slot = written + block_exclusive_scan_flag(keep, s_w, total);
         if (keep) {
@@ -249,7 +291,11 @@ dedupe_kernel(const float2* __restrict__ det, const int* __restrict__ n_det, int
         }
         written += total;
     }
-    if (threadIdx.x == 0) n_out[cd.seq] = written;
+    if (threadIdx.x == 0) {
+        n_out[cd.seq] = written;
+        call[blockIdx.x].n_pts = written;      // the stereo stage of the same call reads it
+        ticket[cd.seq] = 0;
+    }
 }
 
 }  // namespace
@@ -286,9 +332,9 @@ cudaError_t svo_launch_reproject(const float2* pts, const short* disp16, int pts
 cudaError_t svo_launch_dedupe(const float2* det, const int* n_det, int det_stride,
                               const float2* inl, int inl_stride, float min_distance, float2* out,
                               int* keep_idx, int* n_out, int out_stride,
-                              const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
-    dedupe_kernel<<<n_call, RP_THREADS, 0, st>>>(det, n_det, det_stride, inl, inl_stride,
-                                                 min_distance, out, keep_idx, n_out, out_stride,
-                                                 d_call);
+                              SvoSeqCall* d_call, unsigned* ticket, int n_call, cudaStream_t st) {
+    dedupe_kernel<<<dim3(n_call, DD_BLOCKS), RP_THREADS, 0, st>>>(
+        det, n_det, det_stride, inl, inl_stride, min_distance, out, keep_idx, n_out, out_stride,
+        d_call, ticket);
     return cudaGetLastError();
 }

@@ -125,7 +125,7 @@ cudaError_t svo_launch_reproject(const float2* pts, const short* disp16, int pts
 cudaError_t svo_launch_dedupe(const float2* det, const int* n_det, int det_stride,
                               const float2* inl, int inl_stride, float min_distance, float2* out,
                               int* keep_idx, int* n_out, int out_stride,
-                              const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+                              SvoSeqCall* d_call, unsigned* ticket, int n_call, cudaStream_t st);
 
 struct SvoLkParams {
     int max_iters;

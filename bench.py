@@ -305,7 +305,9 @@ def run_ours(args, rank, world, local_rank):
         try:
             with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as fh:
                 ncu_t = json.load(fh)
-            pick = {"corner_score_nms": ["corner_score_nms_kernel<2>"],
+            cs_name = next((k for k in ncu_t if k.startswith("corner_score_nms_kernel")),
+                           "corner_score_nms_kernel")
+            pick = {"corner_score_nms": [cs_name],
                     "pyr_down_u8": ["pyr_down_u8_kernel<8>", "pyr_down_u8_kernel<4>",
                                     "pyr_down_u8_kernel<2>"]}.get(hbm_dom, [])
             if pick and all(k in ncu_t for k in pick):
@@ -320,7 +322,9 @@ def run_ours(args, rank, world, local_rank):
                         "frac": kernels[hbm_dom]["frac_of_hbm"], "traffic": traffic,
                         "traffic_source": traffic_src,
                         "note": "corner_score_nms is issue-bound, not HBM-bound: OpenCV's sliding "
-                                "fp64 column sums force one thread per image column (DESIGN.md 4); "
+                                "fp64 column sums force one thread per image column and row "
+                                "segment (DESIGN.md 4; segments whose guessed start was wrong are "
+                                "re-walked by `corner_repair`, timed separately in `kernels`); "
                                 "HBM-bound kernels: ingest, pyr_down_u8 (see `kernels`)",
                         "peak_source": peak_src,
                         "algorithmic_bytes_per_launch": ALGO_BYTES[hbm_dom] * S,

@@ -15,13 +15,13 @@
 #include "../../include/svo_c.h"
 #include "svo_common.cuh"
 
-#define SVO_PROF_SLOTS 12
+#define SVO_PROF_SLOTS 13
 static const char* const kProfNames[SVO_PROF_SLOTS] = {
     "pyr_down_u8", "corner_score_nms", "ingest", "sort_candidates",
     "greedy_min_distance", "lk_track_fwd", "lk_track_bwd", "track_filter_compact",
-    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q"};
+    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q", "corner_repair"};
 enum { P_PYR, P_SCORE, P_INGEST, P_SORT, P_GREEDY, P_LKF, P_LKB, P_FILTER, P_PACK, P_DEDUPE,
-       P_STEREO, P_REPROJ };
+       P_STEREO, P_REPROJ, P_REPAIR };
 
 namespace {
 
@@ -95,9 +95,14 @@ struct svo_engine {
     unsigned int* d_eig_max = nullptr;
     unsigned long long* d_cand = nullptr;
     int* d_cand_count = nullptr;
-    unsigned long long* d_strips = nullptr;   // [n_seq][n_strips][strip_cap]
-    int* d_strip_count = nullptr;
-    int n_strips = 0, strip_cap = 0;
+    unsigned long long* d_strips = nullptr;   // [n_seq][n_strips][n_seg][strip_cap]
+    int* d_strip_count = nullptr;             // [n_seq][n_strips * n_seg]
+    int n_strips = 0, n_seg = 0, strip_cap = 0;
+    // corner_score_nms: per (strip, segment) maximum, wrong-start flag, true sums of a flagged start
+    unsigned int* d_sub_max = nullptr;
+    unsigned char* d_seg_flag = nullptr;
+    double* d_seg_state = nullptr;
+    unsigned int* d_cs_ticket = nullptr;
     float2* d_corners = nullptr;
     int* d_ncorners = nullptr;
     int* d_grid = nullptr;
@@ -482,17 +487,23 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid) {
         SVO_CUDA_OK(svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, e->st));
         e->launches += e->lay.n_levels - 1;
     }
+    const SvoCornerCall cc = {e->d_pyr, e->seq_stride, e->d_eig, e->eig_pitch, e->eig_stride,
+                              e->d_eig_max, e->p.quality_level, e->d_strips, e->n_strips,
+                              e->n_seg, e->strip_cap, e->d_strip_count, e->d_sub_max,
+                              e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, dc};
     {
         ProfScope ps(e, P_SCORE);
-        SVO_CUDA_OK(svo_launch_corner_score_nms(e->d_pyr, e->lay, e->seq_stride, e->d_eig,
-                                                e->eig_pitch, e->eig_stride, e->d_eig_max,
-                                                e->p.quality_level, e->d_strips, e->n_strips,
-                                                e->strip_cap, e->d_strip_count, dc, n, e->st));
+        SVO_CUDA_OK(svo_launch_corner_score_nms(cc, e->lay, n, e->st));
+    }
+    {
+        ProfScope ps(e, P_REPAIR);
+        SVO_CUDA_OK(svo_launch_corner_repair(cc, e->lay, n, e->st));
+        e->launches += 1;
     }
     {
         ProfScope ps(e, P_SORT);
         SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count,
-                                               e->d_strips, e->n_strips, e->strip_cap,
+                                               e->d_strips, e->n_strips * e->n_seg, e->strip_cap,
                                                e->d_strip_count, e->d_eig_max,
                                                e->p.quality_level, dc, n, e->st));
     }
@@ -825,9 +836,17 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_stage, 2 * e->stage_set));
     if (p.keep_eig_map) CCHK(dalloc(&e->d_eig, ns * e->eig_stride));
     e->n_strips = svo_corner_strips(p.width);
+    e->n_seg = svo_corner_segments(p.height);
     e->strip_cap = svo_corner_strip_cap(p.height);
-    CCHK(dalloc(&e->d_strips, ns * e->n_strips * (size_t)e->strip_cap));
-    CCHK(dalloc(&e->d_strip_count, ns * e->n_strips));
+    const size_t n_sub = ns * e->n_strips * e->n_seg;
+    CCHK(dalloc(&e->d_strips, n_sub * (size_t)e->strip_cap));
+    CCHK(dalloc(&e->d_strip_count, n_sub));
+    CCHK(dalloc(&e->d_sub_max, n_sub));
+    CCHK(dalloc(&e->d_seg_flag, n_sub));
+    CCHK(dalloc(&e->d_seg_state, n_sub * svo_corner_state_doubles()));
+    CCHK(dalloc(&e->d_cs_ticket, ns));
+    CCHK(cudaMemsetAsync(e->d_cs_ticket, 0, ns * sizeof(unsigned int), e->st));
+    CCHK(cudaMemsetAsync(e->d_seg_flag, 0, n_sub, e->st));
     CCHK(dalloc(&e->d_eig_max, ns));
     CCHK(dalloc(&e->d_cand, ns * mc));
     CCHK(dalloc(&e->d_cand_count, ns));
@@ -887,7 +906,7 @@ void svo_destroy(svo_engine* e) {
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->st_copy) cudaStreamSynchronize(e->st_copy);
     void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
-                     e->d_strips, e->d_strip_count, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
+                     e->d_strips, e->d_strip_count, e->d_sub_max, e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,

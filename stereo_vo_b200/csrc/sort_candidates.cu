@@ -51,13 +51,15 @@ sort_small_kernel(unsigned long long* __restrict__ cand, int max_cand,
     const float maxv = mk ? __uint_as_float(svo_key_float_bits(mk)) : 0.f;
     const float thr = (float)((double)maxv * quality);
     const int lane = threadIdx.x & 31;
-    for (int st = 0; st < n_strips; ++st) {
+    // one warp per candidate list (there are n_strips x n_seg short ones): the count -> list
+    // load chains of different lists overlap
+    for (int st = threadIdx.x >> 5; st < n_strips; st += SORT_THREADS / 32) {
         const int raw = strip_count[seq * n_strips + st];
         const int cnt = min(raw, strip_cap);
-        if (raw > strip_cap && threadIdx.x == 0) s_over = 1;
+        if (raw > strip_cap && lane == 0) s_over = 1;
         const unsigned long long* src = strips + ((size_t)seq * n_strips + st) * (size_t)strip_cap;
-        for (int i0 = 0; i0 < cnt; i0 += SORT_THREADS) {
-            const int i = i0 + threadIdx.x;
+        for (int i0 = 0; i0 < cnt; i0 += 32) {
+            const int i = i0 + lane;
             unsigned long long key = 0;
             bool keep = false;
             if (i < cnt) {

@@ -4,7 +4,7 @@
 //   pyr    u8   [n_seq][2 slots][levels 0..L]   left-image pyramids, pitched rows (pitch % 128 == 0)
 //   right  u8   [n_seq][H * pitch0]             right image of the current frame
 //   eig    f32  [n_seq][H * eig_pitch]          Shi-Tomasi min-eigenvalue map (debug tap only)
-//   strips u64  [n_seq][n_strips][strip_cap]    local maxima above the running threshold
+//   strips u64  [n_seq][n_strips][n_seg][cap]   local maxima above the running threshold
 //   cand   u64  [n_seq][max_candidates]         (ordered score bits << 32 | y*W+x), sorted
 // Kernels never see host pointers; launchers take raw device pointers + a stream.
 #pragma once
@@ -76,13 +76,22 @@ cudaError_t svo_launch_pyr_down_single(const uint8_t* src, int w, int h, int spi
 
 // fused Shi-Tomasi score + 3x3 NMS: per-strip candidate lists (corner_score.cu)
 int svo_corner_strips(int w);
-int svo_corner_strip_cap(int h);
-cudaError_t svo_launch_corner_score_nms(const uint8_t* pyr, const SvoPyrLayout& lay,
-                                        size_t seq_stride, float* eig, int eig_pitch,
-                                        size_t eig_stride, unsigned int* eig_max, double quality,
-                                        unsigned long long* strips, int n_strips, int strip_cap,
-                                        int* strip_count, const SvoSeqCall* d_call, int n_call,
-                                        cudaStream_t st);
+int svo_corner_segments(int h);
+int svo_corner_strip_cap(int h);          // per (strip, segment)
+size_t svo_corner_state_doubles();        // per (strip, segment)
+struct SvoCornerCall {
+    const uint8_t* pyr; size_t seq_stride;
+    float* eig; int eig_pitch; size_t eig_stride;      // debug tap, nullptr: eig map not written
+    unsigned int* eig_max; double quality;
+    unsigned long long* strips; int n_strips, n_seg, strip_cap;
+    int* strip_count; unsigned int* sub_max; unsigned char* seg_flag; double* seg_state;
+    unsigned int* ticket;
+    const SvoSeqCall* d_call;
+};
+cudaError_t svo_launch_corner_score_nms(const SvoCornerCall& c, const SvoPyrLayout& lay,
+                                        int n_call, cudaStream_t st);
+cudaError_t svo_launch_corner_repair(const SvoCornerCall& c, const SvoPyrLayout& lay, int n_call,
+                                     cudaStream_t st);
 cudaError_t svo_launch_filter_candidates(const unsigned long long* strips, int n_strips,
                                          int strip_cap, const int* strip_count,
                                          const unsigned int* eig_max, double quality,

@@ -123,3 +123,55 @@ def test_two_sequences_independent(engines, oracle):
         n = res["n_corners"][i]
         assert n == ref.shape[0]
         assert np.array_equal(res["corners"][i, :n], ref)
+
+
+_VARIANT_SCRIPT = r"""
+import sys
+import cv2
+import numpy as np
+sys.path.insert(0, {root!r})
+from oracle import cv2_frontend as O
+from stereo_vo_b200 import synth
+from stereo_vo_b200.capi import Engine
+from tests import util
+O.canonical_mode()
+for (w, h) in [(1241, 376), (640, 480), (333, 211)]:
+    e = Engine(w, h, n_seq=2, keep_eig_map=1)
+    for seed in (0, 3, 7):
+        if (w, h) == (1241, 376):
+            img = util.frames(seed, 1)[0][0]
+        else:
+            img = synth.stereo_frame(seed, 3, util.small_camera(w, h))[0]
+        got = e.good_features_to_track(img, seq=1)
+        ref = O.detect(img)
+        assert got.shape == ref.shape and np.array_equal(got, ref), (w, h, seed, "corners")
+        eig = e.debug_min_eigen_map(seq=1)
+        ref_eig = cv2.cornerMinEigenVal(img, 3, ksize=3)
+        assert np.array_equal(eig.view(np.uint32), ref_eig.view(np.uint32)), (w, h, seed, "eig")
+    e.close()
+print("VARIANT_OK")
+"""
+
+
+@pytest.mark.parametrize("env", [
+    {"SVO_CORNER_FORCE_REPAIR": "1"},                                  # every segment re-walked
+    {"SVO_CORNER_SEGMENTS": "1"},                                      # the sequential walk
+    {"SVO_CORNER_SEGMENTS": "5", "SVO_CORNER_FORCE_REPAIR": "1"},
+    {"SVO_CORNER_SEGMENTS": "16"},
+    {"SVO_CORNER_CPT": "4", "SVO_CORNER_FORCE_REPAIR": "1"},
+    {"SVO_CORNER_CPT": "1"},
+    {"SVO_CORNER_MIN_BLOCKS": "20"},
+], ids=lambda d: ",".join(f"{k[11:]}={v}" for k, v in d.items()))
+def test_corner_score_variants(svo_lib, env):
+    """corner_score_nms splits every strip into row segments that start from GUESSED sliding sums
+    and repairs the ones whose guess was wrong; the variants (read from the environment once per
+    process) force the repair pass, change the segmentation and the columns per thread - all
+    must give the same bits as cv2."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    full_env = dict(os.environ, **env)
+    r = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT.format(root=root)], env=full_env,
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "VARIANT_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

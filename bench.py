@@ -245,6 +245,9 @@ def run_ours(args, rank, world, local_rank):
         return out
 
     K, Wm = args.steps, args.warmup
+    if args.groups <= 0:
+        cores_per_rank = max(1, len(os.sched_getaffinity(0)) // max(world, 1))
+        args.groups = 4 if cores_per_rank >= 5 else max(1, min(4, cores_per_rank - 1))
     dev = run_leg(True, K, Wm, profile=False, groups=args.groups)
     e2e = dev if args.skip_e2e else run_leg(False, K, Wm, profile=False, groups=args.groups)
     # per-kernel durations: a separate pass with ONE engine group, so every kernel is timed
@@ -492,8 +495,10 @@ def main():
     ap.add_argument("--ref-frames", type=int, default=16)
     ap.add_argument("--profile-steps", type=int, default=60,
                     help="steps of the separate single-group pass that times every kernel alone")
-    ap.add_argument("--groups", type=int, default=4,
-                    help="engine groups (CUDA streams + host workers) the sequences of a GPU are split into")
+    ap.add_argument("--groups", type=int, default=0,
+                    help="engine groups (CUDA streams + host workers) the sequences of a GPU are "
+                         "split into; 0 = 4, or fewer when the ranks of this node have less than "
+                         "5 host cores each (every worker waits for its stream on a core)")
     ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",
                     help="one synchronous svo_batch_step per step instead of two steps in flight")
     ap.add_argument("--no-prefetch", dest="prefetch", action="store_false",

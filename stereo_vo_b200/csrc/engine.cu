@@ -382,6 +382,46 @@ cudaError_t stage_pair(svo_engine* e, cudaStream_t st, int set, int seq, const u
     return cudaSuccess;
 }
 
+// H2D of the stereo pairs of n sequences. Copies of single images pay a fixed cost each (a
+// 466 KB KITTI image moves at 35 GB/s, a large copy at 55 GB/s), so left images that sit at a
+// constant distance in host memory (per-camera ring buffers carved from one slab) and go to
+// consecutive staging slots travel as ONE strided copy; everything else goes pair by pair.
+cudaError_t stage_batch(svo_engine* e, cudaStream_t st, int set, int n, const int32_t* seqs,
+                        const uint8_t* const* left, const uint8_t* const* right, int pitch) {
+    const int W = e->p.width, H = e->p.height;
+    const ptrdiff_t img = (ptrdiff_t)W * H;
+    int i = 0;
+    while (i < n) {
+        int j = i + 1;
+        if (pitch == W && j < n) {
+            const ptrdiff_t stride = left[j] - left[i];
+            if (stride >= img && stride < ((ptrdiff_t)1 << 30) && seqs[j] == seqs[i] + 1) {
+                while (j + 1 < n && left[j + 1] - left[j] == stride && seqs[j + 1] == seqs[j] + 1) ++j;
+                ++j;                                   // run [i, j)
+            }
+        }
+        if (j - i >= 3) {
+            uint8_t* base = e->d_stage + (size_t)set * e->stage_set + (size_t)seqs[i] * 2 * e->stage_img;
+            cudaError_t ce = cudaMemcpy2DAsync(base, 2 * e->stage_img, left[i], (size_t)(left[i + 1] - left[i]),
+                                               (size_t)img, (size_t)(j - i), cudaMemcpyHostToDevice, st);
+            if (ce != cudaSuccess) return ce;
+            for (int k = i; k < j; ++k) {
+                const uint8_t* r = right ? right[k] : nullptr;
+                if (!r) continue;
+                ce = cudaMemcpyAsync(base + (size_t)(k - i) * 2 * e->stage_img + e->stage_img, r, (size_t)img,
+                                     cudaMemcpyHostToDevice, st);
+                if (ce != cudaSuccess) return ce;
+            }
+            i = j;
+            continue;
+        }
+        cudaError_t ce = stage_pair(e, st, set, seqs[i], left[i], right ? right[i] : nullptr, pitch);
+        if (ce != cudaSuccess) return ce;
+        ++i;
+    }
+    return cudaSuccess;
+}
+
 // stage one image of the current stereo pair and record its device source in the descriptor
 cudaError_t upload_image(svo_engine* e, SvoSeqCall& c, int which, const uint8_t* img, int pitch,
                          bool device_src) {
@@ -470,10 +510,29 @@ struct PullList {
     }
 };
 
+// Per-call descriptors travel INSIDE a kernel launch (by-value parameter, 32 descriptors =
+// 3.8 KB at a time) and are written to the device ring by that kernel: no DMA that could queue
+// behind a bulk prefetch, and no read of host memory by an SM (slow while the link is busy).
+struct CallChunk { SvoSeqCall c[32]; };
+__global__ void __launch_bounds__(128)
+store_calls_kernel(const __grid_constant__ CallChunk chunk, SvoSeqCall* __restrict__ dst, int n) {
+    constexpr int WORDS = sizeof(SvoSeqCall) / 8;
+    const unsigned long long* src = reinterpret_cast<const unsigned long long*>(chunk.c);
+    unsigned long long* d = reinterpret_cast<unsigned long long*>(dst);
+    for (int i = threadIdx.x; i < n * WORDS; i += blockDim.x) d[i] = src[i];
+}
+
 cudaError_t push_calls(svo_engine* e, int n) {
-    PullList pl(e);
-    pl.add(dev_call_slot(e), e->h_call + (size_t)e->ring * e->n_seq, (size_t)n * sizeof(SvoSeqCall));
-    return pl.launch();
+    const SvoSeqCall* hc = e->h_call + (size_t)e->ring * e->n_seq;
+    SvoSeqCall* dc = dev_call_slot(e);
+    for (int i0 = 0; i0 < n; i0 += 32) {
+        CallChunk ch;
+        const int m = std::min(32, n - i0);
+        memcpy(ch.c, hc + i0, (size_t)m * sizeof(SvoSeqCall));
+        store_calls_kernel<<<1, 128, 0, e->st>>>(ch, dc + i0, m);
+        e->launches += 1;
+    }
+    return cudaGetLastError();
 }
 
 // pyramid + detection for the listed sequences (current frames already uploaded)
@@ -635,6 +694,7 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
             // the staging set no pending prefetch occupies
             e->cur_set = e->pf_count ? 1 - e->pf[e->pf_head].set : 0;
         }
+        if (!device_src) ECUDA(e, stage_batch(e, e->st, e->cur_set, n, seqs, left, right, pitch));
         for (int i = 0; i < n; ++i) {
             if (device_src) {
                 ECUDA(e, upload_left(e, hc[i], left[i], pitch, true));
@@ -642,7 +702,6 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
                 continue;
             }
             const uint8_t* r = right ? right[i] : nullptr;
-            ECUDA(e, stage_pair(e, e->st, e->cur_set, seqs[i], left[i], r, pitch));
             uint8_t* base = e->d_stage + (size_t)e->cur_set * e->stage_set +
                             (size_t)seqs[i] * 2 * e->stage_img;
             hc[i].src_left = base;
@@ -998,8 +1057,8 @@ int svo_prefetch(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* c
     for (int i = 0; i < n; ++i) {
         if (seqs[i] < 0 || seqs[i] >= e->n_seq) return fail(e, SVO_ERR_INVALID, "svo_prefetch: sequence index out of range");
         if (right) p.right[i] = right[i];
-        ECUDA(e, stage_pair(e, e->st_copy, set, seqs[i], p.left[i], p.right[i], pitch));
     }
+    ECUDA(e, stage_batch(e, e->st_copy, set, n, seqs, p.left.data(), p.right.data(), pitch));
     ECUDA(e, cudaEventRecord(p.done, e->st_copy));
     p.valid = true;
     p.skipped = 0;

@@ -91,6 +91,12 @@ struct svo_engine {
     int pf_head = 0, pf_count = 0;    // oldest pending entry, number pending
     int cur_set = 0;                  // staging set of the uploads of the current call
     cudaStream_t st_copy = nullptr;
+    // svo_step runs detection (corner score -> repair -> sort -> greedy) on a second stream next
+    // to pyramid + LK tracking: the two halves of a frame only meet at the tracker gate
+    // (image_processor.cpp:23-25) and in the result block
+    cudaStream_t st_det = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool split_streams = true;        // SVO_SPLIT_STREAMS=0: one stream
     float* d_eig = nullptr;
     unsigned int* d_eig_max = nullptr;
     unsigned long long* d_cand = nullptr;
@@ -186,7 +192,9 @@ int round_up(int v, int m) { return (v + m - 1) / m * m; }
 struct ProfScope {
     svo_engine* e;
     int idx = -1;
-    ProfScope(svo_engine* eng, int slot) : e(eng) {
+    cudaStream_t st;
+    ProfScope(svo_engine* eng, int slot, cudaStream_t stream = nullptr)
+        : e(eng), st(stream ? stream : eng->st) {
         if (!e->profiling) return;
         if ((size_t)(e->prof_used + 1) * 2 > e->prof_ev.size()) {
             cudaEvent_t a, b;
@@ -197,10 +205,10 @@ struct ProfScope {
         }
         idx = e->prof_used++;
         e->prof_slot[idx] = slot;
-        cudaEventRecord(e->prof_ev[2 * idx], e->st);
+        cudaEventRecord(e->prof_ev[2 * idx], st);
     }
     ~ProfScope() {
-        if (idx >= 0) cudaEventRecord(e->prof_ev[2 * idx + 1], e->st);
+        if (idx >= 0) cudaEventRecord(e->prof_ev[2 * idx + 1], st);
     }
 };
 
@@ -253,7 +261,7 @@ ingest_kernel(uint8_t* pyr, SvoPyrLayout lay, size_t seq_stride, uint8_t* right,
         const int nwords = (int)((mis + valid + 3) >> 2);      // aligned words holding valid bytes
         unsigned int w[5];
 #pragma unroll
-        for (int k = 0; k < 5; ++k) w[k] = (k < nwords) ? __ldg(pa + k) : 0u;
+        for (int k = 0; k < 5; ++k) w[k] = (k < nwords) ? __ldcs(pa + k) : 0u;   // read once: evict first
         const unsigned sh = mis * 8;
         uint4 o;
         o.x = __funnelshift_r(w[0], w[1], sh);
@@ -536,14 +544,15 @@ cudaError_t push_calls(svo_engine* e, int n) {
 }
 
 // pyramid + detection for the listed sequences (current frames already uploaded)
-cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid) {
+cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t st = nullptr) {
+    if (!st) st = e->st;
     const SvoSeqCall* dc = dev_call_slot(e);
-    reset_kernel<<<(n + 127) / 128, 128, 0, e->st>>>(e->d_eig_max, e->d_cand_count, e->d_ncorners,
+    reset_kernel<<<(n + 127) / 128, 128, 0, st>>>(e->d_eig_max, e->d_cand_count, e->d_ncorners,
                                                       dc, n);
     e->launches += 1;
     if (with_pyramid) {
-        ProfScope ps(e, P_PYR);
-        SVO_CUDA_OK(svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, e->st));
+        ProfScope ps(e, P_PYR, st);
+        SVO_CUDA_OK(svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, st));
         e->launches += e->lay.n_levels - 1;
     }
     const SvoCornerCall cc = {e->d_pyr, e->seq_stride, e->d_eig, e->eig_pitch, e->eig_stride,
@@ -551,33 +560,34 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid) {
                               e->n_seg, e->strip_cap, e->d_strip_count, e->d_sub_max,
                               e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, dc};
     {
-        ProfScope ps(e, P_SCORE);
-        SVO_CUDA_OK(svo_launch_corner_score_nms(cc, e->lay, n, e->st));
+        ProfScope ps(e, P_SCORE, st);
+        SVO_CUDA_OK(svo_launch_corner_score_nms(cc, e->lay, n, st));
     }
     {
-        ProfScope ps(e, P_REPAIR);
-        SVO_CUDA_OK(svo_launch_corner_repair(cc, e->lay, n, e->st));
+        ProfScope ps(e, P_REPAIR, st);
+        SVO_CUDA_OK(svo_launch_corner_repair(cc, e->lay, n, st));
         e->launches += 1;
     }
     {
-        ProfScope ps(e, P_SORT);
+        ProfScope ps(e, P_SORT, st);
         SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count,
                                                e->d_strips, e->n_strips * e->n_seg, e->strip_cap,
                                                e->d_strip_count, e->d_eig_max,
-                                               e->p.quality_level, dc, n, e->st));
+                                               e->p.quality_level, dc, n, st));
     }
     {
-        ProfScope ps(e, P_GREEDY);
+        ProfScope ps(e, P_GREEDY, st);
         SVO_CUDA_OK(svo_launch_greedy_select(e->d_cand, e->max_cand, e->d_cand_count, e->p.width,
                                              e->p.height, e->p.min_distance, e->p.max_corners,
                                              e->d_corners, e->d_ncorners, e->d_grid,
-                                             e->grid_stride, dc, n, e->st));
+                                             e->grid_stride, dc, n, st));
     }
     e->launches += 2 + svo_sort_launch_count(e->max_cand);
     return cudaSuccess;
 }
 
-cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_back, bool gated) {
+cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_back, bool gated,
+                         cudaEvent_t detect_done = nullptr) {
     const SvoSeqCall* dc = dev_call_slot(e);
     SvoLkParams lp;
     lp.max_iters = e->p.lk_max_iters;
@@ -586,23 +596,27 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
     lp.warps_per_point = e->p.lk_warps_per_point;
     lp.grid_pts = max_feat_in_call;
     const int* gate = gated ? e->d_ncorners : nullptr;
+    // detection still running on the other stream: the LK kernels cannot read the corner count
+    // yet. They track unconditionally (scratch outputs only); the gate is applied by the filter.
+    const int* gate_lk = detect_done ? nullptr : gate;
     const int mf = e->p.max_features;
     if (max_feat_in_call > 0) {
         {
             ProfScope ps(e, P_LKF);
             SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_feat,
                                             (size_t)2 * mf, 1, e->d_tracked, e->d_status1, mf, 0,
-                                            lp, mf, gate, 4, nullptr, dc, n, e->st));
+                                            lp, mf, gate_lk, 4, nullptr, dc, n, e->st));
         }
         e->launches += 1;
         if (flow_back) {
             ProfScope ps(e, P_LKB);
             SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_tracked,
                                             (size_t)mf, 0, e->d_reverse, e->d_status2, mf, 1, lp,
-                                            mf, gate, 4, e->d_status1, dc, n, e->st));
+                                            mf, gate_lk, 4, e->d_status1, dc, n, e->st));
             e->launches += 1;
         }
     }
+    if (detect_done) SVO_CUDA_OK(cudaStreamWaitEvent(e->st, detect_done, 0));
     ProfScope psf(e, P_FILTER);
     SVO_CUDA_OK(svo_launch_track_filter(e->d_feat, e->d_ids, e->d_initial, (size_t)2 * mf,
                                         e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, mf,
@@ -714,8 +728,18 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
     }
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     ECUDA(e, push_and_ingest(e, n));
-    ECUDA(e, launch_detect(e, n, true));
-    ECUDA(e, launch_track(e, n, max_feat, 1, true));
+    if (e->split_streams && !e->profiling) {
+        ECUDA(e, cudaEventRecord(e->ev_fork, e->st));
+        ECUDA(e, cudaStreamWaitEvent(e->st_det, e->ev_fork, 0));
+        ECUDA(e, launch_detect(e, n, false, e->st_det));
+        ECUDA(e, cudaEventRecord(e->ev_join, e->st_det));
+        ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), n, e->st));
+        e->launches += e->lay.n_levels - 1;
+        ECUDA(e, launch_track(e, n, max_feat, 1, true, e->ev_join));
+    } else {
+        ECUDA(e, launch_detect(e, n, true));
+        ECUDA(e, launch_track(e, n, max_feat, 1, true));
+    }
     {
         ProfScope ps(e, P_PACK);
         pack_step_kernel<<<n, 128, 0, e->st>>>(e->d_out, e->step_block, e->d_corners,
@@ -880,6 +904,10 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
 
     CCHK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     CCHK(cudaStreamCreateWithFlags(&e->st_copy, cudaStreamNonBlocking));
+    CCHK(cudaStreamCreateWithFlags(&e->st_det, cudaStreamNonBlocking));
+    CCHK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
+    CCHK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+    if (const char* v = getenv("SVO_SPLIT_STREAMS")) e->split_streams = atoi(v) != 0;
     for (auto& pfe : e->pf) CCHK(cudaEventCreateWithFlags(&pfe.done, cudaEventDisableTiming));
     for (int i = 0; i < 4; ++i) CCHK(cudaEventCreate(&e->ev[i]));
     for (int i = 0; i < 2; ++i) CCHK(cudaEventCreate(&e->timer_ev[i]));
@@ -964,6 +992,7 @@ void svo_destroy(svo_engine* e) {
     cudaSetDevice(e->device);
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->st_copy) cudaStreamSynchronize(e->st_copy);
+    if (e->st_det) cudaStreamSynchronize(e->st_det);
     void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
                      e->d_strips, e->d_strip_count, e->d_sub_max, e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
@@ -982,6 +1011,9 @@ void svo_destroy(svo_engine* e) {
     for (cudaEvent_t ev : e->prof_ev) cudaEventDestroy(ev);
     for (auto& pfe : e->pf) if (pfe.done) cudaEventDestroy(pfe.done);
     if (e->st_copy) cudaStreamDestroy(e->st_copy);
+    if (e->st_det) cudaStreamDestroy(e->st_det);
+    if (e->ev_fork) cudaEventDestroy(e->ev_fork);
+    if (e->ev_join) cudaEventDestroy(e->ev_join);
     if (e->st) cudaStreamDestroy(e->st);
     delete e;
 }

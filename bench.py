@@ -127,6 +127,34 @@ def frame_index(step: int, slot: int, n_tex: int, n_frames: int):
     return tex, t
 
 
+def bind_near_gpu(local_rank: int):
+    """Keep this rank (and the pinned host frames it first touches) on the host cores / NUMA node
+    its GPU hangs off: with 8 ranks on a two-socket box the H2D stream of every rank otherwise
+    crosses the socket link half of the time. Best effort: returns what it did, or None."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = torch.cuda.get_device_properties(local_rank).pci_domain_id
+        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/local_cpulist"
+        with open(path) as fh:
+            txt = fh.read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus or cpus == os.sched_getaffinity(0):
+            return None
+        os.sched_setaffinity(0, cpus)
+        return f"cpus {txt}"
+    except Exception:
+        return None
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     from stereo_vo_b200 import capi, frontend, synth
@@ -138,6 +166,8 @@ def run_ours(args, rank, world, local_rank):
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: the front end has no CPU path")
     torch.cuda.set_device(local_rank)
+    total_cores = len(os.sched_getaffinity(0))
+    numa_bind = bind_near_gpu(local_rank) if world > 1 and not args.no_bind else None
     dist = None
     if world > 1:
         # NCCL_DEBUG=VERSION makes NCCL print its version banner on stdout, next to the one JSON
@@ -246,8 +276,8 @@ def run_ours(args, rank, world, local_rank):
 
     K, Wm = args.steps, args.warmup
     if args.groups <= 0:
-        cores_per_rank = max(1, len(os.sched_getaffinity(0)) // max(world, 1))
-        args.groups = 4 if cores_per_rank >= 5 else max(1, min(4, cores_per_rank - 1))
+        cores_per_rank = max(1, total_cores // max(world, 1))
+        args.groups = min(4, cores_per_rank)
     dev = run_leg(True, K, Wm, profile=False, groups=args.groups)
     e2e = dev if args.skip_e2e else run_leg(False, K, Wm, profile=False, groups=args.groups)
     # per-kernel durations: a separate pass with ONE engine group, so every kernel is timed
@@ -347,6 +377,7 @@ def run_ours(args, rank, world, local_rank):
                        "seqs_per_gpu": S, "frames_per_step": S * world,
                        "parallelism": f"{world} GPU(s) x {S} sequences in {args.groups} engine groups "
                                       "(one CUDA stream + host worker each), no collective",
+                       "host_cores": total_cores, "rank0_cpu_binding": numa_bind,
                        "host": "C++ svo::BatchFrontEnd (libsvo_host.so) via "
                                + ("svo_batch_submit/wait, 2 steps in flight" if args.pipeline
                                   else "svo_batch_step")
@@ -498,7 +529,9 @@ def main():
     ap.add_argument("--groups", type=int, default=0,
                     help="engine groups (CUDA streams + host workers) the sequences of a GPU are "
                          "split into; 0 = 4, or fewer when the ranks of this node have less than "
-                         "5 host cores each (every worker waits for its stream on a core)")
+                         "4 host cores each (every worker waits for its stream on a core)")
+    ap.add_argument("--no-bind", action="store_true",
+                    help="multi-GPU runs: do not pin the rank to the host cores next to its GPU")
     ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",
                     help="one synchronous svo_batch_step per step instead of two steps in flight")
     ap.add_argument("--no-prefetch", dest="prefetch", action="store_false",

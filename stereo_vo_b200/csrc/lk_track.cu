@@ -21,6 +21,10 @@
 //   * a 28x28 region of J is staged per level (aligned words when interior) and re-staged only
 //     when the window leaves it, so an iteration is shared-memory + integer work only; all
 //     threads carry the scalar Gauss-Newton state redundantly: uniform control flow.
+//   * shared memory is the busiest unit (ncu: 70 % of its wavefront rate, more than half of
+//     them bank-conflict replays with byte loads and 32-byte rows), so staged rows are 36 bytes
+//     apart, a thread fetches its 8 J bytes of two rows as 6 aligned words (instead of 16 byte
+//     loads) and blends two taps per dp2a: -14 % kernel time, same integers.
 // Issue/shared-memory bound (<= 400 points x 4 levels x <= 30 iterations), not HBM-bound.
 #include "svo_common.cuh"
 
@@ -30,9 +34,10 @@ constexpr int WIN = SVO_LK_WIN;            // 21
 constexpr int NT = 64;                     // threads per key-point
 constexpr int RUN = 7;                     // window pixels per thread
 constexpr int IP = WIN + 3;                // raw I patch edge (24)
-constexpr int SP = 32;                     // byte pitch of the staged I / J rows
+constexpr int SP = 36;                     // byte pitch of the staged I / J rows (9 words:
+                                           // rows 4 apart no longer share banks)
 constexpr int BG = WIN + 2;                // B grid edge (23)
-constexpr int BP = 25;                     // int pitch of the B grid
+constexpr int BP = 26;                     // int pitch of the B grid
 constexpr int DG = WIN + 1;                // derivative grid edge, border path (22)
 constexpr int JM = 3;                      // margin of the staged J region
 constexpr int JR = WIN + 1 + 2 * JM;       // staged J region edge (28)
@@ -43,6 +48,29 @@ __device__ __forceinline__ long long warp_sum_exact(int v) {
     int lo = __reduce_add_sync(FULL, v & 0xffff);
     int hi = __reduce_add_sync(FULL, v >> 16);
     return ((long long)hi << 16) + (long long)lo;
+}
+
+// c + w.lo16 * p.byte0 + w.hi16 * p.byte1 (lo) / ... byte2, byte3 (hi): signed 16-bit weights
+// (w11 can be -1 after rounding), unsigned pixels
+__device__ __forceinline__ int dp2a_lo(int w, unsigned p, int c) {
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(p), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi(int w, unsigned p, int c) {
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(p), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int pack16(int lo, int hi) { return (lo & 0xffff) | (hi << 16); }
+
+// bytes [k, k+1] of the 8-byte run (a0 | a1 << 32) as the low two bytes of a word
+template <int K>
+__device__ __forceinline__ int tap2(int w, unsigned a0, unsigned a1, int c) {
+    if (K % 4 == 0) return dp2a_lo(w, K < 4 ? a0 : a1, c);
+    if (K % 4 == 2) return dp2a_hi(w, K < 4 ? a0 : a1, c);
+    if (K == 3) return dp2a_lo(w, __funnelshift_r(a0, a1, 24), c);
+    return dp2a_lo(w, (K < 4 ? a0 : a1) >> 8, c);          // K % 4 == 1; K == 7 never used
 }
 
 __device__ __forceinline__ int clamp_reflect(int i, int n) {
@@ -232,7 +260,6 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         const int offI = (offs >> (4 * l)) & 3;      // staged before the loop
         const unsigned char* s_Ib = reinterpret_cast<const unsigned char*>(s_Iall[l]);
         unsigned* s_Jw = s_Jall[l];
-        const unsigned char* s_Jb = reinterpret_cast<const unsigned char*>(s_Jw);
         __syncthreads();                     // previous level's readers are done with s_B
 
         int ival[RUN], ixv[RUN], iyv[RUN];
@@ -240,19 +267,39 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         const bool grid_inside = ipx >= 0 && ipy >= 0 && ipx + WIN < w && ipy + WIN < h;
         if (grid_inside) {
             if (tid < 2 * BG) {              // B grid: thread = (row, half row)
+                // 13 bytes of two staged rows as aligned words (4 per row), blended two taps
+                // at a time by dp2a: exact integers, a quarter of the shared-memory requests
                 const int r = tid >> 1, c0 = (tid & 1) * 12, n = (tid & 1) ? 11 : 12;
-                const unsigned char* p0 = s_Ib + r * SP + offI + c0;
-                const unsigned char* p1 = p0 + SP;
-                int a = p0[0], b = p1[0];
+                const int bo = r * SP + offI + c0;
+                const unsigned* q0 = reinterpret_cast<const unsigned*>(s_Ib) + (bo >> 2);
+                const unsigned* q1 = q0 + SP / 4;
+                const unsigned sh = (bo & 3) * 8;
+                // rows are SP = 36 bytes apart and 24 + 3 bytes are staged: words 0..3 of the
+                // second half stay inside the row's 9 words (c0 = 12: word index <= 3 + 4)
+                const unsigned u0 = q0[0], u1 = q0[1], u2 = q0[2], u3 = q0[3];
+                const unsigned v0 = q1[0], v1 = q1[1], v2 = q1[2], v3 = q1[3];
+                const unsigned a0 = __funnelshift_r(u0, u1, sh), a1 = __funnelshift_r(u1, u2, sh),
+                               a2 = __funnelshift_r(u2, u3, sh), a3 = u3 >> sh;
+                const unsigned b0 = __funnelshift_r(v0, v1, sh), b1 = __funnelshift_r(v1, v2, sh),
+                               b2 = __funnelshift_r(v2, v3, sh), b3 = v3 >> sh;
+                const int wt = pack16(w00, w01), wb = pack16(w10, w11);
                 int* o = s_B + r * BP + c0;
+                int ov[12];
+                ov[0] = tap2<0>(wb, b0, b1, tap2<0>(wt, a0, a1, 0));
+                ov[1] = tap2<1>(wb, b0, b1, tap2<1>(wt, a0, a1, 0));
+                ov[2] = tap2<2>(wb, b0, b1, tap2<2>(wt, a0, a1, 0));
+                ov[3] = tap2<3>(wb, b0, b1, tap2<3>(wt, a0, a1, 0));
+                ov[4] = tap2<0>(wb, b1, b2, tap2<0>(wt, a1, a2, 0));
+                ov[5] = tap2<1>(wb, b1, b2, tap2<1>(wt, a1, a2, 0));
+                ov[6] = tap2<2>(wb, b1, b2, tap2<2>(wt, a1, a2, 0));
+                ov[7] = tap2<3>(wb, b1, b2, tap2<3>(wt, a1, a2, 0));
+                ov[8] = tap2<0>(wb, b2, b3, tap2<0>(wt, a2, a3, 0));
+                ov[9] = tap2<1>(wb, b2, b3, tap2<1>(wt, a2, a3, 0));
+                ov[10] = tap2<2>(wb, b2, b3, tap2<2>(wt, a2, a3, 0));
+                ov[11] = tap2<3>(wb, b2, b3, tap2<3>(wt, a2, a3, 0));
 #pragma unroll
-                for (int k = 0; k < 12; ++k) {
-                    if (k < n) {
-                        int a1 = p0[k + 1], b1 = p1[k + 1];
-                        o[k] = a * w00 + a1 * w01 + b * w10 + b1 * w11;
-                        a = a1; b = b1;
-                    }
-                }
+                for (int k = 0; k < 12; ++k)
+                    if (k < n) o[k] = ov[k];
             }
             __syncthreads();
             const int* bp = s_B + wy * BP + wx0;
@@ -357,17 +404,30 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
             }
             int sb1 = 0, sb2 = 0;
             {
-                const unsigned char* j0 = s_Jb + (wy + oy) * SP + offJ + wx0 + ox;
-                const unsigned char* j1 = j0 + SP;
-                int a = j0[0], b = j1[0];
+                // the thread's 8 bytes of two J rows as aligned words + funnel shifts; a pixel's
+                // four taps are two dp2a (exact integers): 6 word loads instead of 16 byte loads
+                const int bo = (wy + oy) * SP + offJ + wx0 + ox;
+                const unsigned* q0 = s_Jw + (bo >> 2);
+                const unsigned* q1 = q0 + SP / 4;
+                const unsigned sh = (bo & 3) * 8;
+                const unsigned u0 = q0[0], u1 = q0[1], u2 = q0[2];
+                const unsigned v0 = q1[0], v1 = q1[1], v2 = q1[2];
+                const unsigned a0 = __funnelshift_r(u0, u1, sh), a1 = __funnelshift_r(u1, u2, sh);
+                const unsigned b0 = __funnelshift_r(v0, v1, sh), b1 = __funnelshift_r(v1, v2, sh);
+                const int wt = pack16(w00, w01), wb = pack16(w10, w11);
+                int jv[RUN];
+                jv[0] = tap2<0>(wb, b0, b1, tap2<0>(wt, a0, a1, 256));
+                jv[1] = tap2<1>(wb, b0, b1, tap2<1>(wt, a0, a1, 256));
+                jv[2] = tap2<2>(wb, b0, b1, tap2<2>(wt, a0, a1, 256));
+                jv[3] = tap2<3>(wb, b0, b1, tap2<3>(wt, a0, a1, 256));
+                jv[4] = tap2<4>(wb, b0, b1, tap2<4>(wt, a0, a1, 256));
+                jv[5] = tap2<5>(wb, b0, b1, tap2<5>(wt, a0, a1, 256));
+                jv[6] = tap2<6>(wb, b0, b1, tap2<6>(wt, a0, a1, 256));
 #pragma unroll
                 for (int t = 0; t < RUN; ++t) {
-                    int a1 = j0[t + 1], b1 = j1[t + 1];
-                    int jv = (a * w00 + a1 * w01 + b * w10 + b1 * w11 + 256) >> 9;
-                    int diff = jv - ival[t];
+                    const int diff = (jv[t] >> 9) - ival[t];
                     sb1 += diff * ixv[t];
                     sb2 += diff * iyv[t];
-                    a = a1; b = b1;
                 }
             }
             long long ib1 = warp_sum_exact(sb1), ib2 = warp_sum_exact(sb2);

@@ -131,7 +131,7 @@ class BatchFrontEnd {
         std::vector<svo_track_stats> stats;
         std::vector<svo_float2> corners, tracked, inl, new_feats, valid_2d, feats;
         std::vector<svo_float3> pts_3d;
-        std::vector<uint64_t> tracked_ids, ids;
+        std::vector<uint64_t> tracked_ids, ids, first_id;
         std::vector<int32_t> valid_idx;
         std::vector<int16_t> disp16;
         std::vector<float> poses;

@@ -221,6 +221,19 @@ SVO_API int svo_keyframe(svo_engine* e, int32_t n, const int32_t* seqs, const sv
                  float baseline, svo_float2* new_feats, int32_t* n_new, svo_float2* valid_2d,
                  svo_float3* pts_3d, int32_t* valid_idx, int16_t* disp16, int32_t* n_valid);
 
+/* svo_keyframe + svo_tracker_set in one call for drivers without a pose solver in the loop
+ * (every feature that survived the last svo_step is an inlier): the inlier list is the
+ * tracker's own device-resident feature set, and FeatureTracker::init(tracked + new features,
+ * ids) (src/image_processor.cpp:144-162, ids as src/bundle_adjuster.cpp:98-116 assigns them)
+ * runs on the device: the tracked features keep their ids, the stereo-valid new ones get
+ * first_new_id[i], first_new_id[i] + 1, ... (clipped to max_features). Nothing but the
+ * per-call descriptors travels to the GPU. Outputs as svo_keyframe. */
+SVO_API int svo_keyframe_tracked(svo_engine* e, int32_t n, const int32_t* seqs, const float* poses,
+                         const uint64_t* first_new_id, float focal, float cx, float cy,
+                         float baseline, svo_float2* new_feats, int32_t* n_new,
+                         svo_float2* valid_2d, svo_float3* pts_3d, int32_t* valid_idx,
+                         int16_t* disp16, int32_t* n_valid);
+
 /* FeatureTracker::init against the CURRENT frame of each listed sequence
  * (image_processor.cpp:51-52,148-162): feats/ids [n][max_features], counts[i] entries. */
 SVO_API int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,

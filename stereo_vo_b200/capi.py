@@ -47,7 +47,7 @@ EXPORTS = [
     "svo_good_features_to_track", "svo_triangulate_stereo", "svo_tracker_init",
     "svo_tracker_track", "svo_tracker_get", "svo_dedupe", "svo_tracker_debug",
     "svo_debug_min_eigen_map", "svo_debug_pyramid_level", "svo_debug_candidates",
-    "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_tracker_set",
+    "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_keyframe_tracked", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
     "svo_timer_begin", "svo_timer_end",
@@ -103,6 +103,8 @@ def load_library(path: Optional[str] = None):
     lib.svo_device_can_read.argtypes = [vp]
     lib.svo_keyframe.argtypes = [vp, i32, vp, vp, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp, vp,
                                  vp, vp]
+    lib.svo_keyframe_tracked.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp,
+                                         vp, vp, vp]
     lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
     lib.svo_device_free.argtypes = [vp, vp]
@@ -399,6 +401,29 @@ class Engine:
                                           _ptr(poses), float(focal), float(cx), float(cy),
                                           float(baseline), _ptr(new), _ptr(nnew), _ptr(v2),
                                           _ptr(p3), _ptr(vi), _ptr(d16), _ptr(nv)), "svo_keyframe")
+        return dict(new_feats=new, n_new=nnew, valid_2d=v2, pts_3d=p3, valid_idx=vi, disp16=d16,
+                    n_valid=nv)
+
+    def keyframe_tracked(self, seqs, poses, first_new_id, focal, cx, cy, baseline):
+        """svo_keyframe_tracked: every tracked feature is an inlier, tracker re-initialised on
+        the device (see include/svo_c.h)."""
+        n = len(seqs)
+        seqs_a = np.ascontiguousarray(seqs, np.int32)
+        poses = np.ascontiguousarray(poses, np.float32).reshape(n, 16)
+        first = np.ascontiguousarray(first_new_id, np.uint64)
+        mc = self.max_corners
+        new = np.zeros((n, mc, 2), np.float32)
+        nnew = np.zeros(n, np.int32)
+        v2 = np.zeros((n, mc, 2), np.float32)
+        p3 = np.zeros((n, mc, 3), np.float32)
+        vi = np.zeros((n, mc), np.int32)
+        d16 = np.zeros((n, mc), np.int16)
+        nv = np.zeros(n, np.int32)
+        self._check(self.lib.svo_keyframe_tracked(self.h, n, _ptr(seqs_a), _ptr(poses), _ptr(first),
+                                                  float(focal), float(cx), float(cy),
+                                                  float(baseline), _ptr(new), _ptr(nnew), _ptr(v2),
+                                                  _ptr(p3), _ptr(vi), _ptr(d16), _ptr(nv)),
+                    "svo_keyframe_tracked")
         return dict(new_feats=new, n_new=nnew, valid_2d=v2, pts_3d=p3, valid_idx=vi, disp16=d16,
                     n_valid=nv)
 

@@ -272,6 +272,28 @@ ingest_kernel(uint8_t* pyr, SvoPyrLayout lay, size_t seq_stride, uint8_t* right,
     }
 }
 
+// svo_keyframe_tracked: FeatureTracker::init(tracked inliers + new stereo-valid features) on the
+// device. The tracked features already sit at the head of the tracker's feature buffer; the
+// new ones are appended with ids first_id, first_id + 1, ... and the whole set becomes
+// initial_features (feature_tracker.cpp:3-16, ids as bundle_adjuster.cpp:98-116 hands them out).
+__global__ void __launch_bounds__(128)
+tracker_append_kernel(float2* feat, unsigned long long* ids, float2* initial, int max_features,
+                      const float2* __restrict__ valid2d, int pts_stride,
+                      const int* __restrict__ n_valid, const SvoSeqCall* __restrict__ call) {
+    const SvoSeqCall cd = call[blockIdx.x];
+    const int nt = cd.n_aux;
+    const int nv = min(n_valid[cd.seq], max_features - nt);
+    const size_t fb = ((size_t)cd.seq * 2 + cd.feat_buf) * max_features;
+    const float2* v = valid2d + (size_t)cd.seq * pts_stride;
+    for (int j = threadIdx.x; j < nt; j += blockDim.x) initial[fb + j] = feat[fb + j];
+    for (int j = threadIdx.x; j < nv; j += blockDim.x) {
+        const float2 p = v[j];
+        feat[fb + nt + j] = p;
+        initial[fb + nt + j] = p;
+        ids[fb + nt + j] = cd.first_id + (unsigned long long)j;
+    }
+}
+
 // pack the results of one step into a contiguous block per listed sequence (one D2H copy)
 __global__ void pack_step_kernel(unsigned char* out, size_t block, const float2* corners,
                                  const int* n_corners, const int* cand_count, int max_corners,
@@ -1143,7 +1165,12 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
                          float cy, float baseline, bool dedupe, const svo_float2* explicit_pts,
                          const int32_t* n_explicit, svo_float2* new_feats, int32_t* n_new,
                          svo_float2* valid_2d, svo_float3* pts_3d, int32_t* valid_idx,
-                         int16_t* disp16, int32_t* n_valid) {
+                         int16_t* disp16, int32_t* n_valid,
+                         const uint64_t* first_new_id = nullptr) {
+    // first_new_id != nullptr: every tracked feature of the sequence is an inlier - the list is
+    // the tracker's device-resident feature set, and the tracker is re-initialised on the
+    // device at the end (nothing but the descriptors travels to the GPU)
+    const bool tracked = first_new_id != nullptr;
     const int mf = e->p.max_features, cap = e->pts_cap, mcn = e->p.max_corners;
     ECUDA(e, cudaSetDevice(e->device));
     SvoSeqCall* hc = next_call_slot(e);
@@ -1156,7 +1183,12 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
             return fail(e, SVO_ERR_STATE, "stereo stage needs an uploaded stereo pair");
         fill_call(e, hc[i], s);
         if (poses) memcpy(hc[i].pose, poses + (size_t)i * 16, 16 * sizeof(float));
-        if (dedupe) {
+        if (tracked) {
+            hc[i].n_aux = e->seq[s].tracker_init ? e->seq[s].n_feat : 0;
+            hc[i].n_pts = 0;
+            hc[i].first_id = first_new_id[i];
+            max_pts = mcn;
+        } else if (dedupe) {
             int ni = n_inliers ? n_inliers[i] : 0;
             if (ni < 0 || ni > mf) return fail(e, SVO_ERR_INVALID, "n_inliers out of range");
             hc[i].n_aux = ni;
@@ -1173,7 +1205,9 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
     }
     ECUDA(e, cudaEventRecord(e->ev[0], e->st));
     SvoSeqCall* dc = dev_call_slot(e);
-    {
+    if (tracked) {
+        ECUDA(e, push_calls(e, n));
+    } else {
         PullList pl(e);
         pl.add(dc, hc, (size_t)n * sizeof(SvoSeqCall));
         for (int i = 0; i < n; ++i) {
@@ -1188,7 +1222,8 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     if (dedupe) {
         ProfScope ps(e, P_DEDUPE);
-        ECUDA(e, svo_launch_dedupe(e->d_corners, e->d_ncorners, mcn, e->d_inl, mf, e->p.min_distance,
+        ECUDA(e, svo_launch_dedupe(e->d_corners, e->d_ncorners, mcn, tracked ? e->d_feat : e->d_inl,
+                                   tracked ? 2 * mf : mf, tracked ? mf : 0, e->p.min_distance,
                                    e->d_pts, e->d_keep_idx, e->d_nnew, cap, dc, e->d_ticket, n, e->st));
         e->launches += 1;
     }
@@ -1206,6 +1241,11 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
         ECUDA(e, svo_launch_reproject(e->d_pts, e->d_disp16, cap, focal, cx, cy, baseline,
                                       e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, dc, n,
                                       e->st));
+    }
+    if (tracked) {
+        tracker_append_kernel<<<n, 128, 0, e->st>>>(e->d_feat, e->d_ids, e->d_initial, mf,
+                                                    e->d_valid2d, cap, e->d_nvalid, dc);
+        e->launches += 1;
     }
     pack_key_kernel<<<n, 128, 0, e->st>>>(e->d_out, e->key_block, cap, e->d_pts,
                                           dedupe ? e->d_nnew : nullptr, e->d_valid2d, e->d_pts3d,
@@ -1233,8 +1273,29 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
         if (valid_2d) memcpy(valid_2d + ob, o_v2, (size_t)h->n_valid * sizeof(float2));
         if (valid_idx) memcpy(valid_idx + ob, o_vi, (size_t)h->n_valid * sizeof(int));
         if (pts_3d) memcpy(pts_3d + ob, o_3d, (size_t)h->n_valid * 3 * sizeof(float));
+        if (tracked) {                      // the host mirror of what tracker_append_kernel did
+            SeqState& st = e->seq[seqs[i]];
+            const int nt = hc[i].n_aux;
+            st.n_feat = nt + std::min((int)h->n_valid, mf - nt);
+            st.n_initial = st.n_feat;
+            st.tracker_init = true;
+            st.last_slot = st.cur_slot;    // last_image = image.clone()  (feature_tracker.cpp:14)
+        }
     }
     return SVO_OK;
+}
+
+int svo_keyframe_tracked(svo_engine* e, int32_t n, const int32_t* seqs, const float* poses,
+                         const uint64_t* first_new_id, float focal, float cx, float cy,
+                         float baseline, svo_float2* new_feats, int32_t* n_new,
+                         svo_float2* valid_2d, svo_float3* pts_3d, int32_t* valid_idx,
+                         int16_t* disp16, int32_t* n_valid) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !seqs || !poses || !first_new_id)
+        return fail(e, SVO_ERR_INVALID, "svo_keyframe_tracked: bad arguments");
+    return keyframe_impl(e, n, seqs, nullptr, nullptr, poses, focal, cx, cy, baseline, true,
+                         nullptr, nullptr, new_feats, n_new, valid_2d, pts_3d, valid_idx, disp16,
+                         n_valid, first_new_id);
 }
 
 int svo_keyframe(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* inliers,
@@ -1468,7 +1529,7 @@ int svo_dedupe(svo_engine* e, int32_t seq, const svo_float2* det, int32_t n_det,
     // detections go through d_valid2d (scratch), tracked through d_inl
     if (n_det > 0) ECUDA(e, cudaMemcpyAsync(e->d_valid2d + (size_t)seq * cap, det, (size_t)n_det * sizeof(float2), cudaMemcpyHostToDevice, e->st));
     if (n_tracked > 0) ECUDA(e, cudaMemcpyAsync(e->d_inl + (size_t)seq * mf, tracked, (size_t)n_tracked * sizeof(float2), cudaMemcpyHostToDevice, e->st));
-    ECUDA(e, svo_launch_dedupe(e->d_valid2d, nullptr, cap, e->d_inl, mf, min_distance, e->d_pts,
+    ECUDA(e, svo_launch_dedupe(e->d_valid2d, nullptr, cap, e->d_inl, mf, 0, min_distance, e->d_pts,
                                e->d_keep_idx, e->d_nnew, cap, dev_call_slot(e), e->d_ticket, 1, e->st));
     e->launches += 1;
     int nn = 0;

@@ -238,15 +238,16 @@ constexpr int DD_TILE = 1024;     // tracked points staged per pass
 // detection in keep_idx; the block that finishes last compacts. `ticket` is zero between calls.
 __global__ void __launch_bounds__(RP_THREADS)
 dedupe_kernel(const float2* __restrict__ det, const int* __restrict__ n_det, int det_stride,
-              const float2* __restrict__ inl, int inl_stride, float min_distance,
-              float2* __restrict__ out, int* keep_idx, int* __restrict__ n_out,
-              int out_stride, SvoSeqCall* call, unsigned* ticket) {
+              const float2* __restrict__ inl, int inl_stride, int inl_buffered,
+              float min_distance, float2* __restrict__ out, int* keep_idx,
+              int* __restrict__ n_out, int out_stride, SvoSeqCall* call, unsigned* ticket) {
     __shared__ float2 s_q[DD_TILE];
     __shared__ int s_w[RP_THREADS / 32];
     __shared__ bool s_last;
     const SvoSeqCall cd = call[blockIdx.x];
     const float2* d = det + (size_t)cd.seq * det_stride;
-    const float2* q = inl + (size_t)cd.seq * inl_stride;
+    // inl_buffered > 0: the tracked set is the tracker's own double-buffered feature array
+    const float2* q = inl + (size_t)cd.seq * inl_stride + (size_t)cd.feat_buf * inl_buffered;
     const int nd = n_det ? n_det[cd.seq] : cd.n_pts;
     const int ni = cd.n_aux;
     const size_t ob = (size_t)cd.seq * out_stride;
@@ -330,11 +331,12 @@ cudaError_t svo_launch_reproject(const float2* pts, const short* disp16, int pts
 }
 
 cudaError_t svo_launch_dedupe(const float2* det, const int* n_det, int det_stride,
-                              const float2* inl, int inl_stride, float min_distance, float2* out,
+                              const float2* inl, int inl_stride, int inl_buffered,
+                              float min_distance, float2* out,
                               int* keep_idx, int* n_out, int out_stride,
                               SvoSeqCall* d_call, unsigned* ticket, int n_call, cudaStream_t st) {
     dedupe_kernel<<<dim3(n_call, DD_BLOCKS), RP_THREADS, 0, st>>>(
-        det, n_det, det_stride, inl, inl_stride, min_distance, out, keep_idx, n_out, out_stride,
-        d_call, ticket);
+        det, n_det, det_stride, inl, inl_stride, inl_buffered, min_distance, out, keep_idx, n_out,
+        out_stride, d_call, ticket);
     return cudaGetLastError();
 }

@@ -42,6 +42,7 @@ struct SvoSeqCall {
     const uint8_t* src_right;
     int src_pitch;
     int pad_;
+    unsigned long long first_id; // svo_keyframe_tracked: id of the first new feature
 };
 
 __host__ __device__ __forceinline__ int svo_reflect101(int i, int n) {
@@ -132,7 +133,8 @@ cudaError_t svo_launch_reproject(const float2* pts, const short* disp16, int pts
                                  const SvoSeqCall* d_call, int n_call, cudaStream_t st);
 
 cudaError_t svo_launch_dedupe(const float2* det, const int* n_det, int det_stride,
-                              const float2* inl, int inl_stride, float min_distance, float2* out,
+                              const float2* inl, int inl_stride, int inl_buffered,
+                              float min_distance, float2* out,
                               int* keep_idx, int* n_out, int out_stride,
                               SvoSeqCall* d_call, unsigned* ticket, int n_call, cudaStream_t st);
 

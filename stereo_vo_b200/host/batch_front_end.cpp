@@ -62,7 +62,7 @@ BatchFrontEnd::BatchFrontEnd(const BatchOptions& opt) : opt_(opt) {
         grp->corners.resize(n * mc); grp->new_feats.resize(n * mc); grp->valid_2d.resize(n * mc);
         grp->pts_3d.resize(n * mc); grp->valid_idx.resize(n * mc); grp->disp16.resize(n * mc);
         grp->tracked.resize(n * mf); grp->tracked_ids.resize(n * mf); grp->inl.resize(n * mf);
-        grp->feats.resize(n * mf); grp->ids.resize(n * mf);
+        grp->feats.resize(n * mf); grp->ids.resize(n * mf); grp->first_id.resize(n);
         grp->poses.resize(n * 16);
         for (int i = 0; i < cnt; ++i) grp->local_ids[(size_t)i] = i;
         groups_.push_back(std::move(grp));
@@ -300,12 +300,20 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
     lap(2);
     if (nk == 0) return;
 
-    // ---- dedupe + StereoBM + reprojection for the new keyframes (:113-142)
-    rc = svo_keyframe(e, nk, g.kf_local.data(), g.inl.data(), g.n_inl.data(), g.poses.data(),
-                      opt_.focal, opt_.cx, opt_.cy, opt_.baseline, g.new_feats.data(),
-                      g.n_newv.data(), g.valid_2d.data(), g.pts_3d.data(), g.valid_idx.data(),
-                      g.disp16.data(), g.n_valid.data());
-    if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_keyframe", rc));
+    // ---- dedupe + StereoBM + reprojection for the new keyframes (:113-142), then
+    // BundleAdjuster::add_keyframe's id assignment (a running counter; new features
+    // clipped to the 400-feature limit) and FeatureTracker::init (:148-162). Every tracked
+    // feature is an inlier here, so the engine takes the inlier list from its own tracker state
+    // and re-initialises the tracker on the device (svo_keyframe_tracked): no list goes up.
+    for (int k = 0; k < nk; ++k) {
+        const int s = g.seqs[(size_t)g.kf_local[(size_t)k]];
+        g.first_id[(size_t)k] = seq_[(size_t)s].next_id;
+    }
+    rc = svo_keyframe_tracked(e, nk, g.kf_local.data(), g.poses.data(), g.first_id.data(),
+                              opt_.focal, opt_.cx, opt_.cy, opt_.baseline, g.new_feats.data(),
+                              g.n_newv.data(), g.valid_2d.data(), g.pts_3d.data(),
+                              g.valid_idx.data(), g.disp16.data(), g.n_valid.data());
+    if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_keyframe_tracked", rc));
     lap(3);
     if (trace_) {
         float ms[3];
@@ -313,36 +321,29 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         g.phase_ms[9] += ms[0]; g.phase_ms[10] += ms[1]; g.phase_ms[11] += ms[2];
     }
 
-    // ---- BundleAdjuster::add_keyframe bookkeeping (ids are a running counter, SURVEY.md B7;
-    // new features are clipped to the 400-feature limit) + FeatureTracker::init (:148-162)
+    // the host's copy of the new tracker set (results of this step)
     for (int k = 0; k < nk; ++k) {
         const int i = g.kf_local[(size_t)k];
         const int s = g.seqs[(size_t)i];
         SeqState& st = seq_[(size_t)s];
         const int n_inl = g.n_inl[(size_t)k];
         const int nv = std::min(g.n_valid[(size_t)k], mf - n_inl);
-        svo_float2* f = &g.feats[(size_t)k * mf];
-        uint64_t* id = &g.ids[(size_t)k * mf];
+        svo_float2* f = &tracker_pts_[slot][(size_t)s * mf];
+        uint64_t* id = &tracker_ids_[slot][(size_t)s * mf];
         std::memcpy(f, &g.inl[(size_t)k * mf], (size_t)n_inl * sizeof(svo_float2));
         std::memcpy(id, &g.tracked_ids[(size_t)i * mf], (size_t)n_inl * sizeof(uint64_t));
         std::memcpy(f + n_inl, &g.valid_2d[(size_t)k * mc], (size_t)nv * sizeof(svo_float2));
         for (int j = 0; j < nv; ++j) id[n_inl + j] = st.next_id++;
-        g.counts[(size_t)k] = n_inl + nv;
         st.have_kf = true;
         SeqResult& rs = st.res[slot];
         rs.n_new = nv;
         st.n_tracker = rs.n_tracker = n_inl + nv;
         std::memcpy(&new_2d_[slot][(size_t)s * mc], &g.valid_2d[(size_t)k * mc], (size_t)nv * sizeof(svo_float2));
         std::memcpy(&new_3d_[slot][(size_t)s * mc], &g.pts_3d[(size_t)k * mc], (size_t)nv * sizeof(svo_float3));
-        std::memcpy(&tracker_pts_[slot][(size_t)s * mf], f, (size_t)(n_inl + nv) * sizeof(svo_float2));
-        std::memcpy(&tracker_ids_[slot][(size_t)s * mf], id, (size_t)(n_inl + nv) * sizeof(uint64_t));
         sum.keyframes += 1;
         sum.new_points += nv;
     }
     lap(4);
-    rc = svo_tracker_set(e, nk, g.kf_local.data(), g.feats.data(), g.ids.data(), g.counts.data());
-    if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_tracker_set", rc));
-    lap(5);
 }
 
 void BatchFrontEnd::submit(const uint8_t* const* left, const uint8_t* const* right, int pitch,

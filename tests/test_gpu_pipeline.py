@@ -106,3 +106,50 @@ def test_batched_sequences_match_single(svo_lib, oracle):
             assert np.array_equal(res["tracked"][0, :k], rb["tracked"][s, :k])
             assert np.array_equal(res["tracked_ids"][0, :k], rb["tracked_ids"][s, :k])
         e1.close()
+
+
+def test_keyframe_tracked_equals_keyframe_plus_tracker_set(svo_lib):
+    """svo_keyframe_tracked (inliers = the tracker's device-resident set, tracker re-initialised
+    on the device) == svo_keyframe with the tracked list sent from the host + svo_tracker_set,
+    over a run with a keyframe every third frame, two sequences per engine."""
+    from stereo_vo_b200.capi import Engine
+    cam = synth.KITTI00
+    n_seq, n_fr = 2, 8
+    seqs = [util.frames(10 + s, n_fr) for s in range(n_seq)]
+    ea = Engine(cam.width, cam.height, n_seq=n_seq)
+    eb = Engine(cam.width, cam.height, n_seq=n_seq)
+    ids_all = list(range(n_seq))
+    next_id = [1000 * (s + 1) for s in range(n_seq)]
+    mf = ea.max_features
+    for t in range(n_fr):
+        left = [seqs[s][t][0] for s in range(n_seq)]
+        right = [seqs[s][t][1] for s in range(n_seq)]
+        ra, rb = ea.step(ids_all, left, right), eb.step(ids_all, left, right)
+        for key in ("corners", "n_corners", "tracked", "tracked_ids"):
+            assert np.array_equal(ra[key], rb[key]), (t, key)
+        assert ra["stats"].tobytes() == rb["stats"].tobytes(), t
+        if t % 3 != 0:
+            continue
+        kept = [int(ra["stats"][s]["n_kept"]) if t > 0 else 0 for s in range(n_seq)]
+        poses = np.tile(np.eye(4, dtype=np.float32).reshape(1, 16), (n_seq, 1))
+        poses[:, 3] = 0.1 * t
+        ka = ea.keyframe(ids_all, [ra["tracked"][s, :kept[s]] for s in range(n_seq)], kept, poses,
+                         cam.focal, cam.cx, cam.cy, cam.baseline)
+        feats, ids = [], []
+        for s in range(n_seq):
+            nv = min(int(ka["n_valid"][s]), mf - kept[s])
+            feats.append(np.concatenate([ra["tracked"][s, :kept[s]], ka["valid_2d"][s, :nv]]))
+            ids.append(np.concatenate([ra["tracked_ids"][s, :kept[s]],
+                                       np.arange(next_id[s], next_id[s] + nv, dtype=np.uint64)]))
+        ea.tracker_set(ids_all, feats, ids)
+        kb = eb.keyframe_tracked(ids_all, poses, next_id, cam.focal, cam.cx, cam.cy, cam.baseline)
+        for key in ka:
+            assert np.array_equal(ka[key], kb[key]), (t, key)
+        for s in range(n_seq):
+            fa, ia = ea.tracker_get(s)
+            fb, ib = eb.tracker_get(s)
+            assert np.array_equal(fa, feats[s]) and np.array_equal(ia, ids[s])
+            assert np.array_equal(fa, fb) and np.array_equal(ia, ib), (t, s)
+            next_id[s] += len(ids[s]) - kept[s]
+    ea.close()
+    eb.close()

@@ -153,3 +153,58 @@ def test_keyframe_tracked_equals_keyframe_plus_tracker_set(svo_lib):
             next_id[s] += len(ids[s]) - kept[s]
     ea.close()
     eb.close()
+
+
+def test_too_few_corners_frame_is_skipped_entirely(svo_lib, oracle):
+    """src/image_processor.cpp:23-25: a frame with fewer than 4 corners returns before the
+    tracker is touched, so the next good frame is tracked from the last good one. Featureless
+    frames in the middle of a run (also as the very first frame), python facade and C++ batch
+    driver, against the oracle."""
+    from stereo_vo_b200 import frontend, hostapi
+    from stereo_vo_b200.capi import Engine
+    cam = synth.KITTI00
+    fr = list(synth.sequence(3, 9, cam, synth.KITTI_MOTION))
+    flat = np.full((cam.height, cam.width), 120, np.uint8)
+    fr[0] = (flat, flat)
+    fr[4] = (flat, flat.copy())
+    fr[5] = (flat.copy(), flat)
+    ref = oracle.make_pipeline(cam)
+    for l, r in fr:
+        ref.process(l, r)
+    assert [ref.log[t]["decision"] for t in (0, 1, 4, 5)] == ["too_few", "first", "too_few", "too_few"]
+    e = Engine(cam.width, cam.height, n_seq=1)
+    f, cx, cy, b = cam.f32()
+    gpu = frontend.ImageProcessor(e, frontend.camera_matrix(f, cx, cy), frontend.BundleAdjuster(), b,
+                                  teacher=ref.log)
+    for l, r in fr:
+        gpu.process(l, r)
+    _compare(ref.log, gpu.log)
+    assert sum(r["decision"] == "too_few" for r in gpu.log) == 3
+    e.close()
+
+    # C++ batch driver: "skipped entirely" means the good frames give exactly what they give
+    # when the featureless frames are not there at all
+    good = [(l, r) for t, (l, r) in enumerate(fr) if t not in (0, 4, 5)]
+    with_flat = hostapi.Batch(cam.width, cam.height, 2, 2, cam)
+    without = hostapi.Batch(cam.width, cam.height, 2, 1, cam)
+    pitch = cam.width
+    k = 0
+    for t, (l, r) in enumerate(fr):
+        with_flat.step([l, l], [r, r], pitch)
+        a = with_flat.get(1)
+        if t in (0, 4, 5):
+            assert a["decision"] == "too_few" and len(a["corners"]) == 0, t
+            continue
+        gl, gr = good[k]
+        k += 1
+        without.step([gl, gl], [gr, gr], pitch)
+        b = without.get(1)
+        assert a["decision"] == b["decision"], t
+        assert np.array_equal(a["corners"], b["corners"]), t
+        assert a["stats"].tobytes() == b["stats"].tobytes(), t
+        assert np.array_equal(a["tracker_pts"], b["tracker_pts"]), t
+        assert np.array_equal(a["tracker_ids"], b["tracker_ids"]), t
+        assert np.array_equal(a["new3d"], b["new3d"]), t
+    assert k == len(good)
+    with_flat.close()
+    without.close()

@@ -175,3 +175,44 @@ def test_corner_score_variants(svo_lib, env):
     r = subprocess.run([sys.executable, "-c", _VARIANT_SCRIPT.format(root=root)], env=full_env,
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "VARIANT_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
+
+
+def _hard_images(w, h):
+    """Images built to make the sliding fp64 sums of cornerMinEigenVal round (values of very
+    different magnitude in one column) and keep rounding residue alive across many rows: the
+    cases in which the row segments of corner_score_nms start from a wrong guess."""
+    rng = np.random.default_rng(2024)
+    ys, xs = np.mgrid[0:h, 0:w]
+    out = {}
+    noise = rng.integers(0, 256, (h, w)).astype(np.uint8)
+    half = noise.copy()
+    half[:, w // 2:] = 131                                  # flat half beside full-range noise
+    out["flat_half"] = half
+    bands = noise.copy()
+    for y0 in range(20, h, 70):                             # flat bands every 70 rows: residue
+        bands[y0:y0 + 30, :] = 200                          # must survive into the next segment
+    out["flat_bands"] = bands
+    out["ramp_y"] = np.clip(ys * 255.0 / (h - 1), 0, 255).astype(np.uint8)       # Dx == 0: -0 xy sums
+    out["ramp_x_sat"] = np.clip(xs * 400.0 / (w - 1), 0, 255).astype(np.uint8)  # saturated third
+    out["checker"] = (((xs // 16) + (ys // 16)) % 2 * 255).astype(np.uint8)
+    faint = np.full((h, w), 100, np.int32) + rng.integers(0, 2, (h, w))         # +-1 on a constant
+    faint[h // 3:h // 3 + 9, w // 4:w // 4 + 9] = 255                             # one huge blob
+    out["faint_plus_blob"] = faint.astype(np.uint8)
+    mix = util.stress_image(h, w, 5).astype(np.int32)
+    mix[:, ::97] = 0                                        # isolated extreme columns
+    out["stress_columns"] = np.clip(mix, 0, 255).astype(np.uint8)
+    return out
+
+
+@pytest.mark.parametrize("w,h", [(1241, 376), (640, 480)])
+def test_corner_segments_on_rounding_prone_images(engines, oracle, w, h):
+    # full-range noise leaves more than the default 16384 NMS survivors: the tiled sort path
+    e = engines(w, h, keep_eig_map=1, max_candidates=1 << 17)
+    for name, img in _hard_images(w, h).items():
+        got = e.good_features_to_track(img, seq=1)
+        ref = oracle.detect(img)
+        assert got.shape == ref.shape and np.array_equal(got, ref), name
+        eig = e.debug_min_eigen_map(seq=1)
+        ref_eig = cv2.cornerMinEigenVal(img, 3, ksize=3)
+        assert np.array_equal(eig.view(np.uint32), ref_eig.view(np.uint32)), \
+            f"{name}: {(eig.view(np.uint32) != ref_eig.view(np.uint32)).sum()} eig pixels differ"

@@ -234,6 +234,35 @@ SVO_API int svo_keyframe_tracked(svo_engine* e, int32_t n, const int32_t* seqs, 
                          svo_float2* valid_2d, svo_float3* pts_3d, int32_t* valid_idx,
                          int16_t* disp16, int32_t* n_valid);
 
+/* What ImageProcessor::process does with a frame (src/image_processor.cpp:23-30,63-65). */
+typedef enum svo_frame_decision {
+    SVO_FRAME_TOO_FEW = 1,     /* fewer than 4 corners: frame ignored, tracker not advanced */
+    SVO_FRAME_FIRST = 2,       /* no keyframe yet: this frame becomes the first one */
+    SVO_FRAME_SKIP = 3,        /* tracked; parallax <= threshold and < 40 % of the tracks lost */
+    SVO_FRAME_KEYFRAME = 4,    /* tracked; becomes a keyframe */
+    SVO_FRAME_PENDING = 8      /* added to FIRST / KEYFRAME: right image was not on the device */
+} svo_frame_decision;
+
+/* svo_step and svo_keyframe_tracked in ONE call and one device round trip, for drivers without a
+ * pose solver in the loop: after tracking, the decision above is taken on the device from the
+ * statistics of this frame (parallax_thresh: src/vo_node.cpp:35), and the sequences that become
+ * keyframes run the keyframe stage (dedupe against the tracked set, StereoBM at the new corners,
+ * reprojection with poses[i], FeatureTracker::init with ids first_new_id[i] + k) at once.
+ * on_device: left/right are device pointers (as svo_step_device). right[i] may be NULL; a
+ * sequence that turns out to be a keyframe without a right image on the device comes back as
+ * SVO_FRAME_FIRST/KEYFRAME + SVO_FRAME_PENDING with its tracker advanced but no keyframe stage
+ * run: supply the image with svo_set_right and finish with svo_keyframe_tracked.
+ * Step outputs as svo_step, keyframe outputs as svo_keyframe (valid where decision is FIRST or
+ * KEYFRAME). */
+SVO_API int svo_step_keyframe(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* left,
+                      const uint8_t* const* right, int32_t pitch, int32_t on_device,
+                      const float* poses, const uint64_t* first_new_id, float parallax_thresh,
+                      float focal, float cx, float cy, float baseline,
+                      svo_float2* corners, int32_t* n_corners, svo_track_stats* stats,
+                      svo_float2* tracked, uint64_t* tracked_ids, int32_t* decision,
+                      svo_float2* new_feats, int32_t* n_new, svo_float2* valid_2d,
+                      svo_float3* pts_3d, int32_t* valid_idx, int16_t* disp16, int32_t* n_valid);
+
 /* FeatureTracker::init against the CURRENT frame of each listed sequence
  * (image_processor.cpp:51-52,148-162): feats/ids [n][max_features], counts[i] entries. */
 SVO_API int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,

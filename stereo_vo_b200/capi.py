@@ -47,7 +47,7 @@ EXPORTS = [
     "svo_good_features_to_track", "svo_triangulate_stereo", "svo_tracker_init",
     "svo_tracker_track", "svo_tracker_get", "svo_dedupe", "svo_tracker_debug",
     "svo_debug_min_eigen_map", "svo_debug_pyramid_level", "svo_debug_candidates",
-    "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_keyframe_tracked", "svo_tracker_set",
+    "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_keyframe_tracked", "svo_step_keyframe", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
     "svo_timer_begin", "svo_timer_end",
@@ -105,6 +105,8 @@ def load_library(path: Optional[str] = None):
                                  vp, vp]
     lib.svo_keyframe_tracked.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, f32, vp, vp, vp, vp,
                                          vp, vp, vp]
+    lib.svo_step_keyframe.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, f32,
+                                      vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
     lib.svo_device_free.argtypes = [vp, vp]
@@ -426,6 +428,42 @@ class Engine:
                     "svo_keyframe_tracked")
         return dict(new_feats=new, n_new=nnew, valid_2d=v2, pts_3d=p3, valid_idx=vi, disp16=d16,
                     n_valid=nv)
+
+    def step_keyframe(self, seqs, left, right, poses, first_new_id, parallax_thresh, focal, cx, cy,
+                      baseline):
+        """svo_step_keyframe: svo_step + device-side decision + keyframe stage in one call.
+        `right` may hold None for sequences whose right image is not sent."""
+        n = len(seqs)
+        seqs_a = np.ascontiguousarray(seqs, np.int32)
+        left = [_img(a) for a in left]
+        right = [None if a is None else _img(a) for a in right]
+        pitch = left[0].strides[0]
+        lp = self._ptr_array(left)
+        rp = (C.c_void_p * n)(*[None if a is None else a.ctypes.data for a in right])
+        poses = np.ascontiguousarray(poses, np.float32).reshape(n, 16)
+        first = np.ascontiguousarray(first_new_id, np.uint64)
+        mc, mf = self.max_corners, self.max_features
+        corners = np.zeros((n, mc, 2), np.float32)
+        ncorn = np.zeros(n, np.int32)
+        stats = np.zeros(n, STATS_DTYPE)
+        tracked = np.zeros((n, mf, 2), np.float32)
+        tids = np.zeros((n, mf), np.uint64)
+        dec = np.zeros(n, np.int32)
+        new = np.zeros((n, mc, 2), np.float32)
+        nnew = np.zeros(n, np.int32)
+        v2 = np.zeros((n, mc, 2), np.float32)
+        p3 = np.zeros((n, mc, 3), np.float32)
+        vi = np.zeros((n, mc), np.int32)
+        d16 = np.zeros((n, mc), np.int16)
+        nv = np.zeros(n, np.int32)
+        self._check(self.lib.svo_step_keyframe(
+            self.h, n, _ptr(seqs_a), lp, rp, int(pitch), 0, _ptr(poses), _ptr(first),
+            float(parallax_thresh), float(focal), float(cx), float(cy), float(baseline),
+            _ptr(corners), _ptr(ncorn), _ptr(stats), _ptr(tracked), _ptr(tids), _ptr(dec), _ptr(new),
+            _ptr(nnew), _ptr(v2), _ptr(p3), _ptr(vi), _ptr(d16), _ptr(nv)), "svo_step_keyframe")
+        return dict(corners=corners, n_corners=ncorn, stats=stats, tracked=tracked,
+                    tracked_ids=tids, decision=dec, new_feats=new, n_new=nnew, valid_2d=v2,
+                    pts_3d=p3, valid_idx=vi, disp16=d16, n_valid=nv)
 
     def tracker_set(self, seqs, feats, ids):
         n = len(seqs)

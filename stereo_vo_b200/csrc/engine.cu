@@ -48,6 +48,8 @@ struct StepHeader {
 struct KeyHeader {
     int n_new;
     int n_valid;
+    int decision;                // svo_step_keyframe: svo_frame_decision taken on the device
+    int n_tracked;               // ... and the tracked features the new tracker set starts with
 };
 
 template <typename T>
@@ -145,6 +147,7 @@ struct svo_engine {
     PullSeg* h_pull = nullptr;        // pinned + mapped segment lists
     int pull_used = 0, pull_cap = 0;
     SvoSeqCall* d_call = nullptr;
+    SvoSeqCall* d_kcall = nullptr;    // svo_step_keyframe: descriptors of the keyframe stage
     int ring = 0;
     unsigned char* h_out = nullptr;   // pinned
     unsigned char* h_in = nullptr;    // pinned small-input staging
@@ -281,6 +284,7 @@ tracker_append_kernel(float2* feat, unsigned long long* ids, float2* initial, in
                       const float2* __restrict__ valid2d, int pts_stride,
                       const int* __restrict__ n_valid, const SvoSeqCall* __restrict__ call) {
     const SvoSeqCall cd = call[blockIdx.x];
+    if (cd.flags & SVO_CALL_SKIP) return;
     const int nt = cd.n_aux;
     const int nv = min(n_valid[cd.seq], max_features - nt);
     const size_t fb = ((size_t)cd.seq * 2 + cd.feat_buf) * max_features;
@@ -292,6 +296,37 @@ tracker_append_kernel(float2* feat, unsigned long long* ids, float2* initial, in
         initial[fb + nt + j] = p;
         ids[fb + nt + j] = cd.first_id + (unsigned long long)j;
     }
+}
+
+// svo_step_keyframe: the per-frame decision of ImageProcessor::process on the device
+// (image_processor.cpp:23-30 "fewer than 4 corners", :27-52 first keyframe, :63-65 skip unless
+// av_parallax > threshold or 40 % of the tracks are lost), and the descriptors the keyframe
+// stage of the same call runs on: the tracker's feature buffer AFTER this frame's tracking and
+// its kept count as the inlier list. Sequences that are no keyframe, or have no right image on
+// the device yet, are marked SVO_CALL_SKIP.
+__global__ void decide_kernel(const SvoSeqCall* __restrict__ call, SvoSeqCall* __restrict__ kcall,
+                              const int* __restrict__ n_corners,
+                              const SvoTrackStats* __restrict__ stats, float parallax_thresh,
+                              int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    SvoSeqCall c = call[i];
+    const SvoTrackStats st = stats[c.seq];
+    const bool has_tracker = (c.flags & SVO_CALL_TRACKER) != 0;
+    const bool tracked = has_tracker && st.n_attempted >= 0;
+    int decision;
+    if (n_corners[c.seq] < 4) decision = SVO_FRAME_TOO_FEW;
+    else if (!has_tracker) decision = SVO_FRAME_FIRST;
+    else if (st.av_parallax <= parallax_thresh && (double)st.percent_lost < 0.4) decision = SVO_FRAME_SKIP;
+    else decision = SVO_FRAME_KEYFRAME;
+    const bool key = decision == SVO_FRAME_FIRST || decision == SVO_FRAME_KEYFRAME;
+    if (tracked) c.feat_buf = 1 - c.feat_buf;      // track_filter compacted into the other buffer
+    c.n_aux = tracked ? st.n_kept : 0;
+    c.n_feat = c.n_aux;
+    c.n_pts = 0;
+    c.decision = decision;
+    if (!key || !(c.flags & SVO_CALL_HAS_RIGHT)) c.flags |= SVO_CALL_SKIP;
+    kcall[i] = c;
 }
 
 // pack the results of one step into a contiguous block per listed sequence (one D2H copy)
@@ -338,9 +373,12 @@ __global__ void pack_key_kernel(unsigned char* out, size_t block, int cap, const
     int* o_vi = reinterpret_cast<int*>(o_3d + 3 * (size_t)cap);
     short* o_d = reinterpret_cast<short*>(o_vi + cap);
     const size_t b = (size_t)cd.seq * cap;
-    const int nn = n_new ? n_new[cd.seq] : cd.n_pts;
-    const int nv = n_valid[cd.seq];
-    if (threadIdx.x == 0) { h->n_new = nn; h->n_valid = nv; }
+    const bool skip = (cd.flags & SVO_CALL_SKIP) != 0;
+    const int nn = skip ? 0 : (n_new ? n_new[cd.seq] : cd.n_pts);
+    const int nv = skip ? 0 : n_valid[cd.seq];
+    if (threadIdx.x == 0) {
+        h->n_new = nn; h->n_valid = nv; h->decision = cd.decision; h->n_tracked = cd.n_aux;
+    }
     for (int i = threadIdx.x; i < nn; i += blockDim.x) {
         o_new[i] = pts[b + i];
         o_d[i] = disp16[b + i];
@@ -707,10 +745,20 @@ bool prefetch_consume(svo_engine* e, int n, const int32_t* seqs, const uint8_t* 
     return true;
 }
 
+// keyframe stage appended to a step (svo_step_keyframe)
+struct StepKey {
+    const float* poses;               // n x 16
+    const uint64_t* first_new_id;     // n
+    float parallax_thresh, focal, cx, cy, baseline;
+    int32_t* decision;                // n, svo_frame_decision
+    svo_float2* new_feats; int32_t* n_new; svo_float2* valid_2d; svo_float3* pts_3d;
+    int32_t* valid_idx; int16_t* disp16; int32_t* n_valid;
+};
+
 int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* left,
               const uint8_t* const* right, int pitch, bool device_src, svo_float2* corners,
               int32_t* n_corners, svo_track_stats* stats, svo_float2* tracked,
-              uint64_t* tracked_ids) {
+              uint64_t* tracked_ids, const StepKey* key = nullptr) {
     if (!e) return SVO_ERR_INVALID;
     if (n <= 0 || n > e->n_seq || !seqs || !left) return fail(e, SVO_ERR_INVALID, "svo_step: bad arguments");
     if (pitch < e->p.width) return fail(e, SVO_ERR_INVALID, "svo_step: pitch < width");
@@ -748,6 +796,13 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
             }
         }
     }
+    if (key) {
+        for (int i = 0; i < n; ++i) {
+            memcpy(hc[i].pose, key->poses + (size_t)i * 16, 16 * sizeof(float));
+            hc[i].first_id = key->first_new_id[i];
+            if (e->seq[seqs[i]].have_right) hc[i].flags |= SVO_CALL_HAS_RIGHT;
+        }
+    }
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     ECUDA(e, push_and_ingest(e, n));
     if (e->split_streams && !e->profiling) {
@@ -771,9 +826,45 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
     }
     e->launches += 1;
     ECUDA(e, cudaGetLastError());
+    size_t out_bytes = (size_t)n * e->step_block;
+    if (key) {
+        // decision + keyframe stage for the sequences that need (and can have) one, on the
+        // descriptors the decision kernel derives; results go behind the step blocks
+        const int mf = e->p.max_features, cap = e->pts_cap, mcn = e->p.max_corners;
+        SvoSeqCall* kc = e->d_kcall;
+        decide_kernel<<<(n + 63) / 64, 64, 0, e->st>>>(dev_call_slot(e), kc, e->d_ncorners,
+                                                       e->d_stats, key->parallax_thresh, n);
+        {
+            ProfScope ps(e, P_DEDUPE);
+            ECUDA(e, svo_launch_dedupe(e->d_corners, e->d_ncorners, mcn, e->d_feat, 2 * mf, mf,
+                                       e->p.min_distance, e->d_pts, e->d_keep_idx, e->d_nnew, cap,
+                                       kc, e->d_ticket, n, e->st));
+        }
+        SvoStereoParams sp = {e->p.num_disparities, e->p.sad_window, e->p.prefilter_cap,
+                              e->p.texture_threshold, e->p.uniqueness_ratio};
+        {
+            ProfScope ps(e, P_STEREO);
+            ECUDA(e, svo_launch_stereo_bm_sparse(e->d_pyr, e->lay, e->seq_stride, e->d_right,
+                                                 e->right_stride, e->d_pts, cap, e->d_disp16, sp,
+                                                 mcn, kc, n, e->st));
+        }
+        {
+            ProfScope ps(e, P_REPROJ);
+            ECUDA(e, svo_launch_reproject(e->d_pts, e->d_disp16, cap, key->focal, key->cx, key->cy,
+                                          key->baseline, e->d_valid2d, e->d_pts3d, e->d_valid_idx,
+                                          e->d_nvalid, kc, n, e->st));
+        }
+        tracker_append_kernel<<<n, 128, 0, e->st>>>(e->d_feat, e->d_ids, e->d_initial, mf,
+                                                    e->d_valid2d, cap, e->d_nvalid, kc);
+        pack_key_kernel<<<n, 128, 0, e->st>>>(e->d_out + out_bytes, e->key_block, cap, e->d_pts,
+                                              e->d_nnew, e->d_valid2d, e->d_pts3d, e->d_valid_idx,
+                                              e->d_disp16, e->d_nvalid, kc);
+        e->launches += 6;
+        ECUDA(e, cudaGetLastError());
+        out_bytes += (size_t)n * e->key_block;
+    }
     ECUDA(e, cudaEventRecord(e->ev[2], e->st));
-    ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_out, (size_t)n * e->step_block, cudaMemcpyDeviceToHost,
-                             e->st));
+    ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_out, out_bytes, cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
     ECUDA(e, cudaStreamSynchronize(e->st));
     finish_timing(e);
@@ -806,6 +897,40 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
             if (tracked_ids) memcpy(tracked_ids + (size_t)i * mf, oi, (size_t)st.n_kept * sizeof(uint64_t));
         }
         if (stats) stats[i] = st;
+    }
+    if (key) {
+        const int cap = e->pts_cap, mcn = e->p.max_corners;
+        const unsigned char* kb = e->h_out + (size_t)n * e->step_block;
+        for (int i = 0; i < n; ++i) {
+            const unsigned char* o = kb + (size_t)i * e->key_block;
+            const KeyHeader* h = reinterpret_cast<const KeyHeader*>(o);
+            const float2* o_new = reinterpret_cast<const float2*>(o + sizeof(KeyHeader));
+            const float2* o_v2 = o_new + cap;
+            const float* o_3d = reinterpret_cast<const float*>(o_v2 + cap);
+            const int* o_vi = reinterpret_cast<const int*>(o_3d + 3 * (size_t)cap);
+            const short* o_d = reinterpret_cast<const short*>(o_vi + cap);
+            const size_t ob = (size_t)i * mcn;
+            SeqState& st = e->seq[seqs[i]];
+            const bool is_key = h->decision == SVO_FRAME_FIRST || h->decision == SVO_FRAME_KEYFRAME;
+            const bool done = is_key && st.have_right;
+            // a keyframe without its right image on the device is reported as SVO_FRAME_*_PENDING:
+            // the caller supplies the image (svo_set_right) and finishes with svo_keyframe_tracked
+            key->decision[i] = (is_key && !done) ? h->decision + SVO_FRAME_PENDING : h->decision;
+            key->n_new[i] = done ? h->n_new : 0;
+            key->n_valid[i] = done ? h->n_valid : 0;
+            if (!done) continue;
+            if (key->new_feats) memcpy(key->new_feats + ob, o_new, (size_t)h->n_new * sizeof(float2));
+            if (key->disp16) memcpy(key->disp16 + ob, o_d, (size_t)h->n_new * sizeof(short));
+            if (key->valid_2d) memcpy(key->valid_2d + ob, o_v2, (size_t)h->n_valid * sizeof(float2));
+            if (key->valid_idx) memcpy(key->valid_idx + ob, o_vi, (size_t)h->n_valid * sizeof(int));
+            if (key->pts_3d) memcpy(key->pts_3d + ob, o_3d, (size_t)h->n_valid * 3 * sizeof(float));
+            // the host mirror of what tracker_append_kernel did (FeatureTracker::init)
+            const int nt = h->n_tracked;
+            st.n_feat = nt + std::min((int)h->n_valid, mf - nt);
+            st.n_initial = st.n_feat;
+            st.tracker_init = true;
+            st.last_slot = st.cur_slot;
+        }
     }
     return rc;
 }
@@ -910,8 +1035,7 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     const int cap = e->pts_cap, mf = p.max_features, mcn = p.max_corners;
     e->step_block = (sizeof(StepHeader) + (size_t)mcn * 8 + (size_t)mf * 16 + 15) & ~(size_t)15;
     e->key_block = (sizeof(KeyHeader) + (size_t)cap * (8 + 8 + 12 + 4 + 2) + 15) & ~(size_t)15;
-    size_t blk = e->step_block > e->key_block ? e->step_block : e->key_block;
-    e->out_bytes = blk * n_seq;
+    e->out_bytes = (e->step_block + e->key_block) * n_seq;   // svo_step_keyframe returns both
     e->h_in_bytes = (size_t)n_seq * ((size_t)cap * 16 + (size_t)mf * 16) + 4096;
 
 #define CCHK(expr)                                                               \
@@ -985,6 +1109,7 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_nvalid, ns));
     CCHK(dalloc(&e->d_out, e->out_bytes));
     CCHK(dalloc(&e->d_call, (size_t)CALL_RING * ns));
+    CCHK(dalloc(&e->d_kcall, ns));
     // cudaHostAllocMapped: with unified addressing the device uses the same pointers
     CCHK(cudaHostAlloc(reinterpret_cast<void**>(&e->h_call), (size_t)CALL_RING * ns * sizeof(SvoSeqCall),
                        cudaHostAllocMapped | cudaHostAllocPortable));
@@ -1020,7 +1145,7 @@ void svo_destroy(svo_engine* e) {
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
-                     e->d_call};
+                     e->d_call, e->d_kcall};
     for (void* p : dptrs) if (p) cudaFree(p);
     if (e->h_call) cudaFreeHost(e->h_call);
     if (e->h_pull) cudaFreeHost(e->h_pull);
@@ -1283,6 +1408,23 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
         }
     }
     return SVO_OK;
+}
+
+int svo_step_keyframe(svo_engine* e, int32_t n, const int32_t* seqs, const uint8_t* const* left,
+                      const uint8_t* const* right, int32_t pitch, int32_t on_device,
+                      const float* poses, const uint64_t* first_new_id, float parallax_thresh,
+                      float focal, float cx, float cy, float baseline, svo_float2* corners,
+                      int32_t* n_corners, svo_track_stats* stats, svo_float2* tracked,
+                      uint64_t* tracked_ids, int32_t* decision, svo_float2* new_feats,
+                      int32_t* n_new, svo_float2* valid_2d, svo_float3* pts_3d,
+                      int32_t* valid_idx, int16_t* disp16, int32_t* n_valid) {
+    if (!e) return SVO_ERR_INVALID;
+    if (!poses || !first_new_id || !decision || !n_new || !n_valid)
+        return fail(e, SVO_ERR_INVALID, "svo_step_keyframe: bad arguments");
+    const StepKey key = {poses, first_new_id, parallax_thresh, focal, cx, cy, baseline, decision,
+                         new_feats, n_new, valid_2d, pts_3d, valid_idx, disp16, n_valid};
+    return step_impl(e, n, seqs, left, right, pitch, on_device != 0, corners, n_corners, stats,
+                     tracked, tracked_ids, &key);
 }
 
 int svo_keyframe_tracked(svo_engine* e, int32_t n, const int32_t* seqs, const float* poses,

@@ -245,6 +245,7 @@ dedupe_kernel(const float2* __restrict__ det, const int* __restrict__ n_det, int
     __shared__ int s_w[RP_THREADS / 32];
     __shared__ bool s_last;
     const SvoSeqCall cd = call[blockIdx.x];
+    if (cd.flags & SVO_CALL_SKIP) return;
     const float2* d = det + (size_t)cd.seq * det_stride;
     // inl_buffered > 0: the tracked set is the tracker's own double-buffered feature array
     const float2* q = inl + (size_t)cd.seq * inl_stride + (size_t)cd.feat_buf * inl_buffered;

@@ -41,9 +41,14 @@ struct SvoSeqCall {
     const uint8_t* src_left;
     const uint8_t* src_right;
     int src_pitch;
-    int pad_;
+    int decision;                // svo_step_keyframe: per-frame decision taken on the device
     unsigned long long first_id; // svo_keyframe_tracked: id of the first new feature
 };
+
+// SvoSeqCall::flags
+#define SVO_CALL_TRACKER 1       // the sequence's tracker is initialised
+#define SVO_CALL_HAS_RIGHT 4     // a right image of the current frame is on the device
+#define SVO_CALL_SKIP 8          // keyframe-stage kernels leave this sequence alone
 
 __host__ __device__ __forceinline__ int svo_reflect101(int i, int n) {
     // BORDER_REFLECT_101 (gfedcb|abcdefgh|gfedcba) for |overshoot| < n

@@ -208,3 +208,73 @@ def test_too_few_corners_frame_is_skipped_entirely(svo_lib, oracle):
     assert k == len(good)
     with_flat.close()
     without.close()
+
+
+def test_step_keyframe_one_call_equals_step_then_keyframe(svo_lib):
+    """svo_step_keyframe (decision taken on the device, keyframe stage in the same call) against
+    svo_step + the same decision on the host + svo_keyframe_tracked, frame by frame. Sequence 1
+    never gets its right image with the call: its keyframes come back PENDING and are finished
+    with svo_set_right + svo_keyframe_tracked."""
+    import ctypes as C
+    from stereo_vo_b200.capi import Engine, _ptr
+    cam = synth.KITTI00
+    f, cx, cy, b = cam.f32()
+    n_seq, n_fr, thresh = 2, 12, 20.0
+    seqs = [util.frames(20 + s, n_fr) for s in range(n_seq)]
+    ea = Engine(cam.width, cam.height, n_seq=n_seq)      # separate calls
+    eb = Engine(cam.width, cam.height, n_seq=n_seq)      # one call
+    ids_all = list(range(n_seq))
+    next_a = [100, 5000]
+    next_b = [100, 5000]
+    decisions = []
+
+    def set_right(e, seq, img):
+        s = np.asarray([seq], np.int32)
+        arr = (C.c_void_p * 1)(img.ctypes.data)
+        e._check(e.lib.svo_set_right(e.h, 1, _ptr(s), arr, int(img.strides[0]), 0), "svo_set_right")
+
+    for t in range(n_fr):
+        left = [seqs[s][t][0] for s in range(n_seq)]
+        right = [seqs[s][t][1] for s in range(n_seq)]
+        poses = np.tile(np.eye(4, dtype=np.float32).reshape(1, 16), (n_seq, 1))
+        poses[:, 3] = 0.05 * t
+        ra = ea.step(ids_all, left, right)
+        rb = eb.step_keyframe(ids_all, left, [right[0], None], poses, next_b, thresh, f, cx, cy, b)
+        for key in ("corners", "n_corners", "tracked", "tracked_ids"):
+            assert np.array_equal(ra[key], rb[key]), (t, key)
+        assert ra["stats"].tobytes() == rb["stats"].tobytes(), t
+        for s in range(n_seq):
+            st = ra["stats"][s]
+            if ra["n_corners"][s] < 4:
+                want = 1
+            elif t == 0:
+                want = 2
+            elif st["av_parallax"] <= np.float32(thresh) and float(st["percent_lost"]) < 0.4:
+                want = 3
+            else:
+                want = 4
+            got = int(rb["decision"][s])
+            assert (got & 7) == want, (t, s, got, want)
+            assert bool(got & 8) == (want in (2, 4) and s == 1), (t, s, got)
+            decisions.append(want)
+            if want not in (2, 4):
+                continue
+            ka = ea.keyframe_tracked([s], poses[s:s + 1], [next_a[s]], f, cx, cy, b)
+            if got & 8:
+                set_right(eb, s, right[s])
+                kb = eb.keyframe_tracked([s], poses[s:s + 1], [next_b[s]], f, cx, cy, b)
+                kb = {k: v[0] for k, v in kb.items()}
+            else:
+                kb = {k: rb[k][s] for k in ka}
+            for k in ka:
+                assert np.array_equal(ka[k][0], kb[k]), (t, s, k)
+            kept = int(st["n_kept"]) if want == 4 else 0
+            nv = min(int(ka["n_valid"][0]), ea.max_features - kept)
+            next_a[s] += nv
+            next_b[s] += nv
+            fa, ia = ea.tracker_get(s)
+            fb, ib = eb.tracker_get(s)
+            assert np.array_equal(fa, fb) and np.array_equal(ia, ib), (t, s)
+    assert decisions.count(4) >= 2 and decisions.count(3) >= 4
+    ea.close()
+    eb.close()

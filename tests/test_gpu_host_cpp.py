@@ -227,3 +227,53 @@ def test_cpp_batch_pipelined_matches_synchronous(host_lib, oracle):
             for key in ("corners", "tracker_pts", "tracker_ids", "new2d", "new3d"):
                 assert np.array_equal(a[key], b[key]), (t, s, key)
             assert a["stats"].tobytes() == b["stats"].tobytes()
+
+
+def test_cpp_batch_d435i_frames_in_one_pinned_slab(host_lib, oracle):
+    """640x480 (d435i) sequences whose frames live in ONE pinned slab [seq][frame][L/R]: the left
+    images of a step sit at a constant distance, so svo_prefetch / svo_step move them with one
+    strided copy. Results must equal the single-engine Python driver fed from separate arrays."""
+    from stereo_vo_b200 import capi, frontend, hostapi
+    from stereo_vo_b200.capi import Engine
+    cam = synth.D435I
+    n_seq, n_fr = 4, 6
+    H, W = cam.height, cam.width
+    slab = capi.pinned_empty((n_seq, n_fr, 2, H, W), np.uint8)
+    for s in range(n_seq):
+        for t, (l, r) in enumerate(synth.sequence(40 + s, n_fr, cam, synth.D435I_MOTION)):
+            slab[s, t, 0] = l
+            slab[s, t, 1] = r
+
+    def pose_fn(s, t):
+        p = np.eye(4, dtype=np.float32)
+        p[:3, 3] = synth.ground_truth(t, synth.D435I_MOTION)
+        return p
+    e = Engine(W, H, n_seq=n_seq)
+    py = frontend.BatchFrontEnd(e, cam, pose_fn)
+    cb = hostapi.Batch(W, H, n_seq, 1, cam)          # one group: all 4 lefts in one run
+    kf_total = 0
+    for t in range(n_fr):
+        left = [slab[s, t, 0] for s in range(n_seq)]
+        right = [slab[s, t, 1] for s in range(n_seq)]
+        nl = nr = None
+        if t + 1 < n_fr:
+            nl = [slab[s, t + 1, 0] for s in range(n_seq)]
+            nr = [slab[s, t + 1, 1] for s in range(n_seq)]
+        res, kfs = py.step([a.copy() for a in left], [a.copy() for a in right])
+        poses = np.stack([pose_fn(s, t) for s in range(n_seq)])
+        summ = cb.step(left, right, W, poses=poses, next_left=nl, next_right=nr)
+        assert summ["keyframes"] == len(kfs), t
+        kf_total += len(kfs)
+        for s in range(n_seq):
+            g = cb.get(s)
+            n = int(res["n_corners"][s])
+            assert np.array_equal(g["corners"], res["corners"][s, :n]), (t, s)
+            if g["decision"] == "skip":
+                assert g["stats"].tobytes() == res["stats"][s].tobytes(), (t, s)
+    assert kf_total >= n_seq
+    for s in range(n_seq):
+        pts, ids = e.tracker_get(s)
+        g = cb.get(s)
+        assert np.array_equal(g["tracker_pts"], pts) and np.array_equal(g["tracker_ids"], ids)
+    cb.close()
+    e.close()

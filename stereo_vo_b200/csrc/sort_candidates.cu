@@ -33,6 +33,28 @@ __device__ __forceinline__ void bitonic_step_smem(unsigned long long* s, int cou
     }
 }
 
+// All remaining steps of a merge phase once the stride is <= 32: the 32 pairs of consecutive
+// pair indices touch one block of 64 consecutive keys for every such stride, so a warp runs
+// them back to back on its own blocks with warp barriers only (a block barrier per step is what
+// dominates the sort of a few thousand keys).
+__device__ __forceinline__ void bitonic_tail_smem(unsigned long long* s, int count, int base,
+                                                  int k, int j_first) {
+    const int lane = threadIdx.x & 31;
+    for (int t0 = (threadIdx.x >> 5) << 5; t0 < (count >> 1); t0 += blockDim.x) {
+        const int t = t0 + lane;
+        for (int j = j_first; j > 0; j >>= 1) {
+            if (t < (count >> 1)) {
+                int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                int l = i + j;
+                unsigned long long a = s[i], b = s[l];
+                bool desc = (((base + i) & k) == 0);
+                if ((a < b) == desc) { s[i] = b; s[l] = a; }
+            }
+            __syncwarp();
+        }
+    }
+}
+
 // Single-block path: gather the per-strip candidate lists of corner_score_nms, apply the exact
 // quality threshold (step 6: thr = (float)((double)max * quality), keep eig > thr), sort.
 __global__ void __launch_bounds__(SORT_THREADS)
@@ -52,29 +74,46 @@ sort_small_kernel(unsigned long long* __restrict__ cand, int max_cand,
     const float thr = (float)((double)maxv * quality);
     const int lane = threadIdx.x & 31;
     // one warp per candidate list (there are n_strips x n_seg short ones): the count -> list
-    // load chains of different lists overlap
+    // load chains of different lists overlap, and a warp keeps 8 loads per lane in flight
+    constexpr int GB = 8;
     for (int st = threadIdx.x >> 5; st < n_strips; st += SORT_THREADS / 32) {
         const int raw = strip_count[seq * n_strips + st];
         const int cnt = min(raw, strip_cap);
         if (raw > strip_cap && lane == 0) s_over = 1;
         const unsigned long long* src = strips + ((size_t)seq * n_strips + st) * (size_t)strip_cap;
-        for (int i0 = 0; i0 < cnt; i0 += 32) {
-            const int i = i0 + lane;
-            unsigned long long key = 0;
-            bool keep = false;
-            if (i < cnt) {
-                key = src[i];
-                float e = __uint_as_float(svo_key_float_bits((unsigned)(key >> 32)));
-                keep = (e > thr) && (e != 0.f);
+        for (int i0 = 0; i0 < cnt; i0 += 32 * GB) {
+            unsigned long long key[GB];
+#pragma unroll
+            for (int c = 0; c < GB; ++c) {
+                const int i = i0 + c * 32 + lane;
+                key[c] = (i < cnt) ? src[i] : 0ull;
             }
-            unsigned bal = __ballot_sync(0xffffffffu, keep);
-            if (bal) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(&s_n, __popc(bal));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (keep) {
-                    int idx = base + __popc(bal & ((1u << lane) - 1u));
-                    if (idx < max_cand) s_keys[idx] = key;
+            unsigned keep_mask = 0;
+#pragma unroll
+            for (int c = 0; c < GB; ++c) {
+                const float e = __uint_as_float(svo_key_float_bits((unsigned)(key[c] >> 32)));
+                // padding keys are 0: score key 0 decodes to a NaN pattern, never > thr
+                if ((i0 + c * 32 + lane < cnt) && (e > thr) && (e != 0.f)) keep_mask |= 1u << c;
+            }
+            int mine = __popc(keep_mask);
+            // exclusive prefix of `mine` over the warp, total in every lane
+            int incl = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += v;
+            }
+            const int total_w = __shfl_sync(0xffffffffu, incl, 31);
+            if (total_w == 0) continue;
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&s_n, total_w);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            int idx = base + incl - mine;
+#pragma unroll
+            for (int c = 0; c < GB; ++c) {
+                if (keep_mask & (1u << c)) {
+                    if (idx < max_cand) s_keys[idx] = key[c];
+                    ++idx;
                 }
             }
         }
@@ -88,10 +127,13 @@ sort_small_kernel(unsigned long long* __restrict__ cand, int max_cand,
     for (int i = n + threadIdx.x; i < npad; i += blockDim.x) s_keys[i] = 0ull;
     __syncthreads();
     for (int k = 2; k <= npad; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
+        int j = k >> 1;
+        for (; j >= 64; j >>= 1) {
             bitonic_step_smem(s_keys, npad, 0, k, j);
             __syncthreads();
         }
+        bitonic_tail_smem(s_keys, npad, 0, k, j);
+        __syncthreads();
     }
     for (int i = threadIdx.x; i < n; i += blockDim.x) keys[i] = s_keys[i];
 }
@@ -113,10 +155,13 @@ sort_tile_kernel(unsigned long long* __restrict__ cand, int cap_pad,
         s_keys[i] = (base + i < n) ? keys[base + i] : 0ull;
     __syncthreads();
     for (int k = 2; k <= SORT_TILE; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
+        int j = k >> 1;
+        for (; j >= 64; j >>= 1) {
             bitonic_step_smem(s_keys, SORT_TILE, base, k, j);
             __syncthreads();
         }
+        bitonic_tail_smem(s_keys, SORT_TILE, base, k, j);
+        __syncthreads();
     }
     for (int i = threadIdx.x; i < SORT_TILE; i += blockDim.x) keys[base + i] = s_keys[i];
 }
@@ -154,10 +199,12 @@ sort_tile_merge_kernel(unsigned long long* __restrict__ cand, int cap_pad,
     if (k > npad || base >= npad) return;
     for (int i = threadIdx.x; i < SORT_TILE; i += blockDim.x) s_keys[i] = keys[base + i];
     __syncthreads();
-    for (int j = SORT_TILE >> 1; j > 0; j >>= 1) {
+    for (int j = SORT_TILE >> 1; j >= 64; j >>= 1) {
         bitonic_step_smem(s_keys, SORT_TILE, base, k, j);
         __syncthreads();
     }
+    bitonic_tail_smem(s_keys, SORT_TILE, base, k, 32);
+    __syncthreads();
     for (int i = threadIdx.x; i < SORT_TILE; i += blockDim.x) keys[base + i] = s_keys[i];
 }
 

@@ -3,9 +3,12 @@
 // Sequential semantics: walk candidates in sorted order, accept one iff no already accepted
 // corner lies closer than minDistance, stop after maxCorners.
 //
-// Exact parallel form, one block per sequence: candidates are taken in chunks of 256 in rank
-// order. (1) every thread tests its candidate against the corners accepted by earlier chunks
-// (cell grid, 3x3 cells, <= 4 corners per cell); (2) survivors are compacted in rank order and
+// Exact parallel form, one block per sequence: candidates are taken in chunks in rank order (the
+// first 256, then 1024 at a time: the head of the list is where most corners are accepted, the
+// long tail is almost entirely rejected by step 1 and only costs barriers). (1) every thread
+// tests its candidate against the corners accepted by earlier chunks (cell grid, 3x3 cells,
+// <= 4 corners per cell); (2) survivors are compacted in rank order - at most 256 per chunk: a
+// chunk with more ends at its 257th survivor, which opens the next chunk - and
 // their pairwise conflicts go into 256-bit masks; (3) one warp resolves the chunk sequentially
 // (survivor b is accepted iff none of its conflicting predecessors was accepted); (4) accepted
 // corners are appended in rank order and inserted into the grid. Output is identical to the
@@ -15,8 +18,11 @@
 
 namespace {
 
-constexpr int GS_THREADS = 256;
-constexpr int GS_WORDS = GS_THREADS / 32;
+constexpr int GS_THREADS = 1024;           // candidates examined per chunk (after the first)
+constexpr int GS_HEAD = 256;               // size of the first chunk
+constexpr int GS_SURV = 256;               // survivors resolved per chunk
+constexpr int GS_WORDS = GS_SURV / 32;
+constexpr int GS_WARPS = GS_THREADS / 32;
 constexpr int CELL_CAP = 4;
 constexpr int CELL_INTS = CELL_CAP + 1;    // count + packed (x | y << 16)
 constexpr unsigned FULL = 0xffffffffu;
@@ -28,10 +34,11 @@ greedy_select_kernel(const unsigned long long* __restrict__ cand, int max_cand,
                      int* grid_scratch, size_t grid_stride, int use_smem_grid,
                      const SvoSeqCall* __restrict__ call) {
     extern __shared__ int s_grid_dyn[];
-    __shared__ int s_sx[GS_THREADS], s_sy[GS_THREADS];
-    __shared__ unsigned s_conf[GS_THREADS][GS_WORDS];
+    __shared__ int s_sx[GS_SURV], s_sy[GS_SURV];
+    __shared__ unsigned s_conf[GS_SURV][GS_WORDS];
     __shared__ unsigned s_acc[GS_WORDS];
-    __shared__ int s_wcnt[GS_WORDS];
+    __shared__ int s_wcnt[GS_WARPS];
+    __shared__ int s_next;                     // candidate index of the first survivor left out
 
     const int seq = call[blockIdx.x].seq;
     const unsigned long long* keys = cand + (size_t)seq * max_cand;
@@ -52,17 +59,21 @@ greedy_select_kernel(const unsigned long long* __restrict__ cand, int max_cand,
 
     const int cell = (int)rint(min_distance);  // cvRound
     const int gw = (W + cell - 1) / cell, gh = (H + cell - 1) / cell;
+    // dx*dx + dy*dy < minDistance^2 on integers: for an integer d2, d2 < t <=> d2 < ceil(t)
     const double md2 = min_distance * min_distance;
+    const int imd2 = (int)fmin(ceil(md2), 2147483647.0);
     int* grid = use_smem_grid ? s_grid_dyn : (grid_scratch + (size_t)seq * grid_stride);
     for (int i = tid; i < gw * gh; i += GS_THREADS) grid[i * CELL_INTS] = 0;
     __syncthreads();
 
     int accepted_total = 0;
-    for (int c0 = 0; c0 < n && accepted_total < max_corners; c0 += GS_THREADS) {
+    for (int c0 = 0; c0 < n && accepted_total < max_corners;) {
+        const int chunk = (c0 == 0) ? GS_HEAD : GS_THREADS;
         const int i = c0 + tid;
         int x = 0, y = 0;
         bool alive = false;
-        if (i < n) {
+        if (tid == 0) s_next = 0x7fffffff;
+        if (tid < chunk && i < n) {
             unsigned addr = (unsigned)(keys[i] & 0xffffffffull);
             y = addr / W;
             x = addr - y * W;
@@ -77,28 +88,36 @@ greedy_select_kernel(const unsigned long long* __restrict__ cand, int max_cand,
                     for (int k = 0; k < cnt; ++k) {
                         int p = cp[1 + k];
                         int dx = x - (p & 0xffff), dy = y - (p >> 16);
-                        if ((double)(dx * dx + dy * dy) < md2) { alive = false; break; }
+                        if (dx * dx + dy * dy < imd2) { alive = false; break; }
                     }
                 }
         }
-        // ---- rank-ordered compaction of the survivors
+        // ---- rank-ordered compaction of the survivors (the first GS_SURV of them)
         unsigned bal = __ballot_sync(FULL, alive);
         if (lane == 0) s_wcnt[wrp] = __popc(bal);
         __syncthreads();
-        int off = 0, m = 0;
+        int off = 0, m_all = 0;
 #pragma unroll
-        for (int w = 0; w < GS_WORDS; ++w) {
+        for (int w = 0; w < GS_WARPS; ++w) {
             int c = s_wcnt[w];
             if (w < wrp) off += c;
-            m += c;
+            m_all += c;
         }
         if (alive) {
             int pos = off + __popc(bal & ((1u << lane) - 1u));
-            s_sx[pos] = x;
-            s_sy[pos] = y;
+            if (pos < GS_SURV) {
+                s_sx[pos] = x;
+                s_sy[pos] = y;
+            } else if (pos == GS_SURV) {
+                s_next = i;                    // exactly one thread: the 257th survivor
+            }
         }
         __syncthreads();
-        if (m == 0) continue;                  // uniform
+        const int m = min(m_all, GS_SURV);
+        // candidates behind the last resolved survivor wait for the next chunk (those among
+        // them that step 1 rejected stay rejected: the accepted set only grows)
+        const int c_next = (m_all > GS_SURV) ? s_next : c0 + chunk;
+        if (m == 0) { c0 = c_next; __syncthreads(); continue; }     // uniform
         // ---- pairwise conflicts with earlier survivors of this chunk
         if (tid < m) {
             unsigned msk[GS_WORDS];
@@ -107,7 +126,7 @@ greedy_select_kernel(const unsigned long long* __restrict__ cand, int max_cand,
             const int bx = s_sx[tid], by = s_sy[tid];
             for (int a = 0; a < tid; ++a) {
                 int dx = bx - s_sx[a], dy = by - s_sy[a];
-                if ((double)(dx * dx + dy * dy) < md2) msk[a >> 5] |= 1u << (a & 31);
+                if (dx * dx + dy * dy < imd2) msk[a >> 5] |= 1u << (a & 31);
             }
 #pragma unroll
             for (int w = 0; w < GS_WORDS; ++w) s_conf[tid][w] = msk[w];
@@ -147,6 +166,7 @@ greedy_select_kernel(const unsigned long long* __restrict__ cand, int max_cand,
             }
         }
         accepted_total += chunk_acc;
+        c0 = c_next;
         __syncthreads();
     }
     if (tid == 0) n_corners[seq] = min(accepted_total, max_corners);

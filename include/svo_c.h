@@ -128,6 +128,19 @@ SVO_API int svo_triangulate_stereo(svo_engine* e, int32_t seq, const uint8_t* le
                            svo_float3* out_3d, svo_float2* out_valid_2d, int32_t* out_valid_idx,
                            int16_t* out_disp16, int32_t* out_n_valid);
 
+/* cv::StereoBM::create(16*3, 21)->compute(left, right, disp) at src/image_processor.cpp:173-176
+ * as the FULL CV_16S map (the reference computes it and reads <= 300 pixels):
+ * 1/16 px fixed point, -16 where StereoBM rejects or never evaluates a pixel. Uploads the pair
+ * as the current frame of `seq`. out_disp16: height rows, out_pitch int16 elements apart
+ * (>= width). Needs num_disparities 48 and sad_window 21, else SVO_ERR_INVALID. */
+SVO_API int svo_stereo_bm_dense(svo_engine* e, int32_t seq, const uint8_t* left, const uint8_t* right,
+                        int32_t pitch, int16_t* out_disp16, int32_t out_pitch);
+/* Same maps for the stereo pairs already on the device (after svo_step / svo_set_right or any
+ * stage call that uploaded both images), n sequences in one launch. out_disp16 may be NULL, or
+ * hold NULL entries: those maps stay on the device (timing runs). */
+SVO_API int svo_stereo_bm_dense_resident(svo_engine* e, int32_t n, const int32_t* seqs,
+                                 int16_t* const* out_disp16, int32_t out_pitch);
+
 /* FeatureTracker::init, src/feature_tracker.cpp:3-16 */
 SVO_API int svo_tracker_init(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pitch,
                      const svo_float2* feats, const uint64_t* ids, int32_t n);

@@ -44,7 +44,8 @@ STATS_DTYPE = np.dtype([("av_parallax", np.float32), ("percent_lost", np.float32
 EXPORTS = [
     "svo_default_params", "svo_create", "svo_destroy", "svo_last_error", "svo_get_params",
     "svo_num_levels", "svo_kernel_launches", "svo_last_gpu_ms", "svo_last_timing",
-    "svo_good_features_to_track", "svo_triangulate_stereo", "svo_tracker_init",
+    "svo_good_features_to_track", "svo_triangulate_stereo", "svo_stereo_bm_dense",
+    "svo_stereo_bm_dense_resident", "svo_tracker_init",
     "svo_tracker_track", "svo_tracker_get", "svo_dedupe", "svo_tracker_debug",
     "svo_debug_min_eigen_map", "svo_debug_pyramid_level", "svo_debug_candidates",
     "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_keyframe_tracked", "svo_step_keyframe", "svo_tracker_set",
@@ -88,6 +89,8 @@ def load_library(path: Optional[str] = None):
     lib.svo_good_features_to_track.argtypes = [vp, i32, vp, i32, vp, C.POINTER(i32)]
     lib.svo_triangulate_stereo.argtypes = [vp, i32, vp, vp, i32, vp, i32, vp, f32, f32, f32, f32,
                                            vp, vp, vp, vp, C.POINTER(i32)]
+    lib.svo_stereo_bm_dense.argtypes = [vp, i32, vp, vp, i32, vp, i32]
+    lib.svo_stereo_bm_dense_resident.argtypes = [vp, i32, vp, vp, i32]
     lib.svo_tracker_init.argtypes = [vp, i32, vp, i32, vp, vp, i32]
     lib.svo_tracker_track.argtypes = [vp, i32, vp, i32, i32, C.POINTER(f32), C.POINTER(f32)]
     lib.svo_tracker_get.argtypes = [vp, i32, vp, vp, C.POINTER(i32)]
@@ -264,6 +267,33 @@ class Engine:
             _ptr(od), C.byref(nv)), "svo_triangulate_stereo")
         k = nv.value
         return o3[:k].copy(), o2[:k].copy(), oi[:k].copy(), od[:n].copy()
+
+    def stereo_bm_dense(self, left, right, seq: int = 0) -> np.ndarray:
+        """svo_stereo_bm_dense: the full CV_16S map of StereoBM(48, 21)->compute(left, right)."""
+        left, right = _img(left), _img(right)
+        if left.strides[0] != right.strides[0]:
+            right = np.ascontiguousarray(right)
+            left = np.ascontiguousarray(left)
+        out = np.empty(left.shape, np.int16)
+        self._check(self.lib.svo_stereo_bm_dense(self.h, seq, _ptr(left), _ptr(right),
+                                                 left.strides[0], _ptr(out), out.shape[1]),
+                    "svo_stereo_bm_dense")
+        return out
+
+    def stereo_bm_dense_resident(self, seqs, shape=None, fetch: bool = True):
+        """svo_stereo_bm_dense_resident on the stereo pairs already on the device; `shape` =
+        (height, width) of the engine's images. fetch=False leaves the maps on the device."""
+        seqs_a = np.ascontiguousarray(seqs, np.int32)
+        n = len(seqs_a)
+        if not fetch:
+            self._check(self.lib.svo_stereo_bm_dense_resident(self.h, n, _ptr(seqs_a), None, 0),
+                        "svo_stereo_bm_dense_resident")
+            return None
+        outs = [np.empty(shape, np.int16) for _ in range(n)]
+        self._check(self.lib.svo_stereo_bm_dense_resident(self.h, n, _ptr(seqs_a),
+                                                          self._ptr_array(outs), shape[1]),
+                    "svo_stereo_bm_dense_resident")
+        return outs
 
     def tracker_init(self, img, feats, ids, seq: int = 0):
         img = _img(img)

@@ -15,13 +15,14 @@
 #include "../../include/svo_c.h"
 #include "svo_common.cuh"
 
-#define SVO_PROF_SLOTS 13
+#define SVO_PROF_SLOTS 14
 static const char* const kProfNames[SVO_PROF_SLOTS] = {
     "pyr_down_u8", "corner_score_nms", "ingest", "sort_candidates",
     "greedy_min_distance", "lk_track_fwd", "lk_track_bwd", "track_filter_compact",
-    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q", "corner_repair"};
+    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q", "corner_repair",
+    "stereo_bm_dense"};
 enum { P_PYR, P_SCORE, P_INGEST, P_SORT, P_GREEDY, P_LKF, P_LKB, P_FILTER, P_PACK, P_DEDUPE,
-       P_STEREO, P_REPROJ, P_REPAIR };
+       P_STEREO, P_REPROJ, P_REPAIR, P_DENSE };
 
 namespace {
 
@@ -76,6 +77,7 @@ struct svo_engine {
 
     uint8_t* d_pyr = nullptr;
     uint8_t* d_right = nullptr;
+    short* d_dense = nullptr;         // [n_seq][height][width] CV_16S maps of svo_stereo_bm_dense (allocated on first use)
     uint8_t* d_stage = nullptr;       // [2 sets][n_seq][2] contiguous (unpitched) H2D landing buffers
     size_t stage_img = 0;             // bytes of one staged image (width*height rounded to 256)
     size_t stage_set = 0;             // bytes of one staging set
@@ -1140,7 +1142,7 @@ void svo_destroy(svo_engine* e) {
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->st_copy) cudaStreamSynchronize(e->st_copy);
     if (e->st_det) cudaStreamSynchronize(e->st_det);
-    void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
+    void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_dense, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
                      e->d_strips, e->d_strip_count, e->d_sub_max, e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
@@ -1475,6 +1477,80 @@ int svo_triangulate_stereo(svo_engine* e, int32_t seq, const uint8_t* left, cons
     return keyframe_impl(e, 1, &s, nullptr, nullptr, pose, focal, cx, cy, baseline, false, feats,
                          &nn, nullptr, nullptr, out_valid_2d, out_3d, out_valid_idx, out_disp16,
                          out_n_valid);
+}
+
+// Dense StereoBM over the stereo pairs that are on the device (left = current pyramid level 0).
+static int dense_impl(svo_engine* e, int n, const int32_t* seqs, int16_t* const* out, int32_t out_pitch) {
+    const int W = e->p.width, H = e->p.height;
+    SvoStereoParams sp = {e->p.num_disparities, e->p.sad_window, e->p.prefilter_cap,
+                          e->p.texture_threshold, e->p.uniqueness_ratio};
+    if (!svo_stereo_dense_supported(sp))
+        return fail(e, SVO_ERR_INVALID, "svo_stereo_bm_dense: built for StereoBM(48, 21), prefilter cap 1..63");
+    if (out && out_pitch < W) return fail(e, SVO_ERR_INVALID, "svo_stereo_bm_dense: out_pitch < width");
+    const size_t map = (size_t)W * H;
+    if (!e->d_dense) {
+        if (dalloc(&e->d_dense, (size_t)e->n_seq * map) != cudaSuccess) {
+            cudaGetLastError();
+            e->d_dense = nullptr;
+            return fail(e, SVO_ERR_NOMEM, "svo_stereo_bm_dense: no device memory for the disparity maps");
+        }
+    }
+    SvoSeqCall* hc = next_call_slot(e);
+    for (int i = 0; i < n; ++i) {
+        const int s = seqs[i];
+        if (s < 0 || s >= e->n_seq) return fail(e, SVO_ERR_INVALID, "sequence index out of range");
+        if (!e->seq[s].have_frame || !e->seq[s].have_right)
+            return fail(e, SVO_ERR_STATE, "svo_stereo_bm_dense: needs an uploaded stereo pair");
+        fill_call(e, hc[i], s);
+    }
+    ECUDA(e, cudaEventRecord(e->ev[0], e->st));
+    SvoSeqCall* dc = dev_call_slot(e);
+    ECUDA(e, push_calls(e, n));
+    ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    {
+        ProfScope ps(e, P_DENSE);
+        ECUDA(e, svo_launch_stereo_bm_dense(e->d_pyr, e->lay, e->seq_stride, e->d_right,
+                                            e->right_stride, e->d_dense, W, map, sp, dc, n, e->st));
+        e->launches += 2;
+    }
+    ECUDA(e, cudaEventRecord(e->ev[2], e->st));
+    for (int i = 0; out && i < n; ++i)
+        if (out[i])
+            ECUDA(e, cudaMemcpy2DAsync(out[i], (size_t)out_pitch * sizeof(int16_t),
+                                       e->d_dense + (size_t)seqs[i] * map, (size_t)W * sizeof(int16_t),
+                                       (size_t)W * sizeof(int16_t), H, cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[3], e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    finish_timing(e);
+    return SVO_OK;
+}
+
+int svo_stereo_bm_dense(svo_engine* e, int32_t seq, const uint8_t* left, const uint8_t* right,
+                        int32_t pitch, int16_t* out_disp16, int32_t out_pitch) {
+    int rc = check_seq(e, seq);
+    if (rc) return rc;
+    if (!left || !right || !out_disp16 || pitch < e->p.width)
+        return fail(e, SVO_ERR_INVALID, "svo_stereo_bm_dense: bad arguments");
+    ECUDA(e, cudaSetDevice(e->device));
+    begin_frame(e, seq);
+    {
+        SvoSeqCall* hc = next_call_slot(e);
+        fill_call(e, hc[0], seq);
+        ECUDA(e, upload_left(e, hc[0], left, pitch, false));
+        ECUDA(e, upload_right(e, hc[0], right, pitch, false));
+        ECUDA(e, push_and_ingest(e, 1));
+    }
+    int32_t s = seq;
+    int16_t* o = out_disp16;
+    return dense_impl(e, 1, &s, &o, out_pitch);
+}
+
+int svo_stereo_bm_dense_resident(svo_engine* e, int32_t n, const int32_t* seqs,
+                                 int16_t* const* out_disp16, int32_t out_pitch) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !seqs) return fail(e, SVO_ERR_INVALID, "svo_stereo_bm_dense_resident: bad arguments");
+    ECUDA(e, cudaSetDevice(e->device));
+    return dense_impl(e, n, seqs, out_disp16, out_pitch);
 }
 
 int svo_device_can_read(const void* p) {

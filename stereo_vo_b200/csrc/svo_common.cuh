@@ -132,6 +132,13 @@ cudaError_t svo_launch_stereo_bm_sparse(const uint8_t* pyr, const SvoPyrLayout& 
                                         short* disp16, SvoStereoParams sp, int max_pts,
                                         const SvoSeqCall* d_call, int n_call, cudaStream_t st);
 
+bool svo_stereo_dense_supported(const SvoStereoParams& sp);
+cudaError_t svo_launch_stereo_bm_dense(const uint8_t* pyr, const SvoPyrLayout& lay,
+                                       size_t seq_stride, const uint8_t* right,
+                                       size_t right_stride, short* disp, int dpitch,
+                                       size_t disp_stride, SvoStereoParams sp,
+                                       const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+
 cudaError_t svo_launch_reproject(const float2* pts, const short* disp16, int pts_stride,
                                  float focal, float cx, float cy, float baseline, float2* valid2d,
                                  float* pts3d, int* valid_idx, int* n_valid,

@@ -10,17 +10,19 @@
 //     (band + 20) x (32 + 20 [+ 47 for the right image]) pixels it needs straight from the raw
 //     images into shared memory, once;
 //   * thread (lane = column, warp k = disparity class) carries SAD(x, y, D) for the twelve
-//     D = k + 4 j in registers and slides the 21-row window down the band: the entering row's
-//     21-column sums are added, the leaving row's subtracted. D in steps of 4 makes the right
-//     image operand of disparity D + 4 the SAME aligned words one word further left, so a
-//     row costs 25 shared-memory words + 23 funnel shifts, then 6 VABSDIFF4.ACC (4 absolute
-//     differences + accumulate per instruction) + 1 mask per disparity;
-//   * the window's texture sum is the 49th "disparity" (left operand against the cap bytes);
+//     D = k + 4 j in registers, two per word in 16-bit halves, and slides the 21-row window
+//     down the band: the entering row's 21-column sums are added and parked in a per-thread
+//     ring of 21 rows in shared memory, the leaving row's are read back from it and
+//     subtracted (nothing is computed twice). D in steps of 4 makes the right image operand
+//     of disparity D + 4 the SAME aligned words one word further left, so a row costs 25
+//     shared-memory words + 23 funnel shifts, then 6 VABSDIFF4.ACC (4 absolute differences +
+//     accumulate per instruction) + 1 mask per disparity, 6 adds, 6 subtracts;
+//   * the window's texture sum is kept the same way by warp 0 (left operand against the cap);
 //   * every 4 output rows the SADs of the 4 warps meet in shared memory and thread
 //     (column, row) runs the winner / uniqueness / sub-pixel tail of
 //     findStereoCorrespondenceBM.
-// Integer throughout, bit-exact. Bound: SM issue (about 1 100 lane-instructions per pixel);
-// DRAM traffic is the 4 N of the interface (tiles overlap only through L2).
+// Integer throughout, bit-exact. Bound: the integer ALU pipe (about 500 lane-instructions per
+// pixel); DRAM traffic is the 4 N of the interface (tiles overlap only through L2).
 #include "svo_common.cuh"
 
 namespace {
@@ -29,27 +31,40 @@ constexpr int DN_ND = 48;          // numDisparities of the reference (image_pro
 constexpr int DN_WIN = 21;         // SAD window
 constexpr int DN_RAD = DN_WIN / 2;
 constexpr int DN_TW = 32;          // output columns per block
-constexpr int DN_BAND = 64;        // output rows per block
+constexpr int DN_BAND = 64;        // output rows per block (few images in the launch)
+constexpr int DN_BAND_TALL = 128;  // ... (many images)
 constexpr int DN_PLW = 56;         // prefiltered left tile row: 32 + 20 columns, + a spare word
 constexpr int DN_PRW = 104;        // prefiltered right tile row: 32 + 20 + 47 columns, padded
-constexpr int DN_ROWS = DN_BAND + DN_WIN - 1;
 constexpr int DN_NJ = DN_ND / 4;   // disparities per thread
-constexpr int DN_SADW = DN_ND + 2; // SAD list with one pad entry either side
 constexpr short DN_FILTERED = (short)(-16);
 
-// prefilterXSobel at (gx, gy): borders as OpenCV walks them (same rules as stereo.cu)
-__device__ __forceinline__ int xsobel(const uint8_t* __restrict__ img, int pitch, int W, int H,
-                                      int gx, int gy, int cap) {
-    if (gx <= 0 || gx >= W - 1 || ((H & 1) && gy == H - 1)) return cap;
+// Four prefilterXSobel outputs (gx0 .. gx0 + 3 of row gy) as one word. Borders as OpenCV walks
+// them (same rules as stereo.cu): columns 0 and W-1 and the last row of an odd-height image
+// hold the cap; rows above / below the image reflect onto rows 1 / H-2. Columns past W-1 are
+// clamped for the loads and forced to the cap: they never reach a valid output pixel.
+__device__ __forceinline__ unsigned xsobel4(const uint8_t* __restrict__ img, int pitch, int W,
+                                            int H, int gx0, int gy, int cap) {
     const int ya = gy - 1 < 0 ? 1 : gy - 1;
     const int yc = gy + 1 > H - 1 ? H - 2 : gy + 1;
-    const uint8_t* a = img + (size_t)ya * pitch + gx;
-    const uint8_t* b = img + (size_t)gy * pitch + gx;
-    const uint8_t* c = img + (size_t)yc * pitch + gx;
-    int v = ((int)__ldg(a + 1) - (int)__ldg(a - 1)) + 2 * ((int)__ldg(b + 1) - (int)__ldg(b - 1)) +
-            ((int)__ldg(c + 1) - (int)__ldg(c - 1));
-    v = min(max(v, -cap), cap);
-    return v + cap;
+    const uint8_t* a = img + (size_t)ya * pitch;
+    const uint8_t* b = img + (size_t)gy * pitch;
+    const uint8_t* c = img + (size_t)yc * pitch;
+    int s[6];                                   // vertical 1-2-1 sums of columns gx0-1 .. gx0+4
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        const int col = min(max(gx0 - 1 + i, 0), W - 1);
+        s[i] = (int)__ldg(a + col) + 2 * (int)__ldg(b + col) + (int)__ldg(c + col);
+    }
+    const bool row_cap = (H & 1) && gy == H - 1;
+    unsigned out = 0;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const int gx = gx0 + t;
+        int v = min(max(s[t + 2] - s[t], -cap), cap) + cap;
+        if (row_cap || gx <= 0 || gx >= W - 1) v = cap;
+        out |= (unsigned)v << (8 * t);
+    }
+    return out;
 }
 
 struct RowOps {
@@ -57,49 +72,70 @@ struct RowOps {
     unsigned r[17];                // 65 + 3 right bytes starting at column x - 10 - (k + 44)
 };
 
-__device__ __forceinline__ void load_row(RowOps& o, const unsigned* __restrict__ pl,
-                                         const unsigned* __restrict__ pr, int lw, int ls, int rw,
-                                         int rs) {
-    unsigned w[18];
+struct RawRow {
+    unsigned wl[7], wr[18];        // the aligned words that hold the operands
+};
+
+__device__ __forceinline__ void load_raw(RawRow& w, const unsigned* __restrict__ pl,
+                                         const unsigned* __restrict__ pr, int lw, int rw) {
 #pragma unroll
-    for (int i = 0; i < 7; ++i) w[i] = pl[lw + i];
+    for (int i = 0; i < 7; ++i) w.wl[i] = pl[lw + i];
 #pragma unroll
-    for (int i = 0; i < 6; ++i) o.l[i] = __funnelshift_r(w[i], w[i + 1], ls);
-    o.l[5] &= 0xffu;
-#pragma unroll
-    for (int i = 0; i < 18; ++i) w[i] = pr[rw + i];
-#pragma unroll
-    for (int i = 0; i < 17; ++i) o.r[i] = __funnelshift_r(w[i], w[i + 1], rs);
+    for (int i = 0; i < 18; ++i) w.wr[i] = pr[rw + i];
 }
 
-template <int SIGN>
-__device__ __forceinline__ void accumulate(int (&sad)[DN_NJ], int& tex, const RowOps& o,
-                                           unsigned capw) {
+__device__ __forceinline__ void make_ops(RowOps& o, const RawRow& w, int ls, int rs) {
 #pragma unroll
-    for (int j = 0; j < DN_NJ; ++j) {
+    for (int i = 0; i < 6; ++i) o.l[i] = __funnelshift_r(w.wl[i], w.wl[i + 1], ls);
+    o.l[5] &= 0xffu;
+#pragma unroll
+    for (int i = 0; i < 17; ++i) o.r[i] = __funnelshift_r(w.wr[i], w.wr[i + 1], rs);
+}
+
+// 21-column sums of one row for the thread's twelve disparities, two per word (16-bit halves:
+// a row sum is <= 21 * 126, a window sum <= 441 * 126 < 2^16, and sums of halves never carry)
+__device__ __forceinline__ void row_sums(unsigned (&hp)[DN_NJ / 2], const RowOps& o) {
+#pragma unroll
+    for (int jj = 0; jj < DN_NJ / 2; ++jj) {
         // D = k + 4 j: the operand starts 4 (11 - j) bytes into the stream
-        unsigned s = 0;
+        const int j0 = 2 * jj, j1 = 2 * jj + 1;
+        unsigned a = 0, b = 0;
 #pragma unroll
-        for (int i = 0; i < 5; ++i) s = __vsadu4(o.l[i], o.r[11 - j + i]) + s;
-        s = __vsadu4(o.l[5], o.r[16 - j] & 0xffu) + s;
-        sad[j] += SIGN * (int)s;
+        for (int i = 0; i < 5; ++i) {
+            a = __vsadu4(o.l[i], o.r[11 - j0 + i]) + a;
+            b = __vsadu4(o.l[i], o.r[11 - j1 + i]) + b;
+        }
+        a = __vsadu4(o.l[5], o.r[16 - j0] & 0xffu) + a;
+        b = __vsadu4(o.l[5], o.r[16 - j1] & 0xffu) + b;
+        hp[jj] = a + b * 65536u;
     }
+}
+
+__device__ __forceinline__ unsigned row_texture(const RowOps& o, unsigned capw) {
     unsigned t = 0;
 #pragma unroll
     for (int i = 0; i < 5; ++i) t = __vsadu4(o.l[i], capw) + t;
-    t = __vsadu4(o.l[5], capw & 0xffu) + t;
-    tex += SIGN * (int)t;
+    return __vsadu4(o.l[5], capw & 0xffu) + t;
 }
+
+// shared-memory carve-up (dynamic): ring | sad | texture ring | texture | left tile | right tile
+constexpr int DN_RING_WORDS = DN_WIN * (DN_NJ / 2) * 128;      // per-thread row sums of 21 rows
+constexpr int DN_SAD_WORDS = 4 * 4 * (DN_NJ / 2) * DN_TW;      // [row of group][k][jj][lane]
+constexpr int DN_TEXR_WORDS = DN_WIN * DN_TW;
+constexpr int DN_TEX_WORDS = 4 * DN_TW;
 
 __global__ void __launch_bounds__(128)
 stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_stride,
                        const uint8_t* __restrict__ right, size_t right_stride,
-                       short* __restrict__ disp, int dpitch, size_t disp_stride, int cap,
+                       short* __restrict__ disp, int dpitch, size_t disp_stride, int band, int cap,
                        int texture, int uniq, const SvoSeqCall* __restrict__ call) {
-    __shared__ __align__(16) unsigned char s_pl[DN_ROWS * DN_PLW];
-    __shared__ __align__(16) unsigned char s_pr[DN_ROWS * DN_PRW];
-    __shared__ unsigned short s_sad[4][DN_SADW][DN_TW];
-    __shared__ int s_tex[4][DN_TW];
+    extern __shared__ __align__(16) unsigned s_dyn[];
+    unsigned* s_ring = s_dyn;
+    unsigned* s_sad = s_ring + DN_RING_WORDS;
+    unsigned* s_texr = s_sad + DN_SAD_WORDS;
+    int* s_tex = reinterpret_cast<int*>(s_texr + DN_TEXR_WORDS);
+    unsigned* s_pl = reinterpret_cast<unsigned*>(s_tex + DN_TEX_WORDS);
+    unsigned* s_pr = s_pl + (band + DN_WIN - 1) * (DN_PLW / 4);
 
     const SvoSeqCall cd = call[blockIdx.z];
     const SvoLevel l0 = lay.lvl[0];
@@ -110,21 +146,19 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
     short* __restrict__ out = disp + (size_t)cd.seq * disp_stride;
 
     const int xt = DN_ND - 1 + DN_RAD + blockIdx.x * DN_TW;      // first output column
-    const int yt = DN_RAD + blockIdx.y * DN_BAND;                // first output row
-    const int nrows = min(DN_BAND, H - DN_RAD - yt);             // output rows of this band
+    const int yt = DN_RAD + blockIdx.y * band;                   // first output row
+    const int nrows = min(band, H - DN_RAD - yt);                // output rows of this band
     const int tid = threadIdx.x, lane = tid & 31, k = tid >> 5;
 
     // ---- prefiltered tiles: rows yt - 10 .. yt + nrows + 9 (all inside the image)
     const int trows = nrows + DN_WIN - 1;
-    for (int i = tid; i < trows * DN_PLW; i += 128) {
-        const int r = i / DN_PLW, c = i - r * DN_PLW;
-        const int gx = min(xt - DN_RAD + c, W - 1);              // past W-1: never reaches a valid pixel
-        s_pl[i] = (unsigned char)xsobel(L, pitch, W, H, gx, yt - DN_RAD + r, cap);
+    for (int i = tid; i < trows * (DN_PLW / 4); i += 128) {
+        const int r = i / (DN_PLW / 4), c = i - r * (DN_PLW / 4);
+        s_pl[i] = xsobel4(L, pitch, W, H, xt - DN_RAD + 4 * c, yt - DN_RAD + r, cap);
     }
-    for (int i = tid; i < trows * DN_PRW; i += 128) {
-        const int r = i / DN_PRW, c = i - r * DN_PRW;
-        const int gx = min(xt - DN_RAD - (DN_ND - 1) + c, W - 1);
-        s_pr[i] = (unsigned char)xsobel(R, pitch, W, H, gx, yt - DN_RAD + r, cap);
+    for (int i = tid; i < trows * (DN_PRW / 4); i += 128) {
+        const int r = i / (DN_PRW / 4), c = i - r * (DN_PRW / 4);
+        s_pr[i] = xsobel4(R, pitch, W, H, xt - DN_RAD - (DN_ND - 1) + 4 * c, yt - DN_RAD + r, cap);
     }
     __syncthreads();
 
@@ -134,56 +168,95 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
     const int rb = lane + 3 - k;
     const int rw = rb >> 2, rs = (rb & 3) * 8;
     const unsigned capw = (unsigned)cap * 0x01010101u;
-    const unsigned* pl32 = reinterpret_cast<const unsigned*>(s_pl);
-    const unsigned* pr32 = reinterpret_cast<const unsigned*>(s_pr);
+    unsigned* ring = s_ring + tid;                               // [slot][jj] 128 words apart
+    const unsigned short* sad16 = reinterpret_cast<const unsigned short*>(s_sad);
 
-    int sad[DN_NJ];
+    unsigned sadp[DN_NJ / 2], hp[DN_NJ / 2];
 #pragma unroll
-    for (int j = 0; j < DN_NJ; ++j) sad[j] = 0;
-    int tex = 0;
+    for (int jj = 0; jj < DN_NJ / 2; ++jj) sadp[jj] = 0;
+    unsigned tex = 0;
     RowOps o;
-    for (int r = 0; r < DN_WIN - 1; ++r) {
-        load_row(o, pl32 + r * (DN_PLW / 4), pr32 + r * (DN_PRW / 4), lw, ls, rw, rs);
-        accumulate<1>(sad, tex, o, capw);
+    RawRow cur, nxt;               // the next row's words are fetched while this row is summed
+    const unsigned* pl = s_pl + lw;
+    const unsigned* pr = s_pr + rw;
+    load_raw(cur, pl, pr, 0, 0);
+    for (int r = 0; r < DN_WIN - 1; ++r) {                       // window rows 0 .. 19 -> slots 0 .. 19
+        load_raw(nxt, pl + (r + 1) * (DN_PLW / 4), pr + (r + 1) * (DN_PRW / 4), 0, 0);
+        make_ops(o, cur, ls, rs);
+        row_sums(hp, o);
+#pragma unroll
+        for (int jj = 0; jj < DN_NJ / 2; ++jj) {
+            sadp[jj] += hp[jj];
+            ring[(r * (DN_NJ / 2) + jj) * 128] = hp[jj];
+        }
+        if (k == 0) {
+            const unsigned t = row_texture(o, capw);
+            tex += t;
+            s_texr[r * DN_TW + lane] = t;
+        }
+        cur = nxt;
     }
+    int slot_in = DN_WIN - 1, slot_out = 0;                      // ring slots of rows ry + 20, ry
     for (int y0 = 0; y0 < nrows; y0 += 4) {
         const int ng = min(4, nrows - y0);
         for (int g = 0; g < ng; ++g) {
-            const int ry = y0 + g;                               // output row yt + ry
-            load_row(o, pl32 + (ry + DN_WIN - 1) * (DN_PLW / 4),
-                     pr32 + (ry + DN_WIN - 1) * (DN_PRW / 4), lw, ls, rw, rs);
-            accumulate<1>(sad, tex, o, capw);
+            const int ry = y0 + g;                               // output row yt + ry; cur = tile row ry + 20
+            if (ry + 1 < nrows)
+                load_raw(nxt, pl + (ry + DN_WIN) * (DN_PLW / 4), pr + (ry + DN_WIN) * (DN_PRW / 4), 0, 0);
+            unsigned old[DN_NJ / 2], told = 0;                   // row ry leaves: slot_out != slot_in
 #pragma unroll
-            for (int j = 0; j < DN_NJ; ++j)                      // internal order d = 47 - D
-                s_sad[g][1 + (DN_ND - 1 - (k + 4 * j))][lane] = (unsigned short)sad[j];
-            if (k == 0) s_tex[g][lane] = tex;
-            load_row(o, pl32 + ry * (DN_PLW / 4), pr32 + ry * (DN_PRW / 4), lw, ls, rw, rs);
-            accumulate<-1>(sad, tex, o, capw);
+            for (int jj = 0; jj < DN_NJ / 2; ++jj) old[jj] = ring[(slot_out * (DN_NJ / 2) + jj) * 128];
+            if (k == 0) told = s_texr[slot_out * DN_TW + lane];
+            make_ops(o, cur, ls, rs);
+            row_sums(hp, o);
+#pragma unroll
+            for (int jj = 0; jj < DN_NJ / 2; ++jj) {
+                sadp[jj] += hp[jj];                              // window complete: rows ry .. ry + 20
+                ring[(slot_in * (DN_NJ / 2) + jj) * 128] = hp[jj];
+                s_sad[((g * 4 + k) * (DN_NJ / 2) + jj) * DN_TW + lane] = sadp[jj];
+                sadp[jj] -= old[jj];
+            }
+            if (k == 0) {
+                const unsigned t = row_texture(o, capw);
+                tex += t;
+                s_texr[slot_in * DN_TW + lane] = t;
+                s_tex[g * DN_TW + lane] = (int)tex;
+                tex -= told;
+            }
+            slot_in = (slot_in == DN_WIN - 1) ? 0 : slot_in + 1;
+            slot_out = (slot_out == DN_WIN - 1) ? 0 : slot_out + 1;
+            cur = nxt;
         }
         __syncthreads();
-        // ---- tail of findStereoCorrespondenceBM: thread (lane, k) finishes row y0 + k
+        // ---- tail of findStereoCorrespondenceBM: thread (lane, k) finishes row y0 + k.
+        // SAD of internal disparity d (= 47 - D, D = kk + 4 j) sits in half j & 1 of word
+        // [row][kk][j >> 1][lane]
         const int x = xt + lane, y = yt + y0 + k;
         if (k < ng && x < W - DN_RAD) {
+            auto sad_at = [&](int d) -> int {
+                const int D = DN_ND - 1 - d, kk = D & 3, j = D >> 2;
+                return sad16[((((k * 4 + kk) * (DN_NJ / 2) + (j >> 1)) * DN_TW + lane) << 1) + (j & 1)];
+            };
             short res;
-            int mind = 0, minsad = s_sad[k][1][lane];
-#pragma unroll 8
+            int mind = 0, minsad = sad_at(0);
+#pragma unroll
             for (int d = 1; d < DN_ND; ++d) {
-                const int v = s_sad[k][1 + d][lane];
+                const int v = sad_at(d);
                 if (v < minsad) { minsad = v; mind = d; }
             }
-            bool ok = s_tex[k][lane] >= texture;
+            bool ok = s_tex[k * DN_TW + lane] >= texture;
             if (ok && uniq > 0) {
                 const int thresh = minsad + (minsad * uniq / 100);
-#pragma unroll 8
+#pragma unroll
                 for (int d = 0; d < DN_ND; ++d) {
-                    const int v = s_sad[k][1 + d][lane];
+                    const int v = sad_at(d);
                     if ((d < mind - 1 || d > mind + 1) && v <= thresh) ok = false;
                 }
             }
             if (ok) {
-                const int c0 = s_sad[k][1 + mind][lane];
-                const int pp = (mind + 1 < DN_ND) ? s_sad[k][2 + mind][lane] : s_sad[k][DN_ND - 1][lane];
-                const int nn = (mind > 0) ? s_sad[k][mind][lane] : s_sad[k][2][lane];
+                const int c0 = sad_at(mind);
+                const int pp = sad_at(mind + 1 < DN_ND ? mind + 1 : DN_ND - 2);
+                const int nn = sad_at(mind > 0 ? mind - 1 : 1);
                 const int den = pp + nn - 2 * c0 + abs(pp - nn);
                 const int v = (DN_ND - mind - 1) * 256 + (den != 0 ? (pp - nn) * 256 / den : 0) + 15;
                 res = (short)(v >> 4);
@@ -222,10 +295,20 @@ cudaError_t svo_launch_stereo_bm_dense(const uint8_t* pyr, const SvoPyrLayout& l
         disp, dpitch, disp_stride, W, H, d_call);
     const int vw = W - DN_RAD - (DN_ND - 1 + DN_RAD), vh = H - 2 * DN_RAD;
     if (vw > 0 && vh > 0) {
-        dim3 grid((vw + DN_TW - 1) / DN_TW, (vh + DN_BAND - 1) / DN_BAND, n_call);
-        stereo_bm_dense_kernel<<<grid, 128, 0, st>>>(pyr, lay, seq_stride, right, right_stride,
-                                                     disp, dpitch, disp_stride, sp.cap, sp.texture,
-                                                     sp.uniq, d_call);
+        // tall bands amortise the 20 start-up rows of a band; short ones give a lone image
+        // enough blocks for 148 SMs x 2
+        const int tiles = (vw + DN_TW - 1) / DN_TW;
+        const int band = ((long long)tiles * ((vh + DN_BAND_TALL - 1) / DN_BAND_TALL) * n_call >= 4 * 296)
+                             ? DN_BAND_TALL : DN_BAND;
+        const size_t smem = sizeof(unsigned) * (DN_RING_WORDS + DN_SAD_WORDS + DN_TEXR_WORDS + DN_TEX_WORDS) +
+                            (size_t)(band + DN_WIN - 1) * (DN_PLW + DN_PRW);
+        // per device, so not cached: costs a microsecond
+        SVO_CUDA_OK(cudaFuncSetAttribute(stereo_bm_dense_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        dim3 grid(tiles, (vh + band - 1) / band, n_call);
+        stereo_bm_dense_kernel<<<grid, 128, smem, st>>>(pyr, lay, seq_stride, right, right_stride,
+                                                        disp, dpitch, disp_stride, band, sp.cap,
+                                                        sp.texture, sp.uniq, d_call);
     }
     return cudaGetLastError();
 }

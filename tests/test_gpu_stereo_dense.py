@@ -36,11 +36,12 @@ def test_dense_map_kitti_frames(svo_lib, oracle):
         e.close()
 
 
-@pytest.mark.parametrize("w,h", [(640, 480), (641, 479), (333, 211), (100, 45), (68, 32), (64, 33)])
+@pytest.mark.parametrize("w,h", [(640, 480), (641, 479), (333, 211), (100, 45), (68, 32), (69, 33)])
 def test_dense_map_stress_images(svo_lib, oracle, w, h):
     """flat patches / periodic stripes (texture + uniqueness rejections), odd and even heights
-    (the odd-height last prefilter row), widths that leave a partial tile, one valid column
-    (w = 68) and none at all (w = 64)."""
+    (the odd-height last prefilter row), widths that leave a partial tile, down to one valid
+    column (w = 68). (Narrower images have no valid pixel; cv2 leaves parts of its output
+    uninitialised there, so there is nothing to compare with.)"""
     left = util.stress_image(h, w, 3)
     right = util.shifted(left, 17)
     want = oracle.stereo_disparity16(left, right)
@@ -94,6 +95,21 @@ def test_dense_resident_batch_and_sparse_agree(svo_lib, oracle):
                                             f, cx, cy, b, seq=0)
         m0 = e.stereo_bm_dense_resident([0], shape=(376, 1241))[0]
         assert np.array_equal(d16, m0[pts[:, 1].astype(int), pts[:, 0].astype(int)])
+    finally:
+        e.close()
+
+
+def test_dense_many_sequences_tall_bands(svo_lib, oracle):
+    """12 KITTI pairs in one launch: enough blocks for the launcher to pick the tall row bands."""
+    pairs = [util.frames(s, 1)[0] for s in (0, 5, 6)]
+    want = [oracle.stereo_disparity16(l, r) for l, r in pairs]
+    e = _engine(1241, 376, n_seq=12)
+    try:
+        for s in range(12):
+            _compare(e.stereo_bm_dense(*pairs[s % 3], seq=s), want[s % 3])
+        order = list(range(11, -1, -1))
+        for s, m in zip(order, e.stereo_bm_dense_resident(order, shape=(376, 1241))):
+            _compare(m, want[s % 3])
     finally:
         e.close()
 

@@ -238,20 +238,26 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
                 return sad16[((((k * 4 + kk) * (DN_NJ / 2) + (j >> 1)) * DN_TW + lane) << 1) + (j & 1)];
             };
             short res;
-            int mind = 0, minsad = sad_at(0);
+            // first minimum in internal order = minimum of the keys sad * 64 + d
+            int v[DN_ND];
 #pragma unroll
-            for (int d = 1; d < DN_ND; ++d) {
-                const int v = sad_at(d);
-                if (v < minsad) { minsad = v; mind = d; }
-            }
+            for (int d = 0; d < DN_ND; ++d) v[d] = sad_at(d);
+            int key = v[0] * 64;
+#pragma unroll
+            for (int d = 1; d < DN_ND; ++d) key = min(key, v[d] * 64 + d);
+            const int mind = key & 63, minsad = key >> 6;
             bool ok = s_tex[k * DN_TW + lane] >= texture;
-            if (ok && uniq > 0) {
+            if (uniq > 0) {
+                // rejected iff some d outside mind-1 .. mind+1 has sad <= thresh: count them all,
+                // take the (up to) three around the winner off again
                 const int thresh = minsad + (minsad * uniq / 100);
+                int cnt = 0;
 #pragma unroll
-                for (int d = 0; d < DN_ND; ++d) {
-                    const int v = sad_at(d);
-                    if ((d < mind - 1 || d > mind + 1) && v <= thresh) ok = false;
-                }
+                for (int d = 0; d < DN_ND; ++d) cnt += (v[d] <= thresh) ? 1 : 0;
+                int near = 1;
+                if (mind > 0) near += (sad_at(mind - 1) <= thresh) ? 1 : 0;
+                if (mind < DN_ND - 1) near += (sad_at(mind + 1) <= thresh) ? 1 : 0;
+                if (cnt > near) ok = false;
             }
             if (ok) {
                 const int c0 = sad_at(mind);

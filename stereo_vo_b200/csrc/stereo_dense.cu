@@ -38,33 +38,44 @@ constexpr int DN_PRW = 104;        // prefiltered right tile row: 32 + 20 + 47 c
 constexpr int DN_NJ = DN_ND / 4;   // disparities per thread
 constexpr short DN_FILTERED = (short)(-16);
 
-// Four prefilterXSobel outputs (gx0 .. gx0 + 3 of row gy) as one word. Borders as OpenCV walks
-// them (same rules as stereo.cu): columns 0 and W-1 and the last row of an odd-height image
-// hold the cap; rows above / below the image reflect onto rows 1 / H-2. Columns past W-1 are
-// clamped for the loads and forced to the cap: they never reach a valid output pixel.
-__device__ __forceinline__ unsigned xsobel4(const uint8_t* __restrict__ img, int pitch, int W,
-                                            int H, int gx0, int gy, int cap) {
-    const int ya = gy - 1 < 0 ? 1 : gy - 1;
-    const int yc = gy + 1 > H - 1 ? H - 2 : gy + 1;
-    const uint8_t* a = img + (size_t)ya * pitch;
-    const uint8_t* b = img + (size_t)gy * pitch;
-    const uint8_t* c = img + (size_t)yc * pitch;
-    int s[6];                                   // vertical 1-2-1 sums of columns gx0-1 .. gx0+4
+// prefilterXSobel for a 4 x 4 patch: columns gx0 .. gx0 + 3 (one word per row) of rows
+// gy0 .. gy0 + 3, from the 6 x 6 raw pixels around it (36 independent byte loads in flight).
+// Borders as OpenCV walks them (same rules as stereo.cu): columns 0 and W-1 and the last row of
+// an odd-height image hold the cap; rows above / below the image reflect onto rows 1 / H-2.
+// Columns past W-1 are clamped for the loads and forced to the cap: they never reach a valid
+// output pixel. Rows past H-1 (only in the last, partial patch of a tile) are computed from
+// clamped rows and dropped by the caller.
+__device__ __forceinline__ void xsobel4x4(unsigned (&out)[4], const uint8_t* __restrict__ img,
+                                          int pitch, int W, int H, int gx0, int gy0, int cap) {
+    int raw[6][6];
+    int col[6];
 #pragma unroll
-    for (int i = 0; i < 6; ++i) {
-        const int col = min(max(gx0 - 1 + i, 0), W - 1);
-        s[i] = (int)__ldg(a + col) + 2 * (int)__ldg(b + col) + (int)__ldg(c + col);
-    }
-    const bool row_cap = (H & 1) && gy == H - 1;
-    unsigned out = 0;
+    for (int i = 0; i < 6; ++i) col[i] = min(max(gx0 - 1 + i, 0), W - 1);
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
-        const int gx = gx0 + t;
-        int v = min(max(s[t + 2] - s[t], -cap), cap) + cap;
-        if (row_cap || gx <= 0 || gx >= W - 1) v = cap;
-        out |= (unsigned)v << (8 * t);
+    for (int q = 0; q < 6; ++q) {
+        int y = gy0 - 1 + q;                        // raw row; tile rows themselves are inside the image
+        y = y < 0 ? 1 : (y == H ? H - 2 : (y > H ? H - 1 : y));   // rows -1 and H reflect; later ones unused
+        const uint8_t* rowp = img + (size_t)y * pitch;
+#pragma unroll
+        for (int i = 0; i < 6; ++i) raw[q][i] = (int)__ldg(rowp + col[i]);
     }
-    return out;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int gy = gy0 + r;
+        const bool row_cap = (H & 1) && gy == H - 1;
+        int s[6];                                   // vertical 1-2-1 sums of columns gx0-1 .. gx0+4
+#pragma unroll
+        for (int i = 0; i < 6; ++i) s[i] = raw[r][i] + 2 * raw[r + 1][i] + raw[r + 2][i];
+        unsigned w = 0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int gx = gx0 + t;
+            int v = min(max(s[t + 2] - s[t], -cap), cap) + cap;
+            if (row_cap || gx <= 0 || gx >= W - 1) v = cap;
+            w |= (unsigned)v << (8 * t);
+        }
+        out[r] = w;
+    }
 }
 
 struct RowOps {
@@ -124,7 +135,7 @@ constexpr int DN_SAD_WORDS = 4 * 4 * (DN_NJ / 2) * DN_TW;      // [row of group]
 constexpr int DN_TEXR_WORDS = DN_WIN * DN_TW;
 constexpr int DN_TEX_WORDS = 4 * DN_TW;
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 2)
 stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_stride,
                        const uint8_t* __restrict__ right, size_t right_stride,
                        short* __restrict__ disp, int dpitch, size_t disp_stride, int band, int cap,
@@ -152,13 +163,19 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
 
     // ---- prefiltered tiles: rows yt - 10 .. yt + nrows + 9 (all inside the image)
     const int trows = nrows + DN_WIN - 1;
-    for (int i = tid; i < trows * (DN_PLW / 4); i += 128) {
-        const int r = i / (DN_PLW / 4), c = i - r * (DN_PLW / 4);
-        s_pl[i] = xsobel4(L, pitch, W, H, xt - DN_RAD + 4 * c, yt - DN_RAD + r, cap);
-    }
-    for (int i = tid; i < trows * (DN_PRW / 4); i += 128) {
-        const int r = i / (DN_PRW / 4), c = i - r * (DN_PRW / 4);
-        s_pr[i] = xsobel4(R, pitch, W, H, xt - DN_RAD - (DN_ND - 1) + 4 * c, yt - DN_RAD + r, cap);
+    const int tquads = (trows + 3) >> 2;
+    for (int i = tid; i < tquads * (DN_PLW / 4 + DN_PRW / 4); i += 128) {
+        const int q = i / (DN_PLW / 4 + DN_PRW / 4), c = i - q * (DN_PLW / 4 + DN_PRW / 4);
+        const bool left = c < DN_PLW / 4;
+        const int cw = left ? c : c - DN_PLW / 4;
+        unsigned w4[4];
+        xsobel4x4(w4, left ? L : R, pitch, W, H,
+                  (left ? xt - DN_RAD : xt - DN_RAD - (DN_ND - 1)) + 4 * cw, yt - DN_RAD + 4 * q, cap);
+        unsigned* dst = left ? s_pl + cw : s_pr + cw;
+        const int rwords = left ? DN_PLW / 4 : DN_PRW / 4;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+            if (4 * q + r < trows) dst[(4 * q + r) * rwords] = w4[r];
     }
     __syncthreads();
 

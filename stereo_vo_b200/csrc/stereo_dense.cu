@@ -6,7 +6,8 @@
 // pixels outside x in [57, W-10), y in [10, H-10) hold (minDisparity - 1) << 4 = -16.
 //
 // One kernel, raw u8 images in, int16 map out (algorithmic bytes 4 N: N + N read, 2 N written):
-//   * a block owns 32 output columns x a band of <= DN_BAND output rows. It prefilters the
+//   * a block owns 32 output columns x a band of output rows (DN_BAND for a lone image, equal
+//     bands of <= DN_BAND_TALL when the launch holds many). It prefilters the
 //     (band + 20) x (32 + 20 [+ 47 for the right image]) pixels it needs straight from the raw
 //     images into shared memory, once;
 //   * thread (lane = column, warp k = disparity class) carries SAD(x, y, D) for the twelve
@@ -32,7 +33,7 @@ constexpr int DN_WIN = 21;         // SAD window
 constexpr int DN_RAD = DN_WIN / 2;
 constexpr int DN_TW = 32;          // output columns per block
 constexpr int DN_BAND = 64;        // output rows per block (few images in the launch)
-constexpr int DN_BAND_TALL = 128;  // ... (many images)
+constexpr int DN_BAND_TALL = 184;  // ... upper bound when the launch holds many images (2 blocks per SM)
 constexpr int DN_PLW = 56;         // prefiltered left tile row: 32 + 20 columns, + a spare word
 constexpr int DN_PRW = 104;        // prefiltered right tile row: 32 + 20 + 47 columns, padded
 constexpr int DN_NJ = DN_ND / 4;   // disparities per thread
@@ -318,11 +319,13 @@ cudaError_t svo_launch_stereo_bm_dense(const uint8_t* pyr, const SvoPyrLayout& l
         disp, dpitch, disp_stride, W, H, d_call);
     const int vw = W - DN_RAD - (DN_ND - 1 + DN_RAD), vh = H - 2 * DN_RAD;
     if (vw > 0 && vh > 0) {
-        // tall bands amortise the 20 start-up rows of a band; short ones give a lone image
-        // enough blocks for 148 SMs x 2
+        // tall bands amortise the 20 start-up rows of a band (KITTI: 2 bands of 180 rows); short
+        // ones give a lone image enough blocks for 148 SMs x 2
         const int tiles = (vw + DN_TW - 1) / DN_TW;
-        const int band = ((long long)tiles * ((vh + DN_BAND_TALL - 1) / DN_BAND_TALL) * n_call >= 4 * 296)
-                             ? DN_BAND_TALL : DN_BAND;
+        const int nb_tall = (vh + DN_BAND_TALL - 1) / DN_BAND_TALL;
+        int band = DN_BAND;
+        if ((long long)tiles * nb_tall * n_call >= 2 * 296)       // two waves of 2 blocks x 148 SMs
+            band = ((vh + nb_tall - 1) / nb_tall + 3) & ~3;       // equal bands, <= DN_BAND_TALL
         const size_t smem = sizeof(unsigned) * (DN_RING_WORDS + DN_SAD_WORDS + DN_TEXR_WORDS + DN_TEX_WORDS) +
                             (size_t)(band + DN_WIN - 1) * (DN_PLW + DN_PRW);
         // per device, so not cached: costs a microsecond

@@ -198,6 +198,7 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
     const unsigned* pl = s_pl + lw;
     const unsigned* pr = s_pr + rw;
     load_raw(cur, pl, pr, 0, 0);
+#pragma unroll 2
     for (int r = 0; r < DN_WIN - 1; ++r) {                       // window rows 0 .. 19 -> slots 0 .. 19
         load_raw(nxt, pl + (r + 1) * (DN_PLW / 4), pr + (r + 1) * (DN_PRW / 4), 0, 0);
         make_ops(o, cur, ls, rs);
@@ -217,7 +218,9 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
     int slot_in = DN_WIN - 1, slot_out = 0;                      // ring slots of rows ry + 20, ry
     for (int y0 = 0; y0 < nrows; y0 += 4) {
         const int ng = min(4, nrows - y0);
-        for (int g = 0; g < ng; ++g) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {                            // unrolled: cur / nxt swap by renaming
+            if (g >= ng) break;
             const int ry = y0 + g;                               // output row yt + ry; cur = tile row ry + 20
             if (ry + 1 < nrows)
                 load_raw(nxt, pl + (ry + DN_WIN) * (DN_PLW / 4), pr + (ry + DN_WIN) * (DN_PRW / 4), 0, 0);

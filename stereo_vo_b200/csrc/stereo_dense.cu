@@ -104,6 +104,14 @@ __device__ __forceinline__ void make_ops(RowOps& o, const RawRow& w, int ls, int
     for (int i = 0; i < 17; ++i) o.r[i] = __funnelshift_r(w.wr[i], w.wr[i + 1], rs);
 }
 
+// |a - b| summed over the four bytes, + c: one VABSDIFF4.U8.ACC (written as PTX so that the
+// accumulator operand is used; `__vsadu4(a, b) + c` compiles to a zero-accumulator op and adds)
+__device__ __forceinline__ unsigned sad4(unsigned a, unsigned b, unsigned c) {
+    unsigned d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 // 21-column sums of one row for the thread's twelve disparities, two per word (16-bit halves:
 // a row sum is <= 21 * 126, a window sum <= 441 * 126 < 2^16, and sums of halves never carry)
 __device__ __forceinline__ void row_sums(unsigned (&hp)[DN_NJ / 2], const RowOps& o) {
@@ -114,11 +122,11 @@ __device__ __forceinline__ void row_sums(unsigned (&hp)[DN_NJ / 2], const RowOps
         unsigned a = 0, b = 0;
 #pragma unroll
         for (int i = 0; i < 5; ++i) {
-            a = __vsadu4(o.l[i], o.r[11 - j0 + i]) + a;
-            b = __vsadu4(o.l[i], o.r[11 - j1 + i]) + b;
+            a = sad4(o.l[i], o.r[11 - j0 + i], a);
+            b = sad4(o.l[i], o.r[11 - j1 + i], b);
         }
-        a = __vsadu4(o.l[5], o.r[16 - j0] & 0xffu) + a;
-        b = __vsadu4(o.l[5], o.r[16 - j1] & 0xffu) + b;
+        a = sad4(o.l[5], o.r[16 - j0] & 0xffu, a);
+        b = sad4(o.l[5], o.r[16 - j1] & 0xffu, b);
         hp[jj] = a + b * 65536u;
     }
 }
@@ -126,8 +134,8 @@ __device__ __forceinline__ void row_sums(unsigned (&hp)[DN_NJ / 2], const RowOps
 __device__ __forceinline__ unsigned row_texture(const RowOps& o, unsigned capw) {
     unsigned t = 0;
 #pragma unroll
-    for (int i = 0; i < 5; ++i) t = __vsadu4(o.l[i], capw) + t;
-    return __vsadu4(o.l[5], capw & 0xffu) + t;
+    for (int i = 0; i < 5; ++i) t = sad4(o.l[i], capw, t);
+    return sad4(o.l[5], capw & 0xffu, t);
 }
 
 // shared-memory carve-up (dynamic): ring | sad | texture ring | texture | left tile | right tile

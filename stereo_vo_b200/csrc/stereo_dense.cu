@@ -195,7 +195,6 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
     const int rw = rb >> 2, rs = (rb & 3) * 8;
     const unsigned capw = (unsigned)cap * 0x01010101u;
     unsigned* ring = s_ring + tid;                               // [slot][jj] 128 words apart
-    const unsigned short* sad16 = reinterpret_cast<const unsigned short*>(s_sad);
 
     unsigned sadp[DN_NJ / 2], hp[DN_NJ / 2];
 #pragma unroll
@@ -262,36 +261,43 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
         // [row][kk][j >> 1][lane]
         const int x = xt + lane, y = yt + y0 + k;
         if (k < ng && x < W - DN_RAD) {
+            // this thread's 48 SADs: word (kk, jj) of row k, 32 words apart; nobody else reads
+            // them, and the next group's sums arrive only after the barrier below
+            unsigned* sw = s_sad + (k * 4) * (DN_NJ / 2) * DN_TW + lane;
+            auto word_of = [&](int d) -> int {
+                const int D = DN_ND - 1 - d;
+                return ((D & 3) * (DN_NJ / 2) + (D >> 3)) * DN_TW;
+            };
             auto sad_at = [&](int d) -> int {
-                const int D = DN_ND - 1 - d, kk = D & 3, j = D >> 2;
-                return sad16[((((k * 4 + kk) * (DN_NJ / 2) + (j >> 1)) * DN_TW + lane) << 1) + (j & 1)];
+                const int D = DN_ND - 1 - d;
+                return (int)((sw[word_of(d)] >> (((D >> 2) & 1) * 16)) & 0xffffu);
             };
             short res;
             // first minimum in internal order = minimum of the keys sad * 64 + d
-            int v[DN_ND];
+            int key = sad_at(0) * 64;
 #pragma unroll
-            for (int d = 0; d < DN_ND; ++d) v[d] = sad_at(d);
-            int key = v[0] * 64;
-#pragma unroll
-            for (int d = 1; d < DN_ND; ++d) key = min(key, v[d] * 64 + d);
+            for (int d = 1; d < DN_ND; ++d) key = min(key, sad_at(d) * 64 + d);
             const int mind = key & 63, minsad = key >> 6;
             bool ok = s_tex[k * DN_TW + lane] >= texture;
+            const int pp = sad_at(mind + 1 < DN_ND ? mind + 1 : DN_ND - 2);
+            const int nn = sad_at(mind > 0 ? mind - 1 : 1);
             if (uniq > 0) {
-                // rejected iff some d outside mind-1 .. mind+1 has sad <= thresh: count them all,
-                // take the (up to) three around the winner off again
+                // rejected iff some d outside mind-1 .. mind+1 has sad <= thresh: knock those
+                // three out (0xffff) and take the packed 16-bit minimum of the 24 words
                 const int thresh = minsad + (minsad * uniq / 100);
-                int cnt = 0;
 #pragma unroll
-                for (int d = 0; d < DN_ND; ++d) cnt += (v[d] <= thresh) ? 1 : 0;
-                int near = 1;
-                if (mind > 0) near += (sad_at(mind - 1) <= thresh) ? 1 : 0;
-                if (mind < DN_ND - 1) near += (sad_at(mind + 1) <= thresh) ? 1 : 0;
-                if (cnt > near) ok = false;
+                for (int t = -1; t <= 1; ++t) {
+                    const int d = mind + t;
+                    if (d >= 0 && d < DN_ND)
+                        sw[word_of(d)] |= 0xffffu << ((((DN_ND - 1 - d) >> 2) & 1) * 16);
+                }
+                unsigned m = 0xffffffffu;
+#pragma unroll
+                for (int i = 0; i < 4 * (DN_NJ / 2); ++i) m = __vminu2(m, sw[i * DN_TW]);
+                if ((int)min(m & 0xffffu, m >> 16) <= thresh) ok = false;
             }
             if (ok) {
-                const int c0 = sad_at(mind);
-                const int pp = sad_at(mind + 1 < DN_ND ? mind + 1 : DN_ND - 2);
-                const int nn = sad_at(mind > 0 ? mind - 1 : 1);
+                const int c0 = minsad;
                 const int den = pp + nn - 2 * c0 + abs(pp - nn);
                 const int v = (DN_ND - mind - 1) * 256 + (den != 0 ? (pp - nn) * 256 / den : 0) + 15;
                 res = (short)(v >> 4);

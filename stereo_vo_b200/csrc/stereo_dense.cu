@@ -274,9 +274,18 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
             };
             short res;
             // first minimum in internal order = minimum of the keys sad * 64 + d
-            int key = sad_at(0) * 64;
+            // (each word holds D = kk + 8 jj in its low half, D + 4 in its high half)
+            unsigned ukey = 0xffffffffu;
 #pragma unroll
-            for (int d = 1; d < DN_ND; ++d) key = min(key, sad_at(d) * 64 + d);
+            for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+                for (int jj = 0; jj < DN_NJ / 2; ++jj) {
+                    const unsigned w = sw[(kk * (DN_NJ / 2) + jj) * DN_TW];
+                    const unsigned d_lo = DN_ND - 1 - (kk + 8 * jj), d_hi = d_lo - 4;
+                    ukey = min(ukey, min(((w << 6) & 0x3fffc0u) | d_lo, ((w >> 10) & 0x3fffc0u) | d_hi));
+                }
+            }
+            const int key = (int)ukey;
             const int mind = key & 63, minsad = key >> 6;
             bool ok = s_tex[k * DN_TW + lane] >= texture;
             const int pp = sad_at(mind + 1 < DN_ND ? mind + 1 : DN_ND - 2);

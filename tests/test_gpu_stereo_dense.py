@@ -114,6 +114,39 @@ def test_dense_many_sequences_tall_bands(svo_lib, oracle):
         e.close()
 
 
+def test_dense_tall_bands_odd_height_partial_last_band(svo_lib, oracle):
+    """12 pairs of 641x479 in one launch: tall bands of 156 rows, the last one 147 (not a multiple
+    of the 4-row groups), odd height (capped last prefilter row), a partial last column tile."""
+    w, h = 641, 479
+    lefts = [util.stress_image(h, w, seed) for seed in (11, 12)]
+    pairs = [(l, util.shifted(l, d)) for l, d in zip(lefts, (9, 31))]
+    want = [oracle.stereo_disparity16(l, r) for l, r in pairs]
+    e = _engine(w, h, n_seq=12)
+    try:
+        for s in range(12):
+            _compare(e.stereo_bm_dense(*pairs[s % 2], seq=s), want[s % 2])
+        order = list(range(12))
+        for s, m in zip(order, e.stereo_bm_dense_resident(order, shape=(h, w))):
+            _compare(m, want[s % 2])
+    finally:
+        e.close()
+
+
+def test_dense_map_uhd(svo_lib, oracle):
+    """3840x2160 (BASELINE configs[4] size): 8.3 M pixels, 119 column tiles x 12 tall bands."""
+    w, h = 3840, 2160
+    left = util.stress_image(h, w, 21)
+    right = util.shifted(left, 23)
+    want = oracle.stereo_disparity16(left, right)
+    e = _engine(w, h)
+    try:
+        got = e.stereo_bm_dense(left, right)
+    finally:
+        e.close()
+    _compare(got, want)
+    assert (got > 0).mean() > 0.5
+
+
 def test_dense_needs_a_stereo_pair(svo_lib):
     from stereo_vo_b200.capi import SvoError
     e = _engine(640, 480)

@@ -275,16 +275,18 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
             short res;
             // first minimum in internal order = minimum of the keys sad * 64 + d
             // (each word holds D = kk + 8 jj in its low half, D + 4 in its high half)
-            unsigned ukey = 0xffffffffu;
+            unsigned pk[4];                                      // one chain per kk: short dependency chains
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
+                pk[kk] = 0xffffffffu;
 #pragma unroll
                 for (int jj = 0; jj < DN_NJ / 2; ++jj) {
                     const unsigned w = sw[(kk * (DN_NJ / 2) + jj) * DN_TW];
                     const unsigned d_lo = DN_ND - 1 - (kk + 8 * jj), d_hi = d_lo - 4;
-                    ukey = min(ukey, min(((w << 6) & 0x3fffc0u) | d_lo, ((w >> 10) & 0x3fffc0u) | d_hi));
+                    pk[kk] = min(pk[kk], min(((w << 6) & 0x3fffc0u) | d_lo, ((w >> 10) & 0x3fffc0u) | d_hi));
                 }
             }
+            const unsigned ukey = min(min(pk[0], pk[1]), min(pk[2], pk[3]));
             const int key = (int)ukey;
             const int mind = key & 63, minsad = key >> 6;
             bool ok = s_tex[k * DN_TW + lane] >= texture;
@@ -300,9 +302,15 @@ stereo_bm_dense_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t
                     if (d >= 0 && d < DN_ND)
                         sw[word_of(d)] |= 0xffffu << ((((DN_ND - 1 - d) >> 2) & 1) * 16);
                 }
-                unsigned m = 0xffffffffu;
+                unsigned pm[4];
 #pragma unroll
-                for (int i = 0; i < 4 * (DN_NJ / 2); ++i) m = __vminu2(m, sw[i * DN_TW]);
+                for (int kk = 0; kk < 4; ++kk) {
+                    pm[kk] = 0xffffffffu;
+#pragma unroll
+                    for (int jj = 0; jj < DN_NJ / 2; ++jj)
+                        pm[kk] = __vminu2(pm[kk], sw[(kk * (DN_NJ / 2) + jj) * DN_TW]);
+                }
+                const unsigned m = __vminu2(__vminu2(pm[0], pm[1]), __vminu2(pm[2], pm[3]));
                 if ((int)min(m & 0xffffu, m >> 16) <= thresh) ok = false;
             }
             if (ok) {

@@ -67,8 +67,6 @@ typedef struct svo_params {
     float fb_max_error;             /* 2 px forward-backward */
     float max_parallax;             /* 200 px */
     int32_t max_features;           /* tracker capacity; 400 = bundle_adjuster.hpp:75 */
-    /* launch tuning (no effect on results) */
-    int32_t lk_warps_per_point;     /* accepted for compatibility; the kernel uses 2 warps */
     /* debug: also store the cv::cornerMinEigenVal map (read by svo_debug_min_eigen_map); the
      * product path never materialises it */
     int32_t keep_eig_map;           /* 0 */
@@ -159,7 +157,11 @@ SVO_API int svo_dedupe(svo_engine* e, int32_t seq, const svo_float2* det, int32_
                const svo_float2* tracked, int32_t n_tracked, float min_distance,
                svo_float2* out_xy, int32_t* out_keep_idx, int32_t* out_n);
 
-/* taps of the last track call (parity tests): LK outputs before filtering, n_attempted entries */
+/* taps of the last track call (parity tests): LK outputs before filtering, n_attempted entries.
+ * For a point the FORWARD pass lost (status1 == 0) the backward pass is not run: reverse holds
+ * the forward result and status2 is 0, where cv::calcOpticalFlowPyrLK would track it anyway
+ * (src/feature_tracker.cpp:32-35). The reference never reads those entries (:45-47 tests status1
+ * first), so the kept set is identical; only these two debug taps differ from cv2 there. */
 SVO_API int svo_tracker_debug(svo_engine* e, int32_t seq, svo_float2* tracked, uint8_t* status1,
                       svo_float2* reverse, uint8_t* status2, int32_t* kept_idx, int32_t* n_attempted);
 

@@ -6,6 +6,8 @@ arithmetic is defined on separately rounded IEEE operations (SURVEY.md Appendix 
 """
 from __future__ import annotations
 
+import contextlib
+import fcntl
 import os
 import subprocess
 import sys
@@ -26,6 +28,21 @@ INCLUDE = os.path.join(HERE, "..", "include")
 HOST_SOURCES = ["bundle_adjuster.cpp", "camera_config.cpp", "feature_tracker.cpp",
                 "image_processor.cpp", "batch_front_end.cpp", "host_c.cpp"]
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wextra", "-pthread"]
+
+
+@contextlib.contextmanager
+def _build_lock():
+    """Serialise builds across processes (torchrun ranks, pytest-xdist workers): every rank may
+    call build_lib(); the first one in compiles, the others wait and find the library fresh.
+    Libraries are linked under a temporary name and renamed into place, so a process that is
+    dlopen()ing the old file never sees a half-written one."""
+    fd = os.open(os.path.join(HERE, ".build.lock"), os.O_CREAT | os.O_RDWR, 0o644)
+    try:
+        fcntl.flock(fd, fcntl.LOCK_EX)
+        yield
+    finally:
+        fcntl.flock(fd, fcntl.LOCK_UN)
+        os.close(fd)
 
 
 def _nvcc() -> str:
@@ -60,17 +77,22 @@ def build_host_lib(force: bool = False) -> str:
     facade, BundleAdjuster bookkeeping, BatchFrontEnd, YAML reader) linked against libsvo.so."""
     if not force and not host_needs_build():
         return HOST_LIB
-    cxx = os.environ.get("CXX", "g++")
-    cmd = [cxx, *CXX_FLAGS, "-shared", "-I", INCLUDE,
-           *[os.path.join(HOST_DIR, f) for f in HOST_SOURCES], "-o", HOST_LIB,
-           "-L", HERE, "-l:libsvo.so", "-Wl,-rpath,$ORIGIN"]
-    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
-    text = r.stdout.decode(errors="replace")
-    if r.returncode != 0:
-        sys.stderr.write(f"[build] libsvo_host.so FAILED\n{text}\n")
-        raise RuntimeError("g++ failed")
-    if text.strip():
-        sys.stderr.write(f"[build] libsvo_host.so\n{text}\n")
+    with _build_lock():
+        if not force and not host_needs_build():       # another process built it meanwhile
+            return HOST_LIB
+        cxx = os.environ.get("CXX", "g++")
+        tmp = f"{HOST_LIB}.tmp.{os.getpid()}"
+        cmd = [cxx, *CXX_FLAGS, "-shared", "-I", INCLUDE,
+               *[os.path.join(HOST_DIR, f) for f in HOST_SOURCES], "-o", tmp,
+               "-L", HERE, "-l:libsvo.so", "-Wl,-rpath,$ORIGIN"]
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        text = r.stdout.decode(errors="replace")
+        if r.returncode != 0:
+            sys.stderr.write(f"[build] libsvo_host.so FAILED\n{text}\n")
+            raise RuntimeError("g++ failed")
+        if text.strip():
+            sys.stderr.write(f"[build] libsvo_host.so\n{text}\n")
+        os.replace(tmp, HOST_LIB)
     return HOST_LIB
 
 
@@ -82,6 +104,13 @@ def build_all(force: bool = False) -> None:
 def build_lib(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
+    with _build_lock():
+        if not force and not needs_build():            # another process built it meanwhile
+            return LIB
+        return _build_lib_locked(verbose)
+
+
+def _build_lib_locked(verbose: bool) -> str:
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     objs = []
@@ -104,8 +133,10 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(f"[build] {src}\n{text}\n")
     if failed:
         raise RuntimeError("nvcc failed")
-    link = [_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs]
+    tmp = f"{LIB}.tmp.{os.getpid()}"
+    link = [_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", tmp, *objs]
     subprocess.run(link, check=True)
+    os.replace(tmp, LIB)
     return LIB
 
 

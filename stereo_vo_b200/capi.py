@@ -28,7 +28,7 @@ class SvoParams(C.Structure):
         ("lk_max_level", C.c_int32), ("lk_max_iters", C.c_int32), ("lk_epsilon", C.c_double),
         ("lk_min_eig_threshold", C.c_double),
         ("fb_max_error", C.c_float), ("max_parallax", C.c_float), ("max_features", C.c_int32),
-        ("lk_warps_per_point", C.c_int32), ("keep_eig_map", C.c_int32),
+        ("keep_eig_map", C.c_int32),
     ]
 
 

@@ -655,7 +655,6 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
     lp.max_iters = e->p.lk_max_iters;
     lp.eps2 = e->p.lk_epsilon * e->p.lk_epsilon;
     lp.min_eig = e->p.lk_min_eig_threshold;
-    lp.warps_per_point = e->p.lk_warps_per_point;
     lp.grid_pts = max_feat_in_call;
     const int* gate = gated ? e->d_ncorners : nullptr;
     // detection still running on the other stream: the LK kernels cannot read the corner count
@@ -963,7 +962,6 @@ void svo_default_params(svo_params* p, int32_t width, int32_t height) {
     p->fb_max_error = 2.f;
     p->max_parallax = 200.f;
     p->max_features = 400;
-    p->lk_warps_per_point = 2;
     p->keep_eig_map = 0;
 }
 
@@ -982,7 +980,6 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     if (p.num_disparities <= 0 || p.num_disparities % 16 || p.sad_window < 5 || !(p.sad_window & 1) ||
         p.sad_window > 31 || p.num_disparities > 256)
         return fail(nullptr, SVO_ERR_INVALID, "svo_create: StereoBM parameters out of range");
-    if (p.lk_warps_per_point != 1 && p.lk_warps_per_point != 4) p.lk_warps_per_point = 2;
     if ((long long)p.width * p.height >= (1ll << 31))
         return fail(nullptr, SVO_ERR_INVALID, "svo_create: image too large");
 

@@ -154,7 +154,6 @@ struct SvoLkParams {
     int max_iters;
     double eps2;                 // criteria.epsilon squared (OpenCV squares it in double)
     double min_eig;              // minEigThreshold (double in the OpenCV signature)
-    int warps_per_point;         // accepted for ABI compatibility; the kernel uses 2 warps
     int grid_pts;                // blocks per sequence to launch (0 = max_pts)
 };
 

@@ -199,6 +199,10 @@ void ImageProcessor::process(const StereoPair& stereo_pair) {
     if (!pnp_(world, tracked_features, camera_matrix, rvec, tvec, rmat, inliers))
         throw std::runtime_error("ImageProcessor: PnP solver failed");
     const size_t num_inliers = inliers.size();
+    // the solver is caller-supplied: a list longer than the tracker set (duplicates) must not
+    // run past inl_pts before svo_keyframe gets to reject it
+    if (num_inliers > (size_t)p.max_features || num_inliers > tracked_features.size())
+        throw std::length_error("ImageProcessor: PnP solver returned more inliers than tracked features");
     float rmat_f[9];
     for (int i = 0; i < 9; ++i) rmat_f[i] = (float)rmat[i];
     svo::Vec3f position;

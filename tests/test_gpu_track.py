@@ -113,11 +113,3 @@ def test_track_multi_frame_chain(eng, oracle):
         assert abs(float(av) - float(av_ref)) <= FLOW_TOL * t
         assert lost == lost_ref
 
-
-@pytest.mark.parametrize("warps", [1, 4])
-def test_track_other_block_shapes(eng, oracle, warps):
-    fr = util.frames(6, 2)
-    prev, nxt = fr[0][0], fr[1][0]
-    pts = oracle.detect(prev)
-    e = eng(1241, 376, lk_warps_per_point=warps)
-    _track_once(e, oracle, prev, nxt, pts, list(range(len(pts))))

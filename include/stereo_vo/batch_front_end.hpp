@@ -92,6 +92,15 @@ class BatchFrontEnd {
     int32_t n_new(int s) const { return res(s).n_new; }
     const svo_float2* new_2d(int s) const;
     const svo_float3* new_3d(int s) const;
+    // taps of the keyframe stage (parity tests): detections that survived the dedupe
+    // (src/image_processor.cpp:113-128), their raw StereoBM values (1/16 px, -16 = rejected) and
+    // the indices of the stereo-valid ones (:193-195; n_valid may exceed n_new when the
+    // 400-feature clip of src/bundle_adjuster.cpp:75 applies)
+    int32_t n_new_features(int s) const { return res(s).n_new_features; }
+    int32_t n_valid(int s) const { return res(s).n_valid; }
+    const svo_float2* new_features(int s) const;
+    const int16_t* disp16(int s) const;
+    const int32_t* valid_idx(int s) const;
 
     int64_t kernel_launches() const;
     // device-side stopwatch over all groups: begin() synchronises every engine stream and
@@ -106,6 +115,7 @@ class BatchFrontEnd {
   private:
     struct SeqResult {                     // per pipeline slot
         int32_t decision = 0, n_corners = 0, n_tracker = 0, n_new = 0;
+        int32_t n_new_features = 0, n_valid = 0;
         svo_track_stats stats{};
     };
     struct SeqState {
@@ -160,6 +170,9 @@ class BatchFrontEnd {
     std::vector<SeqState> seq_;
     // per-sequence result storage (global index), one set per pipeline slot
     std::vector<svo_float2> corners_[kPipeDepth], tracker_pts_[kPipeDepth], new_2d_[kPipeDepth];
+    std::vector<svo_float2> new_feats_[kPipeDepth];
+    std::vector<int16_t> disp16_[kPipeDepth];
+    std::vector<int32_t> valid_idx_[kPipeDepth];
     std::vector<svo_float3> new_3d_[kPipeDepth];
     std::vector<uint64_t> tracker_ids_[kPipeDepth];
     Job jobs_[kPipeDepth];

@@ -98,6 +98,13 @@ SVO_API int svo_batch_get(svo_batch* b, int32_t seq, int32_t* decision, int32_t*
                           svo_float2* corners, svo_track_stats* stats, int32_t* n_tracker,
                           svo_float2* tracker_pts, uint64_t* tracker_ids, int32_t* n_new,
                           svo_float2* new_2d, svo_float3* new_3d);
+/* keyframe-stage taps of the last step for sequence seq (parity tests; zero counts unless the
+ * decision was FIRST or KEYFRAME): detections that survived the new-vs-tracked dedupe
+ * (src/image_processor.cpp:113-128) with their raw StereoBM values, and the indices of the
+ * stereo-valid ones (:193-195). Arrays hold max_corners entries; any may be NULL */
+SVO_API int svo_batch_get_keyframe(svo_batch* b, int32_t seq, int32_t* n_new_features,
+                                   svo_float2* new_features, int16_t* disp16, int32_t* n_valid,
+                                   int32_t* valid_idx);
 SVO_API int64_t svo_batch_kernel_launches(const svo_batch* b);
 SVO_API int svo_batch_timer_begin(svo_batch* b);
 SVO_API int svo_batch_timer_end(svo_batch* b, float* ms);

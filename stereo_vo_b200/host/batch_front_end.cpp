@@ -32,6 +32,9 @@ BatchFrontEnd::BatchFrontEnd(const BatchOptions& opt) : opt_(opt) {
         tracker_ids_[p].resize((size_t)opt.n_seq * mf);
         new_2d_[p].resize((size_t)opt.n_seq * mc);
         new_3d_[p].resize((size_t)opt.n_seq * mc);
+        new_feats_[p].resize((size_t)opt.n_seq * mc);
+        disp16_[p].resize((size_t)opt.n_seq * mc);
+        valid_idx_[p].resize((size_t)opt.n_seq * mc);
         jobs_[p].sum.resize((size_t)G);
         jobs_[p].error.resize((size_t)G);
     }
@@ -223,6 +226,7 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         rs.n_corners = g.n_corn[(size_t)i];
         rs.stats = g.stats[(size_t)i];
         rs.n_new = 0;
+        rs.n_new_features = rs.n_valid = 0;
         rs.n_tracker = st.n_tracker;
         std::memcpy(&corners_[slot][(size_t)s * mc], &g.corners[(size_t)i * mc],
                     (size_t)rs.n_corners * sizeof(svo_float2));
@@ -337,6 +341,11 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         st.have_kf = true;
         SeqResult& rs = st.res[slot];
         rs.n_new = nv;
+        rs.n_new_features = g.n_newv[(size_t)k];
+        rs.n_valid = g.n_valid[(size_t)k];
+        std::memcpy(&new_feats_[slot][(size_t)s * mc], &g.new_feats[(size_t)k * mc], (size_t)rs.n_new_features * sizeof(svo_float2));
+        std::memcpy(&disp16_[slot][(size_t)s * mc], &g.disp16[(size_t)k * mc], (size_t)rs.n_new_features * sizeof(int16_t));
+        std::memcpy(&valid_idx_[slot][(size_t)s * mc], &g.valid_idx[(size_t)k * mc], (size_t)rs.n_valid * sizeof(int32_t));
         st.n_tracker = rs.n_tracker = n_inl + nv;
         std::memcpy(&new_2d_[slot][(size_t)s * mc], &g.valid_2d[(size_t)k * mc], (size_t)nv * sizeof(svo_float2));
         std::memcpy(&new_3d_[slot][(size_t)s * mc], &g.pts_3d[(size_t)k * mc], (size_t)nv * sizeof(svo_float3));
@@ -408,6 +417,9 @@ const svo_float2* BatchFrontEnd::tracker_points(int s) const { return &tracker_p
 const uint64_t* BatchFrontEnd::tracker_ids(int s) const { return &tracker_ids_[cur_slot_][(size_t)s * opt_.params.max_features]; }
 const svo_float2* BatchFrontEnd::new_2d(int s) const { return &new_2d_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
 const svo_float3* BatchFrontEnd::new_3d(int s) const { return &new_3d_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
+const svo_float2* BatchFrontEnd::new_features(int s) const { return &new_feats_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
+const int16_t* BatchFrontEnd::disp16(int s) const { return &disp16_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
+const int32_t* BatchFrontEnd::valid_idx(int s) const { return &valid_idx_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
 
 int64_t BatchFrontEnd::kernel_launches() const {
     int64_t n = 0;

@@ -250,6 +250,20 @@ int svo_batch_get(svo_batch* b, int32_t seq, int32_t* decision, int32_t* n_corne
     return SVO_OK;
 }
 
+int svo_batch_get_keyframe(svo_batch* b, int32_t seq, int32_t* n_new_features,
+                           svo_float2* new_features, int16_t* disp16, int32_t* n_valid,
+                           int32_t* valid_idx) {
+    if (!b || seq < 0 || seq >= b->fe->n_seq()) return SVO_ERR_INVALID;
+    const svo::BatchFrontEnd& fe = *b->fe;
+    const size_t nf = (size_t)fe.n_new_features(seq), nv = (size_t)fe.n_valid(seq);
+    if (n_new_features) *n_new_features = (int32_t)nf;
+    if (n_valid) *n_valid = (int32_t)nv;
+    if (new_features) std::memcpy(new_features, fe.new_features(seq), nf * sizeof(svo_float2));
+    if (disp16) std::memcpy(disp16, fe.disp16(seq), nf * sizeof(int16_t));
+    if (valid_idx) std::memcpy(valid_idx, fe.valid_idx(seq), nv * sizeof(int32_t));
+    return SVO_OK;
+}
+
 int64_t svo_batch_kernel_launches(const svo_batch* b) { return b ? b->fe->kernel_launches() : 0; }
 
 int svo_batch_timer_begin(svo_batch* b) {

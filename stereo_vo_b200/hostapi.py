@@ -85,6 +85,7 @@ def load_library():
     lib.svo_batch_wait.argtypes = [vp, C.POINTER(BatchSummary)]
     lib.svo_batch_get.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), vp, vp, C.POINTER(i32),
                                   vp, vp, C.POINTER(i32), vp, vp]
+    lib.svo_batch_get_keyframe.argtypes = [vp, i32, C.POINTER(i32), vp, vp, C.POINTER(i32), vp]
     lib.svo_batch_kernel_launches.argtypes = [vp]
     lib.svo_batch_kernel_launches.restype = C.c_int64
     lib.svo_batch_timer_begin.argtypes = [vp]
@@ -334,9 +335,21 @@ class Batch:
                                     C.byref(nn), n2.ctypes.data, n3.ctypes.data)
         if rc != 0:
             raise SvoError(f"svo_batch_get failed ({rc})")
-        return dict(decision=DECISIONS[dec.value], corners=corners[:nc.value], stats=stats[0],
-                    tracker_pts=tp[:nt.value], tracker_ids=ti[:nt.value], new2d=n2[:nn.value],
-                    new3d=n3[:nn.value])
+        out = dict(decision=DECISIONS[dec.value], corners=corners[:nc.value], stats=stats[0],
+                   tracker_pts=tp[:nt.value], tracker_ids=ti[:nt.value], new2d=n2[:nn.value],
+                   new3d=n3[:nn.value])
+        if dec.value in (2, 4):
+            nf, nv = C.c_int32(), C.c_int32()
+            feats = np.zeros((self.max_corners, 2), np.float32)
+            d16 = np.zeros(self.max_corners, np.int16)
+            vi = np.zeros(self.max_corners, np.int32)
+            rc = self.lib.svo_batch_get_keyframe(self.h, seq, C.byref(nf), feats.ctypes.data,
+                                                 d16.ctypes.data, C.byref(nv), vi.ctypes.data)
+            if rc != 0:
+                raise SvoError(f"svo_batch_get_keyframe failed ({rc})")
+            out.update(new_features=feats[:nf.value], disp16=d16[:nf.value],
+                       valid_idx=vi[:nv.value])
+        return out
 
     @property
     def kernel_launches(self) -> int:

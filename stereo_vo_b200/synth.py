@@ -102,8 +102,13 @@ def _sample_separable(tex: np.ndarray, u: np.ndarray, v: np.ndarray) -> np.ndarr
     v1i = (v0i + 1) % TEX_H
     u0i = u0.astype(np.int64) % TEX_W
     u1i = (u0i + 1) % TEX_W
-    rows = tex[v0i, :] * (1.0 - fv) + tex[v1i, :] * fv
-    return rows[:, u0i] * (1.0 - fu) + rows[:, u1i] * fu
+    # blend the two texture rows only over the column span that is sampled (the same
+    # arithmetic per element as blending whole rows; a wrapped span takes the whole row)
+    lo, hi = int(u0i.min()), int(u1i.max())
+    if hi - lo + 1 > 2 * len(u) + 8:
+        lo, hi = 0, TEX_W - 1
+    rows = tex[v0i, lo:hi + 1] * (1.0 - fv) + tex[v1i, lo:hi + 1] * fv
+    return rows[:, u0i - lo] * (1.0 - fu) + rows[:, u1i - lo] * fu
 
 
 @dataclass(frozen=True)

@@ -216,3 +216,40 @@ def test_corner_segments_on_rounding_prone_images(engines, oracle, w, h):
         ref_eig = cv2.cornerMinEigenVal(img, 3, ksize=3)
         assert np.array_equal(eig.view(np.uint32), ref_eig.view(np.uint32)), \
             f"{name}: {(eig.view(np.uint32) != ref_eig.view(np.uint32)).sum()} eig pixels differ"
+
+
+def default_mode_agreement(detect_gpu, images):
+    """Agreement of the GPU detector with cv2 in its DEFAULT (optimized) mode, the mode a stock
+    OpenCV build runs in: its AVX2/AVX-512 cornerMinEigenVal contracts some multiply-adds into
+    FMAs depending on the column, so a few eig values differ in the last
+    bit from the canonical SSE path the GPU kernel reproduces. Returns (frames, frames with the
+    identical corner SET, frames with the identical corner ORDER)."""
+    was = cv2.useOptimized()
+    same_set = same_order = 0
+    try:
+        for img in images:
+            got = detect_gpu(img)
+            cv2.setUseOptimized(True)
+            ref = cv2.goodFeaturesToTrack(img, 300, 0.1, 30)
+            cv2.setUseOptimized(False)
+            ref = np.zeros((0, 2), np.float32) if ref is None else ref.reshape(-1, 2)
+            s_got = {(float(x), float(y)) for x, y in got}
+            s_ref = {(float(x), float(y)) for x, y in ref}
+            same_set += s_got == s_ref
+            same_order += got.shape == ref.shape and bool(np.array_equal(got, ref))
+    finally:
+        cv2.setUseOptimized(was)
+    return len(images), same_set, same_order
+
+
+def test_agreement_with_default_optimized_cv2_is_reported(engines, oracle):
+    """Secondary number promised in SURVEY.md section 0: parity is defined against
+    cv2.setUseOptimized(False); a user's OpenCV runs optimized. 80 KITTI-shaped frames (8 seeds x
+    10 frames). The survey saw 2 of 80 frames with the same corner set in a different order and
+    none with a different set; the bar here is loose on purpose (the number is what matters)."""
+    e = engines(1241, 376)
+    images = [synth.stereo_frame(seed, t)[0] for seed in range(8) for t in range(0, 40, 4)]
+    n, same_set, same_order = default_mode_agreement(e.good_features_to_track, images)
+    print(f"\n[default-mode cv2] {n} frames: identical corner set {same_set}/{n}, "
+          f"identical order {same_order}/{n}")
+    assert same_set >= 0.9 * n and same_order >= 0.8 * n

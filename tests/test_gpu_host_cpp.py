@@ -32,8 +32,12 @@ def _teacher_pnp(log, counter):
 
 
 @pytest.mark.parametrize("cam,motion,seed,n", [
-    (synth.KITTI00, synth.KITTI_MOTION, 0, 14),
-    (synth.D435I, synth.D435I_MOTION, 1, 10),
+    # run length: on the synthetic sequences the reference's own keyframe bookkeeping reaches
+    # its undefined 400-feature truncation (src/bundle_adjuster.cpp:75,98-116) from
+    # frame 89 on (KITTI seed 0; other seeds 92..200) - 80 frames stay
+    # inside the range where the reference is defined
+    (synth.KITTI00, synth.KITTI_MOTION, 0, 80),
+    (synth.D435I, synth.D435I_MOTION, 1, 80),
 ])
 def test_cpp_facade_teacher_forced(host_lib, oracle, cam, motion, seed, n):
     from stereo_vo_b200 import hostapi
@@ -55,7 +59,7 @@ def test_cpp_facade_teacher_forced(host_lib, oracle, cam, motion, seed, n):
             assert np.abs(a["hmat"] - g["hmat"]).max() <= 1e-6 * max(1.0, np.abs(a["hmat"]).max())
             # tracked part: sub-pixel flow tolerance; new part: integer corners, exact
             assert a["tracker_pts"].shape == g["tracker_pts"].shape
-            assert np.abs(a["tracker_pts"] - g["tracker_pts"]).max() <= 0.01 * (1 + t)
+            assert np.abs(a["tracker_pts"] - g["tracker_pts"]).max() <= 0.01
             nn = len(a["new_ids"])
             assert np.array_equal(a["tracker_pts"][len(a["tracker_pts"]) - nn:],
                                   g["tracker_pts"][len(g["tracker_pts"]) - nn:])
@@ -67,7 +71,7 @@ def test_cpp_facade_closed_loop(host_lib, oracle):
     reference's arguments): the pose must stay on the synthetic ground truth."""
     from stereo_vo_b200 import hostapi
     cam = synth.KITTI00
-    fr = util.frames(0, 12)
+    fr = util.frames(0, 48)
     f, cx, cy, b = cam.f32()
 
     def pnp(world, image, K, rvec, tvec):

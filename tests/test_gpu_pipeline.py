@@ -8,7 +8,7 @@ from stereo_vo_b200 import synth
 from tests import util
 
 pytestmark = pytest.mark.gpu
-FLOW_TOL = 0.01
+FLOW_TOL = 0.01          # px, flat: the north_star bound, not growing with the frame index
 
 
 def _compare(recs_ref, recs_gpu, closed_loop=False):
@@ -18,8 +18,9 @@ def _compare(recs_ref, recs_gpu, closed_loop=False):
         assert np.array_equal(a["detected"], b["detected"]), f"frame {t}: corners"
         if "av_parallax" in a:
             assert a["tracked_ids"] == b["tracked_ids"], f"frame {t}: track ids"
-            assert np.abs(a["tracked_pts"] - b["tracked_pts"]).max() <= FLOW_TOL * (1 + t), f"frame {t}"
-            assert abs(float(a["av_parallax"]) - float(b["av_parallax"])) <= FLOW_TOL * (1 + t)
+            d = float(np.abs(a["tracked_pts"] - b["tracked_pts"]).max()) if len(a["tracked_pts"]) else 0.0
+            assert d <= FLOW_TOL, f"frame {t}: flow differs by {d} px"
+            assert abs(float(a["av_parallax"]) - float(b["av_parallax"])) <= FLOW_TOL
             assert a["percent_lost"] == b["percent_lost"]
         if a["decision"] in ("first", "keyframe"):
             kf += 1
@@ -35,8 +36,12 @@ def _compare(recs_ref, recs_gpu, closed_loop=False):
 
 
 @pytest.mark.parametrize("cam,motion,seed,n", [
-    (synth.KITTI00, synth.KITTI_MOTION, 0, 14),
-    (synth.D435I, synth.D435I_MOTION, 1, 10),
+    # run length: on the synthetic sequences the reference's own keyframe bookkeeping reaches
+    # its undefined 400-feature truncation (src/bundle_adjuster.cpp:75,98-116) from
+    # frame 89 on (KITTI seed 0; other seeds 92..200) - 80 frames stay
+    # inside the range where the reference is defined
+    (synth.KITTI00, synth.KITTI_MOTION, 0, 80),
+    (synth.D435I, synth.D435I_MOTION, 1, 80),
 ])
 def test_teacher_forced_sequence(svo_lib, oracle, cam, motion, seed, n):
     from stereo_vo_b200 import frontend
@@ -63,7 +68,7 @@ def test_closed_loop_sequence(svo_lib, oracle):
     from stereo_vo_b200 import frontend
     from stereo_vo_b200.capi import Engine
     cam = synth.KITTI00
-    fr = util.frames(0, 12)
+    fr = util.frames(0, 48)
     e = Engine(cam.width, cam.height, n_seq=1)
     f, cx, cy, b = cam.f32()
     gpu = frontend.ImageProcessor(e, frontend.camera_matrix(f, cx, cy), frontend.BundleAdjuster(), b)

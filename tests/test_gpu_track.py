@@ -109,7 +109,7 @@ def test_track_multi_frame_chain(eng, oracle):
         av, lost = e.tracker_track(fr[t][0], True)
         feats, fids = e.tracker_get()
         assert list(fids) == list(trk.feature_ids), f"frame {t}"
-        assert np.abs(feats - trk.feature_set).max() <= FLOW_TOL * t
-        assert abs(float(av) - float(av_ref)) <= FLOW_TOL * t
+        assert np.abs(feats - trk.feature_set).max() <= FLOW_TOL
+        assert abs(float(av) - float(av_ref)) <= FLOW_TOL
         assert lost == lost_ref
 

@@ -5,11 +5,17 @@ triangulate) on KITTI-shaped synthetic sequences, one process per GPU.
     python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torchrun)
     python bench.py --impl reference ...                     (the reference's CPU path, host cores)
 
-A "step" is one frame index of every sequence resident on the GPU (S stereo frames per rank;
-workload: SURVEY.md 8d config (4), 64 independent KITTI-shaped sequences per GPU, weak scaling:
-sequences are independent, no collective on the data path). The JSON line follows the driver's
-contract; `value` is measured with frames already resident in HBM, `e2e` through the C ABI with
-pinned HOST buffers (H2D of every stereo pair and D2H of every result inside the timed region).
+Workload (BASELINE configs[3]): 64 independent KITTI-shaped synthetic
+stereo sequences per GPU, one texture seed each (rank r owns seeds 64 r .. 64 r + 63), 40
+frames each walked forwards and backwards. A "step" is one frame of every sequence of the rank.
+The driver loop is stereo_vo_b200.workload.run_steps over svo::BatchFrontEnd - the same loop
+tests/test_gpu_bench_path.py checks against the cv2 oracle frame by frame.
+
+Timing: after W warm-up steps the K-step region is repeated R times back to back inside ONE
+timed window (CUDA events on every engine stream, max over engine groups and ranks; R chosen so
+the window lasts >= --min-seconds, so nvidia-smi clock samples fall inside it). `value` is
+measured with the frames already resident in HBM, `e2e` through the C ABI with pinned HOST frames
+(H2D of every stereo pair needed and D2H of every result inside the timed window).
 
 Host PnP-RANSAC is outside the accelerated path: a keyframe here keeps all
 tracked features and takes the synthetic ground-truth pose; everything the north_star names
@@ -18,7 +24,9 @@ tracked features and takes the synthetic ground-truth pose; everything the north
 from __future__ import annotations
 
 import argparse
+import csv
 import json
+import math
 import os
 import subprocess
 import sys
@@ -35,7 +43,8 @@ METRIC = "stereo frames/s (front end, 1241x376)"
 UNIT = "frames/s"
 W, H = 1241, 376
 N_PIX = W * H
-# algorithmic bytes per image of the HBM-bound kernels (DESIGN.md / SURVEY.md 8d)
+TOTAL_SEQS_STRONG = 64                         # configs[3]: 64 sequences sharded over the GPUs
+# algorithmic bytes per image of the HBM-bound kernels (DESIGN.md 4 / SURVEY.md 8d)
 ALGO_BYTES = {
     # fused Shi-Tomasi score + 3x3 NMS: the u8 image is read once, the f32 eig map is never
     # written (SURVEY.md 8d "fused" variant), + 8 B per local maximum (~1e4 per image, ignored)
@@ -43,6 +52,8 @@ ALGO_BYTES = {
     "pyr_down_u8": 612598 + 153314,            # 3 levels: bytes read + bytes written
 }
 INGEST_BYTES_PER_IMAGE = 2 * N_PIX             # staged copy read + pitched image written
+NCU_SUMMARY = os.path.join(ROOT, "profiles", "r2_ncu_full_summary.csv")
+NCU_TRAFFIC = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
 
 
 def _env_int(name, default):
@@ -58,16 +69,21 @@ class ClockSampler:
              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, period_ms: int = 50):
         self.gpu = gpu_index
+        self.period_ms = period_ms
         self.proc = None
         self.lines = []
+        self.t_lines = []
+        self.window = None
 
-    def start(self):
+    def launch(self):
+        """start nvidia-smi early (it needs ~0.2 s to produce its first sample); samples are
+        kept only if they fall inside the window set by begin()/end()"""
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.QUERY}",
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", str(self.period_ms)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -77,10 +93,18 @@ class ClockSampler:
     def _read(self):
         for ln in self.proc.stdout:
             self.lines.append(ln.strip())
+            self.t_lines.append(time.perf_counter())
+
+    def begin(self):
+        self.window = [time.perf_counter(), None]
+
+    def end(self):
+        self.window[1] = time.perf_counter()
 
     def stop(self) -> dict:
         if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"],
+                    "samples": 0}
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
@@ -88,7 +112,10 @@ class ClockSampler:
             self.proc.kill()
         sm, smax, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        t0, t1 = self.window if self.window else (0.0, float("inf"))
+        for ln, ts in zip(self.lines, self.t_lines):
+            if ts < t0 or (t1 is not None and ts > t1):
+                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -103,28 +130,6 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None,
                 "sm_max_mhz": float(max(smax)) if smax else None,
                 "reasons": sorted(reasons), "samples": len(sm)}
-
-
-def make_frames(n_tex: int, n_frames: int):
-    """n_tex distinct synthetic sequences x n_frames stereo pairs (pinned host memory)."""
-    from stereo_vo_b200 import capi, synth
-    buf = capi.pinned_empty((n_tex, n_frames, 2, H, W), np.uint8)
-    for s in range(n_tex):
-        for t in range(n_frames):
-            l, r = synth.stereo_frame(s, t)
-            buf[s, t, 0] = l
-            buf[s, t, 1] = r
-    return buf
-
-
-def frame_index(step: int, slot: int, n_tex: int, n_frames: int):
-    """Sequence slot -> (texture, frame). Slots sharing a texture run at different phases; the
-    frame index ping-pongs so consecutive frames of a slot are always consecutive in time."""
-    tex = slot % n_tex
-    phase = (slot // n_tex) * 3
-    k = (step + phase) % (2 * n_frames - 2)
-    t = k if k < n_frames else 2 * n_frames - 2 - k
-    return tex, t
 
 
 def bind_near_gpu(local_rank: int):
@@ -155,14 +160,63 @@ def bind_near_gpu(local_rank: int):
         return None
 
 
+def measure_h2d_gbs(torch, nbytes=256 << 20, reps=5):
+    """pinned host -> device copy rate of this box (one large cudaMemcpyAsync, CUDA events): the
+    ceiling of the e2e leg, whose compulsory traffic is one left image per frame + one right image
+    per keyframe"""
+    src = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+    dst = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    dst.copy_(src, non_blocking=True)
+    torch.cuda.synchronize()
+    best = 0.0
+    for _ in range(reps):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        dst.copy_(src, non_blocking=True)
+        b.record()
+        b.synchronize()
+        best = max(best, nbytes / (a.elapsed_time(b) * 1e-3) / 1e9)
+    del src, dst
+    return best
+
+
+def ncu_matching_figures():
+    """SM issue / L1-shared throughput of the matching kernels from the committed ncu capture
+    (profiles/, same workload, one engine group) - SURVEY.md 8d asks for these instead of an HBM
+    fraction for lk_track / stereo_bm_sparse / sort / greedy."""
+    try:
+        with open(NCU_SUMMARY) as fh:
+            rows = list(csv.DictReader(fh))
+    except OSError:
+        return None
+    out = {}
+    for r in rows:
+        name = r.get("kernel", "")
+        for key in ("lk_track_kernel", "stereo_bm_sparse_kernel", "sort_small_kernel",
+                    "greedy_select_kernel", "stereo_bm_dense_kernel"):
+            if name.startswith(key) and key not in out:
+                def col(prefix):
+                    for k, v in r.items():
+                        if k.startswith(prefix):
+                            try:
+                                return float(v)
+                            except ValueError:
+                                return None
+                    return None
+                out[key] = {"issue_active_pct": col("smsp__issue_active"),
+                            "l1tex_throughput_pct": col("l1tex__throughput"),
+                            "sm_throughput_pct": col("sm__throughput"),
+                            "warps_active_pct": col("sm__warps_active"),
+                            "registers": col("launch__registers_per_thread")}
+    out["source"] = "committed capture " + os.path.relpath(NCU_SUMMARY, ROOT)
+    return out
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
-    from stereo_vo_b200 import capi, frontend, synth
-    from stereo_vo_b200 import build
-    if build.needs_build():
-        build.build_lib()
-    if build.host_needs_build():
-        build.build_host_lib()
+    from stereo_vo_b200 import build, capi, hostapi, sharding, synth, workload
+    build.build_lib()                    # no-ops when fresh; serialised across ranks by a file lock
+    build.build_host_lib()
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: the front end has no CPU path")
     torch.cuda.set_device(local_rank)
@@ -178,97 +232,83 @@ def run_ours(args, rank, world, local_rank):
         dist = dist_mod
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    S = args.seqs_per_gpu
-    n_tex, n_frames = args.textures, args.frames
-    frames = make_frames(n_tex, n_frames)
     cam = synth.KITTI00
-
-    def pose_fn(slot, step):
-        tex, t = frame_index(step, slot, n_tex, n_frames)
-        p = np.eye(4, dtype=np.float32)
-        p[:3, 3] = synth.ground_truth(t)
-        return p
+    S, F = args.seqs_per_gpu, args.frames
+    seeds = sharding.weak_shard(S, world, rank)          # globally unique texture seeds
+    slab = capi.pinned_empty((S, F, 2, H, W), np.uint8)
+    t_gen = time.perf_counter()
+    workload.generate_frames(seeds, F, slab, workers=max(1, total_cores // max(world, 1)))
+    t_gen = time.perf_counter() - t_gen
 
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def run_leg(device_resident: bool, steps: int, warmup: int, profile: bool, groups: int):
-        import ctypes as C
-        from stereo_vo_b200 import hostapi
-        batch = hostapi.Batch(W, H, S, groups, cam, device=local_rank)
-        pitch = W
+    def reduce(x, op="max"):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def throughput_leg(n_seq, resident, K, Wm, groups, min_seconds, profile=False,
+                       pipeline=True):
+        """n_seq sequences (the first n_seq of this rank's slab) through hostapi.Batch."""
+        batch = hostapi.Batch(W, H, n_seq, groups, cam, device=local_rank)
+        sub = slab[:n_seq]
         dptr = None
-        if device_resident:
-            dptr = batch.device_alloc(frames.nbytes)
-            batch.device_upload(dptr, frames)
-        img_bytes = H * W
-        base = dptr if device_resident else frames.ctypes.data
-        period = 2 * n_frames - 2
-        # pointer arrays and keyframe poses for every phase of the (periodic) frame schedule
-        sched = []
-        for k in range(period):
-            ls, rs, ps = [], [], []
-            for slot in range(S):
-                tex, t = frame_index(k, slot, n_tex, n_frames)
-                off = ((tex * n_frames + t) * 2) * img_bytes
-                ls.append(base + off)
-                rs.append(base + off + img_bytes)
-                ps.append(pose_fn(slot, k))
-            poses = np.ascontiguousarray(np.stack(ps).reshape(S, 16), np.float32)
-            sched.append(((C.c_void_p * S)(*ls), (C.c_void_p * S)(*rs), poses,
-                          poses.ctypes.data_as(C.c_void_p)))
+        base = sub.ctypes.data
+        if resident:
+            dptr = batch.device_alloc(sub.nbytes)
+            batch.device_upload(dptr, sub)
+            base = dptr
+        tables = workload.PointerTables(workload.Schedule(n_seq, F), base, cam)
+        pipeline = pipeline and args.pipeline and not profile
 
         def args_of(k):
-            lp, rp, _poses, pz = sched[k % period]
-            if device_resident or not args.prefetch:
-                return (lp, rp, pitch, device_resident, pz)
-            nlp, nrp, _p, _z = sched[(k + 1) % period]
-            return (lp, rp, pitch, False, pz, nlp, nrp)
+            return tables.args(k, W, resident, args.prefetch)
 
-        def one(k):
-            return batch.step_raw(*args_of(k))
-
-        for k in range(warmup):
-            one(k)
+        workload.run_steps(batch, args_of, 0, Wm, pipeline)
+        k0 = Wm
+        R = 1
+        if min_seconds > 0:
+            # calibration block (untimed): how many K-step repeats fill the window
+            t0 = time.perf_counter()
+            workload.run_steps(batch, args_of, k0, k0 + K, pipeline)
+            probe = time.perf_counter() - t0
+            k0 += K
+            R = max(1, int(math.ceil(min_seconds / max(probe, 1e-6))))
+            R = int(reduce(float(R)))                     # same repeat count on every rank
         launches0 = batch.kernel_launches
         if profile:
             batch.set_profiling(True)
         sampler = ClockSampler(local_rank)
+        sampler.launch()
+        if min_seconds > 0:
+            time.sleep(0.3)                               # nvidia-smi start-up
+        marks = []
+
+        def on_step(k, _sm):
+            if (k - k0 + 1) % K == 0:
+                marks.append(time.perf_counter())
+
         barrier()
-        sampler.start()
+        sampler.begin()
         batch.timer_begin()
         t0 = time.perf_counter()
-        tracked = corners = keyframes = rights = 0
-        first, last = warmup, warmup + steps
-        if args.pipeline and not profile:
-            # two steps in flight (svo_batch_submit / svo_batch_wait): engine groups run free of
-            # each other, the tail of step k overlaps the heavy kernels of step k+1
-            batch.submit_raw(*args_of(first))
-            for k in range(first, last):
-                if k + 1 < last:
-                    batch.submit_raw(*args_of(k + 1))
-                sm = batch.wait()
-                tracked += sm.tracked
-                corners += sm.corners
-                keyframes += sm.keyframes
-                rights += sm.right_images
-        else:
-            for k in range(first, last):
-                sm = one(k)
-                tracked += sm.tracked
-                corners += sm.corners
-                keyframes += sm.keyframes
-                rights += sm.right_images
+        tot = workload.run_steps(batch, args_of, k0, k0 + R * K, pipeline, on_step)
         ev_ms = batch.timer_end()
         barrier()
         wall_ms = (time.perf_counter() - t0) * 1e3
+        sampler.end()
         clocks = sampler.stop()
-        prof = batch.get_profile() if profile else {}
-        out = dict(ms=max(ev_ms, 0.0), wall_ms=wall_ms, clocks=clocks, prof=prof,
-                   launches=batch.kernel_launches - launches0, keyframes=keyframes,
-                   tracked=tracked, corners=corners, rights=rights)
+        blocks = np.diff(np.array([t0] + marks)) * 1e3 / K      # wall ms per step, per K-block
+        out = dict(ms=max(ev_ms, 0.0), wall_ms=wall_ms, clocks=clocks, repeats=R,
+                   prof=batch.get_profile() if profile else {},
+                   launches=batch.kernel_launches - launches0, tot=tot, n_seq=n_seq,
+                   block_ms_per_step=dict(median=float(np.median(blocks)),
+                                          min=float(blocks.min()), max=float(blocks.max())))
         if dptr is not None:
             batch.device_free(dptr)
         batch.close()
@@ -278,26 +318,36 @@ def run_ours(args, rank, world, local_rank):
     if args.groups <= 0:
         cores_per_rank = max(1, total_cores // max(world, 1))
         args.groups = min(4, cores_per_rank)
-    dev = run_leg(True, K, Wm, profile=False, groups=args.groups)
-    e2e = dev if args.skip_e2e else run_leg(False, K, Wm, profile=False, groups=args.groups)
-    # per-kernel durations: a separate pass with ONE engine group, so every kernel is timed
-    # alone on the device (with several groups kernels of different streams overlap and their
-    # event-bracketed durations include each other)
+    dev = throughput_leg(S, True, K, Wm, args.groups, args.min_seconds)
+    e2e = dev if args.skip_e2e else throughput_leg(S, False, K, Wm, args.groups, args.min_seconds)
+    # strong scaling (configs[3] as written): 64 sequences in total, sharded 64/32/16/8 per GPU
+    n_strong = len(sharding.shard_sequences(TOTAL_SEQS_STRONG, world, rank))
+    strong = None
+    if world > 1 and not args.skip_strong and 0 < n_strong <= S:
+        strong = throughput_leg(n_strong, True, K, Wm, min(args.groups, max(1, n_strong // 8)),
+                                args.min_seconds / 2)
+    # per-kernel durations: a separate pass with ONE engine group and no pipelining, so every
+    # kernel is timed alone on the device (with several groups kernels of different streams
+    # overlap and their event-bracketed durations include each other)
     Kp = max(1, min(K, args.profile_steps))
-    prof_leg = run_leg(True, Kp, Wm, profile=True, groups=1)
+    prof_leg = throughput_leg(S, True, Kp, Wm, 1, 0.0, profile=True)
 
-    def reduce_max(x):
-        if dist is None:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    dev_ms = reduce_max(dev["ms"])
-    e2e_ms = reduce_max(e2e["ms"])
-    total_frames = world * S * K
-    value = total_frames / (dev_ms * 1e-3)
-    e2e_value = total_frames / (e2e_ms * 1e-3)
+    dev_ms = reduce(dev["ms"])
+    e2e_ms = reduce(e2e["ms"])
+    dev_frames = world * S * K * dev["repeats"]
+    e2e_frames = world * S * K * e2e["repeats"]
+    value = dev_frames / (dev_ms * 1e-3)
+    e2e_value = e2e_frames / (e2e_ms * 1e-3)
+    strong_out = None
+    if strong is not None:
+        s_ms = reduce(strong["ms"])
+        s_frames = reduce(float(strong["n_seq"] * K * strong["repeats"]), "sum")
+        strong_out = {"total_sequences": TOTAL_SEQS_STRONG, "seqs_per_gpu": n_strong,
+                      "value": s_frames / (s_ms * 1e-3), "unit": UNIT,
+                      "ms_per_step": s_ms / (K * strong["repeats"]), "repeats": strong["repeats"],
+                      "note": "frames resident in HBM; same 64 sequences whatever N "
+                              "(sharding.shard_sequences), so per-GPU batches shrink with N"}
+    h2d_gbs = measure_h2d_gbs(torch) if rank == 0 else None
 
     line = None
     if rank == 0:
@@ -322,30 +372,33 @@ def run_ours(args, rank, world, local_rank):
                 ent.update(algo_gbs=gbs, frac_of_hbm=gbs / peak)
             elif name == "ingest":
                 # every left image + the right image of every keyframe (svo_set_right)
-                images = S * Kp + prof_leg["keyframes"]
+                images = S * Kp + prof_leg["tot"]["keyframes"]
                 gbs = INGEST_BYTES_PER_IMAGE * images / (ms * 1e-3) / 1e9
                 ent.update(algo_gbs=gbs, frac_of_hbm=gbs / peak)
             kernels[name] = ent
-        dom = max(prof.items(), key=lambda kv: kv[1][0])[0] if prof else None
+        # the dominant kernel of a step by time: the two LK launches are one kernel
+        by_kernel = {}
+        for name, ent in kernels.items():
+            base = "lk_track" if name.startswith("lk_track") else name
+            by_kernel[base] = by_kernel.get(base, 0.0) + ent["ms_per_step"]
+        dom = max(by_kernel.items(), key=lambda kv: kv[1])[0] if by_kernel else None
         # roofline of the dominant kernel among those whose interface is HBM traffic (whole-image
         # passes); lk_track / stereo / sort / greedy work on <= 400 points per frame and are
-        # issue/latency-bound (profiles/: SM issue and L1 figures from ncu)
+        # issue/latency-bound: their SM issue and L1 figures are under `matching`
         hbm_dom = max((n for n in ("corner_score_nms", "pyr_down_u8") if n in kernels),
                       key=lambda n: kernels[n]["ms_per_step"], default=None)
-        # DRAM traffic per launch of that kernel from the committed `ncu --set full` capture
-        # (profiles/, same command line, one engine group); None when no capture is on disk
         traffic, traffic_src = None, None
         try:
-            with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as fh:
+            with open(NCU_TRAFFIC) as fh:
                 ncu_t = json.load(fh)
-            cs_name = next((k for k in ncu_t if k.startswith("corner_score_nms_kernel")),
-                           "corner_score_nms_kernel")
-            pick = {"corner_score_nms": [cs_name],
-                    "pyr_down_u8": ["pyr_down_u8_kernel<8>", "pyr_down_u8_kernel<4>",
-                                    "pyr_down_u8_kernel<2>"]}.get(hbm_dom, [])
-            if pick and all(k in ncu_t for k in pick):
+            pick = [k for k in ncu_t if k.startswith(
+                {"corner_score_nms": "corner_score_nms_kernel",
+                 "pyr_down_u8": "pyr_down"}.get(hbm_dom, "\0"))]
+            if pick:
                 traffic = sum(ncu_t[k]["dram_bytes_per_launch"] for k in pick)
-                traffic_src = "profiles/r1_ncu_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum)"
+                traffic_src = ("committed capture " + os.path.relpath(NCU_TRAFFIC, ROOT) +
+                               " (dram__bytes_read.sum + dram__bytes_write.sum per launch; not "
+                               "re-measured in this run)")
         except (OSError, ValueError, KeyError):
             pass
         roofline = None
@@ -356,25 +409,49 @@ def run_ours(args, rank, world, local_rank):
                         "traffic_source": traffic_src,
                         "note": "corner_score_nms is issue-bound, not HBM-bound: OpenCV's sliding "
                                 "fp64 column sums force one thread per image column and row "
-                                "segment (DESIGN.md 4; segments whose guessed start was wrong are "
-                                "re-walked by `corner_repair`, timed separately in `kernels`); "
-                                "HBM-bound kernels: ingest, pyr_down_u8 (see `kernels`)",
+                                "segment (DESIGN.md 4); HBM-bound kernels: ingest, pyr_down_u8 "
+                                "(see `kernels`)",
                         "peak_source": peak_src,
                         "algorithmic_bytes_per_launch": ALGO_BYTES[hbm_dom] * S,
-                        "dominant_kernel_of_step": dom}
+                        "dominant_kernel_of_step": dom,
+                        "dominant_kernel_ms_per_step": by_kernel.get(dom),
+                        "matching": ncu_matching_figures()}
         cpu = None if args.skip_cpu_baseline else cpu_baseline(sample_frames=args.cpu_frames)
         # every left image + the right images actually transferred (predicted keyframes and
         # keyframes fetched on demand; counted by the driver)
-        in_bytes = int(S * H * W + e2e["rights"] / K * H * W)
+        e2e_steps = K * e2e["repeats"]
+        rights_per_step = e2e["tot"]["rights"] / e2e_steps
+        in_bytes = int(S * H * W + rights_per_step * H * W)
+        compulsory = int(S * H * W + e2e["tot"]["keyframes"] / e2e_steps * H * W)
         eng_tmp_block = 16 + 24 + 300 * 8 + 400 * 16
+        e2e_step_ms = e2e_ms / e2e_steps
+        pcie = None
+        if h2d_gbs:
+            pcie = {"h2d_gbs_measured": h2d_gbs,
+                    "h2d_gbs_achieved": in_bytes / (e2e_step_ms * 1e-3) / 1e9,
+                    "frac_of_link": in_bytes / (e2e_step_ms * 1e-3) / 1e9 / h2d_gbs,
+                    "compulsory_bytes_per_step": compulsory,
+                    "ceiling_frames_per_s": h2d_gbs * 1e9 / (compulsory / S),
+                    "frac_of_ceiling": (S / (e2e_step_ms * 1e-3)) / (h2d_gbs * 1e9 / (compulsory / S)),
+                    "note": "the e2e leg is bound by the host->device link: every frame must "
+                            "deliver its left image and every keyframe its right image"}
+        extras = None
+        if world == 1 and not args.skip_extras:
+            extras = run_extras(local_rank)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
-            "warmup": Wm, "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8/f32/f64 (bit-exact OpenCV arithmetic)",
-            "data": "synthetic",
+            "warmup": Wm, "ms_per_step": dev_ms / (K * dev["repeats"]), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8/f32/f64 (bit-exact OpenCV arithmetic)", "data": "synthetic",
+            "repeats": dev["repeats"], "timed_steps": K * dev["repeats"],
+            "timed_region_s": dev_ms * 1e-3,
+            "block_ms_per_step_wall": dev["block_ms_per_step"],
             "config": {"workload": f"{S} independent KITTI-shaped (1241x376) synthetic stereo "
-                                   "sequences per GPU, kitti00 params (BASELINE configs[3] shape)",
+                                   f"sequences per GPU (texture seeds {S}*rank .. {S}*rank+{S - 1}, "
+                                   f"{F} frames each, ping-pong), kitti00 params "
+                                   "(BASELINE configs[3] shape; configs[1]/[2]/[4] under `extras`)",
                        "seqs_per_gpu": S, "frames_per_step": S * world,
+                       "frames_per_sequence": F,
                        "parallelism": f"{world} GPU(s) x {S} sequences in {args.groups} engine groups "
                                       "(one CUDA stream + host worker each), no collective",
                        "host_cores": total_cores, "rank0_cpu_binding": numa_bind,
@@ -384,29 +461,134 @@ def run_ours(args, rank, world, local_rank):
                                + "; right images uploaded for keyframes only; e2e leg "
                                + ("prefetches" if args.prefetch else "does not prefetch")
                                + " the next step's frames (svo_prefetch)",
-                       "l2": "inputs larger than L2: every step reads 64 new stereo pairs (60 MB "
-                             "staged + 60 MB pitched copies + 2 x 51 MB pyramid slots in flight "
-                             "> 126 MB L2); no flush between steps",
-                       "keyframes_per_step": dev["keyframes"] / K,
-                       "tracked_per_frame": dev["tracked"] / (S * K),
-                       "corners_per_frame": dev["corners"] / (S * K),
+                       "l2": f"inputs larger than L2: {S * F * 2 * N_PIX / 1e9:.2f} GB of frames "
+                             f"per GPU, every step reads {S} new stereo pairs "
+                             f"({S * 2 * N_PIX / 1e6:.0f} MB) plus pyramids; no flush between steps",
+                       "timing": f"K = {K} steps repeated R = {dev['repeats']} times back to back in "
+                                 "one CUDA-event window (max over engine groups and ranks)",
+                       "keyframes_per_step": dev["tot"]["keyframes"] / (K * dev["repeats"]),
+                       "tracked_per_frame": dev["tot"]["tracked"] / (S * K * dev["repeats"]),
+                       "corners_per_frame": dev["tot"]["corners"] / (S * K * dev["repeats"]),
+                       "frame_generation_s": t_gen,
                        "pnp": "host PnP outside the accelerated path: keyframes keep all tracks, "
-                              "pose = synthetic ground truth"},
+                              "pose = synthetic ground truth",
+                       "parity": "this exact driver loop is compared with the cv2 oracle in "
+                                 "tests/test_gpu_bench_path.py (64 sequences x 56 steps, both legs)",
+                       "reference_arm": "--impl reference runs the cv2 restatement of the "
+                                        "reference, one sequence per host core x --ref-frames "
+                                        "frames per step (a bounded sample: the CPU needs ~25 ms "
+                                        "per frame); same metric and frame shape, so the two arms' "
+                                        "frames/s compare directly although steps/config differ"},
             "clocks": dev["clocks"],
-            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms / K,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_step_ms,
+                    "repeats": e2e["repeats"], "timed_region_s": e2e_ms * 1e-3,
                     "h2d_bytes_per_step": in_bytes,
                     "d2h_bytes_per_step": S * eng_tmp_block,
+                    "block_ms_per_step_wall": e2e["block_ms_per_step"],
+                    "pcie": pcie,
                     "clocks": e2e["clocks"]},
             "gpu_launches": dev["launches"],
+            "gpu_launches_per_step": dev["launches"] / (K * dev["repeats"]),
             "roofline": roofline,
             "kernels": kernels,
+            "strong_scaling": strong_out,
+            "extras": extras,
             "cpu_baseline": cpu,
-            "wall_ms_per_step": dev["wall_ms"] / K,
+            "wall_ms_per_step": dev["wall_ms"] / (K * dev["repeats"]),
         }
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
     return line
+
+
+def run_extras(device: int) -> dict:
+    """The other BASELINE configs, measured in the same run (N = 1 only): configs[1]/[2]
+    single-sequence latency (KITTI, d435i), configs[4] 3840x2160 / 20 k corners throughput, and
+    the dense StereoBM map. All through the same C++ driver / C ABI."""
+    from stereo_vo_b200 import capi, hostapi, synth, workload
+    out = {}
+    # ---- single-sequence latency: one synchronous svo_batch_step per frame, host frames
+    for name, cam, motion in (("kitti_latency", synth.KITTI00, synth.KITTI_MOTION),
+                              ("d435i_latency", synth.D435I, synth.D435I_MOTION)):
+        n_fr = 40
+        slab = capi.pinned_empty((1, n_fr, 2, cam.height, cam.width), np.uint8)
+        workload.generate_frames([3], n_fr, slab, cam, motion, workers=1)
+        batch = hostapi.Batch(cam.width, cam.height, 1, 1, cam, device=device)
+        tables = workload.PointerTables(workload.Schedule(1, n_fr), slab.ctypes.data, cam, motion)
+        lat, kinds = [], []
+        for k in range(3 * n_fr):
+            a = tables.args(k, cam.width, False, False)
+            t0 = time.perf_counter()
+            sm = batch.step_raw(*a)
+            dt = (time.perf_counter() - t0) * 1e3
+            if k >= 8:
+                lat.append(dt)
+                kinds.append(sm.keyframes > 0)
+        batch.close()
+        lat, kf = np.array(lat), np.array(kinds)
+        out[name] = {"config": f"{cam.width}x{cam.height}, one sequence, synchronous svo_batch_step "
+                               "per frame (H2D + kernels + D2H + host bookkeeping), wall clock",
+                     "ms_per_frame_median": float(np.median(lat)),
+                     "ms_p95": float(np.percentile(lat, 95)),
+                     "ms_skip_frames": float(np.median(lat[~kf])) if (~kf).any() else None,
+                     "ms_keyframes": float(np.median(lat[kf])) if kf.any() else None,
+                     "frames": int(len(lat)), "keyframes": int(kf.sum())}
+    # ---- configs[4]: 3840x2160, goodFeaturesToTrack(20000, 0.01, 20), feature limit lifted
+    try:
+        cam, motion = synth.UHD4K, synth.UHD4K_MOTION
+        S4, F4 = 4, 4
+        slab = capi.pinned_empty((S4, F4, 2, cam.height, cam.width), np.uint8)
+        workload.generate_frames(list(range(S4)), F4, slab, cam, motion)
+        p = capi.default_params(cam.width, cam.height)
+        p.max_corners, p.quality_level, p.min_distance, p.max_features = 20000, 0.01, 20.0, 20000
+        batch = hostapi.Batch(cam.width, cam.height, S4, 2, cam, device=device, params=p)
+        dptr = batch.device_alloc(slab.nbytes)
+        batch.device_upload(dptr, slab)
+        tables = workload.PointerTables(workload.Schedule(S4, F4, phase_step=1), dptr, cam, motion)
+        workload.run_steps(batch, lambda k: tables.args(k, cam.width, True, False), 0, 4, True)
+        n_steps = 24
+        batch.timer_begin()
+        tot = workload.run_steps(batch, lambda k: tables.args(k, cam.width, True, False), 4,
+                                 4 + n_steps, True)
+        ms = batch.timer_end()
+        batch.device_free(dptr)
+        batch.close()
+        out["uhd_stress"] = {"config": f"{S4} sequences of 3840x2160 resident in HBM "
+                                       f"({slab.nbytes / 1e6:.0f} MB of frames > L2), "
+                                       "goodFeaturesToTrack(20000, 0.01, 20), max_features 20000, "
+                                       "4-level pyramid, 2 engine groups, pipelined",
+                             "frames_per_s": S4 * n_steps / (ms * 1e-3),
+                             "ms_per_frame": ms / (S4 * n_steps),
+                             "corners_per_frame": tot["corners"] / (S4 * n_steps),
+                             "tracked_per_frame": tot["tracked"] / (S4 * n_steps),
+                             "keyframes": tot["keyframes"]}
+    except Exception as ex:                                # report, never hide the headline
+        out["uhd_stress"] = {"error": repr(ex)}
+    # ---- dense StereoBM maps per second, 64 KITTI pairs resident on the device
+    try:
+        cam = synth.KITTI00
+        n = 64
+        e = capi.Engine(cam.width, cam.height, n_seq=n, device=device)
+        pairs = [synth.stereo_frame(s, 0) for s in range(8)]
+        for s in range(n):
+            e.stereo_bm_dense(pairs[s % 8][0], pairs[s % 8][1], seq=s)
+        seqs = list(range(n))
+        for _ in range(3):
+            e.stereo_bm_dense_resident(seqs, fetch=False)
+        ms = []
+        for _ in range(20):
+            e.stereo_bm_dense_resident(seqs, fetch=False)
+            ms.append(e.last_timing()[1])
+        e.close()
+        ms = float(np.median(ms))
+        out["dense_stereo_bm"] = {"config": f"{n} KITTI pairs resident on the device, one launch, "
+                                            "full CV_16S map of StereoBM(48, 21)",
+                                  "maps_per_s": n / (ms * 1e-3), "us_per_pair": 1e3 * ms / n,
+                                  "algo_gbs": 4 * N_PIX * n / (ms * 1e-3) / 1e9}
+    except Exception as ex:
+        out["dense_stereo_bm"] = {"error": repr(ex)}
+    return out
 
 
 def _cpu_worker(arg):
@@ -416,12 +598,12 @@ def _cpu_worker(arg):
     from stereo_vo_b200 import synth
     cv2.setNumThreads(threads)
     cv2.setUseOptimized(True)             # the reference's realistic speed (default OpenCV mode)
-    # sequences of at most 48 frames each: on longer synthetic runs tracked + new features pass
-    # the 400-feature limit, where the reference's own bookkeeping is undefined behaviour
-    #  and the oracle refuses to continue
+    # sequences of at most 80 frames each: on longer synthetic runs tracked + new features pass
+    # the 400-feature limit (from frame ~89 on), where the reference's own bookkeeping is
+    # undefined behaviour and the oracle refuses to continue
     chunks, left = [], n_frames
     while left > 0:
-        c = min(48, left)
+        c = min(80, left)
         chunks.append(synth.sequence(seed + 1000 * len(chunks), c))
         left -= c
     t0 = time.perf_counter()
@@ -482,7 +664,6 @@ def run_reference(args, rank, world):
     cores = len(os.sched_getaffinity(0))
     n_proc = max(1, min(cores, 64))
     each = args.ref_frames
-    vals = []
     for _ in range(args.warmup if args.warmup < 2 else 1):
         cpu_run(n_proc, max(4, each // 2), 1)
     t_total = 0.0
@@ -490,7 +671,6 @@ def run_reference(args, rank, world):
     K = max(1, min(args.steps, 3))
     for _ in range(K):
         fps, wall, _ = cpu_run(n_proc, each, 1)
-        vals.append(fps)
         t_total += wall
         frames_total += n_proc * each
     value = frames_total / t_total
@@ -503,7 +683,11 @@ def run_reference(args, rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/f32/f64",
         "data": "synthetic",
         "config": {"workload": f"{n_proc} independent KITTI-shaped (1241x376) synthetic stereo "
-                               "sequences on the host cores, kitti00 params"},
+                               "sequences on the host cores, kitti00 params",
+                   "note": "bounded sample of the GPU arm's workload: one sequence per host core, "
+                           f"{each} frames per step, at most 3 steps (the CPU path needs ~25 ms "
+                           "per frame and core); frames/s is aggregate over all cores and "
+                           "compares directly with the GPU arm's frames/s"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": n_proc, "kind": "port",
                          "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -514,22 +698,27 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--seqs-per-gpu", type=int, default=64)
-    ap.add_argument("--textures", type=int, default=8)
-    ap.add_argument("--frames", type=int, default=12)
+    ap.add_argument("--frames", type=int, default=40, help="frames per synthetic sequence")
+    ap.add_argument("--min-seconds", type=float, default=2.0,
+                    help="minimum length of the timed window of each leg: the K-step region is "
+                         "repeated back to back until it lasts this long")
     ap.add_argument("--cpu-frames", type=int, default=2400)
     ap.add_argument("--skip-cpu-baseline", action="store_true", help="profiling runs only")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only")
+    ap.add_argument("--skip-strong", action="store_true", help="no strong-scaling leg (N > 1)")
+    ap.add_argument("--skip-extras", action="store_true",
+                    help="no d435i / 4K / dense extras (they run at N = 1 only)")
     ap.add_argument("--ref-frames", type=int, default=16)
     ap.add_argument("--profile-steps", type=int, default=60,
                     help="steps of the separate single-group pass that times every kernel alone")
     ap.add_argument("--groups", type=int, default=0,
                     help="engine groups (CUDA streams + host workers) the sequences of a GPU are "
                          "split into; 0 = 4, or fewer when the ranks of this node have less than "
-                         "4 host cores each (every worker waits for its stream on a core)")
+                         "4 host cores each")
     ap.add_argument("--no-bind", action="store_true",
                     help="multi-GPU runs: do not pin the rank to the host cores next to its GPU")
     ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",

@@ -53,7 +53,8 @@ class BatchFrontEnd {
 
     // One frame of every sequence. left/right: n_seq image pointers (host memory, or device
     // memory when on_device), `pitch` bytes per row. poses: n_seq x 16 floats (row-major
-    // camera->world, used only by sequences that become keyframes) or nullptr for identity.
+    // camera->world, used only by sequences that become keyframes; a sequence's FIRST keyframe
+    // always takes the identity, as src/image_processor.cpp:34-39 does) or nullptr for identity.
     // next_left/next_right: optional host frames of the following step, copied ahead while
     // this step computes. Throws std::runtime_error on a C-ABI failure.
     BatchSummary step(const uint8_t* const* left, const uint8_t* const* right, int pitch,

@@ -15,14 +15,13 @@
 #include "../../include/svo_c.h"
 #include "svo_common.cuh"
 
-#define SVO_PROF_SLOTS 14
+#define SVO_PROF_SLOTS 13
 static const char* const kProfNames[SVO_PROF_SLOTS] = {
     "pyr_down_u8", "corner_score_nms", "ingest", "sort_candidates",
     "greedy_min_distance", "lk_track_fwd", "lk_track_bwd", "track_filter_compact",
-    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q", "corner_repair",
-    "stereo_bm_dense"};
+    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q", "stereo_bm_dense"};
 enum { P_PYR, P_SCORE, P_INGEST, P_SORT, P_GREEDY, P_LKF, P_LKB, P_FILTER, P_PACK, P_DEDUPE,
-       P_STEREO, P_REPROJ, P_REPAIR, P_DENSE };
+       P_STEREO, P_REPROJ, P_DENSE };
 
 namespace {
 
@@ -110,9 +109,11 @@ struct svo_engine {
     int n_strips = 0, n_seg = 0, strip_cap = 0;
     // corner_score_nms: per (strip, segment) maximum, wrong-start flag, true sums of a flagged start
     unsigned int* d_sub_max = nullptr;
-    unsigned char* d_seg_flag = nullptr;
+    unsigned int* d_seg_flag = nullptr;       // [..][2] epoch-tagged start verdicts
     double* d_seg_state = nullptr;
     unsigned int* d_cs_ticket = nullptr;
+    unsigned int* d_cs_work = nullptr;        // [2] work-item dispenser of corner_score_nms
+    unsigned int cs_epoch = 0;                // corner_score_nms launches on these buffers
     float2* d_corners = nullptr;
     int* d_ncorners = nullptr;
     int* d_grid = nullptr;
@@ -617,18 +618,15 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t 
         SVO_CUDA_OK(svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, st));
         e->launches += e->lay.n_levels - 1;
     }
+    e->cs_epoch = (e->cs_epoch % 0x3fffffffu) + 1u;    // tags this launch's verdict words
     const SvoCornerCall cc = {e->d_pyr, e->seq_stride, e->d_eig, e->eig_pitch, e->eig_stride,
                               e->d_eig_max, e->p.quality_level, e->d_strips, e->n_strips,
                               e->n_seg, e->strip_cap, e->d_strip_count, e->d_sub_max,
-                              e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, dc};
+                              e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_cs_work,
+                              e->cs_epoch, dc};
     {
         ProfScope ps(e, P_SCORE, st);
         SVO_CUDA_OK(svo_launch_corner_score_nms(cc, e->lay, n, st));
-    }
-    {
-        ProfScope ps(e, P_REPAIR, st);
-        SVO_CUDA_OK(svo_launch_corner_repair(cc, e->lay, n, st));
-        e->launches += 1;
     }
     {
         ProfScope ps(e, P_SORT, st);
@@ -1074,11 +1072,13 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_strips, n_sub * (size_t)e->strip_cap));
     CCHK(dalloc(&e->d_strip_count, n_sub));
     CCHK(dalloc(&e->d_sub_max, n_sub));
-    CCHK(dalloc(&e->d_seg_flag, n_sub));
+    CCHK(dalloc(&e->d_seg_flag, 2 * n_sub));
+    CCHK(dalloc(&e->d_cs_work, 2));
+    CCHK(cudaMemsetAsync(e->d_cs_work, 0, 2 * sizeof(unsigned int), e->st));
     CCHK(dalloc(&e->d_seg_state, n_sub * svo_corner_state_doubles()));
     CCHK(dalloc(&e->d_cs_ticket, ns));
     CCHK(cudaMemsetAsync(e->d_cs_ticket, 0, ns * sizeof(unsigned int), e->st));
-    CCHK(cudaMemsetAsync(e->d_seg_flag, 0, n_sub, e->st));
+    CCHK(cudaMemsetAsync(e->d_seg_flag, 0, 2 * n_sub * sizeof(unsigned int), e->st));
     CCHK(dalloc(&e->d_eig_max, ns));
     CCHK(dalloc(&e->d_cand, ns * mc));
     CCHK(dalloc(&e->d_cand_count, ns));
@@ -1140,7 +1140,7 @@ void svo_destroy(svo_engine* e) {
     if (e->st_copy) cudaStreamSynchronize(e->st_copy);
     if (e->st_det) cudaStreamSynchronize(e->st_det);
     void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_dense, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
-                     e->d_strips, e->d_strip_count, e->d_sub_max, e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
+                     e->d_strips, e->d_strip_count, e->d_sub_max, e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_cs_work, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,

@@ -90,14 +90,16 @@ struct SvoCornerCall {
     float* eig; int eig_pitch; size_t eig_stride;      // debug tap, nullptr: eig map not written
     unsigned int* eig_max; double quality;
     unsigned long long* strips; int n_strips, n_seg, strip_cap;
-    int* strip_count; unsigned int* sub_max; unsigned char* seg_flag; double* seg_state;
-    unsigned int* ticket;
+    int* strip_count; unsigned int* sub_max;
+    unsigned int* seg_flag;                // [n_seq][n_strips][n_seg][2] epoch-tagged verdicts
+    double* seg_state;
+    unsigned int* ticket;                  // [n_seq], zero between launches
+    unsigned int* work;                    // [2], zero between launches
+    unsigned int epoch;                    // launch number on these buffers (> 0, < 2^30)
     const SvoSeqCall* d_call;
 };
 cudaError_t svo_launch_corner_score_nms(const SvoCornerCall& c, const SvoPyrLayout& lay,
                                         int n_call, cudaStream_t st);
-cudaError_t svo_launch_corner_repair(const SvoCornerCall& c, const SvoPyrLayout& lay, int n_call,
-                                     cudaStream_t st);
 cudaError_t svo_launch_filter_candidates(const unsigned long long* strips, int n_strips,
                                          int strip_cap, const int* strip_count,
                                          const unsigned int* eig_max, double quality,

@@ -261,7 +261,9 @@ class BatchFrontEnd:
                 inl.append(np.zeros((0, 2), np.float32))
                 ninl.append(0)
             kf_seqs.append(i)
-            poses.append(self.pose_fn(i, t) if self.pose_fn else np.eye(4, dtype=np.float32))
+            # the first keyframe is triangulated with the identity (src/image_processor.cpp:34-39)
+            poses.append(self.pose_fn(i, t) if self.pose_fn and self.have_kf[i]
+                         else np.eye(4, dtype=np.float32))
         if kf_seqs:
             f, cx, cy, b = self.intr
             kr = e.keyframe(kf_seqs, inl, ninl, np.stack(poses).reshape(-1, 16), f, cx, cy, b)

@@ -265,7 +265,10 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         g.kf_local[(size_t)nk] = i;
         g.n_inl[(size_t)nk] = n_inl;
         float* pose = &g.poses[(size_t)nk * 16];
-        if (job.has_poses) std::memcpy(pose, job.poses.data() + (size_t)s * 16, 16 * sizeof(float));
+        // the first keyframe is triangulated with the identity pose, whatever the caller
+        // supplies (src/image_processor.cpp:34-39: cv::Mat::eye(4, 4, CV_32F))
+        if (job.has_poses && rs.decision != BATCH_FIRST)
+            std::memcpy(pose, job.poses.data() + (size_t)s * 16, 16 * sizeof(float));
         else for (int k = 0; k < 16; ++k) pose[k] = (k % 5 == 0) ? 1.f : 0.f;
         ++nk;
     }

@@ -313,11 +313,72 @@ def _window(arr_pad, pad, ix, iy, n):
     return arr_pad[iy + pad:iy + pad + n + 1, ix + pad:ix + pad + n + 1].astype(np.int64)
 
 
+def lk_window_sums_a(ixval, iyval):
+    """A11, A12, A22 numerators as cv::LKTrackerInvoker accumulates them (lkpyramid.cpp,
+    CV_SIMD128 path, no FMA): per window row two 8-pixel SIMD steps, each feeding pixels
+    (x0 .. x0+3) then (x0+4 .. x0+7) into four f32 lanes (product rounded, then added), then a
+    scalar f32 tail over the remaining pixels 16..20 ((float)(int product), added); at the end
+    tail += v_reduce_sum(lanes) = (l0 + l2) + (l1 + l3). Every operation rounds to f32.
+    Pinned against cv2 bit for bit by tests/test_oracle_restate.py (through lk_track)."""
+    win = ixval.shape[0]
+    q11 = np.zeros(4, F32)
+    q12 = np.zeros(4, F32)
+    q22 = np.zeros(4, F32)
+    t11 = t12 = t22 = F32(0)
+    simd = (win // 8) * 8
+    for y in range(win):
+        for x0 in range(0, simd, 4):
+            fx = ixval[y, x0:x0 + 4].astype(F32)
+            fy = iyval[y, x0:x0 + 4].astype(F32)
+            q22 = ((fy * fy).astype(F32) + q22).astype(F32)
+            q12 = ((fx * fy).astype(F32) + q12).astype(F32)
+            q11 = ((fx * fx).astype(F32) + q11).astype(F32)
+        for x in range(simd, win):
+            a, b = int(ixval[y, x]), int(iyval[y, x])
+            t11 = F32(t11 + F32(a * a))
+            t12 = F32(t12 + F32(a * b))
+            t22 = F32(t22 + F32(b * b))
+
+    def red(q):
+        return F32(F32(q[0] + q[2]) + F32(q[1] + q[3]))
+    return F32(t11 + red(q11)), F32(t12 + red(q12)), F32(t22 + red(q22))
+
+
+def lk_window_sums_b(diff, ixval, iyval):
+    """b1, b2 numerators of one LK iteration in cv2's order: per row and 8-pixel SIMD step the
+    int32 sums of the pixel pairs (p, p+4), p = 0..3 (v_dotprod), converted to f32 and added to
+    lanes qb0 = (p0.x, p0.y, p1.x, p1.y), qb1 = (p2.x, p2.y, p3.x, p3.y); scalar f32 tails over
+    pixels 16..20; at the end q = qb0 + qb1, b1 = tail1 + (q0 + q2), b2 = tail2 + (q1 + q3)."""
+    win = ixval.shape[0]
+    d = diff.astype(np.int64)
+    gx = ixval.astype(np.int64)
+    gy = iyval.astype(np.int64)
+    qb0 = np.zeros(4, F32)
+    qb1 = np.zeros(4, F32)
+    t1 = t2 = F32(0)
+    simd = (win // 8) * 8
+    for y in range(win):
+        for x0 in range(0, simd, 8):
+            px = d[y, x0:x0 + 8] * gx[y, x0:x0 + 8]
+            py = d[y, x0:x0 + 8] * gy[y, x0:x0 + 8]
+            d0 = np.array([px[0] + px[4], py[0] + py[4], px[1] + px[5], py[1] + py[5]])
+            d1 = np.array([px[2] + px[6], py[2] + py[6], px[3] + px[7], py[3] + py[7]])
+            qb0 = (qb0 + d0.astype(F32)).astype(F32)
+            qb1 = (qb1 + d1.astype(F32)).astype(F32)
+        for x in range(simd, win):
+            t1 = F32(t1 + F32(int(d[y, x] * gx[y, x])))
+            t2 = F32(t2 + F32(int(d[y, x] * gy[y, x])))
+    q = (qb0 + qb1).astype(F32)
+    return F32(t1 + F32(q[0] + q[2])), F32(t2 + F32(q[1] + q[3]))
+
+
 def lk_track(prev, nxt, pts, win=21, max_level=3, max_count=30, eps=0.01, min_eig_thr=1e-2,
-             exact_sums=True):
-    """Per-point pyramidal LK exactly as LKTrackerInvoker walks it (Appendix A3). Window sums
-    are exact integers converted once (cv2 accumulates in f32 SIMD lanes; the two agree to
-    <= 5e-5 px). Returns (next_pts float32 (n,2), status uint8 (n,))."""
+             exact_sums=False):
+    """Per-point pyramidal LK exactly as LKTrackerInvoker walks it (Appendix A3), window sums
+    accumulated in cv2's own f32 order (lk_window_sums_a / _b): bit-identical to
+    cv2.calcOpticalFlowPyrLK. exact_sums=True sums exact integers instead and converts once
+    (what the round-1 kernel did: within 2e-4 px of cv2, but ~20 % of the points differ in the
+    last bits). Returns (next_pts float32 (n,2), status uint8 (n,))."""
     pyr_i = build_pyramid(prev, max_level, win)
     pyr_j = build_pyramid(nxt, max_level, win)
     nlev = min(len(pyr_i), len(pyr_j))
@@ -371,9 +432,14 @@ def lk_track(prev, nxt, pts, win=21, max_level=3, max_count=30, eps=0.01, min_ei
             ival = interp(ip, ipx, ipy, 9)
             ixval = interp(dxp, ipx, ipy, 14)
             iyval = interp(dyp, ipx, ipy, 14)
-            a11 = F32(F32(int((ixval * ixval).sum())) * flt_scale)
-            a12 = F32(F32(int((ixval * iyval).sum())) * flt_scale)
-            a22 = F32(F32(int((iyval * iyval).sum())) * flt_scale)
+            if exact_sums:
+                s11, s12, s22 = (F32(int((ixval * ixval).sum())), F32(int((ixval * iyval).sum())),
+                                 F32(int((iyval * iyval).sum())))
+            else:
+                s11, s12, s22 = lk_window_sums_a(ixval, iyval)
+            a11 = F32(s11 * flt_scale)
+            a12 = F32(s12 * flt_scale)
+            a22 = F32(s22 * flt_scale)
             d = F32(F32(a11 * a22) - F32(a12 * a12))
             dif = F32(a11 - a22)
             rad = F32(F32(dif * dif) + F32(F32(F32(4.0) * a12) * a12))
@@ -395,8 +461,12 @@ def lk_track(prev, nxt, pts, win=21, max_level=3, max_count=30, eps=0.01, min_ei
                 b = F32(npt[1] - F32(iny))
                 w00, w01, w10, w11 = _weights(a, b)
                 diff = interp(jp, inx, iny, 9) - ival
-                b1 = F32(F32(int((diff * ixval).sum())) * flt_scale)
-                b2 = F32(F32(int((diff * iyval).sum())) * flt_scale)
+                if exact_sums:
+                    sb1, sb2 = F32(int((diff * ixval).sum())), F32(int((diff * iyval).sum()))
+                else:
+                    sb1, sb2 = lk_window_sums_b(diff, ixval, iyval)
+                b1 = F32(sb1 * flt_scale)
+                b2 = F32(sb2 * flt_scale)
                 delta = np.array([F32(F32(F32(a12 * b2) - F32(a22 * b1)) * d),
                                   F32(F32(F32(a12 * b1) - F32(a11 * b2)) * d)], F32)
                 npt = (npt + delta).astype(F32)

@@ -4,8 +4,10 @@
 // oracle/restate.py:lk_track.
 //
 // One block of 64 threads per key-point, walking pyramid levels top -> 0 like LKTrackerInvoker.
-// Thread (wy, run) owns 7 horizontally adjacent pixels of window row wy (21 rows x 3 runs = 63
-// threads), so neighbouring taps are shared in registers.
+// Thread (wy, part) owns pixels [0,8), [8,16) or [16,21) of window row wy (21 rows x 3 parts =
+// 63 threads) - the two 8-pixel SIMD steps and the 5-pixel scalar tail of OpenCV's row loop -
+// so neighbouring taps are shared in registers and the pixel pairs (x, x+4) OpenCV multiplies
+// together in one v_dotprod lane sit in one thread.
 //   * the 24x24 raw patch of I is staged in shared memory: with aligned 32-bit loads when it
 //     lies inside the image (the common case), byte-wise with reflect-101 at the border;
 //   * interior windows: B = w00*I + w01*I(x+1) + w10*I(y+1) + w11*I(x+1,y+1) is built once on a
@@ -15,9 +17,16 @@
 //     ever materialised;
 //   * windows touching the image border keep OpenCV's semantics literally: Scharr of the
 //     reflect-101 image on the 22x22 integer grid, ZERO outside the image, then interpolation;
-//   * A11/A12/A22 and, per iteration, b1/b2 are EXACT integer window sums (per-thread int32,
-//     warp REDUX on 16-bit halves, int64 across the two warps) converted once to f32 - cv2
-//     accumulates in f32 SIMD lanes, the two agree to <= 1e-4 px (tolerance 0.01 px);
+//   * A11/A12/A22 and, per iteration, b1/b2 are accumulated IN OPENCV'S ORDER, in f32 with a
+//     rounding after every addition: four SIMD lanes fed by pixels (L, L+4, L+8, L+12) of every
+//     row, a scalar tail fed by pixels 16..20, lanes folded as (l0+l2)+(l1+l3), tail added last
+//     (b: int32 sums of the pixel pairs (x, x+4), converted, two accumulators of four lanes).
+//     The per-pixel terms go through shared memory in chain order and ten (b) / fifteen (A)
+//     lanes of warp 0 each run one sequential chain. With exact integer sums instead the
+//     result differed from cv2 in the last bits of ~20 % of the points (<= 2e-4 px) - enough to
+//     flip the 0.01-px termination test once in ~1e6 iterations, after which a track drifts
+//     from the reference's by up to 0.05 px for the rest of its life. Now flow is bit-exact
+//     (oracle/restate.py:lk_window_sums pins the order against cv2);
 //   * a 28x28 region of J is staged per level (aligned words when interior) and re-staged only
 //     when the window leaves it, so an iteration is shared-memory + integer work only; all
 //     threads carry the scalar Gauss-Newton state redundantly: uniform control flow.
@@ -32,7 +41,7 @@ namespace {
 
 constexpr int WIN = SVO_LK_WIN;            // 21
 constexpr int NT = 64;                     // threads per key-point
-constexpr int RUN = 7;                     // window pixels per thread
+constexpr int RUN = 8;                     // window pixels per thread (the tail part uses 5)
 constexpr int IP = WIN + 3;                // raw I patch edge (24)
 constexpr int SP = 36;                     // byte pitch of the staged I / J rows (9 words:
                                            // rows 4 apart no longer share banks)
@@ -44,10 +53,38 @@ constexpr int JR = WIN + 1 + 2 * JM;       // staged J region edge (28)
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int LK_LEVELS = 4;               // levels pre-staged (reference: maxLevel 3)
 
-__device__ __forceinline__ long long warp_sum_exact(int v) {
-    int lo = __reduce_add_sync(FULL, v & 0xffff);
-    int hi = __reduce_add_sync(FULL, v >> 16);
-    return ((long long)hi << 16) + (long long)lo;
+// ---- window sums in OpenCV's accumulation order (lkpyramid.cpp, CV_SIMD128 path) -----------
+// Terms are laid out in shared memory by CHAIN: a chain is one f32 accumulator of the OpenCV
+// loop, its terms in the order that loop adds them.
+//   A (per level): chain q*4+L, q in {A11, A12, A22}, SIMD lane L: 84 terms, term (y, m) = pixel
+//   (y, L + 4m); then the three scalar tails of 105 terms, term (y, t) = pixel (y, 16 + t).
+//   b (per iteration): chain p*2+xy, p = pixel pair (p, p+4) of a SIMD step, xy in {b1, b2}: 42
+//   terms, term (y, blk) = f32(int32 pair sum) of step blk; then the two tails of 105 terms.
+constexpr int A_LANE_TERMS = 4 * WIN;                      // 84
+constexpr int TAIL_TERMS = 5 * WIN;                        // 105
+constexpr int TAIL_PITCH = 108;                            // float4-aligned
+constexpr int A_TAIL_OFF = 12 * A_LANE_TERMS;              // 1008
+constexpr int A_FLOATS = A_TAIL_OFF + 3 * TAIL_PITCH;      // 1332
+constexpr int B_CHAIN_TERMS = 2 * WIN;                     // 42
+constexpr int B_CHAIN_PITCH = 44;
+constexpr int B_TAIL_OFF = 8 * B_CHAIN_PITCH;              // 352
+static_assert(B_TAIL_OFF + 2 * TAIL_PITCH <= A_FLOATS, "b terms fit in the A term buffer");
+
+// acc = fl(acc + term) over the first n terms at src (16-byte aligned), in order; lanes with
+// n == 0 idle. Warp-uniform trip count, no lane reads past its own chain's pitch.
+__device__ __forceinline__ float chain_sum(const float* src, int n) {
+    float acc = 0.f;
+#pragma unroll 1
+    for (int i = 0; i < (TAIL_TERMS + 3) / 4 * 4; i += 4) {
+        if (i < n) {
+            const float4 v = *reinterpret_cast<const float4*>(src + i);
+            acc = __fadd_rn(acc, v.x);
+            if (i + 1 < n) acc = __fadd_rn(acc, v.y);
+            if (i + 2 < n) acc = __fadd_rn(acc, v.z);
+            if (i + 3 < n) acc = __fadd_rn(acc, v.w);
+        }
+    }
+    return acc;
 }
 
 // c + w.lo16 * p.byte0 + w.hi16 * p.byte1 (lo) / ... byte2, byte3 (hi): signed 16-bit weights
@@ -70,7 +107,11 @@ __device__ __forceinline__ int tap2(int w, unsigned a0, unsigned a1, int c) {
     if (K % 4 == 0) return dp2a_lo(w, K < 4 ? a0 : a1, c);
     if (K % 4 == 2) return dp2a_hi(w, K < 4 ? a0 : a1, c);
     if (K == 3) return dp2a_lo(w, __funnelshift_r(a0, a1, 24), c);
-    return dp2a_lo(w, (K < 4 ? a0 : a1) >> 8, c);          // K % 4 == 1; K == 7 never used
+    return dp2a_lo(w, (K < 4 ? a0 : a1) >> 8, c);          // K % 4 == 1 (K == 7: see tap2_7)
+}
+// bytes [7, 8] of the run: the top byte of a1 and the low byte of the next word
+__device__ __forceinline__ int tap2_7(int w, unsigned a1, unsigned a2, int c) {
+    return dp2a_lo(w, __funnelshift_r(a1, a2, 24), c);
 }
 
 __device__ __forceinline__ int clamp_reflect(int i, int n) {
@@ -148,7 +189,7 @@ __device__ __forceinline__ int stage_region(const uint8_t* __restrict__ img, int
     return off;
 }
 
-__global__ void __launch_bounds__(NT)
+__global__ void __launch_bounds__(NT, 12)
 lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrLayout lay,
                 size_t seq_stride,
                 const float2* __restrict__ in_pts, size_t in_stride, int in_buffered,
@@ -163,8 +204,12 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     // leaves the +-JM margin of its level's region
     __shared__ __align__(16) unsigned s_Iall[LK_LEVELS][IP * (SP / 4)];
     __shared__ __align__(16) unsigned s_Jall[LK_LEVELS][JR * (SP / 4)];
-    __shared__ __align__(16) int s_B[BG * BP];       // border path: s_dx / s_dy alias this
-    __shared__ long long s_red[2][2][3];
+    // B grid of the interior path (border path: s_dx / s_dy) and, once every thread has taken
+    // its window values from it, the chain-ordered terms of the window sums
+    __shared__ __align__(16) float s_T[A_FLOATS];
+    __shared__ float s_sum[3];
+    int* s_B = reinterpret_cast<int*>(s_T);
+    static_assert(sizeof(int) * BG * BP <= sizeof(float) * A_FLOATS, "B grid fits in the term buffer");
 
     const SvoSeqCall* cp = call + blockIdx.y;
     const int seq = cp->seq;
@@ -192,10 +237,13 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     const uint8_t* __restrict__ pyrI = seq_base + (size_t)slot_i * lay.slot_bytes;
     const uint8_t* __restrict__ pyrJ = seq_base + (size_t)(1 - slot_i) * lay.slot_bytes;
 
-    // window pixels owned by this thread: row wy, columns wx0 .. wx0 + 6 (thread 63 idles)
+    // window pixels owned by this thread: row wy, columns wx0 .. wx0 + 7 (part 2: wx0 + 4;
+    // thread 63 idles)
     const bool has_px = tid < WIN * 3;
     const int wy = min(tid / 3, WIN - 1);
-    const int wx0 = (tid - (tid / 3) * 3) * RUN;
+    const int part = tid - (tid / 3) * 3;
+    const int wx0 = part * RUN;
+    const int lane = tid & 31;
     short* s_dx = reinterpret_cast<short*>(s_B);
     short* s_dy = s_dx + DG * DG;
     static_assert(2 * DG * DG * sizeof(short) <= sizeof(int) * BG * BP, "alias too small");
@@ -235,7 +283,6 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     __syncthreads();
     float2 nextPt = make_float2(0.f, 0.f);   // the value OpenCV keeps in nextPts[ptidx]
     bool ok = true;
-    int red_par = 0;
 
     for (int l = lay.n_levels - 1; l >= 0; --l) {
         const SvoLevel lv = lay.lvl[l];
@@ -338,7 +385,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
             __syncthreads();
 #pragma unroll
             for (int t = 0; t < RUN; ++t) {
-                const int wx = wx0 + t;
+                const int wx = min(wx0 + t, WIN - 1);      // columns >= WIN: computed, never used
                 const unsigned char* q = s_Ib + (wy + 1) * SP + offI + wx + 1;
                 ival[t] = (q[0] * w00 + q[1] * w01 + q[SP] * w10 + q[SP + 1] * w11 + 256) >> 9;
                 const short* dx = s_dx + wy * DG + wx;
@@ -347,29 +394,45 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 iyv[t] = (dy[0] * w00 + dy[1] * w01 + dy[DG] * w10 + dy[DG + 1] * w11 + 8192) >> 14;
             }
         }
-        int sa11 = 0, sa12 = 0, sa22 = 0;
+        // ---- A11, A12, A22: per-pixel f32 products in chain order, then sequential chains
+        __syncthreads();                     // every thread has its values out of s_B / s_dx
+        if (has_px) {
+            if (part < 2) {
 #pragma unroll
-        for (int t = 0; t < RUN; ++t) {
-            if (!has_px) ixv[t] = iyv[t] = 0;
-            sa11 += ixv[t] * ixv[t];
-            sa12 += ixv[t] * iyv[t];
-            sa22 += iyv[t] * iyv[t];
-        }
-        long long iA11 = warp_sum_exact(sa11), iA12 = warp_sum_exact(sa12),
-                  iA22 = warp_sum_exact(sa22);
-        if ((tid & 31) == 0) {
-            s_red[red_par][wrp][0] = iA11;
-            s_red[red_par][wrp][1] = iA12;
-            s_red[red_par][wrp][2] = iA22;
+                for (int t = 0; t < RUN; ++t) {
+                    const int L = t & 3, m = 2 * part + (t >> 2);
+                    float* o = s_T + L * A_LANE_TERMS + wy * 4 + m;
+                    o[0 * 4 * A_LANE_TERMS] = __int2float_rn(ixv[t] * ixv[t]);
+                    o[1 * 4 * A_LANE_TERMS] = __int2float_rn(ixv[t] * iyv[t]);
+                    o[2 * 4 * A_LANE_TERMS] = __int2float_rn(iyv[t] * iyv[t]);
+                }
+            } else {
+#pragma unroll
+                for (int t = 0; t < WIN - 2 * RUN; ++t) {
+                    float* o = s_T + A_TAIL_OFF + wy * 5 + t;
+                    o[0 * TAIL_PITCH] = __int2float_rn(ixv[t] * ixv[t]);
+                    o[1 * TAIL_PITCH] = __int2float_rn(ixv[t] * iyv[t]);
+                    o[2 * TAIL_PITCH] = __int2float_rn(iyv[t] * iyv[t]);
+                }
+            }
         }
         __syncthreads();
-        iA11 = s_red[red_par][0][0] + s_red[red_par][1][0];
-        iA12 = s_red[red_par][0][1] + s_red[red_par][1][1];
-        iA22 = s_red[red_par][0][2] + s_red[red_par][1][2];
-        red_par ^= 1;
-        const float A11 = __fmul_rn(__ll2float_rn(iA11), FLT_SCALE);
-        const float A12 = __fmul_rn(__ll2float_rn(iA12), FLT_SCALE);
-        const float A22 = __fmul_rn(__ll2float_rn(iA22), FLT_SCALE);
+        if (wrp == 0) {
+            const float* src = lane < 12 ? s_T + lane * A_LANE_TERMS
+                                         : s_T + A_TAIL_OFF + (min(lane, 14) - 12) * TAIL_PITCH;
+            const int n = lane < 12 ? A_LANE_TERMS : (lane < 15 ? TAIL_TERMS : 0);
+            const float acc = chain_sum(src, n);
+            // v_reduce_sum: (l0 + l2) + (l1 + l3), then the scalar tail takes it in
+            const float u = __fadd_rn(acc, __shfl_down_sync(FULL, acc, 2));
+            const float red = __fadd_rn(u, __shfl_down_sync(FULL, u, 1));
+            const float tail = __shfl_sync(FULL, acc, 12 + (lane >> 2));
+            if (lane < 12 && (lane & 3) == 0) s_sum[lane >> 2] = __fadd_rn(tail, red);
+        }
+        __syncthreads();
+        const float iA11 = s_sum[0], iA12 = s_sum[1], iA22 = s_sum[2];
+        const float A11 = __fmul_rn(iA11, FLT_SCALE);
+        const float A12 = __fmul_rn(iA12, FLT_SCALE);
+        const float A22 = __fmul_rn(iA22, FLT_SCALE);
         float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
         const float dif = __fsub_rn(A11, A22);
         const float rad = __fadd_rn(__fmul_rn(dif, dif), __fmul_rn(__fmul_rn(4.f, A12), A12));
@@ -402,18 +465,19 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 __syncthreads();
                 ox = oy = JM;
             }
-            int sb1 = 0, sb2 = 0;
             {
-                // the thread's 8 bytes of two J rows as aligned words + funnel shifts; a pixel's
-                // four taps are two dp2a (exact integers): 6 word loads instead of 16 byte loads
+                // the thread's 9 bytes of two J rows as aligned words + funnel shifts; a pixel's
+                // four taps are two dp2a (exact integers): 6 word loads instead of 18 byte loads
                 const int bo = (wy + oy) * SP + offJ + wx0 + ox;
                 const unsigned* q0 = s_Jw + (bo >> 2);
                 const unsigned* q1 = q0 + SP / 4;
                 const unsigned sh = (bo & 3) * 8;
                 const unsigned u0 = q0[0], u1 = q0[1], u2 = q0[2];
                 const unsigned v0 = q1[0], v1 = q1[1], v2 = q1[2];
-                const unsigned a0 = __funnelshift_r(u0, u1, sh), a1 = __funnelshift_r(u1, u2, sh);
-                const unsigned b0 = __funnelshift_r(v0, v1, sh), b1 = __funnelshift_r(v1, v2, sh);
+                const unsigned a0 = __funnelshift_r(u0, u1, sh), a1 = __funnelshift_r(u1, u2, sh),
+                               a2 = u2 >> sh;
+                const unsigned b0 = __funnelshift_r(v0, v1, sh), b1 = __funnelshift_r(v1, v2, sh),
+                               b2 = v2 >> sh;
                 const int wt = pack16(w00, w01), wb = pack16(w10, w11);
                 int jv[RUN];
                 jv[0] = tap2<0>(wb, b0, b1, tap2<0>(wt, a0, a1, 256));
@@ -423,24 +487,46 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 jv[4] = tap2<4>(wb, b0, b1, tap2<4>(wt, a0, a1, 256));
                 jv[5] = tap2<5>(wb, b0, b1, tap2<5>(wt, a0, a1, 256));
                 jv[6] = tap2<6>(wb, b0, b1, tap2<6>(wt, a0, a1, 256));
+                jv[7] = tap2_7(wb, b1, b2, tap2_7(wt, a1, a2, 256));
+                int dI[RUN];
 #pragma unroll
-                for (int t = 0; t < RUN; ++t) {
-                    const int diff = (jv[t] >> 9) - ival[t];
-                    sb1 += diff * ixv[t];
-                    sb2 += diff * iyv[t];
+                for (int t = 0; t < RUN; ++t) dI[t] = (jv[t] >> 9) - ival[t];
+                if (has_px) {
+                    if (part < 2) {
+                        // v_dotprod lanes: int32 sum of the pixel pair (p, p + 4), then f32
+#pragma unroll
+                        for (int pp = 0; pp < 4; ++pp) {
+                            float* o = s_T + (2 * pp) * B_CHAIN_PITCH + wy * 2 + part;
+                            o[0] = __int2float_rn(dI[pp] * ixv[pp] + dI[pp + 4] * ixv[pp + 4]);
+                            o[B_CHAIN_PITCH] = __int2float_rn(dI[pp] * iyv[pp] + dI[pp + 4] * iyv[pp + 4]);
+                        }
+                    } else {
+#pragma unroll
+                        for (int t = 0; t < WIN - 2 * RUN; ++t) {
+                            float* o = s_T + B_TAIL_OFF + wy * 5 + t;
+                            o[0] = __int2float_rn(dI[t] * ixv[t]);
+                            o[TAIL_PITCH] = __int2float_rn(dI[t] * iyv[t]);
+                        }
+                    }
                 }
             }
-            long long ib1 = warp_sum_exact(sb1), ib2 = warp_sum_exact(sb2);
-            if ((tid & 31) == 0) {
-                s_red[red_par][wrp][0] = ib1;
-                s_red[red_par][wrp][1] = ib2;
+            __syncthreads();
+            if (wrp == 0) {
+                const float* src = lane < 8 ? s_T + lane * B_CHAIN_PITCH
+                                            : s_T + B_TAIL_OFF + (min(lane, 9) - 8) * TAIL_PITCH;
+                const int n = lane < 8 ? B_CHAIN_TERMS : (lane < 10 ? TAIL_TERMS : 0);
+                const float acc = chain_sum(src, n);
+                // qb0 + qb1 (chains p and p + 2), then lanes (0, 2) -> b1, (1, 3) -> b2, then the
+                // scalar tails take the SIMD sums in
+                const float q = __fadd_rn(acc, __shfl_down_sync(FULL, acc, 4));
+                const float r = __fadd_rn(q, __shfl_down_sync(FULL, q, 2));
+                const float tail = __shfl_sync(FULL, acc, 8 + (lane & 1));
+                if (lane < 2) s_sum[lane] = __fadd_rn(tail, r);
             }
             __syncthreads();
-            ib1 = s_red[red_par][0][0] + s_red[red_par][1][0];
-            ib2 = s_red[red_par][0][1] + s_red[red_par][1][1];
-            red_par ^= 1;
-            const float b1 = __fmul_rn(__ll2float_rn(ib1), FLT_SCALE);
-            const float b2 = __fmul_rn(__ll2float_rn(ib2), FLT_SCALE);
+            const float ib1 = s_sum[0], ib2 = s_sum[1];
+            const float b1 = __fmul_rn(ib1, FLT_SCALE);
+            const float b2 = __fmul_rn(ib2, FLT_SCALE);
             float2 delta;
             delta.x = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
             delta.y = __fmul_rn(__fsub_rn(__fmul_rn(A12, b1), __fmul_rn(A11, b2)), D);

@@ -21,7 +21,8 @@ from stereo_vo_b200 import synth, workload
 pytestmark = pytest.mark.gpu
 
 S, F, STEPS, GROUPS = 64, 48, 56, 4
-FLOW_TOL = 0.01          # px (north_star); measured <= 1e-3
+FLOW_TOL = 0.0           # px: north_star allows 0.01; flow is bit-exact (window sums in cv2's f32 order)
+PAR_TOL = 1e-4
 REL_3D = 1e-4
 
 
@@ -89,7 +90,7 @@ def _check(k, s, a, g, worst):
             worst["flow"] = max(worst["flow"], d)
             assert d <= FLOW_TOL, f"{where}: flow differs by {d} px"
         dp = abs(float(a["av_parallax"]) - float(g["stats"]["av_parallax"]))
-        assert dp <= FLOW_TOL or (np.isnan(a["av_parallax"]) and np.isnan(g["stats"]["av_parallax"]))
+        assert dp <= PAR_TOL or (np.isnan(a["av_parallax"]) and np.isnan(g["stats"]["av_parallax"]))
     if a["decision"] in ("first", "keyframe"):
         assert np.array_equal(a["new_features"], g["new_features"]), f"{where}: dedupe"
         assert np.array_equal(a["valid_idx"], g["valid_idx"]), f"{where}: match indices"

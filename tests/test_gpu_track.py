@@ -1,5 +1,5 @@
 """GPU parity: pyramidal LK forward/backward + filter/statistics (FeatureTracker) against the
-cv2 oracle. Status, kept indices and ids bit-exact; sub-pixel flow within 0.01 px
+cv2 oracle. Status, kept indices and ids bit-exact; sub-pixel flow bit-exact (north_star allows 0.01 px)
 (BASELINE.json north_star tolerance)."""
 import numpy as np
 import pytest
@@ -8,7 +8,8 @@ from stereo_vo_b200 import synth
 from tests import util
 
 pytestmark = pytest.mark.gpu
-FLOW_TOL = 0.01
+FLOW_TOL = 0.0           # px: flow is bit-exact (window sums in cv2's own f32 order)
+PAR_TOL = 1e-4           # av_parallax: an f32 mean of f32 norms
 
 
 @pytest.fixture(scope="module")
@@ -46,7 +47,7 @@ def _track_once(e, oracle, prev, nxt, pts, ids):
     assert list(fids) == list(ref_ids), "kept track ids"
     assert np.abs(feats - ref_feats).max() <= FLOW_TOL
     assert np.array_equal(dbg["kept_idx"][:len(ref_ids)], taps["kept_idx"])
-    assert abs(float(av) - float(av_ref)) <= FLOW_TOL
+    assert abs(float(av) - float(av_ref)) <= PAR_TOL
     assert lost == lost_ref
     return trk
 
@@ -110,6 +111,6 @@ def test_track_multi_frame_chain(eng, oracle):
         feats, fids = e.tracker_get()
         assert list(fids) == list(trk.feature_ids), f"frame {t}"
         assert np.abs(feats - trk.feature_set).max() <= FLOW_TOL
-        assert abs(float(av) - float(av_ref)) <= FLOW_TOL
+        assert abs(float(av) - float(av_ref)) <= PAR_TOL
         assert lost == lost_ref
 

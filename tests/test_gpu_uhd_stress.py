@@ -9,7 +9,8 @@ import pytest
 from stereo_vo_b200 import synth
 
 pytestmark = pytest.mark.gpu
-FLOW_TOL = 0.01
+FLOW_TOL = 0.0           # px: flow is bit-exact (window sums in cv2's own f32 order)
+PAR_TOL = 1e-4           # av_parallax: an f32 mean of f32 norms
 MAXC, QUALITY, MIN_DIST = 20000, 0.01, 20.0
 
 
@@ -81,4 +82,4 @@ def test_uhd_track_thousands_of_points(uhd, oracle):
     ref_feats, ref_ids = trk.get_tracked_features()
     assert list(fids) == list(ref_ids)
     assert np.abs(feats - ref_feats).max() <= FLOW_TOL
-    assert abs(float(av) - float(av_ref)) <= FLOW_TOL and lost == lost_ref
+    assert abs(float(av) - float(av_ref)) <= PAR_TOL and lost == lost_ref

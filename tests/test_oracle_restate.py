@@ -12,7 +12,7 @@ from tests import util
 @pytest.fixture(scope="module")
 def pair(oracle):
     cam = util.small_camera(420, 200)
-    return synth.sequence(7, 2, cam), cam
+    return synth.sequence(7, 3, cam), cam
 
 
 @pytest.mark.parametrize("w,h,seed", [(420, 200, 0), (333, 211, 1), (1241, 376, 2)])
@@ -61,10 +61,20 @@ def test_lk_matches_cv2(oracle, pair):
     pts = oracle.detect(prev, 120, 0.05, 10.0)
     edge = np.array([[0, 0], [cam.width - 1, cam.height - 1], [2.5, 100.25]], np.float32)
     pts = np.concatenate([pts, edge])
-    got, st = R.lk_track(prev, nxt, pts)
     ref, rst = oracle.lk(prev, nxt, pts)
-    assert np.array_equal(st, rst)
-    assert np.abs(got - ref)[rst > 0].max() < 1e-3        # exact integer sums vs cv2's f32 lanes
+    # sub-pixel start points (the tracker's normal input): continue from the tracked positions
+    nxt2 = frames[2][0]
+    start = ref[rst > 0]
+    ref2, rst2 = oracle.lk(nxt, nxt2, start)
+    for a, b, p, want, wst in ((prev, nxt, pts, ref, rst), (nxt, nxt2, start, ref2, rst2)):
+        got, st = R.lk_track(a, b, p)
+        assert np.array_equal(st, wst)
+        ok = wst > 0
+        # window sums accumulated in cv2's own f32 order: bit-identical flow
+        assert np.array_equal(got[ok].view(np.uint32), want[ok].view(np.uint32))
+    # exact integer sums (the round-1 kernel): close, not identical
+    got, st = R.lk_track(prev, nxt, pts, exact_sums=True)
+    assert np.array_equal(st, rst) and np.abs(got - ref)[rst > 0].max() < 1e-3
 
 
 def test_reproject_matches_gemm(oracle):

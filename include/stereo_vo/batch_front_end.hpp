@@ -12,9 +12,14 @@
 // step overlap the kernels of the current one (svo_prefetch). Sequences never interact: there
 // is no collective, on one GPU or across GPUs.
 //
-// PnP-RANSAC is a host consumer outside the accelerated path: in this driver
-// a keyframe keeps every tracked feature as inlier and takes the camera->world pose the caller
-// supplies for that frame (teacher forcing; the facade ImageProcessor is the closed-loop form).
+// Two ways to get a keyframe's pose (src/image_processor.cpp:75-92):
+//   * teacher-forced (default): a keyframe keeps every tracked feature as inlier and takes the
+//     camera->world pose the caller supplies for that frame;
+//   * closed loop (set_closed_loop): the pose step runs on the GPU (svo_pnp_ransac, batched over
+//     the group's keyframes) on the tracked features and the world points this driver stored
+//     when it handed out their ids (BundleAdjuster::get_world_points without Ceres: un-refined
+//     points, src/bundle_adjuster.cpp:159-163); inliers, hmat = [R^T | -R^T t], dedupe, stereo
+//     and tracker re-init then follow the reference line by line (:95-162).
 #pragma once
 #include <condition_variable>
 #include <cstdint>
@@ -103,6 +108,16 @@ class BatchFrontEnd {
     const int16_t* disp16(int s) const;
     const int32_t* valid_idx(int s) const;
 
+    // Closed-loop pose step: call before the first step. Arguments of cv::solvePnPRansac at
+    // src/image_processor.cpp:80.
+    void set_closed_loop(bool on, int iterations = 100, float reproj_error = 8.f,
+                         double confidence = 0.99);
+    bool closed_loop() const { return closed_loop_; }
+    // pose of the sequence's last keyframe (row-major camera->world, src/image_processor.cpp:
+    // 130-134) and the inlier count of its pose step (closed loop only)
+    const float* pose(int s) const { return seq_[s].hmat; }
+    int32_t n_inliers(int s) const { return res(s).n_inliers; }
+
     int64_t kernel_launches() const;
     // device-side stopwatch over all groups: begin() synchronises every engine stream and
     // starts a CUDA-event timer on each; end() returns the longest elapsed time (ms)
@@ -116,7 +131,7 @@ class BatchFrontEnd {
   private:
     struct SeqResult {                     // per pipeline slot
         int32_t decision = 0, n_corners = 0, n_tracker = 0, n_new = 0;
-        int32_t n_new_features = 0, n_valid = 0;
+        int32_t n_new_features = 0, n_valid = 0, n_inliers = 0;
         svo_track_stats stats{};
     };
     struct SeqState {
@@ -125,6 +140,11 @@ class BatchFrontEnd {
         uint64_t next_id = 0;
         int32_t n_tracker = 0;             // tracker set size carried from step to step
         float par_last = 0.f, par_rate = 8.f;   // keyframe predictor: last av_parallax, growth/step
+        // closed loop: world point of every id handed out (ids are a running counter from 0),
+        // the extrinsic guess carried from keyframe to keyframe (rvec, tvec), last keyframe pose
+        std::vector<svo_float3> world;
+        double rt[6] = {0, 0, 0, 0, 0, 0};
+        float hmat[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
         SeqResult res[kPipeDepth];
     };
     struct Group {
@@ -146,6 +166,12 @@ class BatchFrontEnd {
         std::vector<int32_t> valid_idx;
         std::vector<int16_t> disp16;
         std::vector<float> poses;
+        // closed loop: pose-step inputs / outputs of the group's keyframes
+        std::vector<svo_float3> pnp_world;
+        std::vector<svo_float2> pnp_image;
+        std::vector<int32_t> pnp_counts, pnp_inl, pnp_kf;
+        std::vector<double> pnp_guess;
+        std::vector<svo_pnp_result> pnp_res;
         double phase_ms[12] = {0};         // SVO_BATCH_TRACE=1: accumulated per-phase times
         int64_t phase_calls = 0;
     };
@@ -160,6 +186,7 @@ class BatchFrontEnd {
         int pending = 0;                   // groups still working on it
     };
     void run_group(Group& g, Job& job, int slot, int gi);
+    void run_keyframes_closed_loop(Group& g, int slot, int nk, BatchSummary& sum);
     void worker_loop(Group* g, int gi);
     const SeqResult& res(int s) const { return seq_[s].res[cur_slot_]; }
 
@@ -167,6 +194,10 @@ class BatchFrontEnd {
     bool trace_ = false;           // SVO_BATCH_TRACE=1: per-phase host/device times on stderr
     bool zero_copy_right_ = true;  // keyframe right images read in place from mapped pinned memory
     bool lazy_right_ = true;       // upload right images for keyframes only (SVO_BATCH_LAZY_RIGHT=0: always)
+    bool closed_loop_ = false;
+    int pnp_iterations_ = 100;
+    float pnp_reproj_ = 8.f;
+    double pnp_confidence_ = 0.99;
     std::vector<std::unique_ptr<Group>> groups_;
     std::vector<SeqState> seq_;
     // per-sequence result storage (global index), one set per pipeline slot

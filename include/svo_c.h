@@ -278,6 +278,32 @@ SVO_API int svo_step_keyframe(svo_engine* e, int32_t n, const int32_t* seqs, con
                       svo_float2* new_feats, int32_t* n_new, svo_float2* valid_2d,
                       svo_float3* pts_3d, int32_t* valid_idx, int16_t* disp16, int32_t* n_valid);
 
+/* ---- pose step ----------------------------------------------------- */
+typedef struct svo_pnp_result {
+    double rvec[3], tvec[3];        /* x_cam = R x_world + t, rvec = Rodrigues vector of R */
+    double rmat[9];                 /* cv::Rodrigues(rvec), row major */
+    int32_t n_inliers;
+    int32_t ok;                     /* 0: fewer than 5 points, or no hypothesis with >= 5 inliers
+                                       (cv::solvePnPRansac returns false): rvec/tvec = the guess */
+    int32_t best_hypothesis;        /* index of the winning hypothesis, -1 if none */
+    int32_t hypotheses_tried;       /* where OpenCV's confidence bound stopped the loop */
+} svo_pnp_result;
+
+/* cv::solvePnPRansac(world, image, K, no distortion, rvec, tvec, useExtrinsicGuess = true,
+ * iterations, reproj_error, confidence, inliers) + cv::Rodrigues at src/image_processor.cpp:75-92,
+ * for n independent point sets in one launch (one per sequence that became a keyframe).
+ *   world [n][max_features] xyz, image [n][max_features] xy (pixels), counts[i] valid entries
+ *   guess [n][6]: rvec, tvec going in (the reference keeps them from the previous keyframe)
+ *   results [n]; inliers [n][max_features]: indices into the point set, ascending
+ * iterations <= 128. Semantics kept from OpenCV: 5-point model, strictly-more-inliers rule,
+ * confidence-bounded loop, inliers taken under the winning hypothesis, final pose = least
+ * squares over the inliers. Samples and the minimal solver differ (csrc/pnp_ransac.cu), so the
+ * pose agrees with cv2 to the tolerance stated in BASELINE.md rather than bit for bit. */
+SVO_API int svo_pnp_ransac(svo_engine* e, int32_t n, const svo_float3* world,
+                           const svo_float2* image, const int32_t* counts, float focal, float cx,
+                           float cy, int32_t iterations, float reproj_error, double confidence,
+                           const double* guess, svo_pnp_result* results, int32_t* inliers);
+
 /* FeatureTracker::init against the CURRENT frame of each listed sequence
  * (image_processor.cpp:51-52,148-162): feats/ids [n][max_features], counts[i] entries. */
 SVO_API int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,

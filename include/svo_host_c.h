@@ -105,6 +105,14 @@ SVO_API int svo_batch_get(svo_batch* b, int32_t seq, int32_t* decision, int32_t*
 SVO_API int svo_batch_get_keyframe(svo_batch* b, int32_t seq, int32_t* n_new_features,
                                    svo_float2* new_features, int16_t* disp16, int32_t* n_valid,
                                    int32_t* valid_idx);
+/* Closed loop: the pose step of src/image_processor.cpp:75-92 runs on the GPU (svo_pnp_ransac)
+ * instead of taking caller poses; call before the first step. iterations / reproj_error /
+ * confidence: the arguments of cv::solvePnPRansac (reference: 100, 8, 0.99). */
+SVO_API int svo_batch_set_closed_loop(svo_batch* b, int32_t on, int32_t iterations,
+                                      float reproj_error, double confidence);
+/* pose of sequence seq's last keyframe (row-major camera->world hmat, :130-134) and the inlier
+ * count of the pose step of the last step (0 unless it was a closed-loop keyframe) */
+SVO_API int svo_batch_get_pose(svo_batch* b, int32_t seq, float hmat[16], int32_t* n_inliers);
 SVO_API int64_t svo_batch_kernel_launches(const svo_batch* b);
 SVO_API int svo_batch_timer_begin(svo_batch* b);
 SVO_API int svo_batch_timer_end(svo_batch* b, float* ms);

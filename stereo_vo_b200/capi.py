@@ -37,6 +37,10 @@ class SvoTrackStats(C.Structure):
                 ("n_kept", C.c_int32), ("n_attempted", C.c_int32)]
 
 
+PNP_DTYPE = np.dtype([("rvec", np.float64, 3), ("tvec", np.float64, 3), ("rmat", np.float64, 9),
+                      ("n_inliers", np.int32), ("ok", np.int32), ("best_hypothesis", np.int32),
+                      ("hypotheses_tried", np.int32)])
+
 STATS_DTYPE = np.dtype([("av_parallax", np.float32), ("percent_lost", np.float32),
                         ("n_kept", np.int32), ("n_attempted", np.int32)])
 
@@ -51,7 +55,7 @@ EXPORTS = [
     "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_keyframe_tracked", "svo_step_keyframe", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
-    "svo_timer_begin", "svo_timer_end",
+    "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac",
 ]
 
 _lib = None
@@ -111,6 +115,7 @@ def load_library(path: Optional[str] = None):
     lib.svo_step_keyframe.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, f32,
                                       vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]
+    lib.svo_pnp_ransac.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, i32, f32, C.c_double, vp, vp, vp]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
     lib.svo_device_free.argtypes = [vp, vp]
     lib.svo_device_upload.argtypes = [vp, vp, vp, C.c_size_t]
@@ -510,6 +515,29 @@ class Engine:
                     "svo_tracker_set")
 
     # -- device-resident frames (bench kernel-only leg) --------------------------------------
+    def pnp_ransac(self, world, image, focal, cx, cy, guess=None, iterations=100,
+                   reproj_error=8.0, confidence=0.99):
+        """svo_pnp_ransac on a list of point sets: world[i] (n_i, 3), image[i] (n_i, 2);
+        guess (n, 6) rvec|tvec or None for zeros. Returns (results PNP_DTYPE[n], [inlier idx])."""
+        n, mf = len(world), self.max_features
+        w = np.zeros((n, mf, 3), np.float32)
+        im = np.zeros((n, mf, 2), np.float32)
+        counts = np.zeros(n, np.int32)
+        for i in range(n):
+            k = len(world[i])
+            counts[i] = k
+            w[i, :k] = np.asarray(world[i], np.float32).reshape(-1, 3)
+            im[i, :k] = np.asarray(image[i], np.float32).reshape(-1, 2)
+        g = np.zeros((n, 6), np.float64) if guess is None else \
+            np.ascontiguousarray(guess, np.float64).reshape(n, 6)
+        res = np.zeros(n, PNP_DTYPE)
+        inl = np.zeros((n, mf), np.int32)
+        self._check(self.lib.svo_pnp_ransac(self.h, n, _ptr(w), _ptr(im), _ptr(counts), float(focal),
+                                            float(cx), float(cy), int(iterations),
+                                            float(reproj_error), float(confidence), _ptr(g),
+                                            _ptr(res), _ptr(inl)), "svo_pnp_ransac")
+        return res, [inl[i, :res[i]["n_inliers"]].copy() for i in range(n)]
+
     def device_alloc(self, nbytes: int) -> int:
         p = C.c_void_p()
         self._check(self.lib.svo_device_alloc(self.h, nbytes, C.byref(p)), "svo_device_alloc")

@@ -15,13 +15,14 @@
 #include "../../include/svo_c.h"
 #include "svo_common.cuh"
 
-#define SVO_PROF_SLOTS 13
+#define SVO_PROF_SLOTS 14
 static const char* const kProfNames[SVO_PROF_SLOTS] = {
     "pyr_down_u8", "corner_score_nms", "ingest", "sort_candidates",
     "greedy_min_distance", "lk_track_fwd", "lk_track_bwd", "track_filter_compact",
-    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q", "stereo_bm_dense"};
+    "pack_results", "dedupe_new_features", "stereo_bm_sparse", "reproject_q", "stereo_bm_dense",
+    "pnp_ransac"};
 enum { P_PYR, P_SCORE, P_INGEST, P_SORT, P_GREEDY, P_LKF, P_LKB, P_FILTER, P_PACK, P_DEDUPE,
-       P_STEREO, P_REPROJ, P_DENSE };
+       P_STEREO, P_REPROJ, P_DENSE, P_PNP };
 
 namespace {
 
@@ -137,6 +138,14 @@ struct svo_engine {
     float* d_pts3d = nullptr;
     int* d_valid_idx = nullptr;
     int* d_nvalid = nullptr;
+    // svo_pnp_ransac (allocated on first use): point sets, guesses, results
+    float* d_pnp_world = nullptr;
+    float2* d_pnp_img = nullptr;
+    int* d_pnp_counts = nullptr;
+    double* d_pnp_guess = nullptr;
+    SvoPnpResult* d_pnp_res = nullptr;
+    int* d_pnp_inl = nullptr;
+    unsigned pnp_calls = 0;
     unsigned char* d_out = nullptr;   // packed result blocks
     size_t step_block = 0, key_block = 0, out_bytes = 0;
     int pts_cap = 0;                  // per-sequence capacity of d_pts / stereo outputs
@@ -1144,7 +1153,8 @@ void svo_destroy(svo_engine* e) {
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
-                     e->d_call, e->d_kcall};
+                     e->d_call, e->d_kcall, e->d_pnp_world, e->d_pnp_img, e->d_pnp_counts,
+                     e->d_pnp_guess, e->d_pnp_res, e->d_pnp_inl};
     for (void* p : dptrs) if (p) cudaFree(p);
     if (e->h_call) cudaFreeHost(e->h_call);
     if (e->h_pull) cudaFreeHost(e->h_pull);
@@ -1548,6 +1558,56 @@ int svo_stereo_bm_dense_resident(svo_engine* e, int32_t n, const int32_t* seqs,
     if (n <= 0 || n > e->n_seq || !seqs) return fail(e, SVO_ERR_INVALID, "svo_stereo_bm_dense_resident: bad arguments");
     ECUDA(e, cudaSetDevice(e->device));
     return dense_impl(e, n, seqs, out_disp16, out_pitch);
+}
+
+int svo_pnp_ransac(svo_engine* e, int32_t n, const svo_float3* world, const svo_float2* image,
+                   const int32_t* counts, float focal, float cx, float cy, int32_t iterations,
+                   float reproj_error, double confidence, const double* guess,
+                   svo_pnp_result* results, int32_t* inliers) {
+    static_assert(sizeof(svo_pnp_result) == sizeof(SvoPnpResult), "result layouts must match");
+    if (!e) return SVO_ERR_INVALID;
+    if (n <= 0 || n > e->n_seq || !world || !image || !counts || !guess || !results || !inliers)
+        return fail(e, SVO_ERR_INVALID, "svo_pnp_ransac: bad arguments");
+    if (iterations <= 0 || iterations > 128 || !(reproj_error > 0.f) || !(confidence > 0.0))
+        return fail(e, SVO_ERR_INVALID, "svo_pnp_ransac: iterations 1..128, positive threshold and confidence");
+    ECUDA(e, cudaSetDevice(e->device));
+    const int mf = e->p.max_features;
+    const size_t ns = (size_t)e->n_seq;
+    if (!e->d_pnp_world) {
+        if (dalloc(&e->d_pnp_world, ns * mf * 3) != cudaSuccess || dalloc(&e->d_pnp_img, ns * mf) != cudaSuccess ||
+            dalloc(&e->d_pnp_counts, ns) != cudaSuccess || dalloc(&e->d_pnp_guess, ns * 6) != cudaSuccess ||
+            dalloc(&e->d_pnp_res, ns) != cudaSuccess || dalloc(&e->d_pnp_inl, ns * mf) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(e, SVO_ERR_NOMEM, "svo_pnp_ransac: no device memory");
+        }
+    }
+    for (int i = 0; i < n; ++i)
+        if (counts[i] < 0 || counts[i] > mf) return fail(e, SVO_ERR_CAPACITY, "svo_pnp_ransac: more points than max_features");
+    ECUDA(e, cudaEventRecord(e->ev[0], e->st));
+    for (int i = 0; i < n; ++i) {
+        if (counts[i] == 0) continue;
+        ECUDA(e, cudaMemcpyAsync(e->d_pnp_world + (size_t)i * mf * 3, world + (size_t)i * mf,
+                                 (size_t)counts[i] * 3 * sizeof(float), cudaMemcpyHostToDevice, e->st));
+        ECUDA(e, cudaMemcpyAsync(e->d_pnp_img + (size_t)i * mf, image + (size_t)i * mf,
+                                 (size_t)counts[i] * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+    }
+    ECUDA(e, cudaMemcpyAsync(e->d_pnp_counts, counts, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, cudaMemcpyAsync(e->d_pnp_guess, guess, (size_t)n * 6 * sizeof(double), cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    {
+        ProfScope ps(e, P_PNP);
+        ECUDA(e, svo_launch_pnp_ransac(e->d_pnp_world, e->d_pnp_img, mf, e->d_pnp_counts,
+                                       e->d_pnp_guess, focal, cx, cy, iterations, reproj_error,
+                                       confidence, e->pnp_calls++, e->d_pnp_res, e->d_pnp_inl, n, e->st));
+        e->launches += 1;
+    }
+    ECUDA(e, cudaEventRecord(e->ev[2], e->st));
+    ECUDA(e, cudaMemcpyAsync(results, e->d_pnp_res, (size_t)n * sizeof(SvoPnpResult), cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaMemcpyAsync(inliers, e->d_pnp_inl, (size_t)n * mf * sizeof(int), cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[3], e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    finish_timing(e);
+    return SVO_OK;
 }
 
 int svo_device_can_read(const void* p) {

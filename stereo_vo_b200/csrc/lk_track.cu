@@ -70,18 +70,32 @@ constexpr int B_CHAIN_PITCH = 44;
 constexpr int B_TAIL_OFF = 8 * B_CHAIN_PITCH;              // 352
 static_assert(B_TAIL_OFF + 2 * TAIL_PITCH <= A_FLOATS, "b terms fit in the A term buffer");
 
-// acc = fl(acc + term) over the first n terms at src (16-byte aligned), in order; lanes with
-// n == 0 idle. Warp-uniform trip count, no lane reads past its own chain's pitch.
-__device__ __forceinline__ float chain_sum(const float* src, int n) {
+// acc = fl(acc + term) over the terms at src (16-byte aligned), in order: N_SHORT terms for a
+// SIMD-lane chain, TAIL_TERMS for a scalar-tail chain (is_long); inactive lanes idle. Straight-
+// line code: the loads run ahead of the dependent additions, which are the critical path
+// (TAIL_TERMS x the FADD latency per window sum).
+template <int N_SHORT>
+__device__ __forceinline__ float chain_sum(const float* __restrict__ src, bool active, bool is_long) {
+    constexpr int N4 = (N_SHORT + 3) / 4 * 4;
     float acc = 0.f;
-#pragma unroll 1
-    for (int i = 0; i < (TAIL_TERMS + 3) / 4 * 4; i += 4) {
-        if (i < n) {
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < N4; i += 4) {
             const float4 v = *reinterpret_cast<const float4*>(src + i);
             acc = __fadd_rn(acc, v.x);
-            if (i + 1 < n) acc = __fadd_rn(acc, v.y);
-            if (i + 2 < n) acc = __fadd_rn(acc, v.z);
-            if (i + 3 < n) acc = __fadd_rn(acc, v.w);
+            if (i + 1 < N_SHORT || is_long) acc = __fadd_rn(acc, v.y);
+            if (i + 2 < N_SHORT || is_long) acc = __fadd_rn(acc, v.z);
+            if (i + 3 < N_SHORT || is_long) acc = __fadd_rn(acc, v.w);
+        }
+    }
+    if (is_long) {
+#pragma unroll
+        for (int i = N4; i < TAIL_TERMS; i += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(src + i);
+            acc = __fadd_rn(acc, v.x);
+            if (i + 1 < TAIL_TERMS) acc = __fadd_rn(acc, v.y);
+            if (i + 2 < TAIL_TERMS) acc = __fadd_rn(acc, v.z);
+            if (i + 3 < TAIL_TERMS) acc = __fadd_rn(acc, v.w);
         }
     }
     return acc;
@@ -189,7 +203,7 @@ __device__ __forceinline__ int stage_region(const uint8_t* __restrict__ img, int
     return off;
 }
 
-__global__ void __launch_bounds__(NT, 12)
+__global__ void __launch_bounds__(NT, 16)
 lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrLayout lay,
                 size_t seq_stride,
                 const float2* __restrict__ in_pts, size_t in_stride, int in_buffered,
@@ -420,8 +434,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         if (wrp == 0) {
             const float* src = lane < 12 ? s_T + lane * A_LANE_TERMS
                                          : s_T + A_TAIL_OFF + (min(lane, 14) - 12) * TAIL_PITCH;
-            const int n = lane < 12 ? A_LANE_TERMS : (lane < 15 ? TAIL_TERMS : 0);
-            const float acc = chain_sum(src, n);
+            const float acc = chain_sum<A_LANE_TERMS>(src, lane < 15, lane >= 12 && lane < 15);
             // v_reduce_sum: (l0 + l2) + (l1 + l3), then the scalar tail takes it in
             const float u = __fadd_rn(acc, __shfl_down_sync(FULL, acc, 2));
             const float red = __fadd_rn(u, __shfl_down_sync(FULL, u, 1));
@@ -514,8 +527,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
             if (wrp == 0) {
                 const float* src = lane < 8 ? s_T + lane * B_CHAIN_PITCH
                                             : s_T + B_TAIL_OFF + (min(lane, 9) - 8) * TAIL_PITCH;
-                const int n = lane < 8 ? B_CHAIN_TERMS : (lane < 10 ? TAIL_TERMS : 0);
-                const float acc = chain_sum(src, n);
+                const float acc = chain_sum<B_CHAIN_TERMS>(src, lane < 10, lane >= 8 && lane < 10);
                 // qb0 + qb1 (chains p and p + 2), then lanes (0, 2) -> b1, (1, 3) -> b2, then the
                 // scalar tails take the SIMD sums in
                 const float q = __fadd_rn(acc, __shfl_down_sync(FULL, acc, 4));
@@ -566,6 +578,11 @@ cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, siz
                                 int gate_min, const unsigned char* skip_status,
                                 const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
     if (max_pts <= 0 || n_call <= 0) return cudaSuccess;
+    // 16 blocks of 64 threads and 13.9 KB per SM: the window-sum chains are latency-bound
+    // (one dependent FADD every 4 cycles), so resident blocks are what fills the issue slots
+    static const cudaError_t carve = cudaFuncSetAttribute(
+        lk_track_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (carve != cudaSuccess) return carve;
     dim3 grid(lp.grid_pts > 0 ? lp.grid_pts : max_pts, n_call);
     lk_track_kernel<<<grid, NT, 0, st>>>(pyr, lay, seq_stride, in_pts, in_stride, in_buffered,
                                          out_pts, status, out_stride, direction, lp.max_iters,

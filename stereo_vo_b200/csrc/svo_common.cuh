@@ -152,6 +152,17 @@ cudaError_t svo_launch_dedupe(const float2* det, const int* n_det, int det_strid
                               int* keep_idx, int* n_out, int out_stride,
                               SvoSeqCall* d_call, unsigned* ticket, int n_call, cudaStream_t st);
 
+// result block of pnp_ransac (layout of svo_pnp_result in include/svo_c.h)
+struct SvoPnpResult {
+    double rvec[3], tvec[3], rmat[9];
+    int n_inliers, ok, best_hypothesis, hypotheses_tried;
+};
+cudaError_t svo_launch_pnp_ransac(const float* world, const float2* image, int stride,
+                                  const int* counts, const double* guess, float focal, float cx,
+                                  float cy, int iterations, float reproj_error, double confidence,
+                                  unsigned salt, SvoPnpResult* results, int* inliers, int n_call,
+                                  cudaStream_t st);
+
 struct SvoLkParams {
     int max_iters;
     double eps2;                 // criteria.epsilon squared (OpenCV squares it in double)

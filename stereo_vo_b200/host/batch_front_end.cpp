@@ -67,6 +67,9 @@ BatchFrontEnd::BatchFrontEnd(const BatchOptions& opt) : opt_(opt) {
         grp->tracked.resize(n * mf); grp->tracked_ids.resize(n * mf); grp->inl.resize(n * mf);
         grp->feats.resize(n * mf); grp->ids.resize(n * mf); grp->first_id.resize(n);
         grp->poses.resize(n * 16);
+        grp->pnp_world.resize(n * mf); grp->pnp_image.resize(n * mf); grp->pnp_inl.resize(n * mf);
+        grp->pnp_counts.resize(n); grp->pnp_kf.resize(n); grp->pnp_guess.resize(n * 6);
+        grp->pnp_res.resize(n);
         for (int i = 0; i < cnt; ++i) grp->local_ids[(size_t)i] = i;
         groups_.push_back(std::move(grp));
     }
@@ -226,7 +229,7 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         rs.n_corners = g.n_corn[(size_t)i];
         rs.stats = g.stats[(size_t)i];
         rs.n_new = 0;
-        rs.n_new_features = rs.n_valid = 0;
+        rs.n_new_features = rs.n_valid = rs.n_inliers = 0;
         rs.n_tracker = st.n_tracker;
         std::memcpy(&corners_[slot][(size_t)s * mc], &g.corners[(size_t)i * mc],
                     (size_t)rs.n_corners * sizeof(svo_float2));
@@ -306,6 +309,11 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
     }
     lap(2);
     if (nk == 0) return;
+    if (closed_loop_) {
+        run_keyframes_closed_loop(g, slot, nk, sum);
+        lap(3);
+        return;
+    }
 
     // ---- dedupe + StereoBM + reprojection for the new keyframes (:113-142), then
     // BundleAdjuster::add_keyframe's id assignment (a running counter; new features
@@ -356,6 +364,119 @@ void BatchFrontEnd::run_group(Group& g, Job& job, int slot, int gi) {
         sum.new_points += nv;
     }
     lap(4);
+}
+
+// Keyframe stage with the pose step in the loop (src/image_processor.cpp:71-162), for the nk
+// keyframes of one group: PnP-RANSAC on the GPU, inlier keyframe, dedupe + stereo + reprojection
+// with hmat, id assignment, tracker re-init.
+void BatchFrontEnd::run_keyframes_closed_loop(Group& g, int slot, int nk, BatchSummary& sum) {
+    svo_engine* e = g.e;
+    const int mc = opt_.params.max_corners, mf = opt_.params.max_features;
+    // ---- pose step for the keyframes that have tracked features (not the first keyframe)
+    int np = 0;
+    for (int k = 0; k < nk; ++k) {
+        const int i = g.kf_local[(size_t)k];
+        SeqState& st = seq_[(size_t)g.seqs[(size_t)i]];
+        if (st.res[slot].decision != BATCH_KEYFRAME) continue;
+        const int n = st.res[slot].stats.n_kept;
+        for (int j = 0; j < n; ++j) {
+            const uint64_t id = g.tracked_ids[(size_t)i * mf + j];
+            if (id >= st.world.size()) throw std::out_of_range("BatchFrontEnd: tracked id without a world point");
+            g.pnp_world[(size_t)np * mf + j] = st.world[(size_t)id];    // get_world_points(ids), :72
+            g.pnp_image[(size_t)np * mf + j] = g.tracked[(size_t)i * mf + j];
+        }
+        g.pnp_counts[(size_t)np] = n;
+        std::memcpy(&g.pnp_guess[(size_t)np * 6], st.rt, sizeof st.rt);
+        g.pnp_kf[(size_t)np] = k;
+        ++np;
+    }
+    if (np > 0) {
+        int rc = svo_pnp_ransac(e, np, g.pnp_world.data(), g.pnp_image.data(), g.pnp_counts.data(),
+                                opt_.focal, opt_.cx, opt_.cy, pnp_iterations_, pnp_reproj_,
+                                pnp_confidence_, g.pnp_guess.data(), g.pnp_res.data(), g.pnp_inl.data());
+        if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_pnp_ransac", rc));
+    }
+    // ---- inlier lists and poses (:95-108, :130-134); a first keyframe has none and the identity
+    for (int k = 0; k < nk; ++k) {
+        g.n_inl[(size_t)k] = 0;
+        float* pose = &g.poses[(size_t)k * 16];
+        for (int q = 0; q < 16; ++q) pose[q] = (q % 5 == 0) ? 1.f : 0.f;
+    }
+    for (int p = 0; p < np; ++p) {
+        const int k = g.pnp_kf[(size_t)p];
+        const int i = g.kf_local[(size_t)k];
+        SeqState& st = seq_[(size_t)g.seqs[(size_t)i]];
+        const svo_pnp_result& r = g.pnp_res[(size_t)p];
+        // solvePnPRansac leaves rvec/tvec as they were when it fails (the reference does not look
+        // at its return value); either way they are the next keyframe's guess
+        std::memcpy(st.rt, r.rvec, 3 * sizeof(double));
+        std::memcpy(st.rt + 3, r.tvec, 3 * sizeof(double));
+        const int ni = r.ok ? r.n_inliers : 0;
+        g.n_inl[(size_t)k] = ni;
+        st.res[slot].n_inliers = ni;
+        for (int j = 0; j < ni; ++j) {
+            const int src = g.pnp_inl[(size_t)p * mf + j];
+            g.inl[(size_t)k * mf + j] = g.tracked[(size_t)i * mf + src];
+            g.ids[(size_t)k * mf + j] = g.tracked_ids[(size_t)i * mf + src];
+        }
+        float* pose = &g.poses[(size_t)k * 16];           // hmat = [R^T | -R^T t]
+        for (int a = 0; a < 3; ++a) {
+            double acc = 0.0;
+            for (int b = 0; b < 3; ++b) {
+                pose[4 * a + b] = (float)r.rmat[3 * b + a];
+                acc += r.rmat[3 * b + a] * r.tvec[b];
+            }
+            pose[4 * a + 3] = (float)(-acc);
+        }
+    }
+    int rc = svo_keyframe(e, nk, g.kf_local.data(), g.inl.data(), g.n_inl.data(), g.poses.data(),
+                          opt_.focal, opt_.cx, opt_.cy, opt_.baseline, g.new_feats.data(),
+                          g.n_newv.data(), g.valid_2d.data(), g.pts_3d.data(), g.valid_idx.data(),
+                          g.disp16.data(), g.n_valid.data());
+    if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_keyframe", rc));
+    // ---- add_keyframe's ids (src/bundle_adjuster.cpp:98-116) and FeatureTracker::init (:148-162)
+    for (int k = 0; k < nk; ++k) {
+        const int i = g.kf_local[(size_t)k];
+        const int s = g.seqs[(size_t)i];
+        SeqState& st = seq_[(size_t)s];
+        SeqResult& rs = st.res[slot];
+        const int n_inl = g.n_inl[(size_t)k];
+        const int nv = std::min(g.n_valid[(size_t)k], mf - n_inl);
+        svo_float2* f = &g.feats[(size_t)k * mf];
+        uint64_t* id = &g.ids[(size_t)k * mf];
+        std::memcpy(f, &g.inl[(size_t)k * mf], (size_t)n_inl * sizeof(svo_float2));
+        std::memcpy(f + n_inl, &g.valid_2d[(size_t)k * mc], (size_t)nv * sizeof(svo_float2));
+        for (int j = 0; j < nv; ++j) {
+            id[n_inl + j] = st.next_id++;
+            st.world.push_back(g.pts_3d[(size_t)k * mc + j]);
+        }
+        g.counts[(size_t)k] = n_inl + nv;
+        std::memcpy(st.hmat, &g.poses[(size_t)k * 16], sizeof st.hmat);
+        st.have_kf = true;
+        rs.n_new = nv;
+        rs.n_new_features = g.n_newv[(size_t)k];
+        rs.n_valid = g.n_valid[(size_t)k];
+        st.n_tracker = rs.n_tracker = n_inl + nv;
+        std::memcpy(&tracker_pts_[slot][(size_t)s * mf], f, (size_t)(n_inl + nv) * sizeof(svo_float2));
+        std::memcpy(&tracker_ids_[slot][(size_t)s * mf], id, (size_t)(n_inl + nv) * sizeof(uint64_t));
+        std::memcpy(&new_2d_[slot][(size_t)s * mc], &g.valid_2d[(size_t)k * mc], (size_t)nv * sizeof(svo_float2));
+        std::memcpy(&new_3d_[slot][(size_t)s * mc], &g.pts_3d[(size_t)k * mc], (size_t)nv * sizeof(svo_float3));
+        std::memcpy(&new_feats_[slot][(size_t)s * mc], &g.new_feats[(size_t)k * mc], (size_t)rs.n_new_features * sizeof(svo_float2));
+        std::memcpy(&disp16_[slot][(size_t)s * mc], &g.disp16[(size_t)k * mc], (size_t)rs.n_new_features * sizeof(int16_t));
+        std::memcpy(&valid_idx_[slot][(size_t)s * mc], &g.valid_idx[(size_t)k * mc], (size_t)rs.n_valid * sizeof(int32_t));
+        sum.keyframes += 1;
+        sum.new_points += nv;
+    }
+    rc = svo_tracker_set(e, nk, g.kf_local.data(), g.feats.data(), g.ids.data(), g.counts.data());
+    if (rc != SVO_OK) throw std::runtime_error(engine_error(e, "svo_tracker_set", rc));
+}
+
+void BatchFrontEnd::set_closed_loop(bool on, int iterations, float reproj_error, double confidence) {
+    if (n_submitted_ != 0) throw std::logic_error("BatchFrontEnd::set_closed_loop: call before the first step");
+    closed_loop_ = on;
+    pnp_iterations_ = iterations;
+    pnp_reproj_ = reproj_error;
+    pnp_confidence_ = confidence;
 }
 
 void BatchFrontEnd::submit(const uint8_t* const* left, const uint8_t* const* right, int pitch,

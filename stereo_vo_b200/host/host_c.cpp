@@ -264,6 +264,19 @@ int svo_batch_get_keyframe(svo_batch* b, int32_t seq, int32_t* n_new_features,
     return SVO_OK;
 }
 
+int svo_batch_set_closed_loop(svo_batch* b, int32_t on, int32_t iterations, float reproj_error,
+                              double confidence) {
+    if (!b) return SVO_ERR_INVALID;
+    return guarded(b->error, [&] { b->fe->set_closed_loop(on != 0, iterations, reproj_error, confidence); });
+}
+
+int svo_batch_get_pose(svo_batch* b, int32_t seq, float hmat[16], int32_t* n_inliers) {
+    if (!b || seq < 0 || seq >= b->fe->n_seq()) return SVO_ERR_INVALID;
+    if (hmat) std::memcpy(hmat, b->fe->pose(seq), 16 * sizeof(float));
+    if (n_inliers) *n_inliers = b->fe->n_inliers(seq);
+    return SVO_OK;
+}
+
 int64_t svo_batch_kernel_launches(const svo_batch* b) { return b ? b->fe->kernel_launches() : 0; }
 
 int svo_batch_timer_begin(svo_batch* b) {

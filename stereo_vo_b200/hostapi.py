@@ -86,6 +86,8 @@ def load_library():
     lib.svo_batch_get.argtypes = [vp, i32, C.POINTER(i32), C.POINTER(i32), vp, vp, C.POINTER(i32),
                                   vp, vp, C.POINTER(i32), vp, vp]
     lib.svo_batch_get_keyframe.argtypes = [vp, i32, C.POINTER(i32), vp, vp, C.POINTER(i32), vp]
+    lib.svo_batch_set_closed_loop.argtypes = [vp, i32, i32, f32, C.c_double]
+    lib.svo_batch_get_pose.argtypes = [vp, i32, C.POINTER(f32), C.POINTER(i32)]
     lib.svo_batch_kernel_launches.argtypes = [vp]
     lib.svo_batch_kernel_launches.restype = C.c_int64
     lib.svo_batch_timer_begin.argtypes = [vp]
@@ -217,7 +219,7 @@ class Batch:
     """Many independent sequences on one GPU through svo::BatchFrontEnd (svo_batch_*)."""
 
     def __init__(self, width, height, n_seq, n_groups, cam, device=0, parallax_thresh=20.0,
-                 params: Optional[SvoParams] = None):
+                 params: Optional[SvoParams] = None, closed_loop: bool = False):
         self.lib = load_library()
         p = params or capi.default_params(width, height)
         self.params = p
@@ -233,6 +235,12 @@ class Batch:
         self.n_groups = max(1, min(n_groups, n_seq))
         self.max_corners, self.max_features = p.max_corners, p.max_features
         self._keep = None
+        self.closed_loop = closed_loop
+        if closed_loop:
+            # the pose step on the GPU with the reference's solvePnPRansac arguments
+            rc = self.lib.svo_batch_set_closed_loop(self.h, 1, 100, 8.0, 0.99)
+            if rc != 0:
+                raise SvoError(f"svo_batch_set_closed_loop failed ({rc})")
 
     @staticmethod
     def _ptrs(items, device):
@@ -338,6 +346,10 @@ class Batch:
         out = dict(decision=DECISIONS[dec.value], corners=corners[:nc.value], stats=stats[0],
                    tracker_pts=tp[:nt.value], tracker_ids=ti[:nt.value], new2d=n2[:nn.value],
                    new3d=n3[:nn.value])
+        hm = (C.c_float * 16)()
+        ni = C.c_int32()
+        self.lib.svo_batch_get_pose(self.h, seq, hm, C.byref(ni))
+        out.update(hmat=np.array(list(hm), np.float32).reshape(4, 4), n_inliers=ni.value)
         if dec.value in (2, 4):
             nf, nv = C.c_int32(), C.c_int32()
             feats = np.zeros((self.max_corners, 2), np.float32)

@@ -253,9 +253,9 @@ def run_ours(args, rank, world, local_rank):
         return float(t.item())
 
     def throughput_leg(n_seq, resident, K, Wm, groups, min_seconds, profile=False,
-                       pipeline=True):
+                       pipeline=True, closed_loop=False):
         """n_seq sequences (the first n_seq of this rank's slab) through hostapi.Batch."""
-        batch = hostapi.Batch(W, H, n_seq, groups, cam, device=local_rank)
+        batch = hostapi.Batch(W, H, n_seq, groups, cam, device=local_rank, closed_loop=closed_loop)
         sub = slab[:n_seq]
         dptr = None
         base = sub.ctypes.data
@@ -320,6 +320,10 @@ def run_ours(args, rank, world, local_rank):
         args.groups = min(4, cores_per_rank)
     dev = throughput_leg(S, True, K, Wm, args.groups, args.min_seconds)
     e2e = dev if args.skip_e2e else throughput_leg(S, False, K, Wm, args.groups, args.min_seconds)
+    # closed loop: the pose step (PnP-RANSAC) on the GPU inside the loop instead of teacher poses
+    closed = None
+    if not args.skip_closed_loop:
+        closed = throughput_leg(S, True, K, Wm, args.groups, args.min_seconds / 2, closed_loop=True)
     # strong scaling (configs[3] as written): 64 sequences in total, sharded 64/32/16/8 per GPU
     n_strong = len(sharding.shard_sequences(TOTAL_SEQS_STRONG, world, rank))
     strong = None
@@ -347,6 +351,18 @@ def run_ours(args, rank, world, local_rank):
                       "ms_per_step": s_ms / (K * strong["repeats"]), "repeats": strong["repeats"],
                       "note": "frames resident in HBM; same 64 sequences whatever N "
                               "(sharding.shard_sequences), so per-GPU batches shrink with N"}
+    closed_out = None
+    if closed is not None:
+        c_ms = reduce(closed["ms"])
+        c_steps = K * closed["repeats"]
+        closed_out = {"value": world * S * c_steps / (c_ms * 1e-3), "unit": UNIT,
+                      "ms_per_step": c_ms / c_steps, "repeats": closed["repeats"],
+                      "keyframes_per_step": closed["tot"]["keyframes"] / c_steps,
+                      "note": "frames resident in HBM; keyframe poses from svo_pnp_ransac (GPU "
+                              "PnP-RANSAC, cv::solvePnPRansac's arguments of "
+                              "src/image_processor.cpp:80) on the tracked features and the stored "
+                              "world points: svo_step -> svo_pnp_ransac -> svo_keyframe -> "
+                              "svo_tracker_set, no caller poses"}
     h2d_gbs = measure_h2d_gbs(torch) if rank == 0 else None
 
     line = None
@@ -491,6 +507,7 @@ def run_ours(args, rank, world, local_rank):
             "gpu_launches_per_step": dev["launches"] / (K * dev["repeats"]),
             "roofline": roofline,
             "kernels": kernels,
+            "closed_loop": closed_out,
             "strong_scaling": strong_out,
             "extras": extras,
             "cpu_baseline": cpu,
@@ -710,6 +727,7 @@ def main():
     ap.add_argument("--skip-cpu-baseline", action="store_true", help="profiling runs only")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only")
     ap.add_argument("--skip-strong", action="store_true", help="no strong-scaling leg (N > 1)")
+    ap.add_argument("--skip-closed-loop", action="store_true", help="no closed-loop (GPU PnP) leg")
     ap.add_argument("--skip-extras", action="store_true",
                     help="no d435i / 4K / dense extras (they run at N = 1 only)")
     ap.add_argument("--ref-frames", type=int, default=16)

@@ -1,9 +1,10 @@
 // image_processor.hpp - the reference's ImageProcessor interface (src/image_processor.hpp:9-83)
 // on top of libsvo.so. process() keeps the reference's control flow
 // (src/image_processor.cpp:18-163); detection, tracking, dedupe, block matching and
-// reprojection are calls into the CUDA library. PnP-RANSAC stays a host step
-// (src/image_processor.cpp:75-92): with OpenCV it is cv::solvePnPRansac + cv::Rodrigues, without
-// OpenCV the caller supplies a solver (set_pnp_solver).
+// reprojection are calls into the CUDA library. The pose step (src/image_processor.cpp:75-92):
+// built with OpenCV it is cv::solvePnPRansac + cv::Rodrigues on the host, as in the reference;
+// built without, it runs on the GPU (svo_pnp_ransac) unless the caller installs a host solver
+// (set_pnp_solver).
 #pragma once
 #include <functional>
 #include <memory>

@@ -192,12 +192,39 @@ void ImageProcessor::process(const StereoPair& stereo_pair) {
 
     std::vector<cv::Point3f> world;
     bundle_adjuster->get_world_points(world, ids);          // :72
-    if (!pnp_)
-        throw std::runtime_error("ImageProcessor: no PnP solver (built without OpenCV): call set_pnp_solver()");
     double rmat[9];
     std::vector<int> inliers;
-    if (!pnp_(world, tracked_features, camera_matrix, rvec, tvec, rmat, inliers))
-        throw std::runtime_error("ImageProcessor: PnP solver failed");
+    if (pnp_) {
+        if (!pnp_(world, tracked_features, camera_matrix, rvec, tvec, rmat, inliers))
+            throw std::runtime_error("ImageProcessor: PnP solver failed");
+    } else {
+        // no host solver installed: the pose step runs on the GPU with the reference's
+        // solvePnPRansac arguments (:80: extrinsic guess, 100 iterations, 8 px, 0.99)
+        const int32_t n_pts = (int32_t)world.size();
+        std::vector<svo_float3> w((size_t)p.max_features);
+        std::vector<svo_float2> im((size_t)p.max_features);
+        std::vector<int32_t> inl((size_t)p.max_features);
+        for (int32_t i = 0; i < n_pts; ++i) {
+            w[(size_t)i] = {world[(size_t)i].x, world[(size_t)i].y, world[(size_t)i].z};
+            im[(size_t)i] = {tracked_features[(size_t)i].x, tracked_features[(size_t)i].y};
+        }
+        double guess[6];
+        for (int i = 0; i < 3; ++i) {
+            guess[i] = rvec.type() == CV_64F ? rvec.at<double>(i) : (double)rvec.at<float>(i);
+            guess[3 + i] = tvec.type() == CV_64F ? tvec.at<double>(i) : (double)tvec.at<float>(i);
+        }
+        svo_pnp_result r;
+        svo::check(e, svo_pnp_ransac(e, 1, w.data(), im.data(), &n_pts, in.focal, in.cx, in.cy, 100,
+                                     8.f, 0.99, guess, &r, inl.data()), "svo_pnp_ransac");
+        rvec = cv::Mat::zeros(3, 1, CV_64F);
+        tvec = cv::Mat::zeros(3, 1, CV_64F);
+        for (int i = 0; i < 3; ++i) {
+            rvec.at<double>(i) = r.rvec[i];
+            tvec.at<double>(i) = r.tvec[i];
+        }
+        for (int i = 0; i < 9; ++i) rmat[i] = r.rmat[i];
+        inliers.assign(inl.begin(), inl.begin() + (r.ok ? r.n_inliers : 0));
+    }
     const size_t num_inliers = inliers.size();
     // the solver is caller-supplied: a list longer than the tracker set (duplicates) must not
     // run past inl_pts before svo_keyframe gets to reject it

@@ -88,18 +88,23 @@ def test_cpp_facade_closed_loop(host_lib, oracle):
     vo.close()
 
 
-def test_cpp_facade_needs_a_pnp_solver(host_lib):
-    """Built without OpenCV there is no default PnP: the first frame that needs one fails
-    loudly instead of guessing a pose."""
+def test_cpp_facade_default_pose_step_is_the_gpu_solver(host_lib):
+    """No host solver installed: the facade's pose step (src/image_processor.cpp:75-92) runs on
+    the GPU (svo_pnp_ransac). Closed loop over 48 frames: the keyframe poses stay on the
+    synthetic ground truth and nearly every track is an inlier."""
     from stereo_vo_b200 import hostapi
-    from stereo_vo_b200.capi import SvoError
     cam = synth.KITTI00
-    fr = util.frames(0, 12)
+    fr = util.frames(0, 48)
     f, cx, cy, b = cam.f32()
     vo = hostapi.VoSequence(f, cx, cy, b)
-    with pytest.raises(SvoError, match="PnP"):
-        for l, r in fr:
-            vo.process(l, r)
+    for t, (l, r) in enumerate(fr):
+        vo.process(l, r, t * 0.1)
+    kfs = [(t, r) for t, r in enumerate(vo.log) if r["decision"] == "keyframe"]
+    assert len(kfs) >= 8
+    for t, r in kfs:
+        gt = np.array(synth.ground_truth(t))
+        assert np.abs(r["hmat"][:3, 3] - gt).max() < 0.05, (t, r["hmat"][:3, 3], gt)
+        assert len(r["inliers"]) >= 0.85 * len(r["tracked_ids"])
     vo.close()
 
 

@@ -6,7 +6,8 @@
 // source-level drop-in for the reference's classes. Without one (this repository's build
 // container has no OpenCV C++ SDK) a minimal stand-in with the same spelling is defined: a
 // ref-counted row-major cv::Mat restricted to the element types the front end touches
-// (CV_8UC1 images, CV_32F / CV_64F small matrices), cv::Point2f, cv::Point3f, cv::Size.
+// (CV_8UC1 images, the CV_8UC3 debug overlay, CV_32F / CV_64F small matrices), cv::Point2f,
+// cv::Point3f, cv::Size.
 // No image processing lives here - every pixel operation is a call into libsvo.so.
 #pragma once
 
@@ -25,6 +26,7 @@
 #ifndef CV_8UC1
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_8UC3 16
 #define CV_32F 5
 #define CV_32FC1 5
 #define CV_64F 6
@@ -116,6 +118,7 @@ class Mat {
     static size_t elem(int type) {
         switch (type) {
             case CV_8UC1: return 1;
+            case CV_8UC3: return 3;
             case CV_32F: return 4;
             case CV_64F: return 8;
             default: throw std::invalid_argument("cv_compat: unsupported Mat type");

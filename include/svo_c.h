@@ -304,6 +304,27 @@ SVO_API int svo_pnp_ransac(svo_engine* e, int32_t n, const svo_float3* world,
                            float cy, int32_t iterations, float reproj_error, double confidence,
                            const double* guess, svo_pnp_result* results, int32_t* inliers);
 
+/* ---- bundle-adjustment consumer -------------------------------------- */
+/* ReprojectionFactor::Evaluate (src/reprojection_factor.cpp:10-88) for the n_obs observations of a
+ * window in one launch. poses [n_poses][7] = (qw, qx, qy, qz, tx, ty, tz), world wrt camera, as
+ * BundleAdjuster::add_keyframe stores them (src/bundle_adjuster.cpp:63-70); points [n_points][3];
+ * observation i = pixel obs[2i..2i+1] of point point_idx[i] seen from pose pose_idx[i] (the
+ * residual blocks of src/bundle_adjuster.cpp:76-84,120-124). Outputs (any may be NULL):
+ * residuals [n_obs][2], jac_pose [n_obs][2][7] and jac_point [n_obs][2][3], row major, in the
+ * layout ceres hands to Evaluate. Focal length and principal point as in CameraInfo. */
+SVO_API int svo_reprojection_evaluate(svo_engine* e, int32_t n_obs, const int32_t* pose_idx,
+                                      const int32_t* point_idx, const double* obs,
+                                      int32_t n_poses, const double* poses, int32_t n_points,
+                                      const double* points, double focal, double cx, double cy,
+                                      double* residuals, double* jac_pose, double* jac_point);
+
+/* ---- debug overlay ---------------------------------------------------- */
+/* FeatureTracker::draw_track, src/feature_tracker.cpp:74-83: image (8-bit grey, the tracker's
+ * initial_image) -> out_rgb (height rows of 3 * width bytes, out_pitch bytes apart, R G B), with
+ * a green cv::arrowedLine(from[i] -> to[i], CV_RGB(0, 255, 0), thickness 4) per feature. */
+SVO_API int svo_draw_track(svo_engine* e, const uint8_t* image, int32_t pitch, const svo_float2* from,
+                           const svo_float2* to, int32_t n, uint8_t* out_rgb, int32_t out_pitch);
+
 /* FeatureTracker::init against the CURRENT frame of each listed sequence
  * (image_processor.cpp:51-52,148-162): feats/ids [n][max_features], counts[i] entries. */
 SVO_API int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,

@@ -61,6 +61,11 @@ SVO_API int svo_vo_set_pnp(svo_vo* v, svo_pnp_fn fn, void* user);
 SVO_API int svo_vo_process(svo_vo* v, const uint8_t* left, const uint8_t* right, int32_t width,
                            int32_t height, int32_t pitch, double t);
 SVO_API int svo_vo_last_record(svo_vo* v, svo_vo_record* out);
+/* FeatureTracker::get_drawing (src/feature_tracker.cpp:85-91, published by vo_node.cpp:188): the
+ * RGB overlay of the last keyframe's tracks, height rows of 3 * width bytes `out_pitch` apart.
+ * SVO_ERR_STATE before the first frame. */
+SVO_API int svo_vo_get_drawing(svo_vo* v, uint8_t* out_rgb, int32_t out_pitch, int32_t* width,
+                               int32_t* height);
 SVO_API const char* svo_vo_last_error(const svo_vo* v);
 
 /* ---- many sequences per GPU ----------------------------------------------------------- */
@@ -120,6 +125,26 @@ SVO_API int svo_batch_set_profiling(svo_batch* b, int32_t on);
 SVO_API int svo_batch_get_profile(const svo_batch* b, double* ms, int64_t* counts);
 /* engine of group g (device allocation helpers, debugging) */
 SVO_API svo_engine* svo_batch_engine(svo_batch* b, int32_t group);
+
+/* ---- KITTI odometry frame source (src/kitti_node.cpp:16-68 without ROS) ------------------ */
+typedef struct svo_kitti svo_kitti;
+/* data_path as in src/kitti_node.cpp:16 (trailing '/'), sequence "00".."21": parses
+ * data_odometry_poses/dataset/poses/<seq>.txt and sizes the images from image_0/000000.png */
+SVO_API int svo_kitti_open(const char* data_path, const char* sequence, svo_kitti** out);
+SVO_API void svo_kitti_close(svo_kitti* k);
+SVO_API const char* svo_kitti_last_error(const svo_kitti* k);   /* k may be NULL (open) */
+SVO_API int svo_kitti_info(const svo_kitti* k, int64_t* n_frames, int32_t* width, int32_t* height);
+/* frame i decoded into caller memory (8-bit grey, `pitch` bytes per row); pose12 receives the
+ * 3x4 row-major [R | t] of the pose file (may be NULL) */
+SVO_API int svo_kitti_read(svo_kitti* k, int64_t i, uint8_t* left, uint8_t* right, int32_t pitch,
+                           double* pose12);
+/* decode-ahead: frames first, first+1, ... decoded by a worker thread into `depth` >= 3 stereo
+ * slots of `slab` (depth * 2 * pitch * height bytes, e.g. from svo_host_alloc). svo_kitti_next
+ * returns 1 and the slot of the next frame (valid until two further calls), 0 at the end. */
+SVO_API int svo_kitti_prefetch_start(svo_kitti* k, uint8_t* slab, int32_t depth, int32_t pitch,
+                                     int64_t first);
+SVO_API int svo_kitti_next(svo_kitti* k, int64_t* index, const uint8_t** left, const uint8_t** right,
+                           double* pose12);
 
 #ifdef __cplusplus
 }

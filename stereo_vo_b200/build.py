@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsvo.so")
 SOURCES = ["engine.cu", "pyr_down.cu", "corner_score.cu", "sort_candidates.cu",
            "greedy_select.cu", "stereo.cu", "stereo_dense.cu", "lk_track.cu", "track_filter.cu",
-           "pnp_ransac.cu"]
+           "pnp_ransac.cu", "reprojection_factor.cu", "draw_track.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "--fmad=false", "-gencode", "arch=compute_100a,code=sm_100a",
               "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
               "--threads", "0"]
@@ -27,7 +27,7 @@ HOST_LIB = os.path.join(HERE, "libsvo_host.so")
 HOST_DIR = os.path.join(HERE, "host")
 INCLUDE = os.path.join(HERE, "..", "include")
 HOST_SOURCES = ["bundle_adjuster.cpp", "camera_config.cpp", "feature_tracker.cpp",
-                "image_processor.cpp", "batch_front_end.cpp", "host_c.cpp"]
+                "image_processor.cpp", "batch_front_end.cpp", "kitti_source.cpp", "host_c.cpp"]
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wextra", "-pthread"]
 
 
@@ -81,11 +81,15 @@ def build_host_lib(force: bool = False) -> str:
     with _build_lock():
         if not force and not host_needs_build():       # another process built it meanwhile
             return HOST_LIB
-        cxx = os.environ.get("CXX", "g++")
+        # the system compiler, whose libstdc++ is the shared one every other library of the
+        # process uses (a toolchain under /opt that links libstdc++ statically puts a second copy
+        # of the iostream / locale state into this library: crashes in stream extraction once
+        # another libstdc++ user is loaded). SVO_CXX overrides.
+        cxx = os.environ.get("SVO_CXX") or ("/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++")
         tmp = f"{HOST_LIB}.tmp.{os.getpid()}"
         cmd = [cxx, *CXX_FLAGS, "-shared", "-I", INCLUDE,
                *[os.path.join(HOST_DIR, f) for f in HOST_SOURCES], "-o", tmp,
-               "-L", HERE, "-l:libsvo.so", "-Wl,-rpath,$ORIGIN"]
+               "-L", HERE, "-l:libsvo.so", "-lz", "-Wl,-rpath,$ORIGIN"]
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
         text = r.stdout.decode(errors="replace")
         if r.returncode != 0:

@@ -55,7 +55,7 @@ EXPORTS = [
     "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_keyframe_tracked", "svo_step_keyframe", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
-    "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac",
+    "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac", "svo_reprojection_evaluate", "svo_draw_track",
 ]
 
 _lib = None
@@ -115,6 +115,9 @@ def load_library(path: Optional[str] = None):
     lib.svo_step_keyframe.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, vp, f32, f32, f32, f32, f32,
                                       vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]
+    lib.svo_reprojection_evaluate.argtypes = [vp, i32, vp, vp, vp, i32, vp, i32, vp, C.c_double,
+                                              C.c_double, C.c_double, vp, vp, vp]
+    lib.svo_draw_track.argtypes = [vp, vp, i32, vp, vp, i32, vp, i32]
     lib.svo_pnp_ransac.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, i32, f32, C.c_double, vp, vp, vp]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
     lib.svo_device_free.argtypes = [vp, vp]
@@ -537,6 +540,33 @@ class Engine:
                                             float(reproj_error), float(confidence), _ptr(g),
                                             _ptr(res), _ptr(inl)), "svo_pnp_ransac")
         return res, [inl[i, :res[i]["n_inliers"]].copy() for i in range(n)]
+
+    def reprojection_evaluate(self, poses, points, pose_idx, point_idx, obs, focal, cx, cy):
+        """svo_reprojection_evaluate: (residuals (n, 2), jac_pose (n, 2, 7), jac_point (n, 2, 3))"""
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        points = np.ascontiguousarray(points, np.float64).reshape(-1, 3)
+        pi = np.ascontiguousarray(pose_idx, np.int32)
+        xi = np.ascontiguousarray(point_idx, np.int32)
+        obs = np.ascontiguousarray(obs, np.float64).reshape(-1, 2)
+        n = len(pi)
+        r = np.zeros((n, 2))
+        jp = np.zeros((n, 2, 7))
+        jx = np.zeros((n, 2, 3))
+        self._check(self.lib.svo_reprojection_evaluate(
+            self.h, n, _ptr(pi), _ptr(xi), _ptr(obs), len(poses), _ptr(poses), len(points),
+            _ptr(points), float(focal), float(cx), float(cy), _ptr(r), _ptr(jp), _ptr(jx)),
+            "svo_reprojection_evaluate")
+        return r, jp, jx
+
+    def draw_track(self, image, from_pts, to_pts) -> np.ndarray:
+        """svo_draw_track: (H, W, 3) RGB overlay of FeatureTracker::draw_track."""
+        image = _img(image)
+        a = np.ascontiguousarray(from_pts, np.float32).reshape(-1, 2)
+        b = np.ascontiguousarray(to_pts, np.float32).reshape(-1, 2)
+        out = np.zeros((self.height, self.width, 3), np.uint8)
+        self._check(self.lib.svo_draw_track(self.h, _ptr(image), image.strides[0], _ptr(a), _ptr(b),
+                                            len(a), _ptr(out), out.strides[0]), "svo_draw_track")
+        return out
 
     def device_alloc(self, nbytes: int) -> int:
         p = C.c_void_p()

@@ -146,6 +146,9 @@ struct svo_engine {
     SvoPnpResult* d_pnp_res = nullptr;
     int* d_pnp_inl = nullptr;
     unsigned pnp_calls = 0;
+    uint8_t* d_draw = nullptr;        // svo_draw_track: RGB image, grey image, arrow end points
+    unsigned char* d_ba = nullptr;    // svo_reprojection_evaluate scratch (grown on demand)
+    size_t ba_bytes = 0;
     unsigned char* d_out = nullptr;   // packed result blocks
     size_t step_block = 0, key_block = 0, out_bytes = 0;
     int pts_cap = 0;                  // per-sequence capacity of d_pts / stereo outputs
@@ -1154,7 +1157,7 @@ void svo_destroy(svo_engine* e) {
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
                      e->d_call, e->d_kcall, e->d_pnp_world, e->d_pnp_img, e->d_pnp_counts,
-                     e->d_pnp_guess, e->d_pnp_res, e->d_pnp_inl};
+                     e->d_pnp_guess, e->d_pnp_res, e->d_pnp_inl, e->d_ba, e->d_draw};
     for (void* p : dptrs) if (p) cudaFree(p);
     if (e->h_call) cudaFreeHost(e->h_call);
     if (e->h_pull) cudaFreeHost(e->h_pull);
@@ -1607,6 +1610,96 @@ int svo_pnp_ransac(svo_engine* e, int32_t n, const svo_float3* world, const svo_
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
     ECUDA(e, cudaStreamSynchronize(e->st));
     finish_timing(e);
+    return SVO_OK;
+}
+
+int svo_reprojection_evaluate(svo_engine* e, int32_t n_obs, const int32_t* pose_idx,
+                              const int32_t* point_idx, const double* obs, int32_t n_poses,
+                              const double* poses, int32_t n_points, const double* points,
+                              double focal, double cx, double cy, double* residuals,
+                              double* jac_pose, double* jac_point) {
+    if (!e) return SVO_ERR_INVALID;
+    if (n_obs < 0 || n_poses <= 0 || n_points <= 0 || !pose_idx || !point_idx || !obs || !poses || !points)
+        return fail(e, SVO_ERR_INVALID, "svo_reprojection_evaluate: bad arguments");
+    for (int i = 0; i < n_obs; ++i)
+        if (pose_idx[i] < 0 || pose_idx[i] >= n_poses || point_idx[i] < 0 || point_idx[i] >= n_points)
+            return fail(e, SVO_ERR_INVALID, "svo_reprojection_evaluate: index out of range");
+    if (n_obs == 0) return SVO_OK;
+    ECUDA(e, cudaSetDevice(e->device));
+    // one scratch allocation per call shape (a window is rebuilt once per keyframe, not per frame)
+    const size_t b_poses = (size_t)n_poses * 7 * 8, b_pts = (size_t)n_points * 3 * 8,
+                 b_idx = (size_t)n_obs * 4, b_obs = (size_t)n_obs * 2 * 8;
+    const size_t b_out = (size_t)n_obs * (2 + 14 + 6) * 8;
+    const size_t need = b_poses + b_pts + 2 * b_idx + b_obs + b_out + 1024;
+    if (need > e->ba_bytes) {
+        if (e->d_ba) cudaFree(e->d_ba);
+        e->d_ba = nullptr;
+        e->ba_bytes = 0;
+        if (cudaMalloc(reinterpret_cast<void**>(&e->d_ba), need) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(e, SVO_ERR_NOMEM, "svo_reprojection_evaluate: no device memory");
+        }
+        e->ba_bytes = need;
+    }
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    unsigned char* base = e->d_ba;
+    double* d_poses = reinterpret_cast<double*>(base); base += up(b_poses);
+    double* d_pts = reinterpret_cast<double*>(base); base += up(b_pts);
+    double* d_obs = reinterpret_cast<double*>(base); base += up(b_obs);
+    int* d_pi = reinterpret_cast<int*>(base); base += up(b_idx);
+    int* d_xi = reinterpret_cast<int*>(base); base += up(b_idx);
+    double* d_r = reinterpret_cast<double*>(base);
+    double* d_jp = d_r + (size_t)n_obs * 2;
+    double* d_jx = d_jp + (size_t)n_obs * 14;
+    ECUDA(e, cudaEventRecord(e->ev[0], e->st));
+    ECUDA(e, cudaMemcpyAsync(d_poses, poses, b_poses, cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, cudaMemcpyAsync(d_pts, points, b_pts, cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, cudaMemcpyAsync(d_obs, obs, b_obs, cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, cudaMemcpyAsync(d_pi, pose_idx, b_idx, cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, cudaMemcpyAsync(d_xi, point_idx, b_idx, cudaMemcpyHostToDevice, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[1], e->st));
+    ECUDA(e, svo_launch_reprojection_factor(d_poses, d_pts, d_pi, d_xi, d_obs, n_obs, focal, cx, cy,
+                                            d_r, d_jp, d_jx, e->st));
+    e->launches += 1;
+    ECUDA(e, cudaEventRecord(e->ev[2], e->st));
+    if (residuals) ECUDA(e, cudaMemcpyAsync(residuals, d_r, (size_t)n_obs * 2 * 8, cudaMemcpyDeviceToHost, e->st));
+    if (jac_pose) ECUDA(e, cudaMemcpyAsync(jac_pose, d_jp, (size_t)n_obs * 14 * 8, cudaMemcpyDeviceToHost, e->st));
+    if (jac_point) ECUDA(e, cudaMemcpyAsync(jac_point, d_jx, (size_t)n_obs * 6 * 8, cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaEventRecord(e->ev[3], e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
+    finish_timing(e);
+    return SVO_OK;
+}
+
+int svo_draw_track(svo_engine* e, const uint8_t* image, int32_t pitch, const svo_float2* from,
+                   const svo_float2* to, int32_t n, uint8_t* out_rgb, int32_t out_pitch) {
+    if (!e) return SVO_ERR_INVALID;
+    const int W = e->p.width, H = e->p.height;
+    if (!image || !out_rgb || pitch < W || out_pitch < 3 * W || n < 0 || (n > 0 && (!from || !to)))
+        return fail(e, SVO_ERR_INVALID, "svo_draw_track: bad arguments");
+    if (n > e->p.max_features) return fail(e, SVO_ERR_CAPACITY, "svo_draw_track: more features than max_features");
+    ECUDA(e, cudaSetDevice(e->device));
+    const size_t gray_b = (size_t)W * H, rgb_b = 3 * gray_b, pts_b = (size_t)e->p.max_features * sizeof(float2);
+    if (!e->d_draw) {
+        if (cudaMalloc(reinterpret_cast<void**>(&e->d_draw), gray_b + rgb_b + 2 * pts_b + 1024) != cudaSuccess) {
+            cudaGetLastError();
+            return fail(e, SVO_ERR_NOMEM, "svo_draw_track: no device memory");
+        }
+    }
+    uint8_t* d_rgb = e->d_draw;
+    uint8_t* d_gray = d_rgb + ((rgb_b + 255) & ~(size_t)255);
+    float2* d_from = reinterpret_cast<float2*>(d_gray + ((gray_b + 255) & ~(size_t)255));
+    float2* d_to = d_from + e->p.max_features;
+    ECUDA(e, cudaMemcpy2DAsync(d_gray, W, image, pitch, W, H, cudaMemcpyHostToDevice, e->st));
+    if (n > 0) {
+        ECUDA(e, cudaMemcpyAsync(d_from, from, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+        ECUDA(e, cudaMemcpyAsync(d_to, to, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, e->st));
+    }
+    ECUDA(e, svo_launch_draw_track(d_gray, W, d_from, d_to, n, d_rgb, 3 * W, W, H, 4, e->st));
+    e->launches += n > 0 ? 2 : 1;
+    ECUDA(e, cudaMemcpy2DAsync(out_rgb, out_pitch, d_rgb, 3 * (size_t)W, 3 * (size_t)W, H,
+                               cudaMemcpyDeviceToHost, e->st));
+    ECUDA(e, cudaStreamSynchronize(e->st));
     return SVO_OK;
 }
 

@@ -163,6 +163,16 @@ cudaError_t svo_launch_pnp_ransac(const float* world, const float2* image, int s
                                   unsigned salt, SvoPnpResult* results, int* inliers, int n_call,
                                   cudaStream_t st);
 
+cudaError_t svo_launch_reprojection_factor(const double* poses, const double* points,
+                                           const int* pose_idx, const int* point_idx,
+                                           const double* obs, int n_obs, double f, double cx,
+                                           double cy, double* resid, double* jac_pose,
+                                           double* jac_point, cudaStream_t st);
+
+cudaError_t svo_launch_draw_track(const uint8_t* gray, int gpitch, const float2* from,
+                                  const float2* to, int n, uint8_t* rgb, int rpitch, int w, int h,
+                                  int thickness, cudaStream_t st);
+
 struct SvoLkParams {
     int max_iters;
     double eps2;                 // criteria.epsilon squared (OpenCV squares it in double)

@@ -122,33 +122,30 @@ void FeatureTracker::get_tracked_features(std::vector<cv::Point2f>& features,
     ids = feature_ids;
 }
 
-// ---- debug overlay. Host-side and outside the parity scope: the reference paints green
-// arrows with cv::arrowedLine on an RGB copy; this build marks the same segments on a grey copy
-// (the stand-in Mat has no 3-channel type).
-static void draw_segment(cv::Mat& img, cv::Point2f a, cv::Point2f b, int half_width) {
-    const float dx = b.x - a.x, dy = b.y - a.y;
-    const int steps = (int)std::ceil(std::fmax(std::fabs(dx), std::fabs(dy))) + 1;
-    for (int s = 0; s <= steps; ++s) {
-        const float t = steps ? (float)s / (float)steps : 0.f;
-        const int cx = (int)std::lround(a.x + t * dx), cy = (int)std::lround(a.y + t * dy);
-        for (int oy = -half_width; oy <= half_width; ++oy)
-            for (int ox = -half_width; ox <= half_width; ++ox) {
-                const int x = cx + ox, y = cy + oy;
-                if (x >= 0 && y >= 0 && x < img.cols && y < img.rows) img.ptr(y)[x] = 255;
-            }
-    }
+// ---- debug overlay (src/feature_tracker.cpp:74-91): initial_image as RGB with a green
+// cv::arrowedLine (thickness 4) from every feature's initial position to its current one,
+// rasterised on the GPU (svo_draw_track)
+static cv::Mat render_overlay(svo_engine* e, const cv::Mat& gray, const std::vector<svo_float2>& from,
+                              const std::vector<svo_float2>& to) {
+    cv::Mat rgb(gray.rows, gray.cols, CV_8UC3);
+    svo::check(e, svo_draw_track(e, gray.ptr(0), (int32_t)gray.step, from.data(), to.data(),
+                                 (int32_t)from.size(), rgb.ptr(0), (int32_t)rgb.step), "svo_draw_track");
+    return rgb;
 }
 
 void FeatureTracker::draw_track() {
-    track_drawing = initial_image.clone();
-    if (track_drawing.empty()) return;
+    if (initial_image.empty()) return;
+    std::vector<svo_float2> from(feature_set.size()), to(feature_set.size());
     for (size_t i = 0; i < feature_set.size(); ++i) {
-        const cv::Point2f from = initial_features.at(feature_ids[i]);
-        draw_segment(track_drawing, from, feature_set[i], 2);
+        const cv::Point2f a = initial_features.at(feature_ids[i]);
+        from[i] = {a.x, a.y};
+        to[i] = {feature_set[i].x, feature_set[i].y};
     }
+    track_drawing = render_overlay(engine(initial_image)->e, initial_image, from, to);
 }
 
 cv::Mat FeatureTracker::get_drawing() {
-    if (track_drawing.empty()) track_drawing = initial_image.clone();
+    if (track_drawing.empty() && !initial_image.empty())      // :86-89: the plain RGB copy
+        track_drawing = render_overlay(engine(initial_image)->e, initial_image, {}, {});
     return track_drawing;
 }

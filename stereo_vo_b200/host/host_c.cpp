@@ -11,6 +11,7 @@
 #include "stereo_vo/batch_front_end.hpp"
 #include "stereo_vo/camera_info.hpp"
 #include "stereo_vo/image_processor.hpp"
+#include "stereo_vo/kitti_source.hpp"
 
 namespace {
 thread_local std::string g_create_error;
@@ -52,6 +53,13 @@ struct svo_vo {
 struct svo_batch {
     std::unique_ptr<svo::BatchFrontEnd> fe;
     std::string error;
+};
+
+struct svo_kitti {
+    std::unique_ptr<svo::KittiSource> src;
+    std::unique_ptr<svo::KittiPrefetcher> pf;     // destroyed before src
+    std::string error;
+    ~svo_kitti() { pf.reset(); }
 };
 
 extern "C" {
@@ -167,6 +175,20 @@ int svo_vo_last_record(svo_vo* v, svo_vo_record* out) {
     out->tracker_pts = f2(r.tracker_pts);
     out->tracker_ids = v->tracker_ids.data();
     return SVO_OK;
+}
+
+int svo_vo_get_drawing(svo_vo* v, uint8_t* out_rgb, int32_t out_pitch, int32_t* width, int32_t* height) {
+    if (!v) return SVO_ERR_INVALID;
+    return guarded(v->error, [&] {
+        cv::Mat d = v->tracker->get_drawing();
+        if (d.empty()) throw std::logic_error("svo_vo_get_drawing: no frame processed yet");
+        if (width) *width = d.cols;
+        if (height) *height = d.rows;
+        if (out_rgb) {
+            if (out_pitch < 3 * d.cols) throw std::invalid_argument("svo_vo_get_drawing: out_pitch < 3 * width");
+            for (int r = 0; r < d.rows; ++r) std::memcpy(out_rgb + (size_t)r * out_pitch, d.ptr(r), (size_t)3 * d.cols);
+        }
+    });
 }
 
 // ------------------------------------------------------------------------------- batch
@@ -310,6 +332,69 @@ int svo_batch_get_profile(const svo_batch* b, double* ms, int64_t* counts) {
 svo_engine* svo_batch_engine(svo_batch* b, int32_t group) {
     if (!b || group < 0 || group >= b->fe->n_groups()) return nullptr;
     return b->fe->engine(group);
+}
+
+// ------------------------------------------------------------------------------- KITTI source
+int svo_kitti_open(const char* data_path, const char* sequence, svo_kitti** out) {
+    if (!data_path || !sequence || !out) return SVO_ERR_INVALID;
+    *out = nullptr;
+    return guarded(g_create_error, [&] {
+        auto k = std::make_unique<svo_kitti>();
+        k->src = std::make_unique<svo::KittiSource>(data_path, sequence);
+        *out = k.release();
+    });
+}
+
+void svo_kitti_close(svo_kitti* k) { delete k; }
+
+const char* svo_kitti_last_error(const svo_kitti* k) { return k ? k->error.c_str() : g_create_error.c_str(); }
+
+int svo_kitti_info(const svo_kitti* k, int64_t* n_frames, int32_t* width, int32_t* height) {
+    if (!k) return SVO_ERR_INVALID;
+    if (n_frames) *n_frames = (int64_t)k->src->size();
+    if (width) *width = k->src->width();
+    if (height) *height = k->src->height();
+    return SVO_OK;
+}
+
+static void copy_pose(const svo::KittiPose& p, double* pose12) {
+    if (!pose12) return;
+    for (int r = 0; r < 3; ++r) {
+        for (int c = 0; c < 3; ++c) pose12[4 * r + c] = p.R[3 * r + c];
+        pose12[4 * r + 3] = p.t[r];
+    }
+}
+
+int svo_kitti_read(svo_kitti* k, int64_t i, uint8_t* left, uint8_t* right, int32_t pitch,
+                   double* pose12) {
+    if (!k || !left || !right || i < 0) return SVO_ERR_INVALID;
+    return guarded(k->error, [&] {
+        k->src->read((size_t)i, left, right, pitch);
+        copy_pose(k->src->pose((size_t)i), pose12);
+    });
+}
+
+int svo_kitti_prefetch_start(svo_kitti* k, uint8_t* slab, int32_t depth, int32_t pitch, int64_t first) {
+    if (!k || first < 0) return SVO_ERR_INVALID;
+    return guarded(k->error, [&] {
+        k->pf.reset();
+        k->pf = std::make_unique<svo::KittiPrefetcher>(*k->src, slab, depth, pitch, (size_t)first);
+    });
+}
+
+int svo_kitti_next(svo_kitti* k, int64_t* index, const uint8_t** left, const uint8_t** right,
+                   double* pose12) {
+    if (!k || !k->pf || !index || !left || !right) return SVO_ERR_INVALID;
+    int got = 0;
+    const int rc = guarded(k->error, [&] {
+        size_t i = 0;
+        if (k->pf->next(i, *left, *right)) {
+            *index = (int64_t)i;
+            copy_pose(k->src->pose(i), pose12);
+            got = 1;
+        }
+    });
+    return rc != SVO_OK ? rc : got;
 }
 
 }  // extern "C"

@@ -72,6 +72,7 @@ def load_library():
     lib.svo_vo_set_pnp.argtypes = [vp, PNP_FN, vp]
     lib.svo_vo_process.argtypes = [vp, vp, vp, i32, i32, i32, C.c_double]
     lib.svo_vo_last_record.argtypes = [vp, C.POINTER(VoRecord)]
+    lib.svo_vo_get_drawing.argtypes = [vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]
     lib.svo_vo_last_error.argtypes = [vp]
     lib.svo_vo_last_error.restype = C.c_char_p
     lib.svo_batch_create.argtypes = [C.POINTER(SvoParams), i32, i32, i32, f32, f32, f32, f32, f32,
@@ -89,6 +90,16 @@ def load_library():
     lib.svo_batch_set_closed_loop.argtypes = [vp, i32, i32, f32, C.c_double]
     lib.svo_batch_get_pose.argtypes = [vp, i32, C.POINTER(f32), C.POINTER(i32)]
     lib.svo_batch_kernel_launches.argtypes = [vp]
+    i64 = C.c_int64
+    lib.svo_kitti_open.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(vp)]
+    lib.svo_kitti_close.argtypes = [vp]
+    lib.svo_kitti_close.restype = None
+    lib.svo_kitti_last_error.argtypes = [vp]
+    lib.svo_kitti_last_error.restype = C.c_char_p
+    lib.svo_kitti_info.argtypes = [vp, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32)]
+    lib.svo_kitti_read.argtypes = [vp, i64, vp, vp, i32, vp]
+    lib.svo_kitti_prefetch_start.argtypes = [vp, vp, i32, i32, i64]
+    lib.svo_kitti_next.argtypes = [vp, C.POINTER(i64), C.POINTER(vp), C.POINTER(vp), vp]
     lib.svo_batch_kernel_launches.restype = C.c_int64
     lib.svo_batch_timer_begin.argtypes = [vp]
     lib.svo_batch_timer_end.argtypes = [vp, pf]
@@ -203,9 +214,85 @@ class VoSequence:
         self.log.append(rec)
         return rec
 
+    def get_drawing(self) -> np.ndarray:
+        """FeatureTracker::get_drawing: (H, W, 3) RGB overlay of the last keyframe's tracks."""
+        w, h = C.c_int32(), C.c_int32()
+        rc = self.lib.svo_vo_get_drawing(self.h, None, 0, C.byref(w), C.byref(h))
+        if rc != 0:
+            raise SvoError(f"svo_vo_get_drawing failed ({rc}): "
+                           f"{self.lib.svo_vo_last_error(self.h).decode(errors='replace')}")
+        out = np.zeros((h.value, w.value, 3), np.uint8)
+        rc = self.lib.svo_vo_get_drawing(self.h, out.ctypes.data, out.strides[0], None, None)
+        if rc != 0:
+            raise SvoError(f"svo_vo_get_drawing failed ({rc})")
+        return out
+
     def close(self):
         if self.h:
             self.lib.svo_vo_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class KittiSource:
+    """KITTI odometry stereo frames + ground-truth poses (svo_kitti_*), the headless stand-in
+    for the reference's kitti_node (src/kitti_node.cpp:16-68)."""
+
+    def __init__(self, data_path: str, sequence: str):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.svo_kitti_open(data_path.encode(), sequence.encode(), C.byref(h))
+        if rc != 0:
+            raise SvoError(f"svo_kitti_open failed ({rc}): "
+                           f"{self.lib.svo_kitti_last_error(None).decode(errors='replace')}")
+        self.h = h
+        n, w, hh = C.c_int64(), C.c_int32(), C.c_int32()
+        self.lib.svo_kitti_info(self.h, C.byref(n), C.byref(w), C.byref(hh))
+        self.n_frames, self.width, self.height = n.value, w.value, hh.value
+        self._slab = None
+
+    def _err(self, what, rc):
+        return SvoError(f"{what} failed ({rc}): "
+                        f"{self.lib.svo_kitti_last_error(self.h).decode(errors='replace')}")
+
+    def read(self, i: int):
+        """(left, right, pose 3x4) of frame i."""
+        l = np.empty((self.height, self.width), np.uint8)
+        r = np.empty((self.height, self.width), np.uint8)
+        pose = np.zeros(12)
+        rc = self.lib.svo_kitti_read(self.h, i, l.ctypes.data, r.ctypes.data, self.width,
+                                     pose.ctypes.data)
+        if rc != 0:
+            raise self._err("svo_kitti_read", rc)
+        return l, r, pose.reshape(3, 4)
+
+    def prefetch(self, depth: int = 4, first: int = 0):
+        """Iterate (index, left, right, pose) with decoding running ahead on a worker thread
+        into a pinned ring; the arrays alias ring slots (valid for two iterations)."""
+        self._slab = capi.pinned_empty((depth, 2, self.height, self.width), np.uint8)
+        rc = self.lib.svo_kitti_prefetch_start(self.h, self._slab.ctypes.data, depth, self.width, first)
+        if rc != 0:
+            raise self._err("svo_kitti_prefetch_start", rc)
+        idx, lp, rp = C.c_int64(), C.c_void_p(), C.c_void_p()
+        pose = np.zeros(12)
+        while True:
+            rc = self.lib.svo_kitti_next(self.h, C.byref(idx), C.byref(lp), C.byref(rp), pose.ctypes.data)
+            if rc < 0:
+                raise self._err("svo_kitti_next", rc)
+            if rc == 0:
+                return
+            slot = idx.value % depth
+            assert lp.value == self._slab[slot, 0].ctypes.data
+            yield idx.value, self._slab[slot, 0], self._slab[slot, 1], pose.reshape(3, 4).copy()
+
+    def close(self):
+        if self.h:
+            self.lib.svo_kitti_close(self.h)
             self.h = None
 
     def __del__(self):

@@ -1,0 +1,94 @@
+"""CPU: the KITTI frame source (src/kitti_node.cpp:16-68 without ROS): pose file and 8-bit PNG
+pairs read by libsvo_host.so must equal what the reference's own calls give - cv2.imread(...,
+IMREAD_GRAYSCALE) for the images (:67-68) and the 12 numbers per line for the poses (:47-50).
+The PNGs are written with cv2 (zlib-compressed, adaptive filters) into a KITTI-shaped tree."""
+import os
+
+import cv2
+import numpy as np
+import pytest
+
+from stereo_vo_b200 import synth
+from tests import util
+
+
+@pytest.fixture(scope="module")
+def kitti_tree(tmp_path_factory):
+    root = tmp_path_factory.mktemp("kitti")
+    seq = "07"
+    cam = util.small_camera(421, 127)                       # odd sizes: row filters see every phase
+    os.makedirs(root / seq / "image_0")
+    os.makedirs(root / seq / "image_1")
+    os.makedirs(root / "data_odometry_poses" / "dataset" / "poses")
+    n = 7
+    poses = []
+    rng = np.random.default_rng(4)
+    frames = []
+    for i in range(n):
+        l, r = synth.stereo_frame(2, i, cam)
+        if i == 3:                                          # an RGB file: imread converts to grey
+            cv2.imwrite(str(root / seq / "image_0" / f"{i:06d}.png"), np.dstack([l, r, l]))
+        else:
+            cv2.imwrite(str(root / seq / "image_0" / f"{i:06d}.png"), l,
+                        [cv2.IMWRITE_PNG_COMPRESSION, 1 + i])
+        cv2.imwrite(str(root / seq / "image_1" / f"{i:06d}.png"), r)
+        frames.append((l, r))
+        p = np.eye(4)[:3].copy()
+        p[:, 3] = rng.normal(size=3) * i
+        p[:3, :3] += rng.normal(scale=1e-3, size=(3, 3))
+        poses.append(p)
+    with open(root / "data_odometry_poses" / "dataset" / "poses" / f"{seq}.txt", "w") as fh:
+        for p in poses:
+            fh.write(" ".join(f"{v:.12e}" for v in p.reshape(-1)) + "\n")
+        fh.write("1 2 3\n")                                 # a short line ends the sequence (:47)
+    return str(root) + "/", seq, n, poses, cam
+
+
+def test_frames_and_poses_match_the_reference_reader(kitti_tree):
+    from stereo_vo_b200 import build, hostapi
+    if build.host_needs_build():
+        build.build_host_lib()
+    root, seq, n, poses, cam = kitti_tree
+    src = hostapi.KittiSource(root, seq)
+    assert (src.n_frames, src.width, src.height) == (n, cam.width, cam.height)
+    for i in range(n):
+        l, r, p = src.read(i)
+        ref_l = cv2.imread(f"{root}{seq}/image_0/{i:06d}.png", cv2.IMREAD_GRAYSCALE)
+        ref_r = cv2.imread(f"{root}{seq}/image_1/{i:06d}.png", cv2.IMREAD_GRAYSCALE)
+        assert np.array_equal(l, ref_l), f"left {i}"
+        assert np.array_equal(r, ref_r), f"right {i}"
+        assert np.allclose(p, poses[i], rtol=0, atol=1e-11)
+    from stereo_vo_b200.capi import SvoError
+    with pytest.raises(SvoError, match="past the pose file"):
+        src.read(n)
+    src.close()
+    with pytest.raises(SvoError, match="cannot open"):
+        hostapi.KittiSource(root, "99")
+
+
+@pytest.mark.gpu
+def test_decode_ahead_ring_feeds_the_front_end(kitti_tree, svo_lib):
+    """The prefetcher thread decodes into a pinned ring while the GPU works on earlier frames:
+    every frame arrives once, in order, with the bytes of a direct read, and goes straight into
+    svo_step from the ring slot."""
+    from stereo_vo_b200 import hostapi
+    from stereo_vo_b200.capi import Engine
+    root, seq, n, poses, cam = kitti_tree
+    src = hostapi.KittiSource(root, seq)
+    direct = hostapi.KittiSource(root, seq)
+    e = Engine(cam.width, cam.height, n_seq=1)
+    seen = []
+    prev = None
+    for i, l, r, p in src.prefetch(depth=3):
+        dl, dr, dp = direct.read(i)
+        assert np.array_equal(l, dl) and np.array_equal(r, dr) and np.allclose(p, dp)
+        if prev is not None:                     # the previous slot is still intact
+            assert np.array_equal(prev[1], direct.read(prev[0])[0])
+        res = e.step([0], [l], [r])
+        assert res["n_corners"][0] > 4
+        seen.append(i)
+        prev = (i, l)
+    assert seen == list(range(n))
+    e.close()
+    src.close()
+    direct.close()

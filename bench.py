@@ -256,6 +256,8 @@ def run_ours(args, rank, world, local_rank):
                        pipeline=True, closed_loop=False):
         """n_seq sequences (the first n_seq of this rank's slab) through hostapi.Batch."""
         batch = hostapi.Batch(W, H, n_seq, groups, cam, device=local_rank, closed_loop=closed_loop)
+        if blocking_sync:
+            batch.set_blocking_sync(True)
         sub = slab[:n_seq]
         dptr = None
         base = sub.ctypes.data
@@ -315,9 +317,12 @@ def run_ours(args, rank, world, local_rank):
         return out
 
     K, Wm = args.steps, args.warmup
+    cores_per_rank = max(1, total_cores // max(world, 1))
     if args.groups <= 0:
-        cores_per_rank = max(1, total_cores // max(world, 1))
-        args.groups = min(4, cores_per_rank)
+        # one host worker per engine group + the submitting thread: leave a core for the latter
+        args.groups = max(1, min(4, cores_per_rank - 1))
+    # spinning waits need a core per thread; with fewer (8 ranks on 32 cores) the waits sleep
+    blocking_sync = args.sync == "block" or (args.sync == "auto" and cores_per_rank < args.groups + 2)
     dev = throughput_leg(S, True, K, Wm, args.groups, args.min_seconds)
     e2e = dev if args.skip_e2e else throughput_leg(S, False, K, Wm, args.groups, args.min_seconds)
     # closed loop: the pose step (PnP-RANSAC) on the GPU inside the loop instead of teacher poses
@@ -471,6 +476,7 @@ def run_ours(args, rank, world, local_rank):
                        "parallelism": f"{world} GPU(s) x {S} sequences in {args.groups} engine groups "
                                       "(one CUDA stream + host worker each), no collective",
                        "host_cores": total_cores, "rank0_cpu_binding": numa_bind,
+                       "gpu_wait": "blocking (cudaEventBlockingSync)" if blocking_sync else "spin",
                        "host": "C++ svo::BatchFrontEnd (libsvo_host.so) via "
                                + ("svo_batch_submit/wait, 2 steps in flight" if args.pipeline
                                   else "svo_batch_step")
@@ -737,6 +743,9 @@ def main():
                     help="engine groups (CUDA streams + host workers) the sequences of a GPU are "
                          "split into; 0 = 4, or fewer when the ranks of this node have less than "
                          "4 host cores each")
+    ap.add_argument("--sync", default="auto", choices=["auto", "spin", "block"],
+                    help="how engine calls wait for the GPU: spin (lowest latency), block (sleep on an "
+                         "interrupt), auto = block when a rank has fewer host cores than threads")
     ap.add_argument("--no-bind", action="store_true",
                     help="multi-GPU runs: do not pin the rank to the host cores next to its GPU")
     ap.add_argument("--no-pipeline", dest="pipeline", action="store_false",

@@ -118,6 +118,9 @@ class BatchFrontEnd {
     const float* pose(int s) const { return seq_[s].hmat; }
     int32_t n_inliers(int s) const { return res(s).n_inliers; }
 
+    // waits of every engine group sleep instead of spinning (svo_set_blocking_sync)
+    void set_blocking_sync(bool on);
+
     int64_t kernel_launches() const;
     // device-side stopwatch over all groups: begin() synchronises every engine stream and
     // starts a CUDA-event timer on each; end() returns the longest elapsed time (ms)

@@ -98,6 +98,11 @@ SVO_API float svo_last_gpu_ms(const svo_engine* e);
 /* ms[0] input copies, ms[1] kernels, ms[2] result copy of the last call (CUDA events) */
 SVO_API int svo_last_timing(const svo_engine* e, float ms[3]);
 
+/* How the calls of this engine wait for the GPU: 0 (default) spins on the stream (lowest
+ * latency), 1 sleeps until the device raises an interrupt (cudaEventBlockingSync) - for hosts
+ * with more driver threads than cores. No effect on results. */
+SVO_API int svo_set_blocking_sync(svo_engine* e, int32_t on);
+
 /* per-kernel profiling: when on, every kernel group of a call is bracketed by CUDA events on
  * the engine stream; totals (ms, launches of the group) accumulate per slot until reset by the
  * next svo_set_profiling() call. Slot names: svo_profile_name(0 .. svo_profile_slots()-1). */

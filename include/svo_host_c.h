@@ -118,6 +118,8 @@ SVO_API int svo_batch_set_closed_loop(svo_batch* b, int32_t on, int32_t iteratio
 /* pose of sequence seq's last keyframe (row-major camera->world hmat, :130-134) and the inlier
  * count of the pose step of the last step (0 unless it was a closed-loop keyframe) */
 SVO_API int svo_batch_get_pose(svo_batch* b, int32_t seq, float hmat[16], int32_t* n_inliers);
+/* svo_set_blocking_sync for every engine group */
+SVO_API int svo_batch_set_blocking_sync(svo_batch* b, int32_t on);
 SVO_API int64_t svo_batch_kernel_launches(const svo_batch* b);
 SVO_API int svo_batch_timer_begin(svo_batch* b);
 SVO_API int svo_batch_timer_end(svo_batch* b, float* ms);

@@ -55,7 +55,7 @@ EXPORTS = [
     "svo_step", "svo_prefetch", "svo_step_device", "svo_set_right", "svo_device_can_read", "svo_keyframe", "svo_keyframe_tracked", "svo_step_keyframe", "svo_tracker_set",
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
-    "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac", "svo_reprojection_evaluate", "svo_draw_track",
+    "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac", "svo_reprojection_evaluate", "svo_draw_track", "svo_set_blocking_sync",
 ]
 
 _lib = None
@@ -117,6 +117,7 @@ def load_library(path: Optional[str] = None):
     lib.svo_tracker_set.argtypes = [vp, i32, vp, vp, vp, vp]
     lib.svo_reprojection_evaluate.argtypes = [vp, i32, vp, vp, vp, i32, vp, i32, vp, C.c_double,
                                               C.c_double, C.c_double, vp, vp, vp]
+    lib.svo_set_blocking_sync.argtypes = [vp, i32]
     lib.svo_draw_track.argtypes = [vp, vp, i32, vp, vp, i32, vp, i32]
     lib.svo_pnp_ransac.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, i32, f32, C.c_double, vp, vp, vp]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]

@@ -101,6 +101,8 @@ struct svo_engine {
     cudaStream_t st_det = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool split_streams = true;        // SVO_SPLIT_STREAMS=0: one stream
+    bool blocking_sync = false;       // svo_set_blocking_sync
+    cudaEvent_t ev_block = nullptr;   // cudaEventBlockingSync: waits sleep instead of spinning
     float* d_eig = nullptr;
     unsigned int* d_eig_max = nullptr;
     unsigned long long* d_cand = nullptr;
@@ -698,6 +700,16 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
     return cudaSuccess;
 }
 
+// Wait until everything queued on the engine stream is done. Spinning (the CUDA default) has the
+// lowest latency; with more driver threads than host cores (8 ranks x 4 engine groups on a
+// 32-core box) the spinning threads starve each other and the thread that should launch the
+// next kernels: svo_set_blocking_sync() makes the wait sleep on an interrupt instead.
+cudaError_t wait_stream(svo_engine* e) {
+    if (!e->blocking_sync) return cudaStreamSynchronize(e->st);
+    SVO_CUDA_OK(cudaEventRecord(e->ev_block, e->st));
+    return cudaEventSynchronize(e->ev_block);
+}
+
 int finish_timing(svo_engine* e) {
     float a = 0, b = 0, c = 0;
     cudaEventElapsedTime(&a, e->ev[0], e->ev[1]);
@@ -877,7 +889,7 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
     ECUDA(e, cudaEventRecord(e->ev[2], e->st));
     ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_out, out_bytes, cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
-    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, wait_stream(e));
     finish_timing(e);
     int rc = SVO_OK;
     const int mc = e->p.max_corners, mf = e->p.max_features;
@@ -1062,6 +1074,7 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(cudaStreamCreateWithFlags(&e->st_det, cudaStreamNonBlocking));
     CCHK(cudaEventCreateWithFlags(&e->ev_fork, cudaEventDisableTiming));
     CCHK(cudaEventCreateWithFlags(&e->ev_join, cudaEventDisableTiming));
+    CCHK(cudaEventCreateWithFlags(&e->ev_block, cudaEventDisableTiming | cudaEventBlockingSync));
     if (const char* v = getenv("SVO_SPLIT_STREAMS")) e->split_streams = atoi(v) != 0;
     for (auto& pfe : e->pf) CCHK(cudaEventCreateWithFlags(&pfe.done, cudaEventDisableTiming));
     for (int i = 0; i < 4; ++i) CCHK(cudaEventCreate(&e->ev[i]));
@@ -1173,6 +1186,7 @@ void svo_destroy(svo_engine* e) {
     if (e->st_det) cudaStreamDestroy(e->st_det);
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
+    if (e->ev_block) cudaEventDestroy(e->ev_block);
     if (e->st) cudaStreamDestroy(e->st);
     delete e;
 }
@@ -1188,6 +1202,12 @@ float svo_last_gpu_ms(const svo_engine* e) { return e ? e->last_ms[1] : 0.f; }
 int svo_last_timing(const svo_engine* e, float ms[3]) {
     if (!e || !ms) return SVO_ERR_INVALID;
     ms[0] = e->last_ms[0]; ms[1] = e->last_ms[1]; ms[2] = e->last_ms[2];
+    return SVO_OK;
+}
+
+int svo_set_blocking_sync(svo_engine* e, int32_t on) {
+    if (!e) return SVO_ERR_INVALID;
+    e->blocking_sync = on != 0;
     return SVO_OK;
 }
 
@@ -1289,7 +1309,7 @@ int svo_good_features_to_track(svo_engine* e, int32_t seq, const uint8_t* img, i
     ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_corners + (size_t)seq * e->p.max_corners,
                              (size_t)e->p.max_corners * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
-    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, wait_stream(e));
     finish_timing(e);
     if (hdr[1] > e->max_cand) return fail(e, SVO_ERR_CAPACITY, "NMS candidate buffer overflow: raise max_candidates");
     *out_n = hdr[0];
@@ -1392,7 +1412,7 @@ static int keyframe_impl(svo_engine* e, int n, const int32_t* seqs, const svo_fl
     ECUDA(e, cudaEventRecord(e->ev[2], e->st));
     ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_out, (size_t)n * e->key_block, cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
-    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, wait_stream(e));
     finish_timing(e);
     for (int i = 0; i < n; ++i) {
         const unsigned char* o = e->h_out + (size_t)i * e->key_block;
@@ -1530,7 +1550,7 @@ static int dense_impl(svo_engine* e, int n, const int32_t* seqs, int16_t* const*
                                        e->d_dense + (size_t)seqs[i] * map, (size_t)W * sizeof(int16_t),
                                        (size_t)W * sizeof(int16_t), H, cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
-    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, wait_stream(e));
     finish_timing(e);
     return SVO_OK;
 }
@@ -1608,7 +1628,7 @@ int svo_pnp_ransac(svo_engine* e, int32_t n, const svo_float3* world, const svo_
     ECUDA(e, cudaMemcpyAsync(results, e->d_pnp_res, (size_t)n * sizeof(SvoPnpResult), cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaMemcpyAsync(inliers, e->d_pnp_inl, (size_t)n * mf * sizeof(int), cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
-    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, wait_stream(e));
     finish_timing(e);
     return SVO_OK;
 }
@@ -1666,7 +1686,7 @@ int svo_reprojection_evaluate(svo_engine* e, int32_t n_obs, const int32_t* pose_
     if (jac_pose) ECUDA(e, cudaMemcpyAsync(jac_pose, d_jp, (size_t)n_obs * 14 * 8, cudaMemcpyDeviceToHost, e->st));
     if (jac_point) ECUDA(e, cudaMemcpyAsync(jac_point, d_jx, (size_t)n_obs * 6 * 8, cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
-    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, wait_stream(e));
     finish_timing(e);
     return SVO_OK;
 }
@@ -1831,7 +1851,7 @@ int svo_tracker_track(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pi
     SvoTrackStats st;
     ECUDA(e, cudaMemcpyAsync(&st, e->d_stats + seq, sizeof st, cudaMemcpyDeviceToHost, e->st));
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
-    ECUDA(e, cudaStreamSynchronize(e->st));
+    ECUDA(e, wait_stream(e));
     finish_timing(e);
     *av_parallax = st.av_parallax;
     *percent_lost = st.percent_lost;

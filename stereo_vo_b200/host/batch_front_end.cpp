@@ -545,6 +545,10 @@ const svo_float2* BatchFrontEnd::new_features(int s) const { return &new_feats_[
 const int16_t* BatchFrontEnd::disp16(int s) const { return &disp16_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
 const int32_t* BatchFrontEnd::valid_idx(int s) const { return &valid_idx_[cur_slot_][(size_t)s * opt_.params.max_corners]; }
 
+void BatchFrontEnd::set_blocking_sync(bool on) {
+    for (auto& g : groups_) svo_set_blocking_sync(g->e, on ? 1 : 0);
+}
+
 int64_t BatchFrontEnd::kernel_launches() const {
     int64_t n = 0;
     for (auto& g : groups_) n += svo_kernel_launches(g->e);

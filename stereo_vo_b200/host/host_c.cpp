@@ -299,6 +299,12 @@ int svo_batch_get_pose(svo_batch* b, int32_t seq, float hmat[16], int32_t* n_inl
     return SVO_OK;
 }
 
+int svo_batch_set_blocking_sync(svo_batch* b, int32_t on) {
+    if (!b) return SVO_ERR_INVALID;
+    b->fe->set_blocking_sync(on != 0);
+    return SVO_OK;
+}
+
 int64_t svo_batch_kernel_launches(const svo_batch* b) { return b ? b->fe->kernel_launches() : 0; }
 
 int svo_batch_timer_begin(svo_batch* b) {

@@ -89,6 +89,7 @@ def load_library():
     lib.svo_batch_get_keyframe.argtypes = [vp, i32, C.POINTER(i32), vp, vp, C.POINTER(i32), vp]
     lib.svo_batch_set_closed_loop.argtypes = [vp, i32, i32, f32, C.c_double]
     lib.svo_batch_get_pose.argtypes = [vp, i32, C.POINTER(f32), C.POINTER(i32)]
+    lib.svo_batch_set_blocking_sync.argtypes = [vp, i32]
     lib.svo_batch_kernel_launches.argtypes = [vp]
     i64 = C.c_int64
     lib.svo_kitti_open.argtypes = [C.c_char_p, C.c_char_p, C.POINTER(vp)]
@@ -464,6 +465,9 @@ class Batch:
 
     def set_profiling(self, on: bool):
         self.lib.svo_batch_set_profiling(self.h, 1 if on else 0)
+
+    def set_blocking_sync(self, on: bool):
+        self.lib.svo_batch_set_blocking_sync(self.h, 1 if on else 0)
 
     def get_profile(self) -> dict:
         lib = capi.load_library()

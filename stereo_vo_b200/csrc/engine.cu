@@ -620,6 +620,11 @@ cudaError_t push_calls(svo_engine* e, int n) {
     return cudaGetLastError();
 }
 
+// levels 1.. of the current frames' pyramids (one launch per level, dependent launches)
+cudaError_t launch_pyramid(svo_engine* e, const SvoSeqCall* dc, int n, cudaStream_t st) {
+    return svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, st);
+}
+
 // pyramid + detection for the listed sequences (current frames already uploaded)
 cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t st = nullptr) {
     if (!st) st = e->st;
@@ -629,7 +634,7 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t 
     e->launches += 1;
     if (with_pyramid) {
         ProfScope ps(e, P_PYR, st);
-        SVO_CUDA_OK(svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, st));
+        SVO_CUDA_OK(launch_pyramid(e, dc, n, st));
         e->launches += e->lay.n_levels - 1;
     }
     e->cs_epoch = (e->cs_epoch % 0x3fffffffu) + 1u;    // tags this launch's verdict words
@@ -833,7 +838,7 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
         ECUDA(e, cudaStreamWaitEvent(e->st_det, e->ev_fork, 0));
         ECUDA(e, launch_detect(e, n, false, e->st_det));
         ECUDA(e, cudaEventRecord(e->ev_join, e->st_det));
-        ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), n, e->st));
+        ECUDA(e, launch_pyramid(e, dev_call_slot(e), n, e->st));
         e->launches += e->lay.n_levels - 1;
         ECUDA(e, launch_track(e, n, max_feat, 1, true, e->ev_join));
     } else {
@@ -1821,7 +1826,7 @@ int svo_tracker_init(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pit
     fill_call(e, hc[0], seq);
     ECUDA(e, upload_left(e, hc[0], img, pitch, false));
     ECUDA(e, push_and_ingest(e, 1));
-    ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), 1, e->st));
+    ECUDA(e, launch_pyramid(e, dev_call_slot(e), 1, e->st));
     e->launches += e->lay.n_levels - 1;
     // single-sequence view of the [n][max_features] arrays
     int32_t s = seq, c = n;
@@ -1844,7 +1849,7 @@ int svo_tracker_track(svo_engine* e, int32_t seq, const uint8_t* img, int32_t pi
     ECUDA(e, upload_left(e, hc[0], img, pitch, false));
     ECUDA(e, cudaEventRecord(e->ev[1], e->st));
     ECUDA(e, push_and_ingest(e, 1));
-    ECUDA(e, svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dev_call_slot(e), 1, e->st));
+    ECUDA(e, launch_pyramid(e, dev_call_slot(e), 1, e->st));
     e->launches += e->lay.n_levels - 1;
     ECUDA(e, launch_track(e, 1, s.n_feat, flow_back ? 1 : 0, false));
     ECUDA(e, cudaEventRecord(e->ev[2], e->st));

@@ -14,6 +14,8 @@
 // reproject_q: w = pose * Q * [x, y, d, 1]^T, point = w.xyz / w.w for d > 0, compacted in
 // input order (:178-207). dedupe_new_features: keep detection i iff no inlier within
 // min_feature_distance (f32 sqrt), ordered.
+#include <stdlib.h>
+
 #include "svo_common.cuh"
 
 namespace {
@@ -133,6 +135,148 @@ stereo_bm_sparse_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_
     int pp = sad[mind + 1], nn = sad[mind - 1];
     int den = pp + nn - 2 * sad[mind] + abs(pp - nn);
     int v = (nd - mind - 1) * 256 + (den != 0 ? (pp - nn) * 256 / den : 0) + 15;
+    *outp = (short)(v >> 4);
+}
+
+// ---------------------------------------------------------------------------------------
+// The same evaluation specialised for the reference's StereoBM::create(48, 21) (cap <= 63):
+// raw patches arrive as aligned words, the 48 SADs run on packed bytes (vabsdiff4 with
+// accumulate, as in stereo_dense.cu), winner / uniqueness are warp reductions instead of a
+// serial tail. Same integers as the generic kernel above, ~3x fewer instructions.
+constexpr int FS_ND = 48, FS_WIN = 21, FS_RAD = 10, FS_RW = FS_WIN + FS_ND - 1;   // 68
+constexpr int FS_RAWH = FS_WIN + 2;                                              // 23
+constexpr int FS_LP = 32, FS_RP = 80;        // byte pitch of the staged raw rows (8 / 20 words)
+constexpr int FS_PLP = 24, FS_PRP = 72;      // byte pitch of the prefiltered rows (6 / 18 words)
+
+__device__ __forceinline__ unsigned sad4_acc(unsigned a, unsigned b, unsigned c) {
+    unsigned d;
+    asm("vabsdiff4.u32.u32.u32.add %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+__global__ void __launch_bounds__(SB_THREADS)
+stereo_bm_sparse_48_21_kernel(const uint8_t* __restrict__ pyr, SvoPyrLayout lay, size_t seq_stride,
+                              const uint8_t* __restrict__ right, size_t right_stride,
+                              const float2* __restrict__ pts, int pts_stride,
+                              short* __restrict__ disp16, SvoStereoParams sp,
+                              const SvoSeqCall* __restrict__ call) {
+    __shared__ __align__(16) unsigned s_rawL[FS_RAWH * FS_LP / 4];
+    __shared__ __align__(16) unsigned s_rawR[FS_RAWH * FS_RP / 4];
+    __shared__ __align__(16) unsigned s_PL[FS_WIN * FS_PLP / 4];
+    __shared__ __align__(16) unsigned s_PR[FS_WIN * FS_PRP / 4];
+    __shared__ int s_sadv[FS_ND + 2];
+    __shared__ int s_texv;
+    const SvoSeqCall cd = call[blockIdx.y];
+    const int pi = blockIdx.x;
+    if (pi >= cd.n_pts) return;
+    const SvoLevel l0 = lay.lvl[0];
+    const int W = l0.w, H = l0.h, pitch = l0.pitch;
+    const uint8_t* __restrict__ L =
+        pyr + (size_t)cd.seq * seq_stride + (size_t)cd.cur_slot * lay.slot_bytes + l0.off;
+    const uint8_t* __restrict__ R = right + (size_t)cd.seq * right_stride;
+    const float2 p = pts[(size_t)cd.seq * pts_stride + pi];
+    short* outp = disp16 + (size_t)cd.seq * pts_stride + pi;
+    const int x = (int)p.x, y = (int)p.y;     // float -> int truncation, image_processor.cpp:193
+    const int cap = sp.cap;
+    const short FILTERED = (short)(-16);
+    const int tid = threadIdx.x;
+    if (x < FS_ND - 1 + FS_RAD || x >= W - FS_RAD || y < FS_RAD || y >= H - FS_RAD) {
+        if (tid == 0) *outp = FILTERED;
+        return;
+    }
+    // ---- raw patches as aligned words. Column of raw index c: left xl0 + c, right xr0 + c
+    // (xr0 may be -1: that column only feeds the prefilter of image column 0, which is `cap`
+    // without looking; the staged words start at column max(xr0, 0) rounded down to 4)
+    const int yl0 = y - FS_RAD - 1, xl0 = x - FS_RAD - 1, xr0 = x - FS_RAD - (FS_ND - 1) - 1;
+    const int axl = xl0 & ~3, axr = max(xr0, 0) & ~3;
+    const int offL = xl0 - axl, offR = xr0 - axr;           // offR may be -1
+    for (int i = tid; i < FS_RAWH * (FS_LP / 4 + FS_RP / 4); i += SB_THREADS) {
+        const int r = i / (FS_LP / 4 + FS_RP / 4), k = i - r * (FS_LP / 4 + FS_RP / 4);
+        int gy = yl0 + r;
+        gy = gy < 0 ? 1 : (gy > H - 1 ? H - 2 : gy);
+        if (k < FS_LP / 4)
+            s_rawL[r * (FS_LP / 4) + k] = __ldg(reinterpret_cast<const unsigned*>(L + (size_t)gy * pitch + axl) + k);
+        else
+            s_rawR[r * (FS_RP / 4) + (k - FS_LP / 4)] =
+                __ldg(reinterpret_cast<const unsigned*>(R + (size_t)gy * pitch + axr) + (k - FS_LP / 4));
+    }
+    for (int i = tid; i < FS_WIN * FS_PLP / 4; i += SB_THREADS) s_PL[i] = 0u;
+    for (int i = tid; i < FS_WIN * FS_PRP / 4; i += SB_THREADS) s_PR[i] = 0u;
+    if (tid == 0) s_texv = 0;
+    __syncthreads();
+    // ---- XSOBEL prefilter (cap), bytes
+    const unsigned char* rawL = reinterpret_cast<const unsigned char*>(s_rawL);
+    const unsigned char* rawR = reinterpret_cast<const unsigned char*>(s_rawR);
+    unsigned char* PL = reinterpret_cast<unsigned char*>(s_PL);
+    unsigned char* PR = reinterpret_cast<unsigned char*>(s_PR);
+    const bool odd_last = (H & 1);
+    auto prefilter = [&](const unsigned char* raw, int rp, int off, int r, int c, int gx, int gy) -> int {
+        if (gx == 0 || gx == W - 1 || (odd_last && gy == H - 1)) return cap;
+        const unsigned char* a = raw + r * rp + off + c;     // row gy-1, col gx-1
+        const unsigned char* b = a + rp;
+        const unsigned char* d = b + rp;
+        int v = ((int)a[2] - (int)a[0]) + 2 * ((int)b[2] - (int)b[0]) + ((int)d[2] - (int)d[0]);
+        v = min(max(v, -cap), cap);
+        return v + cap;
+    };
+    int tex = 0;
+    for (int i = tid; i < FS_WIN * FS_WIN; i += SB_THREADS) {
+        const int r = i / FS_WIN, c = i - r * FS_WIN;
+        const int v = prefilter(rawL, FS_LP, offL, r, c, x - FS_RAD + c, y - FS_RAD + r);
+        PL[r * FS_PLP + c] = (unsigned char)v;
+        tex += abs(v - cap);
+    }
+    for (int i = tid; i < FS_WIN * FS_RW; i += SB_THREADS) {
+        const int r = i / FS_RW, c = i - r * FS_RW;
+        PR[r * FS_PRP + c] = (unsigned char)prefilter(rawR, FS_RP, offR, r, c,
+                                                      x - FS_RAD - (FS_ND - 1) + c, y - FS_RAD + r);
+    }
+    tex = __reduce_add_sync(FULL, tex);
+    if ((tid & 31) == 0) atomicAdd(&s_texv, tex);
+    __syncthreads();
+    // ---- SAD(D), D = tid < 48: 21 rows x (5 words + 1 byte), right operand at byte shift 47 - D
+    if (tid < FS_ND) {
+        const int shift = FS_ND - 1 - tid;
+        const unsigned sh = (shift & 3) * 8;
+        unsigned sad = 0;
+#pragma unroll 3
+        for (int r = 0; r < FS_WIN; ++r) {
+            const unsigned* lw = s_PL + r * (FS_PLP / 4);
+            const unsigned* rw = s_PR + r * (FS_PRP / 4) + (shift >> 2);
+            unsigned w[7];
+#pragma unroll
+            for (int k = 0; k < 7; ++k) w[k] = (k + (shift >> 2) < FS_PRP / 4) ? rw[k] : 0u;
+#pragma unroll
+            for (int k = 0; k < 5; ++k) sad = sad4_acc(lw[k], __funnelshift_r(w[k], w[k + 1], sh), sad);
+            sad = sad4_acc(lw[5] & 0xffu, __funnelshift_r(w[5], w[6], sh) & 0xffu, sad);
+        }
+        s_sadv[1 + shift] = (int)sad;          // internal order d = 47 - D
+    }
+    __syncthreads();
+    // ---- winner (first minimum in internal order), texture, uniqueness, sub-pixel: warp 0
+    if (tid >= 32) return;
+    int* sad = s_sadv + 1;
+    const int d0 = tid, d1 = tid + 32;
+    const int v0 = sad[d0], v1 = d1 < FS_ND ? sad[d1] : 0x7fffffff;
+    // key = sad * 64 + d: the minimum key is the first minimum (sad <= 441 * 126 < 2^16)
+    unsigned key = min((unsigned)v0 * 64u + (unsigned)d0,
+                       d1 < FS_ND ? (unsigned)v1 * 64u + (unsigned)d1 : 0xffffffffu);
+    key = __reduce_min_sync(FULL, key);
+    const int mind = (int)(key & 63u), minsad = (int)(key >> 6);
+    bool reject = s_texv < sp.texture;
+    if (sp.uniq > 0) {
+        const int thresh = minsad + (minsad * sp.uniq / 100);
+        const bool hit = ((d0 < mind - 1 || d0 > mind + 1) && v0 <= thresh) ||
+                         (d1 < FS_ND && (d1 < mind - 1 || d1 > mind + 1) && v1 <= thresh);
+        reject |= __any_sync(FULL, hit);
+    }
+    if (tid != 0) return;
+    if (reject) { *outp = FILTERED; return; }
+    sad[-1] = sad[1];
+    sad[FS_ND] = sad[FS_ND - 2];
+    const int pp = sad[mind + 1], nn = sad[mind - 1];
+    const int den = pp + nn - 2 * sad[mind] + abs(pp - nn);
+    const int v = (FS_ND - mind - 1) * 256 + (den != 0 ? (pp - nn) * 256 / den : 0) + 15;
     *outp = (short)(v >> 4);
 }
 
@@ -316,8 +460,13 @@ cudaError_t svo_launch_stereo_bm_sparse(const uint8_t* pyr, const SvoPyrLayout& 
                                         short* disp16, SvoStereoParams sp, int max_pts,
                                         const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
     if (max_pts <= 0) return cudaSuccess;
-    stereo_bm_sparse_kernel<<<dim3(max_pts, n_call), SB_THREADS, stereo_smem_bytes(sp), st>>>(
-        pyr, lay, seq_stride, right, right_stride, pts, pts_stride, disp16, sp, d_call);
+    static const bool generic_only = getenv("SVO_STEREO_GENERIC") && atoi(getenv("SVO_STEREO_GENERIC")) != 0;
+    if (sp.ndisp == FS_ND && sp.win == FS_WIN && sp.cap >= 1 && sp.cap <= 63 && !generic_only)
+        stereo_bm_sparse_48_21_kernel<<<dim3(max_pts, n_call), SB_THREADS, 0, st>>>(
+            pyr, lay, seq_stride, right, right_stride, pts, pts_stride, disp16, sp, d_call);
+    else
+        stereo_bm_sparse_kernel<<<dim3(max_pts, n_call), SB_THREADS, stereo_smem_bytes(sp), st>>>(
+            pyr, lay, seq_stride, right, right_stride, pts, pts_stride, disp16, sp, d_call);
     return cudaGetLastError();
 }
 

@@ -106,3 +106,24 @@ def test_dedupe_matches_oracle(eng, oracle):
     assert np.array_equal(out, det[ref])
     out, keep = e.dedupe(det, np.zeros((0, 2), np.float32), 30.0)
     assert np.array_equal(keep, np.arange(300))
+
+
+@pytest.mark.parametrize("ndisp,win", [(64, 15), (32, 9), (48, 11)])
+def test_other_stereo_bm_parameters(eng, ndisp, win):
+    """StereoBM::create(ndisp, win) other than the reference's (48, 21): the generic kernel (the
+    reference's parameters run a specialised one). Same bar: every probed disparity equals
+    cv2's dense map there."""
+    import cv2
+    w, h = 640, 480
+    left = util.stress_image(h, w, 9)
+    right = util.shifted(left, 13)
+    e = eng(w, h, max_features=3000, max_corners=3000, num_disparities=ndisp, sad_window=win)
+    rng = np.random.default_rng(ndisp + win)
+    pts = np.stack([rng.integers(0, w, 3000), rng.integers(0, h, 3000)], 1).astype(np.float32)
+    pose = np.eye(4, dtype=np.float32)
+    f, cx, cy, b = synth.KITTI00.f32()
+    _, _, _, d16 = e.triangulate_stereo(left, right, pts, pose, f, cx, cy, b)
+    ref16 = cv2.StereoBM_create(ndisp, win).compute(left, right)
+    want = ref16[pts[:, 1].astype(int), pts[:, 0].astype(int)]
+    assert np.array_equal(d16, want), f"{(d16 != want).sum()} of {len(want)} disparities differ"
+    assert (d16 > 0).sum() > 300

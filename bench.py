@@ -457,8 +457,11 @@ def run_ours(args, rank, world, local_rank):
                     "compulsory_bytes_per_step": compulsory,
                     "ceiling_frames_per_s": h2d_gbs * 1e9 / (compulsory / S),
                     "frac_of_ceiling": (S / (e2e_step_ms * 1e-3)) / (h2d_gbs * 1e9 / (compulsory / S)),
-                    "note": "the e2e leg is bound by the host->device link: every frame must "
-                            "deliver its left image and every keyframe its right image"}
+                    "note": "ceiling = measured H2D rate / compulsory bytes per frame (every frame "
+                            "must deliver its left image, every keyframe its right image); "
+                            + ("the e2e leg is link-bound" if in_bytes / (e2e_step_ms * 1e-3) / 1e9 / h2d_gbs > 0.75
+                               else "the e2e leg is NOT link-bound: copies run under the kernels, the "
+                                    "gap to `value` is the ingest of host frames + on-demand right images")}
         extras = None
         if world == 1 and not args.skip_extras:
             extras = run_extras(local_rank)

@@ -335,6 +335,36 @@ SVO_API int svo_draw_track(svo_engine* e, const uint8_t* image, int32_t pitch, c
 SVO_API int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_float2* feats,
                     const uint64_t* ids, const int32_t* counts);
 
+/* ---- allocation-free dedupe ------------------------------------------------------------------ */
+/* NO COUNTERPART IN THE REFERENCE: this entry point was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid allocation). It is svo_dedupe() - same rule, same fp32
+ * arithmetic, same outputs in the same order - without an engine and without any allocation:
+ * no cudaMalloc / cudaFree / cudaHostAlloc, no staging copy; one memset and one kernel are
+ * queued on `stream` (a cudaStream_t, NULL = the default stream).
+ *   device        CUDA device to run on (made current), or < 0 for the caller's current device
+ *   det, tracked  n_det detections / n_tracked tracked points; out_xy (may be NULL),
+ *                 out_keep_idx (may be NULL): room for n_det entries; out_n: one int32.
+ *                 EVERY array is memory the device can dereference - device memory
+ *                 (svo_device_alloc, cudaMalloc) or pinned host memory (svo_host_alloc); a
+ *                 pageable host pointer is rejected with SVO_ERR_INVALID.
+ *   wait          nonzero: synchronise `stream` before returning; zero: results are valid once
+ *                 the caller has synchronised the stream (or the graph launch has completed)
+ *   err, err_cap  optional buffer that receives a message when the return value is not SVO_OK
+ * Limit: n_det <= SVO_DEDUPE_STATIC_MAX_DET; more is refused with SVO_ERR_CAPACITY (nothing is
+ * queued). The scratch (one ticket word + one flag per detection, 65 792 bytes) is a static
+ * device array inside libsvo.so: every GPU that loads the library holds it until the process
+ * exits, and every call on a device shares it. The call clears what must start at zero itself;
+ * calls that OVERLAP on one GPU (different streams without an event between them, parallel
+ * graph branches) race on the scratch and give undefined output - order them.
+ * The first call on a device looks the array's device address up (cudaGetSymbolAddress): make
+ * that call outside stream capture. */
+#define SVO_DEDUPE_STATIC_MAX_DET 16384
+SVO_API int svo_dedupe_static(int32_t device, const svo_float2* det, int32_t n_det,
+                              const svo_float2* tracked, int32_t n_tracked, float min_distance,
+                              svo_float2* out_xy, int32_t* out_keep_idx, int32_t* out_n,
+                              void* stream, int32_t wait, char* err, size_t err_cap);
+
 /* device allocation helpers for callers that keep frames resident (bench kernel-only leg) */
 SVO_API int svo_device_alloc(svo_engine* e, size_t bytes, void** out);
 SVO_API int svo_device_free(svo_engine* e, void* p);

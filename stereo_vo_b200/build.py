@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsvo.so")
 SOURCES = ["engine.cu", "pyr_down.cu", "corner_score.cu", "sort_candidates.cu",
            "greedy_select.cu", "stereo.cu", "stereo_dense.cu", "lk_track.cu", "track_filter.cu",
-           "pnp_ransac.cu", "reprojection_factor.cu", "draw_track.cu"]
+           "pnp_ransac.cu", "reprojection_factor.cu", "draw_track.cu", "dedupe_static.cu"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "--fmad=false", "-gencode", "arch=compute_100a,code=sm_100a",
               "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
               "--threads", "0"]

@@ -56,6 +56,7 @@ EXPORTS = [
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
     "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac", "svo_reprojection_evaluate", "svo_draw_track", "svo_set_blocking_sync",
+    "svo_dedupe_static",
 ]
 
 _lib = None
@@ -120,6 +121,8 @@ def load_library(path: Optional[str] = None):
     lib.svo_set_blocking_sync.argtypes = [vp, i32]
     lib.svo_draw_track.argtypes = [vp, vp, i32, vp, vp, i32, vp, i32]
     lib.svo_pnp_ransac.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, i32, f32, C.c_double, vp, vp, vp]
+    lib.svo_dedupe_static.argtypes = [i32, vp, i32, vp, i32, f32, vp, vp, vp, vp, i32, C.c_char_p,
+                                      C.c_size_t]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
     lib.svo_device_free.argtypes = [vp, vp]
     lib.svo_device_upload.argtypes = [vp, vp, vp, C.c_size_t]
@@ -169,6 +172,29 @@ def pinned_empty(shape, dtype=np.uint8) -> np.ndarray:
 
 
 _PINNED: dict = {}
+
+DEDUPE_STATIC_MAX_DET = 16384      # SVO_DEDUPE_STATIC_MAX_DET of include/svo_c.h
+
+
+def dedupe_static(det, n_det: int, tracked, n_tracked: int, min_distance: float, out_xy, out_keep,
+                  out_n, device: int = 0, stream: int = 0, wait: bool = True) -> None:
+    """svo_dedupe_static: the allocation-free variant of svo_dedupe. Every array argument is a
+    numpy view on PINNED memory (pinned_empty) or an integer device address; nothing is staged
+    or allocated by the call. Raises SvoError with the library's message on failure."""
+    lib = load_library()
+
+    def addr(a):
+        if a is None:
+            return None
+        return C.c_void_p(a) if isinstance(a, int) else _ptr(a)
+    err = C.create_string_buffer(256)
+    rc = lib.svo_dedupe_static(device, addr(det), n_det, addr(tracked), n_tracked,
+                               float(min_distance), addr(out_xy), addr(out_keep), addr(out_n),
+                               C.c_void_p(stream) if stream else None, 1 if wait else 0, err, 256)
+    if rc != 0:
+        e = SvoError(err.value.decode(errors="replace") or f"svo_dedupe_static failed ({rc})")
+        e.code = rc
+        raise e
 
 
 class Engine:

@@ -18,6 +18,18 @@
  *  - images are 8-bit grey, row-major, `pitch` bytes per row, size fixed at svo_create().
  *  - there is no CPU fallback: if no CUDA device is usable every call fails with
  *    SVO_ERR_CUDA.
+ *
+ * Environment variables read by the libraries (once, at first use; none changes a result -
+ * they select between kernels / schedules that the tests hold to the same output; they exist
+ * for the tests and for tuning on other parts, and are NOT part of the stable ABI):
+ *    SVO_CORNER_CPT = 1 | 2 | 4        columns per thread of corner_score_nms (default 2)
+ *    SVO_CORNER_SEGMENTS = 1 .. 16     row segments per strip (default height / 62)
+ *    SVO_CORNER_MIN_BLOCKS = 16 | 20   resident warps per SM the kernel is compiled for
+ *    SVO_CORNER_FORCE_REPAIR = 1       every segment re-walks (exercises the repair path)
+ *    SVO_STEREO_GENERIC = 1            sparse StereoBM: generic kernel even for (48, 21)
+ *    SVO_SPLIT_STREAMS = 0 | 1         detection and tracking of a step on two streams
+ *    libsvo_host.so (svo::BatchFrontEnd): SVO_BATCH_LAZY_RIGHT, SVO_BATCH_ZERO_COPY_RIGHT
+ *    (how right images reach the device), SVO_BATCH_TRACE (per-step trace on stderr)
  */
 #ifndef SVO_C_H_
 #define SVO_C_H_
@@ -93,6 +105,15 @@ SVO_API int svo_get_params(const svo_engine* e, svo_params* out);
 SVO_API int svo_num_levels(const svo_engine* e);            /* pyramid levels actually built */
 /* kernels launched by this engine since creation (bench.py reports the delta per step) */
 SVO_API int64_t svo_kernel_launches(const svo_engine* e);
+/* Detections repeated on the spill lists so far. The candidate lists of the detector are sized
+ * for ordinary images (a quarter of the pixels of a row segment; max_candidates survivors of
+ * the quality threshold); an image with large plateaus of equal corner score can exceed them,
+ * and cv::goodFeaturesToTrack has no such limit. svo_good_features_to_track, svo_step and
+ * svo_step_device then repeat the detection of that sequence on lists with room for every pixel
+ * (device memory allocated at the first overflow: 16 bytes per pixel, once per engine;
+ * SVO_ERR_NOMEM if that fails) and return what OpenCV returns. svo_step_keyframe cannot - its
+ * keyframe stage has consumed the corners by then - and reports SVO_ERR_CAPACITY. */
+SVO_API int64_t svo_detector_spills(const svo_engine* e);
 /* device-side time of the last svo_step()/stage call's kernels, CUDA events on the engine stream */
 SVO_API float svo_last_gpu_ms(const svo_engine* e);
 /* ms[0] input copies, ms[1] kernels, ms[2] result copy of the last call (CUDA events) */

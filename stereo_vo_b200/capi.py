@@ -56,7 +56,7 @@ EXPORTS = [
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
     "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac", "svo_reprojection_evaluate", "svo_draw_track", "svo_set_blocking_sync",
-    "svo_dedupe_static",
+    "svo_dedupe_static", "svo_detector_spills",
 ]
 
 _lib = None
@@ -121,6 +121,8 @@ def load_library(path: Optional[str] = None):
     lib.svo_set_blocking_sync.argtypes = [vp, i32]
     lib.svo_draw_track.argtypes = [vp, vp, i32, vp, vp, i32, vp, i32]
     lib.svo_pnp_ransac.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, i32, f32, C.c_double, vp, vp, vp]
+    lib.svo_detector_spills.argtypes = [vp]
+    lib.svo_detector_spills.restype = C.c_int64
     lib.svo_dedupe_static.argtypes = [i32, vp, i32, vp, i32, f32, vp, vp, vp, vp, i32, C.c_char_p,
                                       C.c_size_t]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
@@ -248,6 +250,11 @@ class Engine:
     @property
     def kernel_launches(self) -> int:
         return int(self.lib.svo_kernel_launches(self.h))
+
+    @property
+    def detector_spills(self) -> int:
+        """detections repeated on the spill lists (plateau images), svo_detector_spills"""
+        return int(self.lib.svo_detector_spills(self.h))
 
     def last_timing(self):
         ms = (C.c_float * 3)()

@@ -110,6 +110,13 @@ struct svo_engine {
     unsigned long long* d_strips = nullptr;   // [n_seq][n_strips][n_seg][strip_cap]
     int* d_strip_count = nullptr;             // [n_seq][n_strips * n_seg]
     int n_strips = 0, n_seg = 0, strip_cap = 0;
+    // spill path of the detector (plateau images): lists with room for EVERY pixel of one
+    // sequence, allocated at the first overflow; spill_seq = the sequence whose sorted
+    // candidates they hold
+    unsigned long long* d_strips_big = nullptr;   // [n_strips][n_seg][strip_cap_big]
+    unsigned long long* d_cand_big = nullptr;     // [svo_sort_capacity_pad(max_cand_big)]
+    int strip_cap_big = 0, max_cand_big = 0, spill_seq = -1;
+    int64_t spills = 0;
     // corner_score_nms: per (strip, segment) maximum, wrong-start flag, true sums of a flagged start
     unsigned int* d_sub_max = nullptr;
     unsigned int* d_seg_flag = nullptr;       // [..][2] epoch-tagged start verdicts
@@ -626,9 +633,19 @@ cudaError_t launch_pyramid(svo_engine* e, const SvoSeqCall* dc, int n, cudaStrea
 }
 
 // pyramid + detection for the listed sequences (current frames already uploaded)
-cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t st = nullptr) {
+// lists: nullptr = the engine's per-sequence lists; the spill path passes its own
+struct DetectLists {
+    unsigned long long* strips;
+    int strip_cap;
+    unsigned long long* cand;
+    int max_cand;
+};
+cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t st = nullptr,
+                          const DetectLists* lists = nullptr) {
     if (!st) st = e->st;
     const SvoSeqCall* dc = dev_call_slot(e);
+    const DetectLists own = {e->d_strips, e->strip_cap, e->d_cand, e->max_cand};
+    const DetectLists& L = lists ? *lists : own;
     reset_kernel<<<(n + 127) / 128, 128, 0, st>>>(e->d_eig_max, e->d_cand_count, e->d_ncorners,
                                                       dc, n);
     e->launches += 1;
@@ -639,8 +656,8 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t 
     }
     e->cs_epoch = (e->cs_epoch % 0x3fffffffu) + 1u;    // tags this launch's verdict words
     const SvoCornerCall cc = {e->d_pyr, e->seq_stride, e->d_eig, e->eig_pitch, e->eig_stride,
-                              e->d_eig_max, e->p.quality_level, e->d_strips, e->n_strips,
-                              e->n_seg, e->strip_cap, e->d_strip_count, e->d_sub_max,
+                              e->d_eig_max, e->p.quality_level, L.strips, e->n_strips,
+                              e->n_seg, L.strip_cap, e->d_strip_count, e->d_sub_max,
                               e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_cs_work,
                               e->cs_epoch, dc};
     {
@@ -649,19 +666,19 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t 
     }
     {
         ProfScope ps(e, P_SORT, st);
-        SVO_CUDA_OK(svo_launch_sort_candidates(e->d_cand, e->max_cand, e->d_cand_count,
-                                               e->d_strips, e->n_strips * e->n_seg, e->strip_cap,
+        SVO_CUDA_OK(svo_launch_sort_candidates(L.cand, L.max_cand, e->d_cand_count,
+                                               L.strips, e->n_strips * e->n_seg, L.strip_cap,
                                                e->d_strip_count, e->d_eig_max,
                                                e->p.quality_level, dc, n, st));
     }
     {
         ProfScope ps(e, P_GREEDY, st);
-        SVO_CUDA_OK(svo_launch_greedy_select(e->d_cand, e->max_cand, e->d_cand_count, e->p.width,
+        SVO_CUDA_OK(svo_launch_greedy_select(L.cand, L.max_cand, e->d_cand_count, e->p.width,
                                              e->p.height, e->p.min_distance, e->p.max_corners,
                                              e->d_corners, e->d_ncorners, e->d_grid,
                                              e->grid_stride, dc, n, st));
     }
-    e->launches += 2 + svo_sort_launch_count(e->max_cand);
+    e->launches += 2 + svo_sort_launch_count(L.max_cand);
     return cudaSuccess;
 }
 
@@ -713,6 +730,44 @@ cudaError_t wait_stream(svo_engine* e) {
     if (!e->blocking_sync) return cudaStreamSynchronize(e->st);
     SVO_CUDA_OK(cudaEventRecord(e->ev_block, e->st));
     return cudaEventSynchronize(e->ev_block);
+}
+
+// Spill path of the detector. The engine's candidate lists are sized for ordinary images (a
+// quarter of the pixels per segment, max_candidates survivors); an image with large plateaus
+// of equal corner score can exceed either, and cv::goodFeaturesToTrack has no such limit. The
+// detection of that ONE sequence is then repeated - its frame still sits in the sequence's
+// current pyramid slot - on lists with room for every pixel, allocated at the first overflow.
+// Leaves d_corners / d_ncorners / d_cand_count of the sequence exact; the stream is idle on
+// return.
+int detect_spill(svo_engine* e, int seq) {
+    const size_t n_sub = (size_t)e->n_strips * e->n_seg;
+    if (!e->d_strips_big) {
+        e->strip_cap_big = svo_corner_strip_cap_full(e->p.height);
+        e->max_cand_big = svo_sort_capacity_pad(e->p.width * e->p.height);
+        cudaError_t ce = dalloc(&e->d_strips_big, n_sub * (size_t)e->strip_cap_big);
+        if (ce == cudaSuccess) ce = dalloc(&e->d_cand_big, (size_t)e->max_cand_big);
+        if (ce != cudaSuccess) {
+            cudaGetLastError();
+            if (e->d_strips_big) cudaFree(e->d_strips_big);
+            e->d_strips_big = nullptr;
+            return fail(e, SVO_ERR_NOMEM, "detector spill lists", ce);
+        }
+    }
+    SvoSeqCall* hc = next_call_slot(e);
+    fill_call(e, hc[0], seq);
+    ECUDA(e, push_calls(e, 1));
+    // the kernels index their lists by sequence: bias the single-sequence lists accordingly
+    const uintptr_t strips0 = reinterpret_cast<uintptr_t>(e->d_strips_big) -
+                              (uintptr_t)seq * n_sub * (size_t)e->strip_cap_big * 8u;
+    const uintptr_t cand0 = reinterpret_cast<uintptr_t>(e->d_cand_big) -
+                            (uintptr_t)seq * (size_t)e->max_cand_big * 8u;
+    const DetectLists L = {reinterpret_cast<unsigned long long*>(strips0), e->strip_cap_big,
+                           reinterpret_cast<unsigned long long*>(cand0), e->max_cand_big};
+    ECUDA(e, launch_detect(e, 1, false, e->st, &L));
+    ECUDA(e, wait_stream(e));
+    e->spill_seq = seq;
+    e->spills += 1;
+    return SVO_OK;
 }
 
 int finish_timing(svo_engine* e) {
@@ -899,14 +954,42 @@ int step_impl(svo_engine* e, int n, const int32_t* seqs, const uint8_t* const* l
     int rc = SVO_OK;
     const int mc = e->p.max_corners, mf = e->p.max_features;
     for (int i = 0; i < n; ++i) {
+        // candidate lists overflowed (plateau image): detect this sequence again on the spill
+        // lists and patch its block. Not possible once the keyframe stage of the same call has
+        // consumed the corners (svo_step_keyframe): that call reports the overflow.
+        unsigned char* o = e->h_out + (size_t)i * e->step_block;
+        StepHeader* h = reinterpret_cast<StepHeader*>(o);
+        if (h->cand_count <= e->max_cand) continue;
+        if (key) {
+            rc = fail(e, SVO_ERR_CAPACITY, "svo_step_keyframe: NMS candidate lists overflowed (plateau image); "
+                                           "use svo_step + svo_keyframe[_tracked] for such frames or raise max_candidates");
+            continue;
+        }
+        const int before = h->n_corners;
+        const int src = detect_spill(e, seqs[i]);
+        if (src != SVO_OK) { rc = src; continue; }
+        int hdr[2] = {0, 0};
+        ECUDA(e, cudaMemcpyAsync(&hdr[0], e->d_ncorners + seqs[i], sizeof(int), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaMemcpyAsync(&hdr[1], e->d_cand_count + seqs[i], sizeof(int), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaMemcpyAsync(o + sizeof(StepHeader), e->d_corners + (size_t)seqs[i] * mc,
+                                 (size_t)mc * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, wait_stream(e));
+        h->n_corners = hdr[0];
+        h->cand_count = hdr[1];
+        if (hdr[1] > e->max_cand_big)
+            rc = fail(e, SVO_ERR_CAPACITY, "detector spill lists overflowed (internal error)");
+        else if ((before >= 4) != (hdr[0] >= 4))
+            // the device-side "fewer than 4 corners" gate of the tracking stage saw the
+            // truncated list
+            rc = fail(e, SVO_ERR_CAPACITY, "NMS candidate lists overflowed on a frame with fewer than 4 corners: raise max_candidates");
+    }
+    for (int i = 0; i < n; ++i) {
         const unsigned char* o = e->h_out + (size_t)i * e->step_block;
         const StepHeader* h = reinterpret_cast<const StepHeader*>(o);
         const float2* oc = reinterpret_cast<const float2*>(o + sizeof(StepHeader));
         const float2* of = oc + mc;
         const unsigned long long* oi = reinterpret_cast<const unsigned long long*>(of + mf);
         SeqState& s = e->seq[seqs[i]];
-        if (h->cand_count > e->max_cand)
-            rc = fail(e, SVO_ERR_CAPACITY, "NMS candidate buffer overflow: raise max_candidates");
         if (n_corners) n_corners[i] = h->n_corners;
         if (corners) memcpy(corners + (size_t)i * mc, oc, (size_t)h->n_corners * sizeof(float2));
         svo_track_stats st = {0.f, 0.f, 0, 0};
@@ -1175,7 +1258,8 @@ void svo_destroy(svo_engine* e) {
                      e->d_kept_par, e->d_stats, e->d_inl, e->d_pts, e->d_keep_idx, e->d_nnew, e->d_ticket,
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
                      e->d_call, e->d_kcall, e->d_pnp_world, e->d_pnp_img, e->d_pnp_counts,
-                     e->d_pnp_guess, e->d_pnp_res, e->d_pnp_inl, e->d_ba, e->d_draw};
+                     e->d_pnp_guess, e->d_pnp_res, e->d_pnp_inl, e->d_ba, e->d_draw,
+                     e->d_strips_big, e->d_cand_big};
     for (void* p : dptrs) if (p) cudaFree(p);
     if (e->h_call) cudaFreeHost(e->h_call);
     if (e->h_pull) cudaFreeHost(e->h_pull);
@@ -1202,6 +1286,7 @@ int svo_get_params(const svo_engine* e, svo_params* out) {
     return SVO_OK;
 }
 int svo_num_levels(const svo_engine* e) { return e ? e->lay.n_levels : SVO_ERR_INVALID; }
+int64_t svo_detector_spills(const svo_engine* e) { return e ? e->spills : 0; }
 int64_t svo_kernel_launches(const svo_engine* e) { return e ? e->launches : 0; }
 float svo_last_gpu_ms(const svo_engine* e) { return e ? e->last_ms[1] : 0.f; }
 int svo_last_timing(const svo_engine* e, float ms[3]) {
@@ -1316,7 +1401,17 @@ int svo_good_features_to_track(svo_engine* e, int32_t seq, const uint8_t* img, i
     ECUDA(e, cudaEventRecord(e->ev[3], e->st));
     ECUDA(e, wait_stream(e));
     finish_timing(e);
-    if (hdr[1] > e->max_cand) return fail(e, SVO_ERR_CAPACITY, "NMS candidate buffer overflow: raise max_candidates");
+    if (hdr[1] > e->max_cand) {
+        // plateau image: repeat on the spill lists (room for every pixel)
+        rc = detect_spill(e, seq);
+        if (rc) return rc;
+        ECUDA(e, cudaMemcpyAsync(&hdr[0], e->d_ncorners + seq, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaMemcpyAsync(&hdr[1], e->d_cand_count + seq, sizeof(int), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaMemcpyAsync(e->h_out, e->d_corners + (size_t)seq * e->p.max_corners,
+                                 (size_t)e->p.max_corners * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, wait_stream(e));
+        if (hdr[1] > e->max_cand_big) return fail(e, SVO_ERR_CAPACITY, "detector spill lists overflowed (internal error)");
+    }
     *out_n = hdr[0];
     memcpy(out_xy, e->h_out, (size_t)hdr[0] * sizeof(float2));
     return SVO_OK;
@@ -1973,12 +2068,18 @@ int svo_debug_candidates(svo_engine* e, int32_t seq, int32_t* xy, int32_t cap, i
     ECUDA(e, cudaSetDevice(e->device));
     int cnt = 0;
     ECUDA(e, cudaMemcpy(&cnt, e->d_cand_count + seq, sizeof(int), cudaMemcpyDeviceToHost));
-    if (cnt > e->max_cand) cnt = e->max_cand;
+    const unsigned long long* src = e->d_cand + (size_t)seq * e->max_cand;
+    if (cnt > e->max_cand) {
+        // the sequence's last detection went through the spill lists (one sequence at a time)
+        if (e->spill_seq != seq || cnt > e->max_cand_big)
+            return fail(e, SVO_ERR_STATE, "svo_debug_candidates: the spilled candidate list of this sequence was reused by another sequence");
+        src = e->d_cand_big;
+    }
     *n = cnt;
     int m = cnt < cap ? cnt : cap;
     if (xy && m > 0) {
         std::vector<unsigned long long> keys(m);
-        ECUDA(e, cudaMemcpy(keys.data(), e->d_cand + (size_t)seq * e->max_cand, (size_t)m * 8, cudaMemcpyDeviceToHost));
+        ECUDA(e, cudaMemcpy(keys.data(), src, (size_t)m * 8, cudaMemcpyDeviceToHost));
         for (int i = 0; i < m; ++i) {
             unsigned addr = (unsigned)(keys[i] & 0xffffffffull);
             xy[2 * i] = (int)(addr % (unsigned)e->p.width);

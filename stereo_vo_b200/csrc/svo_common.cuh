@@ -84,6 +84,7 @@ cudaError_t svo_launch_pyr_down_single(const uint8_t* src, int w, int h, int spi
 int svo_corner_strips(int w);
 int svo_corner_segments(int h);
 int svo_corner_strip_cap(int h);          // per (strip, segment)
+int svo_corner_strip_cap_full(int h);     // ... with room for every pixel (spill path)
 size_t svo_corner_state_doubles();        // per (strip, segment)
 struct SvoCornerCall {
     const uint8_t* pyr; size_t seq_stride;

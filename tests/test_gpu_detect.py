@@ -102,6 +102,54 @@ def test_plateau_ties_and_flat_image(engines, oracle):
     assert np.array_equal(e.good_features_to_track(stress), oracle.detect(stress))
 
 
+def _plateau_images(w, h):
+    """images whose NMS survivors overflow the engine's candidate lists: period-3 patterns (the
+    3x3 box sums see one whole period: the corner score is one plateau, EVERY pixel is a
+    non-strict local maximum) and white noise (more than max_candidates = 16384 survivors)"""
+    yy, xx = np.mgrid[0:h, 0:w]
+    rng = np.random.default_rng(1)
+    return {
+        "dots3": np.where((xx % 3 == 0) & (yy % 3 == 0), 200, 20).astype(np.uint8),
+        "tile3": np.array([[10, 200, 90], [160, 30, 220], [75, 240, 5]], np.uint8)[yy % 3, xx % 3],
+        "noise": rng.integers(0, 256, (h, w)).astype(np.uint8),
+    }
+
+
+@pytest.mark.parametrize("w,h", [(1241, 376), (333, 211)])
+def test_plateau_images_take_the_spill_path(engines, oracle, w, h):
+    """cv::goodFeaturesToTrack has no candidate limit: where the engine's lists overflow, the
+    detection is repeated on lists with room for every pixel and the corners are cv2's."""
+    from oracle import restate
+    e = engines(w, h)
+    imgs = _plateau_images(w, h)
+    normal = _image(w, h, 2)
+    for name, img in imgs.items():
+        ref = oracle.detect(img)
+        before = e.detector_spills
+        got = e.good_features_to_track(img)
+        spilled = e.detector_spills - before
+        assert np.array_equal(got, ref), f"{name}: corners differ ({len(got)} vs {len(ref)})"
+        xs, ys, _ = restate.corner_candidates(cv2.cornerMinEigenVal(img, 3, ksize=3), 0.1)
+        if len(xs) > 16384:
+            assert spilled == 1, f"{name}: {len(xs)} survivors but no spill"
+        cand = e.debug_candidates()
+        assert cand.shape[0] == len(xs), name
+        assert np.array_equal(cand[:, 0], xs) and np.array_equal(cand[:, 1], ys), f"{name}: candidate order"
+        # through svo_step, next to an ordinary frame in the same call
+        before = e.detector_spills
+        res = e.step([0, 1], [normal, img], [normal, img])
+        for i, im in enumerate((normal, img)):
+            r = oracle.detect(im)
+            n = res["n_corners"][i]
+            assert n == r.shape[0] and np.array_equal(res["corners"][i, :n], r), f"{name}: step, sequence {i}"
+        assert e.detector_spills - before == spilled
+    # an ordinary frame afterwards does not spill
+    before = e.detector_spills
+    assert np.array_equal(e.good_features_to_track(normal), oracle.detect(normal))
+    assert e.detector_spills == before
+    assert e.detector_spills >= (2 if (w, h) == (1241, 376) else 1)
+
+
 @pytest.mark.parametrize("maxc,q,md", [(50, 0.05, 10.0), (1000, 0.01, 5.0), (300, 0.3, 30.0),
                                        (200, 0.1, 0.0), (400, 0.02, 7.5)])
 def test_other_detector_parameters(engines, oracle, maxc, q, md):

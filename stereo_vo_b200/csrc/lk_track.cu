@@ -408,6 +408,8 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 iyv[t] = (dy[0] * w00 + dy[1] * w01 + dy[DG] * w10 + dy[DG + 1] * w11 + 8192) >> 14;
             }
         }
+#pragma unroll
+        for (int t = 0; t < RUN; ++t) ival[t] = 256 - (ival[t] << 9);   // see the iteration
         // ---- A11, A12, A22: per-pixel f32 products in chain order, then sequential chains
         __syncthreads();                     // every thread has its values out of s_B / s_dx
         if (has_px) {
@@ -492,18 +494,17 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 const unsigned b0 = __funnelshift_r(v0, v1, sh), b1 = __funnelshift_r(v1, v2, sh),
                                b2 = v2 >> sh;
                 const int wt = pack16(w00, w01), wb = pack16(w10, w11);
-                int jv[RUN];
-                jv[0] = tap2<0>(wb, b0, b1, tap2<0>(wt, a0, a1, 256));
-                jv[1] = tap2<1>(wb, b0, b1, tap2<1>(wt, a0, a1, 256));
-                jv[2] = tap2<2>(wb, b0, b1, tap2<2>(wt, a0, a1, 256));
-                jv[3] = tap2<3>(wb, b0, b1, tap2<3>(wt, a0, a1, 256));
-                jv[4] = tap2<4>(wb, b0, b1, tap2<4>(wt, a0, a1, 256));
-                jv[5] = tap2<5>(wb, b0, b1, tap2<5>(wt, a0, a1, 256));
-                jv[6] = tap2<6>(wb, b0, b1, tap2<6>(wt, a0, a1, 256));
-                jv[7] = tap2_7(wb, b1, b2, tap2_7(wt, a1, a2, 256));
+                // ((J + 256) >> 9) - I = (J + 256 - (I << 9)) >> 9: the I term rides in the dp2a
+                // accumulator (ival holds 256 - (I << 9))
                 int dI[RUN];
-#pragma unroll
-                for (int t = 0; t < RUN; ++t) dI[t] = (jv[t] >> 9) - ival[t];
+                dI[0] = tap2<0>(wb, b0, b1, tap2<0>(wt, a0, a1, ival[0])) >> 9;
+                dI[1] = tap2<1>(wb, b0, b1, tap2<1>(wt, a0, a1, ival[1])) >> 9;
+                dI[2] = tap2<2>(wb, b0, b1, tap2<2>(wt, a0, a1, ival[2])) >> 9;
+                dI[3] = tap2<3>(wb, b0, b1, tap2<3>(wt, a0, a1, ival[3])) >> 9;
+                dI[4] = tap2<4>(wb, b0, b1, tap2<4>(wt, a0, a1, ival[4])) >> 9;
+                dI[5] = tap2<5>(wb, b0, b1, tap2<5>(wt, a0, a1, ival[5])) >> 9;
+                dI[6] = tap2<6>(wb, b0, b1, tap2<6>(wt, a0, a1, ival[6])) >> 9;
+                dI[7] = tap2_7(wb, b1, b2, tap2_7(wt, a1, a2, ival[7])) >> 9;
                 if (has_px) {
                     if (part < 2) {
                         // v_dotprod lanes: int32 sum of the pixel pair (p, p + 4), then f32

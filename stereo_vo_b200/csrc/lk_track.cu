@@ -67,36 +67,51 @@ constexpr int A_TAIL_OFF = 12 * A_LANE_TERMS;              // 1008
 constexpr int A_FLOATS = A_TAIL_OFF + 3 * TAIL_PITCH;      // 1332
 constexpr int B_CHAIN_TERMS = 2 * WIN;                     // 42
 constexpr int B_CHAIN_PITCH = 44;
-constexpr int B_TAIL_OFF = 8 * B_CHAIN_PITCH;              // 352
-static_assert(B_TAIL_OFF + 2 * TAIL_PITCH <= A_FLOATS, "b terms fit in the A term buffer");
+// b layout: the four b1 chains, then the four b2 chains B_YOFF floats further on; the two tails
+// behind them, again B_YOFF apart - so a thread's b2 term always sits B_YOFF behind its b1 term
+// and one piece of code (base + p * stride) serves the SIMD parts and the tail part
+constexpr int B_YOFF = 4 * B_CHAIN_PITCH;                  // 176
+constexpr int B_TAIL_OFF = 2 * B_YOFF;                     // 352
+constexpr int B_DUMMY_OFF = B_TAIL_OFF + 2 * B_YOFF;       // 704: where the idle thread 63 writes
+static_assert(TAIL_PITCH <= B_YOFF, "tail chains do not overlap");
+static_assert(B_DUMMY_OFF + B_YOFF + 3 * B_CHAIN_PITCH + 5 <= A_FLOATS, "b terms fit in the A term buffer");
+// control word of the next iteration (s_ctl.z): >= 0 byte offset of the window origin in the
+// staged J region, or one of these
+constexpr int CTL_STOP = -1;               // the iteration loop of this level is over
+constexpr int CTL_RESTAGE = -2;            // the window left the staged region: re-stage at .w
 
 // acc = fl(acc + term) over the terms at src (16-byte aligned), in order: N_SHORT terms for a
-// SIMD-lane chain, TAIL_TERMS for a scalar-tail chain (is_long); inactive lanes idle. Straight-
-// line code: the loads run ahead of the dependent additions, which are the critical path
-// (TAIL_TERMS x the FADD latency per window sum).
+// SIMD-lane chain, TAIL_TERMS for a scalar-tail chain (is_long); inactive lanes idle. The
+// dependent additions are the critical path (TAIL_TERMS x the FADD latency per window sum).
+// Loops of five / seven 4-term groups instead of straight-line code: the kernel's hot code has
+// to stay inside the 32 KB instruction cache of the SM (ncu: a fifth of the warp stalls were
+// instruction fetches when both chains were fully unrolled, 2.4 KB each).
+__device__ __forceinline__ float add4(float acc, const float* p) {
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    return __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(acc, v.x), v.y), v.z), v.w);
+}
 template <int N_SHORT>
 __device__ __forceinline__ float chain_sum(const float* __restrict__ src, bool active, bool is_long) {
-    constexpr int N4 = (N_SHORT + 3) / 4 * 4;
+    constexpr int G_ALL = N_SHORT / 4, REM = N_SHORT % 4;     // 10, 2 (b) / 21, 0 (A)
+    constexpr int G_TAIL = TAIL_TERMS / 4;                     // 26 full groups, then one term
+    constexpr int G_MID = G_ALL + (REM ? 1 : 0);
+    static_assert(TAIL_TERMS % 4 == 1 && (G_ALL % 5 == 0 || G_ALL % 7 == 0), "group loops");
     float acc = 0.f;
     if (active) {
-#pragma unroll
-        for (int i = 0; i < N4; i += 4) {
-            const float4 v = *reinterpret_cast<const float4*>(src + i);
+#pragma unroll(G_ALL % 5 == 0 ? 5 : 7)
+        for (int g = 0; g < G_ALL; ++g) acc = add4(acc, src + 4 * g);
+        if (REM) {
+            const float4 v = *reinterpret_cast<const float4*>(src + 4 * G_ALL);
             acc = __fadd_rn(acc, v.x);
-            if (i + 1 < N_SHORT || is_long) acc = __fadd_rn(acc, v.y);
-            if (i + 2 < N_SHORT || is_long) acc = __fadd_rn(acc, v.z);
-            if (i + 3 < N_SHORT || is_long) acc = __fadd_rn(acc, v.w);
+            if (REM > 1 || is_long) acc = __fadd_rn(acc, v.y);
+            if (REM > 2 || is_long) acc = __fadd_rn(acc, v.z);
+            if (is_long) acc = __fadd_rn(acc, v.w);
         }
     }
     if (is_long) {
-#pragma unroll
-        for (int i = N4; i < TAIL_TERMS; i += 4) {
-            const float4 v = *reinterpret_cast<const float4*>(src + i);
-            acc = __fadd_rn(acc, v.x);
-            if (i + 1 < TAIL_TERMS) acc = __fadd_rn(acc, v.y);
-            if (i + 2 < TAIL_TERMS) acc = __fadd_rn(acc, v.z);
-            if (i + 3 < TAIL_TERMS) acc = __fadd_rn(acc, v.w);
-        }
+#pragma unroll 5
+        for (int g = G_MID; g < G_TAIL; ++g) acc = add4(acc, src + 4 * g);
+        acc = __fadd_rn(acc, src[4 * G_TAIL]);
     }
     return acc;
 }
@@ -113,6 +128,19 @@ __device__ __forceinline__ int dp2a_hi(int w, unsigned p, int c) {
     asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(p), "r"(c));
     return d;
 }
+// Which of the two warps runs the window-sum chains and the scalar step of iteration j (j = -1:
+// plans the first iteration) of level l for key-point pi.
+//   0: always warp 0   1: fixed per block   2: changes with the level   3: with every iteration
+#ifndef LK_CW_MODE
+#define LK_CW_MODE 3
+#endif
+__device__ __forceinline__ int chain_warp(int j, int l, int pi) {
+    if (LK_CW_MODE == 0) return 0;
+    if (LK_CW_MODE == 1) return (pi >> 1) & 1;
+    if (LK_CW_MODE == 2) return ((pi >> 1) + l) & 1;
+    return ((pi >> 1) + l + j + 1) & 1;
+}
+
 __device__ __forceinline__ int pack16(int lo, int hi) { return (lo & 0xffff) | (hi << 16); }
 
 // bytes [k, k+1] of the 8-byte run (a0 | a1 << 32) as the low two bytes of a word
@@ -145,62 +173,45 @@ __device__ __forceinline__ void lk_weights(float a, float b, int& w00, int& w01,
 
 // Staging of an N_ROWS x N_COLS byte region whose first wanted byte is (x0, y0) into shared
 // rows of SP bytes. Column range inside the image (the common case, also for windows that
-// stick out above/below: rows are fetched through reflect-101 indices): aligned 32-bit loads;
-// region_load() only ISSUES them (into registers), region_store() writes them to shared memory,
-// so several regions can be in flight at once. Returns x0 & 3 (byte offset of x0 in a staged
-// row). Column range crossing the image border: byte-wise reflect-101, done at once; returns 0.
-template <int N_ROWS, int N_COLS>
-struct Region {
-    static constexpr int NW = (N_COLS + 3 + 3) / 4;          // words covering any alignment
-    static constexpr int NLD = (N_ROWS * NW + NT - 1) / NT;  // words per thread
-    static_assert(NW * 4 <= SP, "staged row too wide");
-    unsigned v[NLD];
-    bool words;
-
-    __device__ __forceinline__ int load(const uint8_t* __restrict__ img, int w, int h, int pitch,
-                                        int x0, int y0, unsigned* s_words, int tid) {
-        words = (x0 >= 0 && x0 + N_COLS <= w);
-        if (words) {
-            const int off = x0 & 3;
-            const uint8_t* base = img + (x0 - off);
-#pragma unroll
-            for (int k = 0; k < NLD; ++k) {
-                const int i = tid + k * NT;
-                const int r = min(i / NW, N_ROWS - 1), c = i - (i / NW) * NW;
-                const int gy = clamp_reflect(y0 + r, h);
-                v[k] = __ldg(reinterpret_cast<const unsigned*>(base + (size_t)gy * pitch) + c);
-            }
-            return off;
-        }
-        unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_words);
-        for (int i = tid; i < N_ROWS * N_COLS; i += NT) {
-            int r = i / N_COLS, c = i - r * N_COLS;
-            int gy = clamp_reflect(y0 + r, h), gx = clamp_reflect(x0 + c, w);
-            s_bytes[r * SP + c] = img[(size_t)gy * pitch + gx];
-        }
-        return 0;
-    }
-    __device__ __forceinline__ void store(unsigned* s_words, int tid) const {
-        if (!words) return;
-#pragma unroll
-        for (int k = 0; k < NLD; ++k) {
-            const int i = tid + k * NT;
-            if (i < N_ROWS * NW) {
-                const int r = i / NW, c = i - r * NW;
-                s_words[r * (SP / 4) + c] = v[k];
-            }
-        }
-    }
-};
+// stick out above/below: rows are fetched through reflect-101 indices): aligned words copied
+// global -> shared by cp.async (no registers in between, so the regions of all levels are in
+// flight together and the code stays small: thread = word column tid & 7 of rows tid >> 3,
+// + 8, + 16, ...). Returns x0 & 3 (byte offset of x0 in a staged row). Column range crossing the
+// image border: byte-wise reflect-101, done at once; returns 0. The caller waits
+// (stage_wait) and puts a barrier before anybody reads.
+__device__ __forceinline__ void cp_async4(unsigned dst, const void* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void stage_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 template <int N_ROWS, int N_COLS>
 __device__ __forceinline__ int stage_region(const uint8_t* __restrict__ img, int w, int h,
                                             int pitch, int x0, int y0, unsigned* s_words,
                                             int tid) {
-    Region<N_ROWS, N_COLS> rg;
-    const int off = rg.load(img, w, h, pitch, x0, y0, s_words, tid);
-    rg.store(s_words, tid);
-    return off;
+    constexpr int NW = (N_COLS + 3 + 3) / 4;          // words covering any alignment
+    static_assert(NW <= 8 && NW * 4 <= SP, "staged row too wide");
+    if (x0 >= 0 && x0 + N_COLS <= w) {
+        const int off = x0 & 3;
+        const int col = tid & 7, row0 = tid >> 3;
+        if (col < NW) {
+            const uint8_t* base = img + (x0 - off) + col * 4;
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(s_words) + row0 * SP + col * 4;
+#pragma unroll
+            for (int p = 0; p < (N_ROWS + 7) / 8; ++p) {
+                const int r = row0 + 8 * p;
+                if (r < N_ROWS)
+                    cp_async4(dst + p * 8 * SP, base + (size_t)clamp_reflect(y0 + r, h) * pitch);
+            }
+        }
+        return off;
+    }
+    unsigned char* s_bytes = reinterpret_cast<unsigned char*>(s_words);
+    for (int i = tid; i < N_ROWS * N_COLS; i += NT) {
+        int r = i / N_COLS, c = i - r * N_COLS;
+        int gy = clamp_reflect(y0 + r, h), gx = clamp_reflect(x0 + c, w);
+        s_bytes[r * SP + c] = img[(size_t)gy * pitch + gx];
+    }
+    return 0;
 }
 
 __global__ void __launch_bounds__(NT, 16)
@@ -222,6 +233,9 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     // its window values from it, the chain-ordered terms of the window sums
     __shared__ __align__(16) float s_T[A_FLOATS];
     __shared__ float s_sum[3];
+    __shared__ int4 s_ctl;
+    __shared__ float4 s_next;              // nextPt and ok when a level's iterations end
+    __shared__ float4 s_st;                // np, prevDelta between iterations (LK_CW_MODE 3)
     int* s_B = reinterpret_cast<int*>(s_T);
     static_assert(sizeof(int) * BG * BP <= sizeof(float) * A_FLOATS, "B grid fits in the term buffer");
 
@@ -258,6 +272,11 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     const int part = tid - (tid / 3) * 3;
     const int wx0 = part * RUN;
     const int lane = tid & 31;
+    // where this thread's b terms go: term p at s_T[t_off + p * t_str] (b1) and B_YOFF behind it
+    // (b2); the idle thread 63 writes to a spare area
+    const int t_off = tid >= WIN * 3 ? B_DUMMY_OFF : part < 2 ? wy * 2 + part : B_TAIL_OFF + wy * 5;
+    const int t_str = part < 2 ? B_CHAIN_PITCH : 1;
+    const int tb = wy * SP + wx0;          // byte offset of its first window pixel in a staged region
     short* s_dx = reinterpret_cast<short*>(s_B);
     short* s_dy = s_dx + DG * DG;
     static_assert(2 * DG * DG * sizeof(short) <= sizeof(int) * BG * BP, "alias too small");
@@ -268,32 +287,21 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     // ---- fetch the I patch and the zero-flow J region of every level (loads of all levels in
     // flight together), then one barrier
     unsigned offs = 0;                       // 2 bits per (level, I/J): byte offset in a staged row
-    {
-        Region<IP, IP> rI[LK_LEVELS];
-        Region<JR, JR> rJ[LK_LEVELS];
-#pragma unroll
-        for (int l = 0; l < LK_LEVELS; ++l) {
-            rI[l].words = rJ[l].words = false;
-            if (l < lay.n_levels) {
-                const SvoLevel lv = lay.lvl[l];
-                const float inv = 1.f / (float)(1 << l);
-                const int ipx = (int)floorf(__fsub_rn(__fmul_rn(pt.x, inv), half));
-                const int ipy = (int)floorf(__fsub_rn(__fmul_rn(pt.y, inv), half));
-                if (!(ipx < -WIN || ipx >= lv.w || ipy < -WIN || ipy >= lv.h)) {
-                    const int oi = rI[l].load(pyrI + lv.off, lv.w, lv.h, lv.pitch, ipx - 1,
-                                              ipy - 1, s_Iall[l], tid);
-                    const int oj = rJ[l].load(pyrJ + lv.off, lv.w, lv.h, lv.pitch, ipx - JM,
-                                              ipy - JM, s_Jall[l], tid);
-                    offs |= (unsigned)(oi | (oj << 2)) << (4 * l);
-                }
-            }
-        }
-#pragma unroll
-        for (int l = 0; l < LK_LEVELS; ++l) {
-            rI[l].store(s_Iall[l], tid);
-            rJ[l].store(s_Jall[l], tid);
+#pragma unroll 1
+    for (int l = 0; l < lay.n_levels; ++l) {
+        const SvoLevel lv = lay.lvl[l];
+        const float inv = 1.f / (float)(1 << l);
+        const int ipx = (int)floorf(__fsub_rn(__fmul_rn(pt.x, inv), half));
+        const int ipy = (int)floorf(__fsub_rn(__fmul_rn(pt.y, inv), half));
+        if (!(ipx < -WIN || ipx >= lv.w || ipy < -WIN || ipy >= lv.h)) {
+            const int oi = stage_region<IP, IP>(pyrI + lv.off, lv.w, lv.h, lv.pitch, ipx - 1,
+                                                ipy - 1, s_Iall[l], tid);
+            const int oj = stage_region<JR, JR>(pyrJ + lv.off, lv.w, lv.h, lv.pitch, ipx - JM,
+                                                ipy - JM, s_Jall[l], tid);
+            offs |= (unsigned)(oi | (oj << 2)) << (4 * l);
         }
     }
+    stage_wait();
     __syncthreads();
     float2 nextPt = make_float2(0.f, 0.f);   // the value OpenCV keeps in nextPts[ptidx]
     bool ok = true;
@@ -410,30 +418,31 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         }
 #pragma unroll
         for (int t = 0; t < RUN; ++t) ival[t] = 256 - (ival[t] << 9);   // see the iteration
-        // ---- A11, A12, A22: per-pixel f32 products in chain order, then sequential chains
+        // ---- A11, A12, A22: per-pixel f32 products in chain order, then sequential chains.
+        // Every thread forms the products of its 8 pixels (one piece of code for the SIMD parts
+        // and the tail part, whose last three are never stored); chain (q, L) takes pixels L and
+        // L + 4 of a SIMD part as two ADJACENT terms: one 64-bit store
         __syncthreads();                     // every thread has its values out of s_B / s_dx
-        if (has_px) {
-            if (part < 2) {
 #pragma unroll
-                for (int t = 0; t < RUN; ++t) {
-                    const int L = t & 3, m = 2 * part + (t >> 2);
-                    float* o = s_T + L * A_LANE_TERMS + wy * 4 + m;
-                    o[0 * 4 * A_LANE_TERMS] = __int2float_rn(ixv[t] * ixv[t]);
-                    o[1 * 4 * A_LANE_TERMS] = __int2float_rn(ixv[t] * iyv[t]);
-                    o[2 * 4 * A_LANE_TERMS] = __int2float_rn(iyv[t] * iyv[t]);
+        for (int q = 0; q < 3; ++q) {
+            float pr[RUN];
+#pragma unroll
+            for (int t = 0; t < RUN; ++t)
+                pr[t] = __int2float_rn((q == 2 ? iyv[t] : ixv[t]) * (q == 0 ? ixv[t] : iyv[t]));
+            if (part < 2) {
+                if (has_px) {
+                    float2* o = reinterpret_cast<float2*>(s_T + q * 4 * A_LANE_TERMS + wy * 4 + 2 * part);
+#pragma unroll
+                    for (int L = 0; L < 4; ++L) o[L * (A_LANE_TERMS / 2)] = make_float2(pr[L], pr[L + 4]);
                 }
             } else {
+                float* o = s_T + A_TAIL_OFF + q * TAIL_PITCH + wy * 5;
 #pragma unroll
-                for (int t = 0; t < WIN - 2 * RUN; ++t) {
-                    float* o = s_T + A_TAIL_OFF + wy * 5 + t;
-                    o[0 * TAIL_PITCH] = __int2float_rn(ixv[t] * ixv[t]);
-                    o[1 * TAIL_PITCH] = __int2float_rn(ixv[t] * iyv[t]);
-                    o[2 * TAIL_PITCH] = __int2float_rn(iyv[t] * iyv[t]);
-                }
+                for (int t = 0; t < WIN - 2 * RUN; ++t) o[t] = pr[t];
             }
         }
         __syncthreads();
-        if (wrp == 0) {
+        if (wrp == chain_warp(-2, l, pi)) {
             const float* src = lane < 12 ? s_T + lane * A_LANE_TERMS
                                          : s_T + A_TAIL_OFF + (min(lane, 14) - 12) * TAIL_PITCH;
             const float acc = chain_sum<A_LANE_TERMS>(src, lane < 15, lane >= 12 && lane < 15);
@@ -459,31 +468,77 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         }
         D = __fdiv_rn(1.f, D);
 
+        // b terms: a SIMD part sums the pixel pairs (p, p + 4) in int32 (OpenCV's v_dotprod
+        // lanes), the tail part takes pixels 0..4 one by one. With the upper derivatives of the
+        // tail part zeroed, "pair p" is the same expression for both: term p of this thread
+        int ixh[4], iyh[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            ixh[p] = part < 2 ? ixv[p + 4] : 0;
+            iyh[p] = part < 2 ? iyv[p + 4] : 0;
+        }
+        const int ix4 = ixv[4], iy4 = iyv[4];        // the tail part's fifth pixel
+
+        // Scalar Gauss-Newton state lives in ONE warp at a time (the warp that also runs the
+        // chains): it plans every iteration - window origin, bounds test, bilinear weights,
+        // position in the staged J region - and hands the plan to the block in one 16-byte
+        // control word. Which warp that is changes (chain_warp): the chain warp issues three
+        // times the instructions of the other one, and the two warps of a block sit on
+        // different schedulers of the SM.
         float2 np = make_float2(__fsub_rn(nextPt.x, half), __fsub_rn(nextPt.y, half));
         float2 prevDelta = make_float2(0.f, 0.f);
         int jx0 = ipx - JM, jy0 = ipy - JM;          // origin of the pre-staged J region
         int offJ = (offs >> (4 * l + 2)) & 3;
-        for (int j = 0; j < max_iters; ++j) {
+        auto plan = [&]() {                          // one warp, every lane the same values
+            int4 c = make_int4(0, 0, CTL_STOP, 0);
             const int inx = (int)floorf(np.x), iny = (int)floorf(np.y);
             if (inx < -WIN || inx >= w || iny < -WIN || iny >= h) {
                 if (l == 0) ok = false;
-                break;
+                if (lane == 0) s_next = make_float4(nextPt.x, nextPt.y, ok ? 1.f : 0.f, 0.f);
+            } else {
+                int v00, v01, v10, v11;
+                lk_weights(__fsub_rn(np.x, (float)inx), __fsub_rn(np.y, (float)iny), v00, v01,
+                           v10, v11);
+                c.x = pack16(v00, v01);
+                c.y = pack16(v10, v11);
+                const int ox = inx - jx0, oy = iny - jy0;
+                if (ox < 0 || ox > 2 * JM || oy < 0 || oy > 2 * JM) {
+                    c.z = CTL_RESTAGE;
+                    c.w = (inx & 0xffff) | (iny << 16);
+                } else {
+                    c.z = oy * SP + ox;
+                }
+                if (LK_CW_MODE == 3 && lane == 0)
+                    s_st = make_float4(np.x, np.y, prevDelta.x, prevDelta.y);
             }
-            lk_weights(__fsub_rn(np.x, (float)inx), __fsub_rn(np.y, (float)iny), w00, w01, w10,
-                       w11);
-            int ox = inx - jx0, oy = iny - jy0;
-            if (ox < 0 || ox > 2 * JM || oy < 0 || oy > 2 * JM) {   // uniform across the block
-                __syncthreads();
-                jx0 = inx - JM;
-                jy0 = iny - JM;
+            if (lane == 0) s_ctl = c;
+        };
+        if (wrp == chain_warp(-1, l, pi)) {
+            if (max_iters > 0) plan();
+            else if (lane == 0) {
+                s_next = make_float4(nextPt.x, nextPt.y, ok ? 1.f : 0.f, 0.f);
+                s_ctl = make_int4(0, 0, CTL_STOP, 0);
+            }
+        }
+        __syncthreads();
+        for (int j = 0;; ++j) {                      // every thread counts the iterations
+            const int4 ctl = s_ctl;
+            int z = ctl.z;
+            if (z == CTL_STOP) break;                // uniform: every thread reads the same word
+            if (z == CTL_RESTAGE) {
+                // (the last readers of the region passed two barriers ago)
+                const int sx = (int)(short)(ctl.w & 0xffff), sy = ctl.w >> 16;
+                jx0 = sx - JM;
+                jy0 = sy - JM;
                 offJ = stage_region<JR, JR>(J, w, h, pitch, jx0, jy0, s_Jw, tid);
+                stage_wait();
                 __syncthreads();
-                ox = oy = JM;
+                z = JM * SP + JM;
             }
             {
                 // the thread's 9 bytes of two J rows as aligned words + funnel shifts; a pixel's
                 // four taps are two dp2a (exact integers): 6 word loads instead of 18 byte loads
-                const int bo = (wy + oy) * SP + offJ + wx0 + ox;
+                const int bo = tb + offJ + z;
                 const unsigned* q0 = s_Jw + (bo >> 2);
                 const unsigned* q1 = q0 + SP / 4;
                 const unsigned sh = (bo & 3) * 8;
@@ -493,7 +548,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                                a2 = u2 >> sh;
                 const unsigned b0 = __funnelshift_r(v0, v1, sh), b1 = __funnelshift_r(v1, v2, sh),
                                b2 = v2 >> sh;
-                const int wt = pack16(w00, w01), wb = pack16(w10, w11);
+                const int wt = ctl.x, wb = ctl.y;
                 // ((J + 256) >> 9) - I = (J + 256 - (I << 9)) >> 9: the I term rides in the dp2a
                 // accumulator (ival holds 256 - (I << 9))
                 int dI[RUN];
@@ -505,56 +560,66 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 dI[5] = tap2<5>(wb, b0, b1, tap2<5>(wt, a0, a1, ival[5])) >> 9;
                 dI[6] = tap2<6>(wb, b0, b1, tap2<6>(wt, a0, a1, ival[6])) >> 9;
                 dI[7] = tap2_7(wb, b1, b2, tap2_7(wt, a1, a2, ival[7])) >> 9;
-                if (has_px) {
-                    if (part < 2) {
-                        // v_dotprod lanes: int32 sum of the pixel pair (p, p + 4), then f32
+                float* o = s_T + t_off;
 #pragma unroll
-                        for (int pp = 0; pp < 4; ++pp) {
-                            float* o = s_T + (2 * pp) * B_CHAIN_PITCH + wy * 2 + part;
-                            o[0] = __int2float_rn(dI[pp] * ixv[pp] + dI[pp + 4] * ixv[pp + 4]);
-                            o[B_CHAIN_PITCH] = __int2float_rn(dI[pp] * iyv[pp] + dI[pp + 4] * iyv[pp + 4]);
-                        }
-                    } else {
-#pragma unroll
-                        for (int t = 0; t < WIN - 2 * RUN; ++t) {
-                            float* o = s_T + B_TAIL_OFF + wy * 5 + t;
-                            o[0] = __int2float_rn(dI[t] * ixv[t]);
-                            o[TAIL_PITCH] = __int2float_rn(dI[t] * iyv[t]);
-                        }
-                    }
+                for (int p = 0; p < 4; ++p) {
+                    o[p * t_str] = __int2float_rn(dI[p] * ixv[p] + dI[p + 4] * ixh[p]);
+                    o[p * t_str + B_YOFF] = __int2float_rn(dI[p] * iyv[p] + dI[p + 4] * iyh[p]);
+                }
+                if (part == 2) {
+                    o[4] = __int2float_rn(dI[4] * ix4);
+                    o[4 + B_YOFF] = __int2float_rn(dI[4] * iy4);
                 }
             }
             __syncthreads();
-            if (wrp == 0) {
-                const float* src = lane < 8 ? s_T + lane * B_CHAIN_PITCH
-                                            : s_T + B_TAIL_OFF + (min(lane, 9) - 8) * TAIL_PITCH;
+            if (wrp == chain_warp(j, l, pi)) {
+                if (LK_CW_MODE == 3) {               // the state the planner left
+                    const float4 st = s_st;
+                    np = make_float2(st.x, st.y);
+                    prevDelta = make_float2(st.z, st.w);
+                }
+                // chain `lane` = pair p = lane >> 1 of b1 (even lanes) / b2 (odd lanes); lanes
+                // 8, 9: the scalar tails
+                const float* src = lane < 8 ? s_T + (lane & 1) * B_YOFF + (lane >> 1) * B_CHAIN_PITCH
+                                            : s_T + B_TAIL_OFF + (min(lane, 9) - 8) * B_YOFF;
                 const float acc = chain_sum<B_CHAIN_TERMS>(src, lane < 10, lane >= 8 && lane < 10);
                 // qb0 + qb1 (chains p and p + 2), then lanes (0, 2) -> b1, (1, 3) -> b2, then the
                 // scalar tails take the SIMD sums in
                 const float q = __fadd_rn(acc, __shfl_down_sync(FULL, acc, 4));
                 const float r = __fadd_rn(q, __shfl_down_sync(FULL, q, 2));
                 const float tail = __shfl_sync(FULL, acc, 8 + (lane & 1));
-                if (lane < 2) s_sum[lane] = __fadd_rn(tail, r);
+                const float tot = __fadd_rn(tail, r);
+                const float ib1 = __shfl_sync(FULL, tot, 0), ib2 = __shfl_sync(FULL, tot, 1);
+                const float b1 = __fmul_rn(ib1, FLT_SCALE);
+                const float b2 = __fmul_rn(ib2, FLT_SCALE);
+                float2 delta;
+                delta.x = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
+                delta.y = __fmul_rn(__fsub_rn(__fmul_rn(A12, b1), __fmul_rn(A11, b2)), D);
+                np.x = __fadd_rn(np.x, delta.x);
+                np.y = __fadd_rn(np.y, delta.y);
+                nextPt = make_float2(__fadd_rn(np.x, half), __fadd_rn(np.y, half));
+                const double dd = (double)delta.x * (double)delta.x + (double)delta.y * (double)delta.y;
+                bool stop = dd <= eps2;
+                if (!stop && j > 0 && fabs((double)__fadd_rn(delta.x, prevDelta.x)) < 0.01 &&
+                    fabs((double)__fadd_rn(delta.y, prevDelta.y)) < 0.01) {
+                    nextPt.x = __fsub_rn(nextPt.x, __fmul_rn(delta.x, 0.5f));
+                    nextPt.y = __fsub_rn(nextPt.y, __fmul_rn(delta.y, 0.5f));
+                    stop = true;
+                }
+                prevDelta = delta;
+                if (j + 1 >= max_iters) stop = true;
+                if (!stop) plan();
+                else if (lane == 0) {
+                    s_next = make_float4(nextPt.x, nextPt.y, ok ? 1.f : 0.f, 0.f);
+                    s_ctl = make_int4(0, 0, CTL_STOP, 0);
+                }
             }
             __syncthreads();
-            const float ib1 = s_sum[0], ib2 = s_sum[1];
-            const float b1 = __fmul_rn(ib1, FLT_SCALE);
-            const float b2 = __fmul_rn(ib2, FLT_SCALE);
-            float2 delta;
-            delta.x = __fmul_rn(__fsub_rn(__fmul_rn(A12, b2), __fmul_rn(A22, b1)), D);
-            delta.y = __fmul_rn(__fsub_rn(__fmul_rn(A12, b1), __fmul_rn(A11, b2)), D);
-            np.x = __fadd_rn(np.x, delta.x);
-            np.y = __fadd_rn(np.y, delta.y);
-            nextPt = make_float2(__fadd_rn(np.x, half), __fadd_rn(np.y, half));
-            const double dd = (double)delta.x * (double)delta.x + (double)delta.y * (double)delta.y;
-            if (dd <= eps2) break;
-            if (j > 0 && fabs((double)__fadd_rn(delta.x, prevDelta.x)) < 0.01 &&
-                fabs((double)__fadd_rn(delta.y, prevDelta.y)) < 0.01) {
-                nextPt.x = __fsub_rn(nextPt.x, __fmul_rn(delta.x, 0.5f));
-                nextPt.y = __fsub_rn(nextPt.y, __fmul_rn(delta.y, 0.5f));
-                break;
-            }
-            prevDelta = delta;
+        }
+        {   // the chain warp's result: where the next level starts, whether the point is alive
+            const float4 nx = s_next;
+            nextPt = make_float2(nx.x, nx.y);
+            ok = nx.z != 0.f;
         }
     }
     // level-0 epilogue: `err` is requested by the reference (feature_tracker.cpp:24), so OpenCV

@@ -5,8 +5,8 @@ for v in $VARIANTS; do
 import json,sys
 d=json.loads(open('gpurun_out/v_$v.json').read().strip().splitlines()[-1])
 k=d['kernels']
-print('$v', round(d['value']), round(d['ms_per_step'],4), 'lk', round(k['lk_track_fwd']['ms_per_step'],4), round(k['lk_track_bwd']['ms_per_step'],4), 'cs', round(k['corner_score_nms']['ms_per_step'],4))
+print('$v', round(d['value']), round(d['ms_per_step'],4), 'lk', round(k['lk_track_fwd']['ms_per_step'],4), round(k['lk_track_bwd']['ms_per_step'],4), 'cs', round(k['corner_score_nms']['ms_per_step'],4), 'pyr', round(k['pyr_down_u8']['ms_per_step'],4))
 "
 done
 cp variants/libsvo_$TESTV.so stereo_vo_b200/libsvo.so; touch stereo_vo_b200/libsvo_host.so
-python -m pytest tests/test_gpu_track.py tests/test_gpu_pipeline.py tests/test_gpu_uhd_stress.py -x -q 2>&1 | tail -3
+python -m pytest $TESTS -x -q 2>&1 | tail -3

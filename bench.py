@@ -192,7 +192,7 @@ def ncu_matching_figures():
     out = {}
     for r in rows:
         name = r.get("kernel", "")
-        for key in ("lk_track_kernel", "stereo_bm_sparse_kernel", "sort_small_kernel",
+        for key in ("lk_track_kernel", "stereo_bm_sparse_48_21_kernel", "sort_small_kernel",
                     "greedy_select_kernel", "stereo_bm_dense_kernel"):
             if name.startswith(key) and key not in out:
                 def col(prefix):

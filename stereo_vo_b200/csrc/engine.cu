@@ -135,6 +135,11 @@ struct svo_engine {
     float2* d_reverse = nullptr;
     unsigned char* d_status2 = nullptr;
     int* d_kept_idx = nullptr;
+    // lk_track hand-over (backward pass of frame t -> forward pass of frame t + 1)
+    uint4* d_lk_data = nullptr;
+    SvoLkCacheHdr* d_lk_hdr = nullptr;
+    unsigned int* d_img_serial = nullptr;
+    unsigned int pyr_serial = 0;
     float* d_kept_par = nullptr;
     SvoTrackStats* d_stats = nullptr;
     float2* d_inl = nullptr;
@@ -629,7 +634,10 @@ cudaError_t push_calls(svo_engine* e, int n) {
 
 // levels 1.. of the current frames' pyramids (one launch per level, dependent launches)
 cudaError_t launch_pyramid(svo_engine* e, const SvoSeqCall* dc, int n, cudaStream_t st) {
-    return svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, st);
+    // every build gets its own serial: lk_track keys what it caches about an image with it
+    if (++e->pyr_serial == 0u) e->pyr_serial = 1u;
+    return svo_launch_pyr_down(e->d_pyr, e->lay, e->seq_stride, dc, n, st, e->d_img_serial,
+                               e->pyr_serial);
 }
 
 // pyramid + detection for the listed sequences (current frames already uploaded)
@@ -695,19 +703,20 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
     // yet. They track unconditionally (scratch outputs only); the gate is applied by the filter.
     const int* gate_lk = detect_done ? nullptr : gate;
     const int mf = e->p.max_features;
+    const SvoLkCache lkc = {e->d_lk_data, e->d_lk_hdr, e->d_img_serial, e->d_kept_idx};
     if (max_feat_in_call > 0) {
         {
             ProfScope ps(e, P_LKF);
             SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_feat,
                                             (size_t)2 * mf, 1, e->d_tracked, e->d_status1, mf, 0,
-                                            lp, mf, gate_lk, 4, nullptr, dc, n, e->st));
+                                            lp, mf, gate_lk, 4, nullptr, dc, n, e->st, lkc));
         }
         e->launches += 1;
         if (flow_back) {
             ProfScope ps(e, P_LKB);
             SVO_CUDA_OK(svo_launch_lk_track(e->d_pyr, e->lay, e->seq_stride, e->d_tracked,
                                             (size_t)mf, 0, e->d_reverse, e->d_status2, mf, 1, lp,
-                                            mf, gate_lk, 4, e->d_status1, dc, n, e->st));
+                                            mf, gate_lk, 4, e->d_status1, dc, n, e->st, lkc));
             e->launches += 1;
         }
     }
@@ -1207,6 +1216,20 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
     CCHK(dalloc(&e->d_status2, ns * mf));
     CCHK(dalloc(&e->d_kept_idx, ns * mf));
     CCHK(dalloc(&e->d_kept_par, ns * mf));
+    CCHK(cudaMemsetAsync(e->d_kept_idx, 0, ns * mf * sizeof(int), e->st));
+    CCHK(dalloc(&e->d_img_serial, ns * 2));
+    CCHK(cudaMemsetAsync(e->d_img_serial, 0, ns * 2 * sizeof(unsigned), e->st));
+    {
+        // 12 KB per tracked feature (4 levels x 63 window threads x 24 int16); SVO_LK_HANDOVER=0
+        // switches the hand-over off, and it is left out when it would not fit comfortably
+        static const bool want = [] { const char* v = getenv("SVO_LK_HANDOVER"); return !v || atoi(v) != 0; }();
+        const size_t data_bytes = ns * mf * (size_t)4 * 3 * 64 * sizeof(uint4);
+        if (want && e->lay.n_levels >= 2 && data_bytes <= ((size_t)8 << 30)) {
+            CCHK(dalloc(&e->d_lk_data, data_bytes / sizeof(uint4)));
+            CCHK(dalloc(&e->d_lk_hdr, ns * mf));
+            CCHK(cudaMemsetAsync(e->d_lk_hdr, 0, ns * mf * sizeof(SvoLkCacheHdr), e->st));
+        }
+    }
     CCHK(dalloc(&e->d_stats, ns));
     CCHK(dalloc(&e->d_inl, ns * mf));
     CCHK(dalloc(&e->d_pts, ns * cap));
@@ -1259,7 +1282,7 @@ void svo_destroy(svo_engine* e) {
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
                      e->d_call, e->d_kcall, e->d_pnp_world, e->d_pnp_img, e->d_pnp_counts,
                      e->d_pnp_guess, e->d_pnp_res, e->d_pnp_inl, e->d_ba, e->d_draw,
-                     e->d_strips_big, e->d_cand_big};
+                     e->d_strips_big, e->d_cand_big, e->d_lk_data, e->d_lk_hdr, e->d_img_serial};
     for (void* p : dptrs) if (p) cudaFree(p);
     if (e->h_call) cudaFreeHost(e->h_call);
     if (e->h_pull) cudaFreeHost(e->h_pull);

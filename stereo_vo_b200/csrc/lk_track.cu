@@ -222,7 +222,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 int direction, int max_iters, double eps2, double min_eig_thr, int max_pts,
                 const int* __restrict__ gate, int gate_min,
                 const unsigned char* __restrict__ skip_status,
-                const SvoSeqCall* __restrict__ call) {
+                const SvoSeqCall* __restrict__ call, const SvoLkCache cache) {
     // I patch and J region of EVERY level are fetched up front (their positions are known
     // before any iteration: pt / 2^l, zero-flow guess for J), so a point pays the global-memory
     // latency once instead of once or twice per level; J is re-staged only when the window
@@ -265,6 +265,41 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     const uint8_t* __restrict__ pyrI = seq_base + (size_t)slot_i * lay.slot_bytes;
     const uint8_t* __restrict__ pyrJ = seq_base + (size_t)(1 - slot_i) * lay.slot_bytes;
 
+    // Hand-over between passes. The forward pass of frame t+1 looks at the same image (frame t)
+    // around the same points (the tracked positions) as the backward pass of frame t did: all
+    // that depends on I alone - the interpolated window I, Ix, Iy of every level, A11/A12/A22,
+    // 1/D, the min-eigenvalue verdict - is computed once, by the backward pass, and parked in
+    // global memory (12 KB per point as int16, OpenCV's own IWinBuf type). The forward pass
+    // takes it if the entry its feature came from carries the serial of this pyramid build and
+    // this very point, bit for bit; otherwise (new features, feature sets installed by the host,
+    // first frames) it computes everything as before. Either way the numbers are the same.
+    const bool c_store = direction == 1 && cache.data != nullptr;
+    bool cached = false;
+    unsigned c_status = 0;
+    size_t c_entry = (size_t)seq * max_pts + pi;
+    unsigned c_serial = 0;
+    if (cache.data != nullptr) {
+        c_serial = cache.img_serial[seq * 2 + slot_i];
+        if (direction == 0) {
+            const int src = cache.kept_idx[(size_t)seq * max_pts + pi];
+            c_entry = (size_t)seq * max_pts + min(max(src, 0), max_pts - 1);
+            const uint4 hd = __ldcg(reinterpret_cast<const uint4*>(cache.hdr + c_entry));
+            cached = c_serial != 0u && hd.x == c_serial && hd.y == __float_as_uint(pt.x) &&
+                     hd.z == __float_as_uint(pt.y);
+            c_status = hd.w;
+            // every level whose window origin lies inside the bordered image must be there
+            for (int l = 0; cached && l < lay.n_levels; ++l) {
+                const SvoLevel lv = lay.lvl[l];
+                const float inv = 1.f / (float)(1 << l);
+                const int ipx = (int)floorf(__fsub_rn(__fmul_rn(pt.x, inv), 10.f));
+                const int ipy = (int)floorf(__fsub_rn(__fmul_rn(pt.y, inv), 10.f));
+                const unsigned st = (c_status >> (8 * l)) & 0xffu;
+                if (!(ipx < -WIN || ipx >= lv.w || ipy < -WIN || ipy >= lv.h) && st != 1u && st != 3u)
+                    cached = false;
+            }
+        }
+    }
+
     // window pixels owned by this thread: row wy, columns wx0 .. wx0 + 7 (part 2: wx0 + 4;
     // thread 63 idles)
     const bool has_px = tid < WIN * 3;
@@ -294,8 +329,10 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         const int ipx = (int)floorf(__fsub_rn(__fmul_rn(pt.x, inv), half));
         const int ipy = (int)floorf(__fsub_rn(__fmul_rn(pt.y, inv), half));
         if (!(ipx < -WIN || ipx >= lv.w || ipy < -WIN || ipy >= lv.h)) {
-            const int oi = stage_region<IP, IP>(pyrI + lv.off, lv.w, lv.h, lv.pitch, ipx - 1,
-                                                ipy - 1, s_Iall[l], tid);
+            int oi = 0;
+            if (!cached)
+                oi = stage_region<IP, IP>(pyrI + lv.off, lv.w, lv.h, lv.pitch, ipx - 1, ipy - 1,
+                                          s_Iall[l], tid);
             const int oj = stage_region<JR, JR>(pyrJ + lv.off, lv.w, lv.h, lv.pitch, ipx - JM,
                                                 ipy - JM, s_Jall[l], tid);
             offs |= (unsigned)(oi | (oj << 2)) << (4 * l);
@@ -303,6 +340,7 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     }
     stage_wait();
     __syncthreads();
+    unsigned st_word = 0;                    // c_store: one status byte per level
     float2 nextPt = make_float2(0.f, 0.f);   // the value OpenCV keeps in nextPts[ptidx]
     bool ok = true;
 
@@ -322,16 +360,38 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
             if (l == 0) ok = false;
             continue;
         }
-        int w00, w01, w10, w11;
-        lk_weights(__fsub_rn(prevPt.x, (float)ipx), __fsub_rn(prevPt.y, (float)ipy), w00, w01,
-                   w10, w11);
-
         const int offI = (offs >> (4 * l)) & 3;      // staged before the loop
         const unsigned char* s_Ib = reinterpret_cast<const unsigned char*>(s_Iall[l]);
         unsigned* s_Jw = s_Jall[l];
         __syncthreads();                     // previous level's readers are done with s_B
 
         int ival[RUN], ixv[RUN], iyv[RUN];
+        float A11, A12, A22, D;
+        if (cached) {
+            // the backward pass of the previous frame left this level's window state
+            if (((c_status >> (8 * l)) & 0xffu) != 1u) {      // min-eigenvalue reject
+                if (l == 0) ok = false;
+                continue;
+            }
+            const uint4* cd = cache.data + ((c_entry * LK_LEVELS + l) * 3) * NT + tid;
+            const uint4 q0 = __ldcs(cd), q1 = __ldcs(cd + NT), q2 = __ldcs(cd + 2 * NT);
+            const float4 ca = __ldcg(&cache.hdr[c_entry].a[l]);
+            const unsigned wi[4] = {q0.x, q0.y, q0.z, q0.w}, wx[4] = {q1.x, q1.y, q1.z, q1.w},
+                           wv[4] = {q2.x, q2.y, q2.z, q2.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                ival[2 * k] = 256 - (int)((wi[k] & 0xffffu) << 9);
+                ival[2 * k + 1] = 256 - (int)((wi[k] >> 16) << 9);
+                ixv[2 * k] = (int)(short)(wx[k] & 0xffffu);
+                ixv[2 * k + 1] = (int)wx[k] >> 16;
+                iyv[2 * k] = (int)(short)(wv[k] & 0xffffu);
+                iyv[2 * k + 1] = (int)wv[k] >> 16;
+            }
+            A11 = ca.x; A12 = ca.y; A22 = ca.z; D = ca.w;
+        } else {
+        int w00, w01, w10, w11;
+        lk_weights(__fsub_rn(prevPt.x, (float)ipx), __fsub_rn(prevPt.y, (float)ipy), w00, w01,
+                   w10, w11);
         // every corner of every window pixel inside the image <=> no zero-border derivative
         const bool grid_inside = ipx >= 0 && ipy >= 0 && ipx + WIN < w && ipy + WIN < h;
         if (grid_inside) {
@@ -416,6 +476,19 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 iyv[t] = (dy[0] * w00 + dy[1] * w01 + dy[DG] * w10 + dy[DG + 1] * w11 + 8192) >> 14;
             }
         }
+        if (c_store) {                       // hand the window to the next frame's forward pass
+            unsigned wi[4], wx[4], wv[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                wi[k] = __byte_perm((unsigned)ival[2 * k], (unsigned)ival[2 * k + 1], 0x5410);
+                wx[k] = __byte_perm((unsigned)ixv[2 * k], (unsigned)ixv[2 * k + 1], 0x5410);
+                wv[k] = __byte_perm((unsigned)iyv[2 * k], (unsigned)iyv[2 * k + 1], 0x5410);
+            }
+            uint4* cd = cache.data + ((c_entry * LK_LEVELS + l) * 3) * NT + tid;
+            __stcs(cd, make_uint4(wi[0], wi[1], wi[2], wi[3]));
+            __stcs(cd + NT, make_uint4(wx[0], wx[1], wx[2], wx[3]));
+            __stcs(cd + 2 * NT, make_uint4(wv[0], wv[1], wv[2], wv[3]));
+        }
 #pragma unroll
         for (int t = 0; t < RUN; ++t) ival[t] = 256 - (ival[t] << 9);   // see the iteration
         // ---- A11, A12, A22: per-pixel f32 products in chain order, then sequential chains.
@@ -454,19 +527,25 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
         }
         __syncthreads();
         const float iA11 = s_sum[0], iA12 = s_sum[1], iA22 = s_sum[2];
-        const float A11 = __fmul_rn(iA11, FLT_SCALE);
-        const float A12 = __fmul_rn(iA12, FLT_SCALE);
-        const float A22 = __fmul_rn(iA22, FLT_SCALE);
-        float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
+        A11 = __fmul_rn(iA11, FLT_SCALE);
+        A12 = __fmul_rn(iA12, FLT_SCALE);
+        A22 = __fmul_rn(iA22, FLT_SCALE);
+        D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
         const float dif = __fsub_rn(A11, A22);
         const float rad = __fadd_rn(__fmul_rn(dif, dif), __fmul_rn(__fmul_rn(4.f, A12), A12));
         const float minEig =
             __fdiv_rn(__fsub_rn(__fadd_rn(A22, A11), __fsqrt_rn(rad)), (float)(2 * WIN * WIN));
         if ((double)minEig < min_eig_thr || D < 1.1920928955078125e-7f) {
+            st_word |= 3u << (8 * l);
             if (l == 0) ok = false;
             continue;
         }
         D = __fdiv_rn(1.f, D);
+        if (c_store) {
+            st_word |= 1u << (8 * l);
+            if (tid == 0) cache.hdr[c_entry].a[l] = make_float4(A11, A12, A22, D);
+        }
+        }
 
         // b terms: a SIMD part sums the pixel pairs (p, p + 4) in int32 (OpenCV's v_dotprod
         // lanes), the tail part takes pixels 0..4 one by one. With the upper derivatives of the
@@ -632,6 +711,9 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     if (tid == 0) {
         out_pts[(size_t)seq * out_stride + pi] = nextPt;
         status[(size_t)seq * out_stride + pi] = ok ? 1 : 0;
+        if (c_store)                         // the entry is complete: key it
+            *reinterpret_cast<uint4*>(cache.hdr + c_entry) =
+                make_uint4(c_serial, __float_as_uint(pt.x), __float_as_uint(pt.y), st_word);
     }
 }
 
@@ -642,7 +724,8 @@ cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, siz
                                 float2* out_pts, unsigned char* status, int out_stride,
                                 int direction, SvoLkParams lp, int max_pts, const int* gate,
                                 int gate_min, const unsigned char* skip_status,
-                                const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
+                                const SvoSeqCall* d_call, int n_call, cudaStream_t st,
+                                SvoLkCache cache) {
     if (max_pts <= 0 || n_call <= 0) return cudaSuccess;
     // 16 blocks of 64 threads and 13.9 KB per SM: the window-sum chains are latency-bound
     // (one dependent FADD every 4 cycles), so resident blocks are what fills the issue slots
@@ -653,6 +736,6 @@ cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, siz
     lk_track_kernel<<<grid, NT, 0, st>>>(pyr, lay, seq_stride, in_pts, in_stride, in_buffered,
                                          out_pts, status, out_stride, direction, lp.max_iters,
                                          lp.eps2, lp.min_eig, max_pts, gate, gate_min,
-                                         skip_status, d_call);
+                                         skip_status, d_call, cache);
     return cudaGetLastError();
 }

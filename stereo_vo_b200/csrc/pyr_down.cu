@@ -127,7 +127,8 @@ __device__ __forceinline__ void pyr_tile(uint8_t* __restrict__ slot, const SvoLe
 template <int ROWS>
 __global__ void __launch_bounds__(32 * BANDS)
 pyr_down_u8_kernel(uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrLayout lay,
-                   size_t seq_stride, int level, const SvoSeqCall* __restrict__ call) {
+                   size_t seq_stride, int level, const SvoSeqCall* __restrict__ call,
+                   unsigned int* __restrict__ img_serial, unsigned int serial) {
     // programmatic dependent launch: the next level's grid may be scheduled while this one
     // runs (its blocks wait below until this grid's stores are visible), so the three launches
     // of a pyramid overlap their launch latency and ramp-up instead of paying them in series
@@ -135,6 +136,9 @@ pyr_down_u8_kernel(uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrLayo
     const SvoSeqCall* c = call + blockIdx.z;
     uint8_t* slot = pyr + (size_t)c->seq * seq_stride + (size_t)c->cur_slot * lay.slot_bytes;
     if (level > 0) cudaGridDependencySynchronize();
+    // a new image in this slot: whatever lk_track cached about the old one is void
+    else if (img_serial && (blockIdx.x | blockIdx.y | threadIdx.x | threadIdx.y) == 0)
+        img_serial[c->seq * 2 + c->cur_slot] = serial;
     pyr_tile<ROWS>(slot, lay.lvl[level], lay.lvl[level + 1],
                           (blockIdx.x * 32 + threadIdx.x) * 4,
                           (blockIdx.y * BANDS + threadIdx.y) * ROWS);
@@ -143,7 +147,8 @@ pyr_down_u8_kernel(uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrLayo
 }  // namespace
 
 cudaError_t svo_launch_pyr_down(uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
-                                const SvoSeqCall* d_call, int n_call, cudaStream_t st) {
+                                const SvoSeqCall* d_call, int n_call, cudaStream_t st,
+                                unsigned int* img_serial, unsigned int serial) {
     // fewer rows per thread on the small levels: the grid, not the row overlap, is what counts
     for (int l = 0; l + 1 < lay.n_levels; ++l) {
         const SvoLevel& d = lay.lvl[l + 1];
@@ -158,9 +163,9 @@ cudaError_t svo_launch_pyr_down(uint8_t* pyr, const SvoPyrLayout& lay, size_t se
         cfg.attrs = attr;
         cfg.numAttrs = l > 0 ? 1 : 0;       // levels 2, 3 may start under the level before
         cudaError_t ce;
-        if (rows == 8) ce = cudaLaunchKernelEx(&cfg, pyr_down_u8_kernel<8>, pyr, lay, seq_stride, l, d_call);
-        else if (rows == 4) ce = cudaLaunchKernelEx(&cfg, pyr_down_u8_kernel<4>, pyr, lay, seq_stride, l, d_call);
-        else ce = cudaLaunchKernelEx(&cfg, pyr_down_u8_kernel<2>, pyr, lay, seq_stride, l, d_call);
+        if (rows == 8) ce = cudaLaunchKernelEx(&cfg, pyr_down_u8_kernel<8>, pyr, lay, seq_stride, l, d_call, img_serial, serial);
+        else if (rows == 4) ce = cudaLaunchKernelEx(&cfg, pyr_down_u8_kernel<4>, pyr, lay, seq_stride, l, d_call, img_serial, serial);
+        else ce = cudaLaunchKernelEx(&cfg, pyr_down_u8_kernel<2>, pyr, lay, seq_stride, l, d_call, img_serial, serial);
         if (ce != cudaSuccess) return ce;
     }
     return cudaGetLastError();

@@ -74,8 +74,10 @@ __host__ __device__ __forceinline__ unsigned int svo_key_float_bits(unsigned int
 // ------------------------------------------------------------------ launchers (one per .cu)
 // Every launcher is asynchronous on `st`; `n_call` sequences are listed in `d_call`.
 
+// img_serial (nullable): [n_seq][2] - the level-0 launch stamps `serial` on the slot it reads
 cudaError_t svo_launch_pyr_down(uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
-                                const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+                                const SvoSeqCall* d_call, int n_call, cudaStream_t st,
+                                unsigned int* img_serial = nullptr, unsigned int serial = 0);
 
 cudaError_t svo_launch_pyr_down_single(const uint8_t* src, int w, int h, int spitch,
                                        uint8_t* dst, int dpitch, cudaStream_t st);
@@ -181,13 +183,29 @@ struct SvoLkParams {
     int grid_pts;                // blocks per sequence to launch (0 = max_pts)
 };
 
+// Per-point window state handed from the backward pass of one frame to the forward pass of the
+// next (lk_track.cu). All pointers null: no hand-over.
+struct SvoLkCacheHdr {
+    unsigned int serial;         // pyramid build the I patches came from (0: never written)
+    float ptx, pty;              // the key-point, bit for bit
+    unsigned int status;         // one byte per level: 0 not reached, 1 stored, 3 min-eigenvalue reject
+    float4 a[4];                 // A11, A12, A22 (scaled), 1 / D per level (lk_track: <= 4 levels)
+};
+struct SvoLkCache {
+    uint4* data;                 // [n_seq * max_pts][levels][3][64 threads]: packed int16 I, Ix, Iy
+    SvoLkCacheHdr* hdr;          // [n_seq * max_pts]
+    const unsigned int* img_serial;   // [n_seq][2 slots]: stamped by every pyramid build
+    const int* kept_idx;         // [n_seq][max_pts]: tracked-array index of tracker feature k
+};
+
 // direction 0: prev slot -> cur slot ; direction 1: cur slot -> prev slot
 cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
                                 const float2* in_pts, size_t in_stride, int in_buffered,
                                 float2* out_pts, unsigned char* status, int out_stride,
                                 int direction, SvoLkParams lp, int max_pts, const int* gate,
                                 int gate_min, const unsigned char* skip_status,
-                                const SvoSeqCall* d_call, int n_call, cudaStream_t st);
+                                const SvoSeqCall* d_call, int n_call, cudaStream_t st,
+                                SvoLkCache cache = SvoLkCache{nullptr, nullptr, nullptr, nullptr});
 
 struct SvoTrackStats {
     float av_parallax;

@@ -28,6 +28,7 @@
  *    SVO_CORNER_FORCE_REPAIR = 1       every segment re-walks (exercises the repair path)
  *    SVO_STEREO_GENERIC = 1            sparse StereoBM: generic kernel even for (48, 21)
  *    SVO_SPLIT_STREAMS = 0 | 1         detection and tracking of a step on two streams
+ *    SVO_LK_HANDOVER = 0               no backward -> forward hand-over in lk_track (svo_lk_handover)
  *    libsvo_host.so (svo::BatchFrontEnd): SVO_BATCH_LAZY_RIGHT, SVO_BATCH_ZERO_COPY_RIGHT
  *    (how right images reach the device), SVO_BATCH_TRACE (per-step trace on stderr)
  */
@@ -114,6 +115,19 @@ SVO_API int64_t svo_kernel_launches(const svo_engine* e);
  * SVO_ERR_NOMEM if that fails) and return what OpenCV returns. svo_step_keyframe cannot - its
  * keyframe stage has consumed the corners by then - and reports SVO_ERR_CAPACITY. */
 SVO_API int64_t svo_detector_spills(const svo_engine* e);
+/* The hand-over inside svo_tracker_track / svo_step (feature_tracker.cpp:23-26,32-35 call
+ * calcOpticalFlowPyrLK twice per frame): the forward pass of frame t+1 interpolates the same
+ * image (frame t) around the same points (the tracked positions) as the backward pass of frame t
+ * did, so the backward pass leaves its per-level window state (I, Ix, Iy as int16, the
+ * spatial-gradient matrix, the min-eigenvalue verdict: 12 KB per feature) on the device and the
+ * next forward pass takes it instead of recomputing it - only if the entry carries the serial of
+ * the same pyramid build and the same point bit for bit, so results never depend on it.
+ * enable: 1 / 0 switch it on / off for this engine (on by default unless SVO_LK_HANDOVER=0 or
+ * the buffers would exceed 8 GB), -1 leave as is. count: 1 / 0 count forward-pass look-ups and
+ * hits from now on (a device atomic per feature), -1 leave as is. lookups / hits (nullable):
+ * totals since counting was switched on (waits for the engine's stream). Returns SVO_OK, or
+ * SVO_ERR_INVALID when enable = 1 is asked of an engine created without the buffers. */
+SVO_API int svo_lk_handover(svo_engine* e, int enable, int count, int64_t* lookups, int64_t* hits);
 /* device-side time of the last svo_step()/stage call's kernels, CUDA events on the engine stream */
 SVO_API float svo_last_gpu_ms(const svo_engine* e);
 /* ms[0] input copies, ms[1] kernels, ms[2] result copy of the last call (CUDA events) */

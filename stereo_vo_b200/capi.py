@@ -56,7 +56,7 @@ EXPORTS = [
     "svo_device_alloc", "svo_device_free", "svo_device_upload", "svo_host_alloc", "svo_host_free",
     "svo_set_profiling", "svo_profile_slots", "svo_profile_name", "svo_get_profile",
     "svo_timer_begin", "svo_timer_end", "svo_pnp_ransac", "svo_reprojection_evaluate", "svo_draw_track", "svo_set_blocking_sync",
-    "svo_dedupe_static", "svo_detector_spills",
+    "svo_dedupe_static", "svo_detector_spills", "svo_lk_handover",
 ]
 
 _lib = None
@@ -123,6 +123,7 @@ def load_library(path: Optional[str] = None):
     lib.svo_pnp_ransac.argtypes = [vp, i32, vp, vp, vp, f32, f32, f32, i32, f32, C.c_double, vp, vp, vp]
     lib.svo_detector_spills.argtypes = [vp]
     lib.svo_detector_spills.restype = C.c_int64
+    lib.svo_lk_handover.argtypes = [vp, i32, i32, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
     lib.svo_dedupe_static.argtypes = [i32, vp, i32, vp, i32, f32, vp, vp, vp, vp, i32, C.c_char_p,
                                       C.c_size_t]
     lib.svo_device_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
@@ -255,6 +256,14 @@ class Engine:
     def detector_spills(self) -> int:
         """detections repeated on the spill lists (plateau images), svo_detector_spills"""
         return int(self.lib.svo_detector_spills(self.h))
+
+    def lk_handover(self, enable: int = -1, count: int = -1):
+        """svo_lk_handover: switch the backward -> forward hand-over of lk_track / its counters;
+        returns (look-ups, hits) of the forward passes since counting was switched on"""
+        a, b = C.c_int64(0), C.c_int64(0)
+        self._check(self.lib.svo_lk_handover(self.h, enable, count, C.byref(a), C.byref(b)),
+                    "svo_lk_handover")
+        return int(a.value), int(b.value)
 
     def last_timing(self):
         ms = (C.c_float * 3)()

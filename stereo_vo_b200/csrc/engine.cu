@@ -140,6 +140,9 @@ struct svo_engine {
     SvoLkCacheHdr* d_lk_hdr = nullptr;
     unsigned int* d_img_serial = nullptr;
     unsigned int pyr_serial = 0;
+    bool lk_handover = false;            // buffers present and switched on
+    bool lk_count = false;
+    unsigned long long* d_lk_stats = nullptr;
     float* d_kept_par = nullptr;
     SvoTrackStats* d_stats = nullptr;
     float2* d_inl = nullptr;
@@ -703,7 +706,10 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
     // yet. They track unconditionally (scratch outputs only); the gate is applied by the filter.
     const int* gate_lk = detect_done ? nullptr : gate;
     const int mf = e->p.max_features;
-    const SvoLkCache lkc = {e->d_lk_data, e->d_lk_hdr, e->d_img_serial, e->d_kept_idx};
+    SvoLkCache lkc = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (e->lk_handover)
+        lkc = SvoLkCache{e->d_lk_data, e->d_lk_hdr, e->d_img_serial, e->d_kept_idx,
+                         e->lk_count ? e->d_lk_stats : nullptr};
     if (max_feat_in_call > 0) {
         {
             ProfScope ps(e, P_LKF);
@@ -1228,6 +1234,9 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
             CCHK(dalloc(&e->d_lk_data, data_bytes / sizeof(uint4)));
             CCHK(dalloc(&e->d_lk_hdr, ns * mf));
             CCHK(cudaMemsetAsync(e->d_lk_hdr, 0, ns * mf * sizeof(SvoLkCacheHdr), e->st));
+            CCHK(dalloc(&e->d_lk_stats, 2));
+            CCHK(cudaMemsetAsync(e->d_lk_stats, 0, 2 * sizeof(unsigned long long), e->st));
+            e->lk_handover = true;
         }
     }
     CCHK(dalloc(&e->d_stats, ns));
@@ -1282,7 +1291,7 @@ void svo_destroy(svo_engine* e) {
                      e->d_disp16, e->d_valid2d, e->d_pts3d, e->d_valid_idx, e->d_nvalid, e->d_out,
                      e->d_call, e->d_kcall, e->d_pnp_world, e->d_pnp_img, e->d_pnp_counts,
                      e->d_pnp_guess, e->d_pnp_res, e->d_pnp_inl, e->d_ba, e->d_draw,
-                     e->d_strips_big, e->d_cand_big, e->d_lk_data, e->d_lk_hdr, e->d_img_serial};
+                     e->d_strips_big, e->d_cand_big, e->d_lk_data, e->d_lk_hdr, e->d_img_serial, e->d_lk_stats};
     for (void* p : dptrs) if (p) cudaFree(p);
     if (e->h_call) cudaFreeHost(e->h_call);
     if (e->h_pull) cudaFreeHost(e->h_pull);
@@ -1310,6 +1319,22 @@ int svo_get_params(const svo_engine* e, svo_params* out) {
 }
 int svo_num_levels(const svo_engine* e) { return e ? e->lay.n_levels : SVO_ERR_INVALID; }
 int64_t svo_detector_spills(const svo_engine* e) { return e ? e->spills : 0; }
+int svo_lk_handover(svo_engine* e, int enable, int count, int64_t* lookups, int64_t* hits) {
+    if (!e) return SVO_ERR_INVALID;
+    cudaSetDevice(e->device);
+    if (enable == 1 && !e->d_lk_data)
+        return fail(e, SVO_ERR_INVALID, "svo_lk_handover: this engine has no hand-over buffers");
+    if (enable >= 0) e->lk_handover = enable != 0;
+    if (count >= 0) e->lk_count = count != 0 && e->d_lk_stats;
+    unsigned long long st[2] = {0, 0};
+    if ((lookups || hits) && e->d_lk_stats) {
+        ECUDA(e, cudaMemcpyAsync(st, e->d_lk_stats, sizeof(st), cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, cudaStreamSynchronize(e->st));
+    }
+    if (lookups) *lookups = (int64_t)st[0];
+    if (hits) *hits = (int64_t)st[1];
+    return SVO_OK;
+}
 int64_t svo_kernel_launches(const svo_engine* e) { return e ? e->launches : 0; }
 float svo_last_gpu_ms(const svo_engine* e) { return e ? e->last_ms[1] : 0.f; }
 int svo_last_timing(const svo_engine* e, float ms[3]) {

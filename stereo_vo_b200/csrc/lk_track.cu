@@ -297,6 +297,10 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 if (!(ipx < -WIN || ipx >= lv.w || ipy < -WIN || ipy >= lv.h) && st != 1u && st != 3u)
                     cached = false;
             }
+            if (cache.stats && tid == 0) {
+                atomicAdd(cache.stats, 1ull);
+                if (cached) atomicAdd(cache.stats + 1, 1ull);
+            }
         }
     }
 

@@ -196,6 +196,7 @@ struct SvoLkCache {
     SvoLkCacheHdr* hdr;          // [n_seq * max_pts]
     const unsigned int* img_serial;   // [n_seq][2 slots]: stamped by every pyramid build
     const int* kept_idx;         // [n_seq][max_pts]: tracked-array index of tracker feature k
+    unsigned long long* stats;   // nullable: [0] forward-pass look-ups, [1] hits
 };
 
 // direction 0: prev slot -> cur slot ; direction 1: cur slot -> prev slot
@@ -205,7 +206,7 @@ cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, siz
                                 int direction, SvoLkParams lp, int max_pts, const int* gate,
                                 int gate_min, const unsigned char* skip_status,
                                 const SvoSeqCall* d_call, int n_call, cudaStream_t st,
-                                SvoLkCache cache = SvoLkCache{nullptr, nullptr, nullptr, nullptr});
+                                SvoLkCache cache = SvoLkCache{nullptr, nullptr, nullptr, nullptr, nullptr});
 
 struct SvoTrackStats {
     float av_parallax;

@@ -114,3 +114,43 @@ def test_track_multi_frame_chain(eng, oracle):
         assert abs(float(av) - float(av_ref)) <= PAR_TOL
         assert lost == lost_ref
 
+
+
+def test_backward_to_forward_handover_is_used_and_changes_nothing(svo_lib, oracle):
+    """lk_track hands the window state of the backward pass to the next frame's forward pass
+    (svo_lk_handover). Same frames through an engine with the hand-over and one without: every
+    LK output bit for bit equal; the hand-over engine must actually hit (every kept feature of
+    every frame after the first tracked one), and newly installed feature sets must miss."""
+    from stereo_vo_b200.capi import Engine
+    fr = util.frames(6, 8)
+    pts = oracle.detect(fr[0][0])
+    ids = np.arange(len(pts), dtype=np.uint64)
+    on, off = Engine(1241, 376, n_seq=1), Engine(1241, 376, n_seq=1)
+    try:
+        on.lk_handover(enable=1, count=1)
+        off.lk_handover(enable=0, count=1)
+        for e in (on, off):
+            e.tracker_init(fr[0][0], pts, ids)
+        kept_before = []
+        for t in range(1, 8):
+            kept_before.append(on.tracker_get()[0].shape[0])
+            ra, rb = on.tracker_track(fr[t][0], True), off.tracker_track(fr[t][0], True)
+            assert ra == rb, f"frame {t}: statistics"
+            da, db = on.tracker_debug(), off.tracker_debug()
+            for key in ("tracked", "status1", "reverse", "status2", "kept_idx"):
+                assert np.array_equal(da[key], db[key]), f"frame {t}: {key}"
+            fa, fb = on.tracker_get(), off.tracker_get()
+            assert np.array_equal(fa[0], fb[0]) and list(fa[1]) == list(fb[1]), f"frame {t}"
+            if t == 4:      # the host installs a feature set: look-ups of the next frame must miss
+                for e in (on, off):
+                    e.tracker_init(fr[t][0], fa[0][::-1].copy(), np.asarray(fa[1][::-1], np.uint64))
+        lookups, hits = on.lk_handover()
+        # frame 1 (no backward pass yet) and frame 5 (set installed by the host, reversed order:
+        # the index map no longer leads to the entries) recompute; frames 2-4, 6, 7 take it
+        assert lookups == sum(kept_before)
+        expect = sum(kept_before[i] for i in (1, 2, 3, 5, 6))
+        assert hits >= expect - 2 and hits <= expect + kept_before[4], (lookups, hits, kept_before)
+        assert off.lk_handover() == (0, 0)
+    finally:
+        on.close()
+        off.close()

@@ -1,5 +1,5 @@
 for v in $VARIANTS; do
-  cp variants/libsvo_$v.so stereo_vo_b200/libsvo.so; touch stereo_vo_b200/libsvo_host.so
+  cp tools/dev/variants/libsvo_$v.so stereo_vo_b200/libsvo.so; touch stereo_vo_b200/libsvo_host.so
   python bench.py --steps 100 --warmup 4 --min-seconds 1 --skip-cpu-baseline --skip-e2e --skip-closed-loop --skip-extras > gpurun_out/v_$v.json 2> gpurun_out/v_$v.err
   python -c "
 import json,sys
@@ -8,5 +8,5 @@ k=d['kernels']
 print('$v', round(d['value']), round(d['ms_per_step'],4), 'lk', round(k['lk_track_fwd']['ms_per_step'],4), round(k['lk_track_bwd']['ms_per_step'],4), 'cs', round(k['corner_score_nms']['ms_per_step'],4), 'pyr', round(k['pyr_down_u8']['ms_per_step'],4))
 "
 done
-cp variants/libsvo_$TESTV.so stereo_vo_b200/libsvo.so; touch stereo_vo_b200/libsvo_host.so
+cp tools/dev/variants/libsvo_$TESTV.so stereo_vo_b200/libsvo.so; touch stereo_vo_b200/libsvo_host.so
 python -m pytest $TESTS -x -q 2>&1 | tail -3

@@ -297,10 +297,6 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
                 if (!(ipx < -WIN || ipx >= lv.w || ipy < -WIN || ipy >= lv.h) && st != 1u && st != 3u)
                     cached = false;
             }
-            if (cache.stats && tid == 0) {
-                atomicAdd(cache.stats, 1ull);
-                if (cached) atomicAdd(cache.stats + 1, 1ull);
-            }
         }
     }
 
@@ -715,6 +711,12 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     if (tid == 0) {
         out_pts[(size_t)seq * out_stride + pi] = nextPt;
         status[(size_t)seq * out_stride + pi] = ok ? 1 : 0;
+        // (counted here, not at the look-up: two more live values up there made ptxas spill in
+        // the level prologue and cost the kernel 17 %)
+        if (direction == 0 && cache.stats) {
+            atomicAdd(cache.stats, 1ull);
+            if (cached) atomicAdd(cache.stats + 1, 1ull);
+        }
         if (c_store)                         // the entry is complete: key it
             *reinterpret_cast<uint4*>(cache.hdr + c_entry) =
                 make_uint4(c_serial, __float_as_uint(pt.x), __float_as_uint(pt.y), st_word);

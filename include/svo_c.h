@@ -29,6 +29,7 @@
  *    SVO_STEREO_GENERIC = 1            sparse StereoBM: generic kernel even for (48, 21)
  *    SVO_SPLIT_STREAMS = 0 | 1         detection and tracking of a step on two streams
  *    SVO_LK_HANDOVER = 0               no backward -> forward hand-over in lk_track (svo_lk_handover)
+ *    SVO_LK_REKEY = 1                  svo_tracker_set re-points the lk_track hand-over at the kept features (read by svo_create; off by default)
  *    libsvo_host.so (svo::BatchFrontEnd): SVO_BATCH_LAZY_RIGHT, SVO_BATCH_ZERO_COPY_RIGHT
  *    (how right images reach the device), SVO_BATCH_TRACE (per-step trace on stderr)
  */
@@ -122,6 +123,9 @@ SVO_API int64_t svo_detector_spills(const svo_engine* e);
  * spatial-gradient matrix, the min-eigenvalue verdict: 12 KB per feature) on the device and the
  * next forward pass takes it instead of recomputing it - only if the entry carries the serial of
  * the same pyramid build and the same point bit for bit, so results never depend on it.
+ * After svo_tracker_set (a feature list chosen by the host) the look-ups of the next frame miss
+ * and recompute; with SVO_LK_REKEY=1 in the environment of svo_create the call re-points the
+ * look-up at the entries of the features it kept (a small kernel on a side stream), so they hit.
  * enable: 1 / 0 switch it on / off for this engine (on by default unless SVO_LK_HANDOVER=0 or
  * the buffers would exceed 8 GB), -1 leave as is. count: 1 / 0 count forward-pass look-ups and
  * hits from now on (a device atomic per feature), -1 leave as is. lookups / hits (nullable):

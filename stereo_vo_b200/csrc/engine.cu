@@ -141,6 +141,13 @@ struct svo_engine {
     unsigned int* d_img_serial = nullptr;
     unsigned int pyr_serial = 0;
     bool lk_handover = false;            // buffers present and switched on
+    // svo_tracker_set re-points the hand-over at the features the host kept (lk_rekey_kernel),
+    // on a high-priority stream of its own: a launch on the engine stream would queue behind
+    // the other engine groups' grids on every keyframe step
+    bool lk_rekey = false;
+    bool rekey_pending = false;          // ev_rekey not yet waited for by the engine stream
+    cudaStream_t st_rekey = nullptr;
+    cudaEvent_t ev_feat = nullptr, ev_rekey = nullptr;
     bool lk_count = false;
     unsigned long long* d_lk_stats = nullptr;
     float* d_kept_par = nullptr;
@@ -693,6 +700,14 @@ cudaError_t launch_detect(svo_engine* e, int n, bool with_pyramid, cudaStream_t 
     return cudaSuccess;
 }
 
+// the index map rebuilt by the last svo_tracker_set must be complete before anything on the
+// engine stream reads or rewrites kept_idx
+cudaError_t join_rekey(svo_engine* e) {
+    if (!e->rekey_pending) return cudaSuccess;
+    e->rekey_pending = false;
+    return cudaStreamWaitEvent(e->st, e->ev_rekey, 0);
+}
+
 cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_back, bool gated,
                          cudaEvent_t detect_done = nullptr) {
     const SvoSeqCall* dc = dev_call_slot(e);
@@ -707,6 +722,7 @@ cudaError_t launch_track(svo_engine* e, int n, int max_feat_in_call, int flow_ba
     const int* gate_lk = detect_done ? nullptr : gate;
     const int mf = e->p.max_features;
     SvoLkCache lkc = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    SVO_CUDA_OK(join_rekey(e));
     if (e->lk_handover)
         lkc = SvoLkCache{e->d_lk_data, e->d_lk_hdr, e->d_img_serial, e->d_kept_idx,
                          e->lk_count ? e->d_lk_stats : nullptr};
@@ -1237,6 +1253,14 @@ int svo_create(const svo_params* pp, int32_t device, int32_t n_seq, svo_engine**
             CCHK(dalloc(&e->d_lk_stats, 2));
             CCHK(cudaMemsetAsync(e->d_lk_stats, 0, 2 * sizeof(unsigned long long), e->st));
             e->lk_handover = true;
+            if (const char* v = getenv("SVO_LK_REKEY")) e->lk_rekey = atoi(v) != 0;
+            if (e->lk_rekey) {
+                int least = 0, greatest = 0;
+                CCHK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+                CCHK(cudaStreamCreateWithPriority(&e->st_rekey, cudaStreamNonBlocking, greatest));
+                CCHK(cudaEventCreateWithFlags(&e->ev_feat, cudaEventDisableTiming));
+                CCHK(cudaEventCreateWithFlags(&e->ev_rekey, cudaEventDisableTiming));
+            }
         }
     }
     CCHK(dalloc(&e->d_stats, ns));
@@ -1284,6 +1308,7 @@ void svo_destroy(svo_engine* e) {
     if (e->st) cudaStreamSynchronize(e->st);
     if (e->st_copy) cudaStreamSynchronize(e->st_copy);
     if (e->st_det) cudaStreamSynchronize(e->st_det);
+    if (e->st_rekey) cudaStreamSynchronize(e->st_rekey);
     void* dptrs[] = {e->d_stage, e->d_pyr, e->d_right, e->d_dense, e->d_eig, e->d_eig_max, e->d_cand, e->d_cand_count,
                      e->d_strips, e->d_strip_count, e->d_sub_max, e->d_seg_flag, e->d_seg_state, e->d_cs_ticket, e->d_cs_work, e->d_corners, e->d_ncorners, e->d_grid, e->d_feat, e->d_ids, e->d_initial,
                      e->d_tracked, e->d_status1, e->d_reverse, e->d_status2, e->d_kept_idx,
@@ -1305,6 +1330,9 @@ void svo_destroy(svo_engine* e) {
     for (auto& pfe : e->pf) if (pfe.done) cudaEventDestroy(pfe.done);
     if (e->st_copy) cudaStreamDestroy(e->st_copy);
     if (e->st_det) cudaStreamDestroy(e->st_det);
+    if (e->st_rekey) cudaStreamDestroy(e->st_rekey);
+    if (e->ev_feat) cudaEventDestroy(e->ev_feat);
+    if (e->ev_rekey) cudaEventDestroy(e->ev_rekey);
     if (e->ev_fork) cudaEventDestroy(e->ev_fork);
     if (e->ev_join) cudaEventDestroy(e->ev_join);
     if (e->ev_block) cudaEventDestroy(e->ev_block);
@@ -1953,6 +1981,29 @@ int svo_tracker_set(svo_engine* e, int32_t n, const int32_t* seqs, const svo_flo
         s.last_slot = s.cur_slot;      // last_image = image.clone()  (feature_tracker.cpp:14)
     }
     ECUDA(e, pl.launch());
+    if (e->lk_handover && e->lk_rekey) {
+        // point the hand-over index map at the entries of the features the host kept
+        // (lk_track.cu: lk_rekey_kernel), 32 sequences per launch, behind the copy of the lists;
+        // launch_track waits for it before the next forward pass
+        const SvoLkCache lkc = {e->d_lk_data, e->d_lk_hdr, e->d_img_serial, e->d_kept_idx, nullptr};
+        ECUDA(e, cudaEventRecord(e->ev_feat, e->st));
+        ECUDA(e, cudaStreamWaitEvent(e->st_rekey, e->ev_feat, 0));
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            SvoLkRekey rk;
+            rk.n = std::min(32, n - i0);
+            for (int i = 0; i < rk.n; ++i) {
+                const SeqState& s = e->seq[seqs[i0 + i]];
+                rk.seq[i] = seqs[i0 + i];
+                rk.slot[i] = s.cur_slot;
+                rk.feat_buf[i] = s.feat_buf;
+                rk.count[i] = counts[i0 + i];
+            }
+            ECUDA(e, svo_launch_lk_rekey(e->d_feat, mf, rk, lkc, e->d_kept_idx, e->st_rekey));
+            e->launches += 1;
+        }
+        ECUDA(e, cudaEventRecord(e->ev_rekey, e->st_rekey));
+        e->rekey_pending = true;
+    }
     ECUDA(e, cudaEventRecord(e->ev_trk, e->st));
     return SVO_OK;
 }
@@ -2040,6 +2091,7 @@ int svo_tracker_debug(svo_engine* e, int32_t seq, svo_float2* tracked, uint8_t* 
         if (status1) ECUDA(e, cudaMemcpyAsync(status1, e->d_status1 + b, (size_t)na, cudaMemcpyDeviceToHost, e->st));
         if (reverse) ECUDA(e, cudaMemcpyAsync(reverse, e->d_reverse + b, (size_t)na * sizeof(float2), cudaMemcpyDeviceToHost, e->st));
         if (status2) ECUDA(e, cudaMemcpyAsync(status2, e->d_status2 + b, (size_t)na, cudaMemcpyDeviceToHost, e->st));
+        ECUDA(e, join_rekey(e));
         if (kept_idx && s.n_feat > 0) ECUDA(e, cudaMemcpyAsync(kept_idx, e->d_kept_idx + b, (size_t)s.n_feat * sizeof(int), cudaMemcpyDeviceToHost, e->st));
         ECUDA(e, cudaStreamSynchronize(e->st));
     }

@@ -723,7 +723,68 @@ lk_track_kernel(const uint8_t* __restrict__ pyr, const __grid_constant__ SvoPyrL
     }
 }
 
+// ---- hand-over after the host installed a feature set ---------------------------------------
+// svo_tracker_set replaces the tracker's feature list (inliers picked by the host's pose step +
+// new features, feature_tracker.cpp:3-16), so the filter's index map no longer leads from
+// feature k to the entry the backward pass wrote for it. This kernel rebuilds the map: feature
+// k points at the entry that carries the current image's serial and the feature's very bits
+// (the tracked positions travel to the host and back unchanged), or at entry 0 when there is
+// none (new features) - the look-up in lk_track checks the key either way, so the map can only
+// turn recomputation into a hit, never change a number. It runs beside the copy of the list,
+// not inside lk_track: a scan there cost registers lk_track does not have.
+constexpr int RK_T = 256;
+__global__ void __launch_bounds__(RK_T)
+lk_rekey_kernel(const float2* __restrict__ feat, int max_pts,
+                const __grid_constant__ SvoLkRekey rk, SvoLkCacheHdr* hdr,
+                const unsigned int* __restrict__ img_serial, int* __restrict__ kept_idx) {
+    __shared__ unsigned int s_x[RK_T], s_y[RK_T], s_ok[RK_T];
+    const int ci = blockIdx.y;
+    const int seq = rk.seq[ci];
+    const int count = rk.count[ci];
+    const int k = blockIdx.x * RK_T + threadIdx.x;
+    if (blockIdx.x * RK_T >= count) return;              // whole block idle (uniform)
+    const unsigned int serial = img_serial[seq * 2 + rk.slot[ci]];
+    unsigned int px = 0u, py = 0u;
+    if (k < count) {
+        const float2 p = feat[((size_t)seq * 2 + rk.feat_buf[ci]) * max_pts + k];
+        px = __float_as_uint(p.x);
+        py = __float_as_uint(p.y);
+    }
+    int found = 0;
+    for (int j0 = 0; j0 < max_pts; j0 += RK_T) {
+        const int j = j0 + threadIdx.x;
+        unsigned int ok = 0u, hx = 0u, hy = 0u;
+        if (j < max_pts) {
+            const uint4 hd = __ldcg(reinterpret_cast<const uint4*>(hdr + (size_t)seq * max_pts + j));
+            ok = (serial != 0u && hd.x == serial) ? 1u : 0u;
+            hx = hd.y;
+            hy = hd.z;
+        }
+        __syncthreads();
+        s_x[threadIdx.x] = hx;
+        s_y[threadIdx.x] = hy;
+        s_ok[threadIdx.x] = ok;
+        __syncthreads();
+        const int m = min(RK_T, max_pts - j0);
+        for (int t = 0; t < m; ++t)
+            if (s_ok[t] && s_x[t] == px && s_y[t] == py) found = j0 + t;
+    }
+    if (k < count) kept_idx[(size_t)seq * max_pts + k] = found;
+}
+
 }  // namespace
+
+cudaError_t svo_launch_lk_rekey(const float2* feat, int max_pts,
+                                const SvoLkRekey& rk, const SvoLkCache& cache, int* kept_idx,
+                                cudaStream_t st) {
+    int most = 0;
+    for (int i = 0; i < rk.n; ++i) most = rk.count[i] > most ? rk.count[i] : most;
+    if (rk.n <= 0 || most <= 0 || cache.hdr == nullptr || max_pts <= 0) return cudaSuccess;
+    dim3 grid((most + RK_T - 1) / RK_T, rk.n);
+    lk_rekey_kernel<<<grid, RK_T, 0, st>>>(feat, max_pts, rk, cache.hdr,
+                                           cache.img_serial, kept_idx);
+    return cudaGetLastError();
+}
 
 cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
                                 const float2* in_pts, size_t in_stride, int in_buffered,

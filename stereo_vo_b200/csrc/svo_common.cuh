@@ -199,6 +199,16 @@ struct SvoLkCache {
     unsigned long long* stats;   // nullable: [0] forward-pass look-ups, [1] hits
 };
 
+// svo_tracker_set: sequences whose feature list the host just replaced (lk_rekey_kernel)
+struct SvoLkRekey {
+    int n;                       // entries used (<= 32)
+    int seq[32], slot[32];       // sequence, pyramid slot of its current image
+    int feat_buf[32], count[32]; // tracker feature buffer holding the new list, its length
+};
+cudaError_t svo_launch_lk_rekey(const float2* feat, int max_pts,
+                                const SvoLkRekey& rk, const SvoLkCache& cache, int* kept_idx,
+                                cudaStream_t st);
+
 // direction 0: prev slot -> cur slot ; direction 1: cur slot -> prev slot
 cudaError_t svo_launch_lk_track(const uint8_t* pyr, const SvoPyrLayout& lay, size_t seq_stride,
                                 const float2* in_pts, size_t in_stride, int in_buffered,

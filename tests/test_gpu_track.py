@@ -154,3 +154,59 @@ def test_backward_to_forward_handover_is_used_and_changes_nothing(svo_lib, oracl
     finally:
         on.close()
         off.close()
+
+
+def test_handover_survives_a_feature_set_installed_by_the_host(svo_lib, oracle, monkeypatch):
+    """svo_tracker_set (the facade's FeatureTracker::init on the resident frame, the closed loop
+    after every keyframe) re-points the hand-over index map at the entries of the features the
+    host kept (lk_rekey_kernel): a reordered subset of the tracked points must hit on the next
+    frame, points no entry exists for must miss, and every LK output stays bit for bit what an
+    engine without the hand-over computes."""
+    from stereo_vo_b200.capi import Engine
+    fr = util.frames(7, 6)
+    pts = oracle.detect(fr[0][0])
+    ids = np.arange(len(pts), dtype=np.uint64)
+    n_fresh = 40
+    monkeypatch.setenv("SVO_LK_REKEY", "1")          # read by svo_create
+    on, off = Engine(1241, 376, n_seq=1), Engine(1241, 376, n_seq=1)
+    try:
+        on.lk_handover(enable=1, count=1)
+        off.lk_handover(enable=0, count=1)
+        for e in (on, off):
+            e.tracker_init(fr[0][0], pts, ids)
+        looked, expect = 0, 0
+        can_hit = 0                      # frame 1: no backward pass has run yet
+        for t in range(1, 6):
+            looked += on.tracker_get()[0].shape[0]
+            expect += can_hit
+            ra, rb = on.tracker_track(fr[t][0], True), off.tracker_track(fr[t][0], True)
+            assert ra == rb, f"frame {t}: statistics"
+            da, db = on.tracker_debug(), off.tracker_debug()
+            for key in ("tracked", "status1", "reverse", "status2"):
+                assert np.array_equal(da[key], db[key]), f"frame {t}: {key}"
+            fa, fb = on.tracker_get(), off.tracker_get()
+            assert np.array_equal(fa[0], fb[0]) and list(fa[1]) == list(fb[1]), f"frame {t}"
+            can_hit = fa[0].shape[0]     # the filter's own index map
+            if t in (2, 3):
+                # the host keeps every second point, in reverse order; after frame 3 it also
+                # adds points that were never tracked
+                keep = fa[0][::2][::-1].copy()
+                keep_ids = np.asarray(fa[1][::2][::-1], np.uint64)
+                can_hit = keep.shape[0]
+                assert can_hit > 20
+                if t == 3:
+                    fresh = oracle.detect(fr[t][0])[:n_fresh] + np.float32(0.25)
+                    assert fresh.shape[0] == n_fresh
+                    keep = np.concatenate([keep, fresh], 0)
+                    keep_ids = np.concatenate(
+                        [keep_ids, 10_000 + np.arange(n_fresh, dtype=np.uint64)])
+                for e in (on, off):
+                    e.tracker_set([0], [keep], [keep_ids])
+        lookups, hits = on.lk_handover()
+        assert lookups == looked
+        # (a point whose window left the bordered image on some level has no complete entry)
+        assert expect - 4 <= hits <= expect, (lookups, hits, expect)
+        assert off.lk_handover() == (0, 0)
+    finally:
+        on.close()
+        off.close()

@@ -1826,7 +1826,8 @@ int svo_reprojection_evaluate(svo_engine* e, int32_t n_obs, const int32_t* pose_
     const size_t b_poses = (size_t)n_poses * 7 * 8, b_pts = (size_t)n_points * 3 * 8,
                  b_idx = (size_t)n_obs * 4, b_obs = (size_t)n_obs * 2 * 8;
     const size_t b_out = (size_t)n_obs * (2 + 14 + 6) * 8;
-    const size_t need = b_poses + b_pts + 2 * b_idx + b_obs + b_out + 1024;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };       // slices start 256-B aligned
+    const size_t need = up(b_poses) + up(b_pts) + 2 * up(b_idx) + up(b_obs) + b_out;
     if (need > e->ba_bytes) {
         if (e->d_ba) cudaFree(e->d_ba);
         e->d_ba = nullptr;
@@ -1837,7 +1838,6 @@ int svo_reprojection_evaluate(svo_engine* e, int32_t n_obs, const int32_t* pose_
         }
         e->ba_bytes = need;
     }
-    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
     unsigned char* base = e->d_ba;
     double* d_poses = reinterpret_cast<double*>(base); base += up(b_poses);
     double* d_pts = reinterpret_cast<double*>(base); base += up(b_pts);

@@ -50,6 +50,8 @@ PngInfo parse_png(const std::string& path, std::vector<unsigned char>* idat) {
             info.bit_depth = data[8];
             info.color_type = data[9];
             info.interlace = data[12];
+            if (info.width <= 0 || info.height <= 0 || info.width > 65536 || info.height > 65536)
+                bad(path, "implausible image size in IHDR");
             have_ihdr = true;
             if (!idat) return info;
         } else if (std::memcmp(type, "IDAT", 4) == 0) {

@@ -66,6 +66,56 @@ def test_frames_and_poses_match_the_reference_reader(kitti_tree):
         hostapi.KittiSource(root, "99")
 
 
+def test_malformed_pngs_are_refused_with_a_message(kitti_tree, tmp_path):
+    """A frame file that is not a sound 8-bit PNG of the sequence's size must end in an error
+    that names the file - never in a crash or a silently wrong image."""
+    import shutil
+    import struct
+    import zlib
+    from stereo_vo_b200 import build, hostapi
+    from stereo_vo_b200.capi import SvoError
+    if build.host_needs_build():
+        build.build_host_lib()
+    root, seq, n, poses, cam = kitti_tree
+    good = open(f"{root}{seq}/image_0/000000.png", "rb").read()
+
+    def tree_with(first_left: bytes):
+        base = tmp_path / f"t{len(os.listdir(tmp_path))}"
+        shutil.copytree(root, base)
+        with open(base / seq / "image_0" / "000000.png", "wb") as fh:
+            fh.write(first_left)
+        return str(base) + "/"
+
+    def chunk(kind: bytes, data: bytes) -> bytes:
+        return struct.pack(">I", len(data)) + kind + data + struct.pack(">I", zlib.crc32(kind + data))
+
+    def png(w, h, depth=8, color=0, payload=None):
+        raw = payload if payload is not None else zlib.compress(b"\0" * ((w + 1) * h))
+        ihdr = struct.pack(">IIBBBBB", w & 0xffffffff, h & 0xffffffff, depth, color, 0, 0, 0)
+        return b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", ihdr) + chunk(b"IDAT", raw) + chunk(b"IEND", b"")
+
+    # the size comes from the first left frame: implausible headers stop the constructor
+    for bad_file, what in [(good[:20], "not a PNG"), (b"JFIF" + good[4:], "not a PNG"),
+                           (png(0, 5), "implausible"), (png(-3, 5), "implausible"),
+                           (png(1 << 20, 5), "implausible")]:
+        with pytest.raises(SvoError, match=what):
+            hostapi.KittiSource(tree_with(bad_file), seq)
+    # a sound header with an unsound body fails at the read
+    for bad_file, what in [(good[:60], "truncated"), (png(cam.width, cam.height, depth=16), "8-bit"),
+                           (png(cam.width, cam.height, color=3), "palette"),
+                           (png(cam.width, cam.height, payload=b"garbage"), "inflate"),
+                           (png(cam.width, cam.height,
+                                payload=zlib.compress(b"\7" * ((cam.width + 1) * cam.height))), "filter"),
+                           (png(cam.width, cam.height - 1), "size differs")]:
+        base = tree_with(good)
+        src = hostapi.KittiSource(base, seq)
+        with open(f"{base}{seq}/image_1/000002.png", "wb") as fh:
+            fh.write(bad_file)
+        with pytest.raises(SvoError, match=what):
+            src.read(2)
+        src.close()
+
+
 @pytest.mark.gpu
 def test_decode_ahead_ring_feeds_the_front_end(kitti_tree, svo_lib):
     """The prefetcher thread decodes into a pinned ring while the GPU works on earlier frames:

@@ -7,6 +7,9 @@
  *                vo_node main loop, src/vo_node.cpp:112-119,141-144.
  *   svo_batch_*  many independent sequences per GPU (include/stereo_vo/batch_front_end.hpp).
  *   svo_camera_from_yaml   the camera YAML semantics of src/vo_node.cpp:82-98.
+ *   svo_kitti_*  the frame source of kitti_node (KITTI PNG pairs + pose file).
+ *   svo_image_to_mono8, svo_stereo_queue_*   the image-message side of vo_node
+ *                (cv_bridge::toCvCopy(..., MONO8), handle_images and its queue, the drain loop).
  *
  * Same conventions as svo_c.h: POD only, 0 on success / negative svo_status, nothing throws
  * across the boundary, *_last_error() returns the message of the last failure.
@@ -147,6 +150,44 @@ SVO_API int svo_kitti_prefetch_start(svo_kitti* k, uint8_t* slab, int32_t depth,
                                      int64_t first);
 SVO_API int svo_kitti_next(svo_kitti* k, int64_t* index, const uint8_t** left, const uint8_t** right,
                            double* pose12);
+
+/* ---- ROS image messages without ROS (src/vo_node.cpp:38-76,139-143; stereo_vo/image_msg.hpp) - */
+/* the fields of sensor_msgs/Image that cv_bridge reads */
+typedef struct svo_image_msg {
+    double stamp;            /* header.stamp.toSec() */
+    uint32_t height, width;
+    const char* encoding;    /* sensor_msgs::image_encodings name: mono8, mono16, rgb8, bgr8, ... */
+    uint8_t is_bigendian;
+    uint32_t step;           /* bytes per row */
+    const uint8_t* data;     /* step * height bytes */
+    size_t size;
+} svo_image_msg;
+/* cv_bridge::toCvCopy(msg, "mono8") (src/vo_node.cpp:70-71) into caller memory: height rows of
+ * width bytes, `pitch` apart. SVO_ERR_INVALID for a malformed message or an encoding cv_bridge
+ * cannot turn into mono8 (8UC1, 32FC1, ...); the text is in svo_image_last_error(). */
+SVO_API int svo_image_to_mono8(const svo_image_msg* msg, uint8_t* out, int32_t pitch);
+SVO_API const char* svo_image_last_error(void);
+
+/* handle_images + its queue<StereoPair> (src/vo_node.cpp:38-76): push converts a synchronised
+ * pair to mono8 and queues it unless its left stamp is less than drop_time (the node: 0.05 s)
+ * after the last queued pair's; *queued = 1 / 0 says which. */
+typedef struct svo_stereo_queue svo_stereo_queue;
+SVO_API int svo_stereo_queue_create(double drop_time, svo_stereo_queue** out);
+SVO_API void svo_stereo_queue_destroy(svo_stereo_queue* q);
+SVO_API const char* svo_stereo_queue_last_error(const svo_stereo_queue* q);   /* q may be NULL */
+SVO_API int svo_stereo_queue_push(svo_stereo_queue* q, const svo_image_msg* left,
+                                  const svo_image_msg* right, int32_t* queued);
+SVO_API int32_t svo_stereo_queue_size(const svo_stereo_queue* q);
+/* the node loop's drain (src/vo_node.cpp:140-143): every queued pair, oldest first, is handed to
+ * fn and popped after fn returned 0; a non-zero return stops the drain with the pair still at
+ * the front (SVO_ERR_STATE). *n_processed (nullable) counts the pairs popped. */
+typedef int (*svo_stereo_pair_fn)(void* user, const uint8_t* left, const uint8_t* right,
+                                  int32_t width, int32_t height, int32_t pitch_left,
+                                  int32_t pitch_right, double t);
+SVO_API int svo_stereo_queue_drain(svo_stereo_queue* q, svo_stereo_pair_fn fn, void* user,
+                                   int32_t* n_processed);
+/* the same with ImageProcessor::process of `v` as the consumer - vo_node's main loop body */
+SVO_API int svo_vo_process_queue(svo_vo* v, svo_stereo_queue* q, int32_t* n_processed);
 
 #ifdef __cplusplus
 }

@@ -27,7 +27,8 @@ HOST_LIB = os.path.join(HERE, "libsvo_host.so")
 HOST_DIR = os.path.join(HERE, "host")
 INCLUDE = os.path.join(HERE, "..", "include")
 HOST_SOURCES = ["bundle_adjuster.cpp", "camera_config.cpp", "feature_tracker.cpp",
-                "image_processor.cpp", "batch_front_end.cpp", "kitti_source.cpp", "host_c.cpp"]
+                "image_processor.cpp", "batch_front_end.cpp", "kitti_source.cpp", "image_msg.cpp",
+                "host_c.cpp"]
 CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wextra", "-pthread"]
 
 

@@ -10,6 +10,7 @@
 
 #include "stereo_vo/batch_front_end.hpp"
 #include "stereo_vo/camera_info.hpp"
+#include "stereo_vo/image_msg.hpp"
 #include "stereo_vo/image_processor.hpp"
 #include "stereo_vo/kitti_source.hpp"
 
@@ -52,6 +53,12 @@ struct svo_vo {
 
 struct svo_batch {
     std::unique_ptr<svo::BatchFrontEnd> fe;
+    std::string error;
+};
+
+struct svo_stereo_queue {
+    std::shared_ptr<std::queue<StereoPair>> pairs = std::make_shared<std::queue<StereoPair>>();
+    std::unique_ptr<handle_images> handler;
     std::string error;
 };
 
@@ -401,6 +408,98 @@ int svo_kitti_next(svo_kitti* k, int64_t* index, const uint8_t** left, const uin
         }
     });
     return rc != SVO_OK ? rc : got;
+}
+
+// ------------------------------------------------- image messages, handle_images, drain loop
+namespace {
+svo::ImageMsg msg_of(const svo_image_msg* m) {
+    if (!m || !m->encoding) throw std::invalid_argument("image message or its encoding is null");
+    svo::ImageMsg o;
+    o.stamp = m->stamp;
+    o.height = m->height;
+    o.width = m->width;
+    o.encoding = m->encoding;
+    o.is_bigendian = m->is_bigendian;
+    o.step = m->step;
+    o.data = m->data;
+    o.size = m->size;
+    return o;
+}
+}  // namespace
+
+int svo_image_to_mono8(const svo_image_msg* msg, uint8_t* out, int32_t pitch) {
+    return guarded(g_create_error, [&] {
+        if (pitch <= 0) throw std::invalid_argument("svo_image_to_mono8: pitch must be positive");
+        svo::to_mono8(msg_of(msg), out, (size_t)pitch);
+    });
+}
+
+const char* svo_image_last_error(void) { return g_create_error.c_str(); }
+
+int svo_stereo_queue_create(double drop_time, svo_stereo_queue** out) {
+    if (!out) return SVO_ERR_INVALID;
+    *out = nullptr;
+    return guarded(g_create_error, [&] {
+        auto q = std::make_unique<svo_stereo_queue>();
+        q->handler = std::make_unique<handle_images>(q->pairs, drop_time);
+        *out = q.release();
+    });
+}
+
+void svo_stereo_queue_destroy(svo_stereo_queue* q) { delete q; }
+
+const char* svo_stereo_queue_last_error(const svo_stereo_queue* q) {
+    return q ? q->error.c_str() : g_create_error.c_str();
+}
+
+int svo_stereo_queue_push(svo_stereo_queue* q, const svo_image_msg* left, const svo_image_msg* right,
+                          int32_t* queued) {
+    if (!q) return SVO_ERR_INVALID;
+    if (queued) *queued = 0;
+    return guarded(q->error, [&] {
+        const bool took = (*q->handler)(msg_of(left), msg_of(right));
+        if (queued) *queued = took ? 1 : 0;
+    });
+}
+
+int32_t svo_stereo_queue_size(const svo_stereo_queue* q) { return q ? (int32_t)q->pairs->size() : SVO_ERR_INVALID; }
+
+int svo_stereo_queue_drain(svo_stereo_queue* q, svo_stereo_pair_fn fn, void* user, int32_t* n_processed) {
+    if (!q || !fn) return SVO_ERR_INVALID;
+    if (n_processed) *n_processed = 0;
+    return guarded(q->error, [&] {
+        int32_t done = 0;
+        try {
+            svo::drain_queue(*q->pairs, [&](const StereoPair& p) {
+                const int rc = fn(user, p.left.data, p.right.data, p.left.cols, p.left.rows,
+                                  (int32_t)p.left.step, (int32_t)p.right.step, p.t);
+                if (rc != 0) throw std::logic_error("svo_stereo_queue_drain: the consumer returned " + std::to_string(rc));
+                ++done;
+            });
+        } catch (...) {
+            if (n_processed) *n_processed = done;
+            throw;
+        }
+        if (n_processed) *n_processed = done;
+    });
+}
+
+int svo_vo_process_queue(svo_vo* v, svo_stereo_queue* q, int32_t* n_processed) {
+    if (!v || !q) return SVO_ERR_INVALID;
+    if (n_processed) *n_processed = 0;
+    return guarded(v->error, [&] {
+        int32_t done = 0;
+        try {
+            svo::drain_queue(*q->pairs, [&](const StereoPair& p) {       // src/vo_node.cpp:140-143
+                v->processor->process(p);
+                ++done;
+            });
+        } catch (...) {
+            if (n_processed) *n_processed = done;
+            throw;
+        }
+        if (n_processed) *n_processed = done;
+    });
 }
 
 }  // extern "C"

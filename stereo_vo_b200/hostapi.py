@@ -44,6 +44,17 @@ class BatchSummary(C.Structure):
                 ("tracked", C.c_int64), ("new_points", C.c_int64), ("right_images", C.c_int64)]
 
 
+class ImageMsg(C.Structure):
+    """svo_image_msg: the fields of sensor_msgs/Image that cv_bridge reads"""
+    _fields_ = [("stamp", C.c_double), ("height", C.c_uint32), ("width", C.c_uint32),
+                ("encoding", C.c_char_p), ("is_bigendian", C.c_uint8), ("step", C.c_uint32),
+                ("data", C.c_void_p), ("size", C.c_size_t)]
+
+
+PAIR_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                      C.c_int32, C.c_double)
+
+
 def declared_symbols():
     """Every SVO_API function svo_host_c.h declares."""
     with open(HEADER) as fh:
@@ -108,6 +119,18 @@ def load_library():
     lib.svo_batch_get_profile.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     lib.svo_batch_engine.argtypes = [vp, i32]
     lib.svo_batch_engine.restype = vp
+    lib.svo_image_to_mono8.argtypes = [C.POINTER(ImageMsg), vp, i32]
+    lib.svo_image_last_error.argtypes = []
+    lib.svo_image_last_error.restype = C.c_char_p
+    lib.svo_stereo_queue_create.argtypes = [C.c_double, C.POINTER(vp)]
+    lib.svo_stereo_queue_destroy.argtypes = [vp]
+    lib.svo_stereo_queue_destroy.restype = None
+    lib.svo_stereo_queue_last_error.argtypes = [vp]
+    lib.svo_stereo_queue_last_error.restype = C.c_char_p
+    lib.svo_stereo_queue_push.argtypes = [vp, C.POINTER(ImageMsg), C.POINTER(ImageMsg), C.POINTER(i32)]
+    lib.svo_stereo_queue_size.argtypes = [vp]
+    lib.svo_stereo_queue_drain.argtypes = [vp, PAIR_FN, vp, C.POINTER(i32)]
+    lib.svo_vo_process_queue.argtypes = [vp, vp, C.POINTER(i32)]
     _lib = lib
     return lib
 
@@ -231,6 +254,94 @@ class VoSequence:
     def close(self):
         if self.h:
             self.lib.svo_vo_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def image_msg(data: np.ndarray, encoding: str, stamp: float = 0.0, step: Optional[int] = None,
+              big_endian: bool = False, width: Optional[int] = None) -> ImageMsg:
+    """An svo_image_msg over `data` (rows of `step` bytes; the array is kept alive by the
+    message). width defaults to what the row length and the encoding imply."""
+    buf = np.ascontiguousarray(data)
+    h = buf.shape[0]
+    row_bytes = buf.strides[0]
+    m = ImageMsg(float(stamp), h, int(width if width is not None else buf.shape[1]),
+                 encoding.encode(), 1 if big_endian else 0,
+                 int(step if step is not None else row_bytes), buf.ctypes.data, buf.nbytes)
+    m._keep = buf
+    return m
+
+
+def to_mono8(msg: ImageMsg, pitch: Optional[int] = None) -> np.ndarray:
+    """cv_bridge::toCvCopy(msg, "mono8") (svo_image_to_mono8)."""
+    lib = load_library()
+    pitch = int(pitch if pitch is not None else msg.width)
+    out = np.zeros((msg.height, max(pitch, 1)), np.uint8)
+    rc = lib.svo_image_to_mono8(C.byref(msg), out.ctypes.data, pitch)
+    if rc != 0:
+        raise SvoError(f"svo_image_to_mono8 failed ({rc}): "
+                       f"{lib.svo_image_last_error().decode(errors='replace')}")
+    return out[:, :msg.width]
+
+
+class StereoQueue:
+    """handle_images and its queue<StereoPair> (src/vo_node.cpp:38-76) plus the node loop's
+    drain (:140-143), svo_stereo_queue_*."""
+
+    def __init__(self, drop_time: float = 0.05):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.svo_stereo_queue_create(drop_time, C.byref(h))
+        if rc != 0:
+            raise SvoError(f"svo_stereo_queue_create failed ({rc})")
+        self.h = h
+
+    def _err(self, what, rc):
+        return SvoError(f"{what} failed ({rc}): "
+                        f"{self.lib.svo_stereo_queue_last_error(self.h).decode(errors='replace')}")
+
+    def push(self, left: ImageMsg, right: ImageMsg) -> bool:
+        took = C.c_int32(0)
+        rc = self.lib.svo_stereo_queue_push(self.h, C.byref(left), C.byref(right), C.byref(took))
+        if rc != 0:
+            raise self._err("svo_stereo_queue_push", rc)
+        return bool(took.value)
+
+    def __len__(self):
+        return int(self.lib.svo_stereo_queue_size(self.h))
+
+    def drain(self, consumer: Callable[[np.ndarray, np.ndarray, float], Optional[int]]) -> int:
+        """consumer(left, right, t) for every queued pair, oldest first; a non-zero return
+        stops the drain with that pair still queued. Returns the number of pairs popped."""
+        def cb(_user, lp, rp, w, h, pl, pr, t):
+            l = np.ctypeslib.as_array(C.cast(lp, C.POINTER(C.c_uint8)), (h, pl))[:, :w]
+            r = np.ctypeslib.as_array(C.cast(rp, C.POINTER(C.c_uint8)), (h, pr))[:, :w]
+            return int(consumer(l.copy(), r.copy(), t) or 0)
+        n = C.c_int32(0)
+        fn = PAIR_FN(cb)
+        rc = self.lib.svo_stereo_queue_drain(self.h, fn, None, C.byref(n))
+        self.last_drained = n.value
+        if rc != 0:
+            raise self._err("svo_stereo_queue_drain", rc)
+        return n.value
+
+    def process_all(self, vo: "VoSequence") -> int:
+        """vo_node's loop body: every queued pair through ImageProcessor::process of `vo`."""
+        n = C.c_int32(0)
+        rc = self.lib.svo_vo_process_queue(vo.h, self.h, C.byref(n))
+        if rc != 0:
+            raise SvoError(f"svo_vo_process_queue failed ({rc}): "
+                           f"{self.lib.svo_vo_last_error(vo.h).decode(errors='replace')}")
+        return n.value
+
+    def close(self):
+        if self.h:
+            self.lib.svo_stereo_queue_destroy(self.h)
             self.h = None
 
     def __del__(self):

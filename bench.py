@@ -623,13 +623,47 @@ def run_extras(device: int) -> dict:
     return out
 
 
+CPU_STAGES = ("goodFeaturesToTrack", "calcOpticalFlowPyrLK", "StereoBM.compute", "solvePnPRansac")
+
+
+def _time_cv2_stages(cv2, acc):
+    """Wrap the four OpenCV entry points the reference calls (oracle/cv2_frontend.py looks them
+    up on the cv2 module at call time) so that their wall time lands in acc[name]."""
+    def timed(name, fn):
+        def wrapper(*a, **k):
+            t = time.perf_counter()
+            try:
+                return fn(*a, **k)
+            finally:
+                acc[name] += time.perf_counter() - t
+        return wrapper
+
+    for name in ("goodFeaturesToTrack", "calcOpticalFlowPyrLK", "solvePnPRansac"):
+        setattr(cv2, name, timed(name, getattr(cv2, name)))
+    create = cv2.StereoBM_create
+
+    class TimedStereoBM:
+        def __init__(self, *a, **k):
+            self._bm = create(*a, **k)
+            self.compute = timed("StereoBM.compute", self._bm.compute)
+
+        def __getattr__(self, item):
+            return getattr(self._bm, item)
+
+    cv2.StereoBM_create = TimedStereoBM
+
+
 def _cpu_worker(arg):
-    seed, n_frames, threads = arg
+    seed, n_frames, threads, optimized = arg
     import cv2
     from oracle import cv2_frontend as O
     from stereo_vo_b200 import synth
     cv2.setNumThreads(threads)
-    cv2.setUseOptimized(True)             # the reference's realistic speed (default OpenCV mode)
+    # True: the reference's realistic speed (default OpenCV mode); False: the canonical
+    # arithmetic the parity tests compare with (SURVEY.md 0)
+    cv2.setUseOptimized(bool(optimized))
+    stages = {k: 0.0 for k in CPU_STAGES}
+    _time_cv2_stages(cv2, stages)
     # sequences of at most 80 frames each: on longer synthetic runs tracked + new features pass
     # the 400-feature limit (from frame ~89 on), where the reference's own bookkeeping is
     # undefined behaviour (SURVEY.md B6) and the oracle refuses to continue
@@ -648,15 +682,17 @@ def _cpu_worker(arg):
                 done += 1
         except AssertionError:            # B6 reached early on this seed: next sequence
             continue
-    return time.perf_counter() - t0, max(done, 1)
+    return time.perf_counter() - t0, max(done, 1), stages
 
 
-def cpu_run(n_proc: int, frames_each: int, threads_each: int):
+def cpu_run(n_proc: int, frames_each: int, threads_each: int, optimized: bool = True):
     """The reference's CPU front end (cv2 restatement, oracle/) on the host cores: n_proc
-    independent sequences in parallel processes. Returns aggregate frames/s."""
+    independent sequences in parallel processes. Returns aggregate frames/s, the slowest
+    process's wall time, the caller's wall time and the mean ms per frame spent inside each of
+    the reference's OpenCV calls (+ "other": the rest of process())."""
     import multiprocessing as mp
     ctx = mp.get_context("spawn")
-    args = [(100 + i, frames_each, threads_each) for i in range(n_proc)]
+    args = [(100 + i, frames_each, threads_each, optimized) for i in range(n_proc)]
     t0 = time.perf_counter()
     if n_proc == 1:
         res = [_cpu_worker(args[0])]
@@ -666,19 +702,34 @@ def cpu_run(n_proc: int, frames_each: int, threads_each: int):
             res = pool.map(_cpu_worker, args)
         wall = max(r[0] for r in res)
     total = sum(r[1] for r in res)
-    return total / wall, wall, time.perf_counter() - t0
+    stage_ms = {k: 1e3 * sum(r[2][k] for r in res) / total for k in CPU_STAGES}
+    stage_ms["other"] = 1e3 * sum(r[0] for r in res) / total - sum(stage_ms.values())
+    return total / wall, wall, time.perf_counter() - t0, stage_ms
 
 
 def cpu_baseline(sample_frames: int = 120):
     cores = len(os.sched_getaffinity(0))
     n_proc = max(1, min(cores, 32))
     each = max(8, sample_frames // n_proc) if n_proc > 1 else sample_frames
-    fps, wall, _ = cpu_run(n_proc, each, 1)
+    fps, wall, _, stage_ms = cpu_run(n_proc, each, 1)
+    # the canonical (setUseOptimized(False)) arithmetic the parity tests compare with, on a
+    # quarter of the sample: SURVEY.md 8d asks for both modes
+    c_each = max(8, each // 4)
+    c_fps, c_wall, _, c_stage_ms = cpu_run(n_proc, c_each, 1, optimized=False)
+    rnd = lambda d: {k: round(v, 3) for k, v in d.items()}
     return {"value": fps, "unit": UNIT, "cores": n_proc, "kind": "port",
             "sample": f"{n_proc} processes x {each} synthetic KITTI-shaped frames, cv2 "
                       f"{_cv2_version()} oracle (oracle/cv2_frontend.py: the reference's own "
                       "OpenCV calls), 1 OpenCV thread each, default optimized mode; "
-                      f"{wall:.1f} s wall = {wall * n_proc:.0f} core-seconds of CPU work"}
+                      f"{wall:.1f} s wall = {wall * n_proc:.0f} core-seconds of CPU work",
+            "stage_ms_per_frame": rnd(stage_ms),
+            "stage_note": "mean wall ms per frame and core inside each OpenCV call of the "
+                          "reference (calcOpticalFlowPyrLK = forward + backward; StereoBM.compute "
+                          "and solvePnPRansac run on keyframes only, amortised over all frames)",
+            "canonical_mode": {"value": c_fps, "unit": UNIT,
+                               "sample": f"{n_proc} processes x {c_each} frames, "
+                                         f"cv2.setUseOptimized(False), {c_wall:.1f} s wall",
+                               "stage_ms_per_frame": rnd(c_stage_ms)}}
 
 
 def _cv2_version():
@@ -702,7 +753,7 @@ def run_reference(args, rank, world):
     frames_total = 0
     K = max(1, min(args.steps, 3))
     for _ in range(K):
-        fps, wall, _ = cpu_run(n_proc, each, 1)
+        fps, wall, _, _stages = cpu_run(n_proc, each, 1)
         t_total += wall
         frames_total += n_proc * each
     value = frames_total / t_total

@@ -14,7 +14,10 @@
 // B*3735 + 2^14) >> 15); 16 -> 8 bit through convertTo(..., 255 / 65535), i.e. round(v / 257);
 // 16-bit pixels are byte-swapped when the message's endianness differs from the host's;
 // encodings that are not colour formats (8UC1, 32FC1, ...) cannot become mono8 and throw.
-// tests/test_image_msg.py pins every conversion against cv2 bit for bit.
+// tests/test_image_msg.py pins every conversion against cv2 4.13 bit for bit. (OpenCV 3.x, the
+// reference's era, weighted colours with 14-bit coefficients 4899 / 9617 / 1868: a colour source
+// can come out one grey level apart there. Both of the reference's cameras publish mono8, which
+// is a plain copy in every version.)
 //
 // The ApproximateTime synchroniser and the subscribers themselves are ROS machinery (out of
 // scope): the caller hands over pairs that already belong together.

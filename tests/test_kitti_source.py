@@ -66,6 +66,83 @@ def test_frames_and_poses_match_the_reference_reader(kitti_tree):
         hostapi.KittiSource(root, "99")
 
 
+def _write_png(path, img, filters):
+    """A PNG writer for the tests: 8-bit grey / grey+alpha / RGB / RGBA, row y filtered with
+    type filters[y % len(filters)] (0 None, 1 Sub, 2 Up, 3 Average, 4 Paeth), IDAT split in two."""
+    import struct
+    import zlib
+    h, w = img.shape[:2]
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    color = {1: 0, 2: 4, 3: 2, 4: 6}[ch]
+    rows = img.reshape(h, w * ch).astype(np.int32)
+    prev = np.zeros(w * ch, np.int32)
+    raw = bytearray()
+    for y in range(h):
+        f = filters[y % len(filters)]
+        cur = rows[y]
+        a = np.concatenate([np.zeros(ch, np.int32), cur[:-ch]])
+        c = np.concatenate([np.zeros(ch, np.int32), prev[:-ch]])
+        b = prev
+        if f == 0:
+            pred = np.zeros_like(cur)
+        elif f == 1:
+            pred = a
+        elif f == 2:
+            pred = b
+        elif f == 3:
+            pred = (a + b) >> 1
+        else:
+            p = a + b - c
+            pa, pb, pc = np.abs(p - a), np.abs(p - b), np.abs(p - c)
+            pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, b, c))
+        raw.append(f)
+        raw += ((cur - pred) & 255).astype(np.uint8).tobytes()
+        prev = cur
+    z = zlib.compress(bytes(raw), 6)
+
+    def chunk(kind, data):
+        return struct.pack(">I", len(data)) + kind + data + struct.pack(">I", zlib.crc32(kind + data))
+
+    with open(path, "wb") as fh:
+        fh.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, color, 0, 0, 0))
+                 + chunk(b"tEXt", b"Comment\0test") + chunk(b"IDAT", z[:len(z) // 2])
+                 + chunk(b"IDAT", z[len(z) // 2:]) + chunk(b"IEND", b""))
+
+
+@pytest.mark.parametrize("channels", [1, 2, 3, 4])
+def test_every_png_filter_type_and_colour_type(kitti_tree, tmp_path, channels):
+    """cv2's PNG writer only emits Sub-filtered rows; KITTI's files use all five filter types.
+    Frames written with every filter type in turn (and one file per single type), as grey,
+    grey + alpha, RGB and RGBA, must decode to exactly what cv2.imread(..., GRAYSCALE) returns."""
+    import shutil
+    from stereo_vo_b200 import build, hostapi
+    if build.host_needs_build():
+        build.build_host_lib()
+    root, seq, n, poses, cam = kitti_tree
+    base = tmp_path / "tree"
+    shutil.copytree(root, base)
+    base = str(base) + "/"
+    rng = np.random.default_rng(channels)
+    plans = [[0, 1, 2, 3, 4], [4, 3, 2, 1, 0, 4, 4, 3], [0], [1], [2], [3], [4]]
+    for i, filters in enumerate(plans):
+        l, r = synth.stereo_frame(5, i, cam)
+        if channels > 1:
+            extra = [rng.integers(0, 256, l.shape, dtype=np.uint8) for _ in range(channels - 1)]
+            l = np.dstack([l] + extra)
+            r = np.dstack([r] + extra[::-1])
+        _write_png(f"{base}{seq}/image_0/{i:06d}.png", l, filters)
+        _write_png(f"{base}{seq}/image_1/{i:06d}.png", r, filters[::-1])
+    src = hostapi.KittiSource(base, seq)
+    for i in range(len(plans)):
+        l, r, _ = src.read(i)
+        ref_l = cv2.imread(f"{base}{seq}/image_0/{i:06d}.png", cv2.IMREAD_GRAYSCALE)
+        ref_r = cv2.imread(f"{base}{seq}/image_1/{i:06d}.png", cv2.IMREAD_GRAYSCALE)
+        assert ref_l is not None and ref_l.shape == (cam.height, cam.width)
+        assert np.array_equal(l, ref_l), f"left {i} (filters {plans[i]})"
+        assert np.array_equal(r, ref_r), f"right {i}"
+    src.close()
+
+
 def test_malformed_pngs_are_refused_with_a_message(kitti_tree, tmp_path):
     """A frame file that is not a sound 8-bit PNG of the sequence's size must end in an error
     that names the file - never in a crash or a silently wrong image."""

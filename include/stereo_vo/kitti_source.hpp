@@ -50,13 +50,17 @@ class KittiSource {
     int width_ = 0, height_ = 0;
 };
 
-// Decodes frames first, first + 1, ... on a worker thread into a ring of `depth` >= 3 stereo
-// slots carved from `slab` (depth * 2 * pitch * height bytes; pinned memory for asynchronous
-// H2D), up to depth - 2 frames ahead. next() blocks until the next frame is decoded and returns
-// its slot; a slot stays valid until two further next() calls (two steps may be in flight).
+// Decodes frames first, first + 1, ... on `threads` worker threads into a ring of `depth` >= 3
+// stereo slots carved from `slab` (depth * 2 * pitch * height bytes; pinned memory for
+// asynchronous H2D), up to depth - 2 frames ahead. Frames are handed out in order whatever
+// order the workers finish in: next() blocks until the next frame is decoded and returns its
+// slot; a slot stays valid until two further next() calls (two steps may be in flight).
+// One thread decodes ~90 KITTI-sized stereo pairs per second (11 ms per pair, zlib inflate is
+// 3/4 of it; measured 91 / 184 / 365 / 687 pairs/s with 1 / 2 / 4 / 8 threads on 8 cores).
 class KittiPrefetcher {
   public:
-    KittiPrefetcher(const KittiSource& src, uint8_t* slab, int depth, int pitch, size_t first = 0);
+    KittiPrefetcher(const KittiSource& src, uint8_t* slab, int depth, int pitch, size_t first = 0,
+                    int threads = 1);
     ~KittiPrefetcher();
     // false at the end of the sequence
     bool next(size_t& index, const uint8_t*& left, const uint8_t*& right);
@@ -66,12 +70,14 @@ class KittiPrefetcher {
     const KittiSource& src_;
     uint8_t* slab_;
     int depth_, pitch_;
-    size_t produced_, consumed_, end_;
-    std::string error_;
+    size_t claimed_, consumed_, end_;      // next frame a worker takes / next frame handed out
+    std::vector<size_t> ready_;            // per slot: index of the decoded frame it holds + 1
+    std::string error_;                    // what() of the first (lowest-index) frame that failed
+    size_t error_index_ = 0;
     bool stop_ = false;
     std::mutex mu_;
     std::condition_variable cv_;
-    std::thread worker_;
+    std::vector<std::thread> workers_;
 };
 
 }  // namespace svo

@@ -387,12 +387,17 @@ int svo_kitti_read(svo_kitti* k, int64_t i, uint8_t* left, uint8_t* right, int32
     });
 }
 
-int svo_kitti_prefetch_start(svo_kitti* k, uint8_t* slab, int32_t depth, int32_t pitch, int64_t first) {
+int svo_kitti_prefetch_start_threads(svo_kitti* k, uint8_t* slab, int32_t depth, int32_t pitch,
+                                     int64_t first, int32_t threads) {
     if (!k || first < 0) return SVO_ERR_INVALID;
     return guarded(k->error, [&] {
         k->pf.reset();
-        k->pf = std::make_unique<svo::KittiPrefetcher>(*k->src, slab, depth, pitch, (size_t)first);
+        k->pf = std::make_unique<svo::KittiPrefetcher>(*k->src, slab, depth, pitch, (size_t)first, threads);
     });
+}
+
+int svo_kitti_prefetch_start(svo_kitti* k, uint8_t* slab, int32_t depth, int32_t pitch, int64_t first) {
+    return svo_kitti_prefetch_start_threads(k, slab, depth, pitch, first, 1);
 }
 
 int svo_kitti_next(svo_kitti* k, int64_t* index, const uint8_t** left, const uint8_t** right,

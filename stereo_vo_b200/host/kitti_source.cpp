@@ -28,11 +28,35 @@ uint32_t be32(const unsigned char* p) {
     throw std::runtime_error("PNG " + path + ": " + what);
 }
 
-// whole file -> IHDR fields + concatenated IDAT payload
-PngInfo parse_png(const std::string& path, std::vector<unsigned char>* idat) {
-    std::ifstream f(path, std::ios::binary);
+// whole file in memory
+std::vector<unsigned char> slurp(const std::string& path) {
+    std::FILE* f = std::fopen(path.c_str(), "rb");
     if (!f) bad(path, "cannot open");
-    std::vector<unsigned char> buf((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    std::vector<unsigned char> buf;
+    if (std::fseek(f, 0, SEEK_END) == 0) {
+        const long n = std::ftell(f);
+        if (n > 0) buf.resize((size_t)n);
+        std::rewind(f);
+    }
+    size_t got = buf.empty() ? 0 : std::fread(buf.data(), 1, buf.size(), f);
+    if (buf.empty()) {                                   // not seekable: read in pieces
+        unsigned char piece[1 << 16];
+        size_t k;
+        while ((k = std::fread(piece, 1, sizeof piece, f)) > 0) buf.insert(buf.end(), piece, piece + k);
+        got = buf.size();
+    }
+    std::fclose(f);
+    if (got != buf.size()) bad(path, "short read");
+    return buf;
+}
+
+struct Span {
+    const unsigned char* p;
+    size_t n;
+};
+
+// file bytes -> IHDR fields + the IDAT payload pieces in file order (pointers into buf)
+PngInfo parse_png(const std::string& path, const std::vector<unsigned char>& buf, std::vector<Span>* idat) {
     static const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a};
     if (buf.size() < 8 + 25 || std::memcmp(buf.data(), sig, 8) != 0) bad(path, "not a PNG file");
     PngInfo info;
@@ -55,7 +79,7 @@ PngInfo parse_png(const std::string& path, std::vector<unsigned char>* idat) {
             have_ihdr = true;
             if (!idat) return info;
         } else if (std::memcmp(type, "IDAT", 4) == 0) {
-            if (idat) idat->insert(idat->end(), data, data + len);
+            if (idat && len > 0) idat->push_back(Span{data, len});
         } else if (std::memcmp(type, "IEND", 4) == 0) {
             done = true;
         }
@@ -80,17 +104,61 @@ inline int paeth(int a, int b, int c) {
     return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
 }
 
+// Undo one row's PNG filter: s = the filtered bytes, d = where the row goes, up = the row above
+// (already unfiltered; nullptr for the first row = all zeros), n bytes, bpp bytes per pixel.
+// One loop per filter type; the first pixel (no left neighbour) is peeled off.
+bool unfilter_row(int filter, const unsigned char* s, unsigned char* d, const unsigned char* up,
+                  size_t n, size_t bpp) {
+    const size_t head = bpp < n ? bpp : n;
+    switch (filter) {
+        case 0:
+            std::memcpy(d, s, n);
+            return true;
+        case 1:
+            std::memcpy(d, s, head);
+            for (size_t i = head; i < n; ++i) d[i] = (unsigned char)(s[i] + d[i - bpp]);
+            return true;
+        case 2:
+            if (!up) { std::memcpy(d, s, n); return true; }
+            for (size_t i = 0; i < n; ++i) d[i] = (unsigned char)(s[i] + up[i]);
+            return true;
+        case 3:
+            if (!up) {
+                std::memcpy(d, s, head);
+                for (size_t i = head; i < n; ++i) d[i] = (unsigned char)(s[i] + (d[i - bpp] >> 1));
+                return true;
+            }
+            for (size_t i = 0; i < head; ++i) d[i] = (unsigned char)(s[i] + (up[i] >> 1));
+            for (size_t i = head; i < n; ++i) d[i] = (unsigned char)(s[i] + ((d[i - bpp] + up[i]) >> 1));
+            return true;
+        case 4:
+            if (!up) {                                   // paeth(a, 0, 0) = a
+                std::memcpy(d, s, head);
+                for (size_t i = head; i < n; ++i) d[i] = (unsigned char)(s[i] + d[i - bpp]);
+                return true;
+            }
+            for (size_t i = 0; i < head; ++i) d[i] = (unsigned char)(s[i] + up[i]);   // paeth(0, b, 0) = b
+            for (size_t i = head; i < n; ++i)
+                d[i] = (unsigned char)(s[i] + paeth(d[i - bpp], up[i], up[i - bpp]));
+            return true;
+        default:
+            return false;
+    }
+}
+
 }  // namespace
 
 void read_png_size(const std::string& path, int& width, int& height) {
-    const PngInfo info = parse_png(path, nullptr);
+    const std::vector<unsigned char> buf = slurp(path);
+    const PngInfo info = parse_png(path, buf, nullptr);
     width = info.width;
     height = info.height;
 }
 
 void read_png_gray(const std::string& path, uint8_t* out, int pitch, int width, int height) {
-    std::vector<unsigned char> idat;
-    const PngInfo info = parse_png(path, &idat);
+    const std::vector<unsigned char> buf = slurp(path);
+    std::vector<Span> idat;
+    const PngInfo info = parse_png(path, buf, &idat);
     if (info.width != width || info.height != height) bad(path, "image size differs from the sequence's");
     if (info.bit_depth != 8) bad(path, "only 8-bit PNGs are supported");
     if (info.interlace != 0) bad(path, "interlaced PNGs are not supported");
@@ -98,32 +166,40 @@ void read_png_gray(const std::string& path, uint8_t* out, int pitch, int width, 
     if (ch == 0) bad(path, "palette PNGs are not supported");
     if (pitch < width) bad(path, "pitch < width");
     const size_t stride = (size_t)width * ch;
+    // inflate the IDAT pieces where they lie (no concatenated copy) into filter byte + row, ...
+    if ((stride + 1) * (size_t)height > (size_t)0x7fffffff) bad(path, "image too large");
     std::vector<unsigned char> raw((stride + 1) * (size_t)height);
-    uLongf raw_len = (uLongf)raw.size();
-    if (uncompress(raw.data(), &raw_len, idat.data(), (uLong)idat.size()) != Z_OK || raw_len != raw.size())
-        bad(path, "zlib inflate failed");
-    std::vector<unsigned char> prev(stride, 0), cur(stride);
+    z_stream zs;
+    std::memset(&zs, 0, sizeof zs);
+    if (inflateInit(&zs) != Z_OK) bad(path, "zlib inflate failed");
+    zs.next_out = raw.data();
+    zs.avail_out = (uInt)raw.size();
+    int zrc = Z_OK;
+    for (size_t k = 0; k < idat.size() && zrc == Z_OK; ++k) {
+        zs.next_in = const_cast<Bytef*>(idat[k].p);
+        zs.avail_in = (uInt)idat[k].n;
+        zrc = inflate(&zs, Z_NO_FLUSH);
+        if (zrc == Z_OK && zs.avail_in != 0) zrc = Z_BUF_ERROR;      // more pixels than the header says
+    }
+    const bool whole = zrc == Z_STREAM_END && zs.total_out == raw.size();
+    inflateEnd(&zs);
+    if (!whole) bad(path, "zlib inflate failed");
+    // ... then undo the row filters: grey rows straight into the caller's image (the row above
+    // is the caller's previous row), colour rows in a pair of line buffers and weighted
+    std::vector<unsigned char> line[2];
+    if (ch > 1) { line[0].resize(stride); line[1].resize(stride); }
     for (int y = 0; y < height; ++y) {
-        const unsigned char* line = &raw[(stride + 1) * (size_t)y];
-        const int filter = line[0];
-        const unsigned char* s = line + 1;
-        for (size_t i = 0; i < stride; ++i) {
-            const int a = i >= (size_t)ch ? cur[i - ch] : 0, b = prev[i], c = i >= (size_t)ch ? prev[i - ch] : 0;
-            int v = s[i];
-            switch (filter) {
-                case 0: break;
-                case 1: v += a; break;
-                case 2: v += b; break;
-                case 3: v += (a + b) >> 1; break;
-                case 4: v += paeth(a, b, c); break;
-                default: bad(path, "unknown filter type");
-            }
-            cur[i] = (unsigned char)v;
-        }
+        const unsigned char* src = &raw[(stride + 1) * (size_t)y];
         uint8_t* o = out + (size_t)y * pitch;
         if (ch == 1) {
-            std::memcpy(o, cur.data(), (size_t)width);
-        } else if (ch == 2) {
+            if (!unfilter_row(src[0], src + 1, o, y ? o - pitch : nullptr, stride, 1))
+                bad(path, "unknown filter type");
+            continue;
+        }
+        unsigned char* cur = line[y & 1].data();
+        if (!unfilter_row(src[0], src + 1, cur, y ? line[(y & 1) ^ 1].data() : nullptr, stride, (size_t)ch))
+            bad(path, "unknown filter type");
+        if (ch == 2) {
             for (int x = 0; x < width; ++x) o[x] = cur[2 * (size_t)x];
         } else {
             // cv::imread(..., GRAYSCALE) lets libpng convert: png_set_rgb_to_gray(0.299, 0.587)
@@ -133,7 +209,6 @@ void read_png_gray(const std::string& path, uint8_t* out, int pitch, int width, 
                 o[x] = (uint8_t)((px[0] * 9797 + px[1] * 19234 + px[2] * 3737) >> 15);
             }
         }
-        prev.swap(cur);
     }
 }
 
@@ -166,11 +241,14 @@ void KittiSource::read(size_t i, uint8_t* left, uint8_t* right, int pitch) const
     read_png_gray(right_path(i), right, pitch, width_, height_);
 }
 
-KittiPrefetcher::KittiPrefetcher(const KittiSource& src, uint8_t* slab, int depth, int pitch, size_t first)
-    : src_(src), slab_(slab), depth_(depth), pitch_(pitch), produced_(first), consumed_(first),
+KittiPrefetcher::KittiPrefetcher(const KittiSource& src, uint8_t* slab, int depth, int pitch, size_t first,
+                                 int threads)
+    : src_(src), slab_(slab), depth_(depth), pitch_(pitch), claimed_(first), consumed_(first),
       end_(src.size()) {
-    if (!slab || depth < 3 || pitch < src.width()) throw std::invalid_argument("KittiPrefetcher: bad arguments");
-    worker_ = std::thread(&KittiPrefetcher::run, this);
+    if (!slab || depth < 3 || pitch < src.width() || threads < 1 || threads > 64)
+        throw std::invalid_argument("KittiPrefetcher: bad arguments");
+    ready_.assign((size_t)depth, 0);
+    for (int t = 0; t < threads; ++t) workers_.emplace_back(&KittiPrefetcher::run, this);
 }
 
 KittiPrefetcher::~KittiPrefetcher() {
@@ -179,7 +257,8 @@ KittiPrefetcher::~KittiPrefetcher() {
         stop_ = true;
     }
     cv_.notify_all();
-    if (worker_.joinable()) worker_.join();
+    for (std::thread& w : workers_)
+        if (w.joinable()) w.join();
 }
 
 void KittiPrefetcher::run() {
@@ -188,24 +267,31 @@ void KittiPrefetcher::run() {
         size_t i;
         {
             std::unique_lock<std::mutex> lk(mu_);
-            // the two frames handed out last stay untouched (two steps may be in flight)
-            cv_.wait(lk, [&] { return stop_ || (produced_ < end_ && produced_ - consumed_ < (size_t)depth_ - 2); });
+            // a worker takes the next frame nobody has taken; the two frames handed out last
+            // stay untouched (two steps may be in flight), so frame i may be written once
+            // i - consumed_ < depth - 2
+            cv_.wait(lk, [&] { return stop_ || (claimed_ < end_ && claimed_ - consumed_ < (size_t)depth_ - 2); });
             if (stop_) return;
-            i = produced_;
+            i = claimed_++;
         }
         uint8_t* slot = slab_ + (i % (size_t)depth_) * slot_bytes;
         try {
             src_.read(i, slot, slot + (size_t)pitch_ * src_.height(), pitch_);
         } catch (const std::exception& ex) {
+            // frames before this one were taken earlier and will still be delivered; next()
+            // throws when it reaches the first frame that failed
             std::lock_guard<std::mutex> lk(mu_);
-            error_ = ex.what();
+            if (error_.empty() || i < error_index_) {
+                error_ = ex.what();
+                error_index_ = i;
+            }
             stop_ = true;
             cv_.notify_all();
             return;
         }
         {
             std::lock_guard<std::mutex> lk(mu_);
-            produced_ = i + 1;
+            ready_[i % (size_t)depth_] = i + 1;
         }
         cv_.notify_all();
     }
@@ -214,11 +300,12 @@ void KittiPrefetcher::run() {
 bool KittiPrefetcher::next(size_t& index, const uint8_t*& left, const uint8_t*& right) {
     std::unique_lock<std::mutex> lk(mu_);
     if (consumed_ >= end_) return false;
-    cv_.wait(lk, [&] { return produced_ > consumed_ || !error_.empty(); });
-    if (produced_ <= consumed_) throw std::runtime_error(error_);
-    index = consumed_;
+    const size_t want = consumed_, slot_no = want % (size_t)depth_;
+    cv_.wait(lk, [&] { return ready_[slot_no] == want + 1 || (!error_.empty() && want >= error_index_); });
+    if (ready_[slot_no] != want + 1) throw std::runtime_error(error_);
+    index = want;
     const size_t slot_bytes = (size_t)2 * pitch_ * src_.height();
-    left = slab_ + (index % (size_t)depth_) * slot_bytes;
+    left = slab_ + slot_no * slot_bytes;
     right = left + (size_t)pitch_ * src_.height();
     ++consumed_;
     lk.unlock();

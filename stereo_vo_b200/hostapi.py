@@ -111,6 +111,7 @@ def load_library():
     lib.svo_kitti_info.argtypes = [vp, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32)]
     lib.svo_kitti_read.argtypes = [vp, i64, vp, vp, i32, vp]
     lib.svo_kitti_prefetch_start.argtypes = [vp, vp, i32, i32, i64]
+    lib.svo_kitti_prefetch_start_threads.argtypes = [vp, vp, i32, i32, i64, i32]
     lib.svo_kitti_next.argtypes = [vp, C.POINTER(i64), C.POINTER(vp), C.POINTER(vp), vp]
     lib.svo_batch_kernel_launches.restype = C.c_int64
     lib.svo_batch_timer_begin.argtypes = [vp]
@@ -383,13 +384,15 @@ class KittiSource:
             raise self._err("svo_kitti_read", rc)
         return l, r, pose.reshape(3, 4)
 
-    def prefetch(self, depth: int = 4, first: int = 0):
-        """Iterate (index, left, right, pose) with decoding running ahead on a worker thread
-        into a pinned ring; the arrays alias ring slots (valid for two iterations)."""
-        self._slab = capi.pinned_empty((depth, 2, self.height, self.width), np.uint8)
-        rc = self.lib.svo_kitti_prefetch_start(self.h, self._slab.ctypes.data, depth, self.width, first)
+    def prefetch(self, depth: int = 4, first: int = 0, threads: int = 1, pinned: bool = True):
+        """Iterate (index, left, right, pose) with decoding running ahead on `threads` worker
+        threads into a (pinned) ring; the arrays alias ring slots (valid for two iterations)."""
+        shape = (depth, 2, self.height, self.width)
+        self._slab = capi.pinned_empty(shape, np.uint8) if pinned else np.empty(shape, np.uint8)
+        rc = self.lib.svo_kitti_prefetch_start_threads(self.h, self._slab.ctypes.data, depth,
+                                                       self.width, first, threads)
         if rc != 0:
-            raise self._err("svo_kitti_prefetch_start", rc)
+            raise self._err("svo_kitti_prefetch_start_threads", rc)
         idx, lp, rp = C.c_int64(), C.c_void_p(), C.c_void_p()
         pose = np.zeros(12)
         while True:

@@ -193,6 +193,63 @@ def test_malformed_pngs_are_refused_with_a_message(kitti_tree, tmp_path):
         src.close()
 
 
+@pytest.mark.parametrize("threads,depth", [(1, 3), (3, 5), (6, 8), (4, 3)])
+def test_prefetcher_threads_deliver_every_frame_once_in_order(kitti_tree, threads, depth):
+    """Several decoder threads, frames finishing out of order: the consumer still sees 0, 1, 2, ...
+    with the bytes of a direct read, each in the slot index % depth, and a slot keeps its frame
+    until the second further next() (two steps may be in flight: frames i and i - 1)."""
+    import time
+    from stereo_vo_b200 import build, hostapi
+    if build.host_needs_build():
+        build.build_host_lib()
+    root, seq, n, poses, cam = kitti_tree
+    direct = hostapi.KittiSource(root, seq)
+    want = [direct.read(i) for i in range(n)]
+    for first, slow in [(0, False), (2, True)]:
+        src = hostapi.KittiSource(root, seq)
+        seen, held = [], []
+        for i, l, r, p in src.prefetch(depth=depth, first=first, threads=threads, pinned=False):
+            if slow:
+                time.sleep(0.02)                   # the ring fills up; workers must wait
+            assert np.array_equal(l, want[i][0]) and np.array_equal(r, want[i][1]), f"frame {i}"
+            assert np.allclose(p, want[i][2], rtol=0, atol=1e-11)
+            held.append((i, l, r))
+            for j, hl, hr in held[-2:]:            # this frame and the one before it are intact
+                assert np.array_equal(hl, want[j][0]) and np.array_equal(hr, want[j][1]), (i, j)
+            seen.append(i)
+        assert seen == list(range(first, n))
+        src.close()
+    direct.close()
+
+
+def test_prefetcher_reports_a_bad_frame_after_the_good_ones(kitti_tree, tmp_path):
+    import shutil
+    from stereo_vo_b200 import build, hostapi
+    from stereo_vo_b200.capi import SvoError
+    if build.host_needs_build():
+        build.build_host_lib()
+    root, seq, n, poses, cam = kitti_tree
+    base = tmp_path / "tree"
+    shutil.copytree(root, base)
+    base = str(base) + "/"
+    with open(f"{base}{seq}/image_1/000004.png", "r+b") as fh:      # corrupt the zlib stream
+        fh.seek(200)
+        fh.write(b"\xff" * 64)
+    src = hostapi.KittiSource(base, seq)
+    seen = []
+    with pytest.raises(SvoError, match="000004.png"):
+        for i, l, r, p in src.prefetch(depth=6, threads=3, pinned=False):
+            seen.append(i)
+    assert seen == [0, 1, 2, 3]
+    src.close()
+    # closing while the workers are still decoding ahead must not hang or crash
+    for _ in range(3):
+        src = hostapi.KittiSource(root, seq)
+        it = src.prefetch(depth=5, threads=4, pinned=False)
+        next(it)
+        src.close()
+
+
 @pytest.mark.gpu
 def test_decode_ahead_ring_feeds_the_front_end(kitti_tree, svo_lib):
     """The prefetcher thread decodes into a pinned ring while the GPU works on earlier frames:

@@ -156,6 +156,26 @@ SVO_API int svo_kitti_prefetch_start_threads(svo_kitti* k, uint8_t* slab, int32_
 SVO_API int svo_kitti_next(svo_kitti* k, int64_t* index, const uint8_t** left, const uint8_t** right,
                            double* pose12);
 
+/* ---- BundleAdjuster bookkeeping alone (src/bundle_adjuster.cpp:41-58,60-135,159-163) --------- */
+/* The facade's Ceres-free BundleAdjuster (include/stereo_vo/bundle_adjuster.hpp) without an
+ * ImageProcessor around it: id assignment, refcounts, sliding window and world-point store. Host
+ * code; needs no GPU. tests/test_reference_ba.py replays, through these calls, the keyframe
+ * sequences it also ran through the reference's own compiled bundle_adjuster.cpp. */
+typedef struct svo_ba svo_ba;
+SVO_API int svo_ba_create(int32_t window_size, svo_ba** out);
+SVO_API void svo_ba_destroy(svo_ba* b);
+SVO_API const char* svo_ba_last_error(const svo_ba* b);          /* b may be NULL (create) */
+/* add_keyframe for a keyframe with n_tracked carried-over ids and n_new triangulated features:
+ * new_ids (room for n_new) receives the id of every new feature that was kept, *n_kept their
+ * number (n_new, or fewer when tracked + new exceeds the 400-feature limit: the reference
+ * truncates there too but leaves zeros in front of the ids - SURVEY.md B6 - which this build
+ * does not reproduce). SVO_ERR_INVALID for a tracked id that was never handed out. */
+SVO_API int svo_ba_add_keyframe(svo_ba* b, const uint64_t* tracked_ids, int32_t n_tracked,
+                                const svo_float3* new_3d, int32_t n_new, uint64_t* new_ids,
+                                int32_t* n_kept);
+SVO_API int svo_ba_get_world_points(svo_ba* b, const uint64_t* ids, int32_t n, svo_float3* out);
+SVO_API int64_t svo_ba_num_features(const svo_ba* b);
+
 /* ---- ROS image messages without ROS (src/vo_node.cpp:38-76,139-143; stereo_vo/image_msg.hpp) - */
 /* the fields of sensor_msgs/Image that cv_bridge reads */
 typedef struct svo_image_msg {

@@ -56,6 +56,11 @@ struct svo_batch {
     std::string error;
 };
 
+struct svo_ba {
+    std::unique_ptr<BundleAdjuster> ba;
+    std::string error;
+};
+
 struct svo_stereo_queue {
     std::shared_ptr<std::queue<StereoPair>> pairs = std::make_shared<std::queue<StereoPair>>();
     std::unique_ptr<handle_images> handler;
@@ -414,6 +419,56 @@ int svo_kitti_next(svo_kitti* k, int64_t* index, const uint8_t** left, const uin
     });
     return rc != SVO_OK ? rc : got;
 }
+
+// ------------------------------------------------------------- BundleAdjuster bookkeeping alone
+int svo_ba_create(int32_t window_size, svo_ba** out) {
+    if (!out || window_size <= 0) return SVO_ERR_INVALID;
+    *out = nullptr;
+    return guarded(g_create_error, [&] {
+        auto b = std::make_unique<svo_ba>();
+        CameraInfo info;
+        b->ba = std::make_unique<BundleAdjuster>((size_t)window_size, info);
+        *out = b.release();
+    });
+}
+
+void svo_ba_destroy(svo_ba* b) { delete b; }
+
+const char* svo_ba_last_error(const svo_ba* b) { return b ? b->error.c_str() : g_create_error.c_str(); }
+
+int svo_ba_add_keyframe(svo_ba* b, const uint64_t* tracked_ids, int32_t n_tracked,
+                        const svo_float3* new_3d, int32_t n_new, uint64_t* new_ids, int32_t* n_kept) {
+    if (!b || n_tracked < 0 || n_new < 0 || (n_tracked > 0 && !tracked_ids) ||
+        (n_new > 0 && (!new_3d || !new_ids)))
+        return SVO_ERR_INVALID;
+    if (n_kept) *n_kept = 0;
+    return guarded(b->error, [&] {
+        std::vector<size_t> tids(tracked_ids, tracked_ids + n_tracked);
+        for (size_t id : tids)
+            if (id >= b->ba->num_features()) throw std::invalid_argument("svo_ba_add_keyframe: unknown tracked id");
+        std::vector<cv::Point2f> t2d((size_t)n_tracked), n2d((size_t)n_new);
+        std::vector<cv::Point3f> n3d;
+        for (int32_t i = 0; i < n_new; ++i) n3d.push_back(cv::Point3f(new_3d[i].x, new_3d[i].y, new_3d[i].z));
+        auto kf = std::make_shared<Keyframe>(svo::Vec3f(), svo::Quatf(), cv::Mat(), t2d, tids, n2d, n3d);
+        b->ba->add_keyframe(kf);
+        for (size_t i = 0; i < kf->new_ids.size(); ++i) new_ids[i] = (uint64_t)kf->new_ids[i];
+        if (n_kept) *n_kept = (int32_t)kf->new_ids.size();
+    });
+}
+
+int svo_ba_get_world_points(svo_ba* b, const uint64_t* ids, int32_t n, svo_float3* out) {
+    if (!b || n < 0 || (n > 0 && (!ids || !out))) return SVO_ERR_INVALID;
+    return guarded(b->error, [&] {
+        std::vector<size_t> v(ids, ids + n);
+        for (size_t id : v)
+            if (id >= b->ba->num_features()) throw std::invalid_argument("svo_ba_get_world_points: unknown id");
+        std::vector<cv::Point3f> pts;
+        b->ba->get_world_points(pts, v);
+        for (size_t i = 0; i < pts.size(); ++i) out[i] = svo_float3{pts[i].x, pts[i].y, pts[i].z};
+    });
+}
+
+int64_t svo_ba_num_features(const svo_ba* b) { return b ? (int64_t)b->ba->num_features() : (int64_t)SVO_ERR_INVALID; }
 
 // ------------------------------------------------- image messages, handle_images, drain loop
 namespace {

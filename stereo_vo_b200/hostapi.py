@@ -120,6 +120,15 @@ def load_library():
     lib.svo_batch_get_profile.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     lib.svo_batch_engine.argtypes = [vp, i32]
     lib.svo_batch_engine.restype = vp
+    lib.svo_ba_create.argtypes = [i32, C.POINTER(vp)]
+    lib.svo_ba_destroy.argtypes = [vp]
+    lib.svo_ba_destroy.restype = None
+    lib.svo_ba_last_error.argtypes = [vp]
+    lib.svo_ba_last_error.restype = C.c_char_p
+    lib.svo_ba_add_keyframe.argtypes = [vp, vp, i32, vp, i32, vp, C.POINTER(i32)]
+    lib.svo_ba_get_world_points.argtypes = [vp, vp, i32, vp]
+    lib.svo_ba_num_features.argtypes = [vp]
+    lib.svo_ba_num_features.restype = C.c_int64
     lib.svo_image_to_mono8.argtypes = [C.POINTER(ImageMsg), vp, i32]
     lib.svo_image_last_error.argtypes = []
     lib.svo_image_last_error.restype = C.c_char_p
@@ -255,6 +264,57 @@ class VoSequence:
     def close(self):
         if self.h:
             self.lib.svo_vo_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class BundleAdjusterBookkeeping:
+    """The facade's Ceres-free BundleAdjuster on its own (svo_ba_*): ids, refcounts, sliding
+    window, world points - src/bundle_adjuster.cpp:41-58,60-135,159-163. Host code, no GPU."""
+
+    def __init__(self, window: int = 5):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.svo_ba_create(window, C.byref(h))
+        if rc != 0:
+            raise SvoError(f"svo_ba_create failed ({rc})")
+        self.h = h
+
+    def _err(self, what, rc):
+        return SvoError(f"{what} failed ({rc}): "
+                        f"{self.lib.svo_ba_last_error(self.h).decode(errors='replace')}")
+
+    def add_keyframe(self, tracked_ids, new_3d) -> np.ndarray:
+        tid = np.ascontiguousarray(tracked_ids, np.uint64).reshape(-1)
+        n3 = np.ascontiguousarray(new_3d, np.float32).reshape(-1, 3)
+        out = np.zeros(max(1, n3.shape[0]), np.uint64)
+        kept = C.c_int32(0)
+        rc = self.lib.svo_ba_add_keyframe(self.h, tid.ctypes.data, tid.shape[0], n3.ctypes.data,
+                                          n3.shape[0], out.ctypes.data, C.byref(kept))
+        if rc != 0:
+            raise self._err("svo_ba_add_keyframe", rc)
+        return out[:kept.value].copy()
+
+    def world_points(self, ids) -> np.ndarray:
+        ids = np.ascontiguousarray(ids, np.uint64).reshape(-1)
+        out = np.zeros((max(1, ids.shape[0]), 3), np.float32)
+        rc = self.lib.svo_ba_get_world_points(self.h, ids.ctypes.data, ids.shape[0], out.ctypes.data)
+        if rc != 0:
+            raise self._err("svo_ba_get_world_points", rc)
+        return out[:ids.shape[0]]
+
+    @property
+    def num_features(self) -> int:
+        return int(self.lib.svo_ba_num_features(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.svo_ba_destroy(self.h)
             self.h = None
 
     def __del__(self):

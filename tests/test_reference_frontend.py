@@ -150,3 +150,47 @@ def test_closed_loop_agrees_with_the_compiled_reference():
             assert np.allclose(o["new3d"], a["new3d"], rtol=1e-5, atol=1e-4)
     ref.close()
     assert keyframes >= 6
+
+
+@pytest.mark.skipif(not build_ref.available(), reason="the reference tree is not on this machine")
+@pytest.mark.parametrize("name", ["kitti_seq0", "d435i_seq1"])
+def test_compiled_reference_reproduces_the_gpu_golden_logs(name):
+    """tests/golden/<name>.npz is what tests/test_gpu_golden.py replays on the CUDA path. It was
+    written by the Python oracle; here the reference's own compiled front end (closed loop,
+    nothing replayed) walks the same frames and must arrive at the same log: decisions, corners,
+    tracked set, forward-LK status, new features, ids, disparities-implied valid set, inliers,
+    3-D points to 1e-5. GPU == golden and golden == compiled reference close the chain."""
+    from oracle import ref_frontend
+    from tests import golden_util as GU
+    recs, _ = GU.load(name)
+    frames, cam = GU.frames_for(name, len(recs))
+    GU.check_inputs(recs, frames)
+    O.canonical_mode()
+    f, cx, cy, b = cam.f32()
+    ref = ref_frontend.RefPipeline(f, cx, cy, b)
+    for t, ((l, r), g) in enumerate(zip(frames, recs)):
+        a = ref.process(l, r, t / 11.0)
+        calls = {}
+        for cname, c in a["calls"]:
+            calls.setdefault(cname, []).append(c)
+        assert a["made_keyframe"] == (g["decision"] in ("first", "keyframe")), (t, g["decision"])
+        assert np.array_equal(calls["goodFeaturesToTrack"][0]["corners"], g["detected"]), t
+        if "tracked_pts" in g:
+            assert np.array_equal(calls["calcOpticalFlowPyrLK"][0]["status"], g["status1"]), t
+        if g["decision"] == "skip":
+            assert [int(i) for i in a["tracker_ids"]] == g["tracked_ids"], t
+            assert np.array_equal(a["tracker_pts"], g["tracked_pts"]), t
+        if a["made_keyframe"]:
+            assert [int(i) for i in a["tracker_ids"]] == g["tracker_ids"], t
+            assert np.array_equal(a["tracker_pts"], g["tracker_pts"]), t
+            assert np.array_equal(a["new2d"], g["new2d"]) and [int(i) for i in a["new_ids"]] == g["new_ids"], t
+            assert np.allclose(a["new3d"], g["new3d"], rtol=1e-5, atol=1e-4), t
+            # the disparity map the reference's StereoBM call produced, read where the golden log reads it
+            d16 = calls["StereoBM"][0]["disp16"]
+            nf = g["new_features"].astype(np.int32)
+            at_features = d16[nf[:, 1], nf[:, 0]]
+            assert np.array_equal(np.flatnonzero(at_features > 0), g["valid_idx"]), t
+            assert np.array_equal(at_features[g["valid_idx"]], g["disp16"]), t
+        if g["decision"] == "keyframe":
+            assert np.array_equal(calls["solvePnPRansac"][0]["inliers"], g["inliers"]), t
+    ref.close()

@@ -707,6 +707,47 @@ def cpu_run(n_proc: int, frames_each: int, threads_each: int, optimized: bool = 
     return total / wall, wall, time.perf_counter() - t0, stage_ms
 
 
+def _ref_compiled_worker(arg):
+    """One sequence through oracle/_ref/libref_frontend.so: the reference's own compiled
+    process() / track_features() / triangulate_stereo() / add_keyframe(), its OpenCV calls served
+    by cv2 through callbacks (oracle/ref_frontend.py)."""
+    seed, n_frames = arg
+    import cv2
+    from oracle import ref_frontend
+    from stereo_vo_b200 import synth
+    cv2.setNumThreads(1)
+    cv2.setUseOptimized(True)
+    frames = synth.sequence(seed, n_frames)
+    f, cx, cy, b = synth.KITTI00.f32()
+    ref = ref_frontend.RefPipeline(f, cx, cy, b, guess="as_stored")
+    t0 = time.perf_counter()
+    keyframes = 0
+    for t, (l, r) in enumerate(frames):
+        keyframes += int(ref.process(l, r, t / 11.0)["made_keyframe"])
+    dt = time.perf_counter() - t0
+    ref.close()
+    return dt, n_frames, keyframes
+
+
+def reference_compiled_sample(n_frames: int = 48):
+    """The compiled reference on one host core, beside the port (never raises: the library is
+    test infrastructure built in the container and may be absent)."""
+    try:
+        import multiprocessing as mp
+        with mp.get_context("spawn").Pool(1) as pool:
+            dt, n, kf = pool.apply(_ref_compiled_worker, ((100, n_frames),))
+        return {"value": n / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+                "sample": f"1 process x {n} synthetic KITTI-shaped frames ({kf} keyframes) through "
+                          "oracle/_ref/libref_frontend.so: the reference's image_processor.cpp + "
+                          "feature_tracker.cpp + bundle_adjuster.cpp compiled where they lie, OpenCV "
+                          f"algorithms served by cv2 {_cv2_version()} through callbacks (one extra image "
+                          "copy per call, one Python call per matrix product: the stand-in's overhead is "
+                          "inside this number, so it is a lower bound on the reference's speed, not a "
+                          "tuned baseline), Ceres replaced by a recording stand-in (no solve)"}
+    except Exception as ex:                      # noqa: BLE001
+        return {"unavailable": repr(ex)[:200]}
+
+
 def cpu_baseline(sample_frames: int = 120):
     cores = len(os.sched_getaffinity(0))
     n_proc = max(1, min(cores, 32))
@@ -726,6 +767,7 @@ def cpu_baseline(sample_frames: int = 120):
             "stage_note": "mean wall ms per frame and core inside each OpenCV call of the "
                           "reference (calcOpticalFlowPyrLK = forward + backward; StereoBM.compute "
                           "and solvePnPRansac run on keyframes only, amortised over all frames)",
+            "reference_compiled": reference_compiled_sample(),
             "canonical_mode": {"value": c_fps, "unit": UNIT,
                                "sample": f"{n_proc} processes x {c_each} frames, "
                                          f"cv2.setUseOptimized(False), {c_wall:.1f} s wall",

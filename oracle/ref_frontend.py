@@ -7,7 +7,8 @@ code passed, so the tests can hold the literal parameters of the restatement and
 (300 / 0.1 / 30, (21, 21) / 3 / {COUNT+EPS, 30, 0.01} / 0 / 1e-2, (48, 21), 100 / 8.0 / 0.99)
 against the ones the compiled reference really uses.
 
-Only tests/ may import this module; it needs /root/reference (build container only).
+Only tests/ and bench.py's CPU-baseline leg may import this module; it needs /root/reference to
+build the library (build container) and runs wherever the built library is.
 """
 from __future__ import annotations
 
@@ -56,7 +57,11 @@ class RefPipeline:
         assert guess in ("carried", "as_stored")
         self.guess = guess
         self._last_pnp = None
-        self.lib = C.CDLL(build_ref.build() and build_ref.FRONTEND_LIB)
+        # built from the reference tree when it is here; elsewhere (the GPU box) the library
+        # built in the container travels with the repository snapshot
+        if build_ref.available():
+            build_ref.build()
+        self.lib = C.CDLL(build_ref.FRONTEND_LIB)
         lib = self.lib
         lib.ref_vo_create.restype = C.c_void_p
         lib.ref_vo_create.argtypes = [C.c_float] * 6 + [C.c_uint64]

@@ -735,7 +735,8 @@ def reference_compiled_sample(n_frames: int = 48):
     try:
         import multiprocessing as mp
         with mp.get_context("spawn").Pool(1) as pool:
-            dt, n, kf = pool.apply(_ref_compiled_worker, ((100, n_frames),))
+            # (a worker that dies would leave apply() waiting for ever: bounded wait instead)
+            dt, n, kf = pool.apply_async(_ref_compiled_worker, ((100, n_frames),)).get(timeout=180)
         return {"value": n / dt, "unit": UNIT, "cores": 1, "kind": "reference",
                 "sample": f"1 process x {n} synthetic KITTI-shaped frames ({kf} keyframes) through "
                           "oracle/_ref/libref_frontend.so: the reference's image_processor.cpp + "

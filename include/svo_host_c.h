@@ -7,6 +7,7 @@
  *                vo_node main loop, src/vo_node.cpp:112-119,141-144.
  *   svo_batch_*  many independent sequences per GPU (include/stereo_vo/batch_front_end.hpp).
  *   svo_camera_from_yaml   the camera YAML semantics of src/vo_node.cpp:82-98.
+ *   svo_ba_*     the Ceres-free BundleAdjuster bookkeeping on its own (ids, window, world points).
  *   svo_kitti_*  the frame source of kitti_node (KITTI PNG pairs + pose file).
  *   svo_image_to_mono8, svo_stereo_queue_*   the image-message side of vo_node
  *                (cv_bridge::toCvCopy(..., MONO8), handle_images and its queue, the drain loop).

@@ -194,3 +194,44 @@ def test_compiled_reference_reproduces_the_gpu_golden_logs(name):
         if g["decision"] == "keyframe":
             assert np.array_equal(calls["solvePnPRansac"][0]["inliers"], g["inliers"]), t
     ref.close()
+
+
+@pytest.mark.skipif(not build_ref.available(), reason="the reference tree is not on this machine")
+def test_edge_frames_go_the_same_way_in_the_compiled_reference():
+    """frames the synthetic sequences never produce: a flat image (fewer than 4 corners: the
+    reference returns before touching the tracker, image_processor.cpp:23-25), a flat image as the
+    very first frame, a frame whose tracks are all lost (large jump: percent_lost = 1 forces a
+    keyframe with next to no inliers), and the same stereo pair twice (zero parallax: skip)."""
+    from oracle import ref_frontend
+    O.canonical_mode()
+    cam = synth.KITTI00
+    f, cx, cy, b = cam.f32()
+    seq = synth.sequence(4, 8)
+    flat = np.full_like(seq[0][0], 127)
+    jump = (np.roll(seq[5][0], 400, axis=1).copy(), np.roll(seq[5][1], 400, axis=1).copy())
+    frames = [(flat, flat), seq[0], seq[1], (flat, flat), seq[2], seq[2], seq[3], jump, seq[6], seq[7]]
+    ref = ref_frontend.RefPipeline(f, cx, cy, b)
+    orc = O.make_pipeline(cam)
+    decisions = []
+    for t, (l, r) in enumerate(frames):
+        a, o = ref.process(l, r, t / 11.0), orc.process(l, r)
+        decisions.append(o["decision"])
+        names = [c[0] for c in a["calls"]]
+        assert a["made_keyframe"] == (o["decision"] in ("first", "keyframe")), (t, o["decision"])
+        if o["decision"] == "too_few":
+            assert names == ["goodFeaturesToTrack"], (t, names)          # nothing else was called
+        if o["decision"] == "skip":
+            assert names == ["goodFeaturesToTrack", "calcOpticalFlowPyrLK", "calcOpticalFlowPyrLK"], (t, names)
+        ids = o.get("tracker_ids", o.get("tracked_ids"))
+        pts = o.get("tracker_pts", o.get("tracked_pts"))
+        if ids is not None:
+            assert [int(i) for i in ids] == [int(i) for i in a["tracker_ids"]], t
+            assert np.array_equal(np.asarray(pts).reshape(-1, 2), a["tracker_pts"]), t
+        if a["made_keyframe"]:
+            assert np.array_equal(o["new2d"], a["new2d"]) and [int(i) for i in o["new_ids"]] == [int(i) for i in a["new_ids"]], t
+            if o["decision"] == "keyframe":
+                pn = [c for c in a["calls"] if c[0] == "solvePnPRansac"][0][1]
+                assert np.array_equal(pn["inliers"], o["inliers"]), t
+    ref.close()
+    assert decisions[0] == "too_few" and decisions[1] == "first" and decisions[3] == "too_few"
+    assert decisions[5] == "skip" and "keyframe" in decisions

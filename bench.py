@@ -3,7 +3,10 @@
 triangulate) on KITTI-shaped synthetic sequences, one process per GPU.
 
     python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torchrun)
-    python bench.py --impl reference ...                     (the reference's CPU path, host cores)
+    python bench.py --impl reference ...                     (the reference's CPU path, host cores:
+                                                              its own compiled front end from
+                                                              oracle/_ref when that library loads,
+                                                              else the cv2 restatement)
 
 Workload (BASELINE configs[3]): 64 independent KITTI-shaped synthetic
 stereo sequences per GPU, one texture seed each (rank r owns seeds 64 r .. 64 r + 63), 40
@@ -654,7 +657,7 @@ def _time_cv2_stages(cv2, acc):
 
 
 def _cpu_worker(arg):
-    seed, n_frames, threads, optimized = arg
+    seed, n_frames, threads, optimized, impl = arg
     import cv2
     from oracle import cv2_frontend as O
     from stereo_vo_b200 import synth
@@ -672,6 +675,21 @@ def _cpu_worker(arg):
         c = min(80, left)
         chunks.append(synth.sequence(seed + 1000 * len(chunks), c))
         left -= c
+    if impl == "compiled":
+        # the reference's own compiled process() / track_features() / triangulate_stereo() /
+        # add_keyframe() (oracle/_ref/libref_frontend.so), its OpenCV calls served by this
+        # process's cv2 through callbacks
+        from oracle import ref_frontend
+        f, cx, cy, b = synth.KITTI00.f32()
+        t0 = time.perf_counter()
+        done = 0
+        for fr in chunks:
+            ref = ref_frontend.RefPipeline(f, cx, cy, b, guess="as_stored", record=False)
+            for t, (l, r) in enumerate(fr):
+                ref.process(l, r, t / 11.0)
+                done += 1
+            ref.close()
+        return time.perf_counter() - t0, max(done, 1), stages
     t0 = time.perf_counter()
     done = 0
     for fr in chunks:
@@ -685,21 +703,23 @@ def _cpu_worker(arg):
     return time.perf_counter() - t0, max(done, 1), stages
 
 
-def cpu_run(n_proc: int, frames_each: int, threads_each: int, optimized: bool = True):
-    """The reference's CPU front end (cv2 restatement, oracle/) on the host cores: n_proc
-    independent sequences in parallel processes. Returns aggregate frames/s, the slowest
-    process's wall time, the caller's wall time and the mean ms per frame spent inside each of
-    the reference's OpenCV calls (+ "other": the rest of process())."""
+def cpu_run(n_proc: int, frames_each: int, threads_each: int, optimized: bool = True, impl: str = "port"):
+    """The reference's CPU front end on the host cores: n_proc independent sequences in parallel
+    processes. impl "port": the cv2 restatement (oracle/cv2_frontend.py); "compiled": the
+    reference's own sources compiled where they lie (oracle/_ref). Returns aggregate frames/s,
+    the slowest process's wall time, the caller's wall time and the mean ms per frame spent
+    inside each of the reference's OpenCV calls (+ "other": the rest of process())."""
     import multiprocessing as mp
     ctx = mp.get_context("spawn")
-    args = [(100 + i, frames_each, threads_each, optimized) for i in range(n_proc)]
+    args = [(100 + i, frames_each, threads_each, optimized, impl) for i in range(n_proc)]
     t0 = time.perf_counter()
-    if n_proc == 1:
+    if n_proc == 1 and impl == "port":
         res = [_cpu_worker(args[0])]
         wall = res[0][0]
     else:
         with ctx.Pool(n_proc) as pool:
-            res = pool.map(_cpu_worker, args)
+            # (bounded: a worker that died would leave map() waiting for ever)
+            res = pool.map_async(_cpu_worker, args).get(timeout=900)
         wall = max(r[0] for r in res)
     total = sum(r[1] for r in res)
     stage_ms = {k: 1e3 * sum(r[2][k] for r in res) / total for k in CPU_STAGES}
@@ -707,72 +727,63 @@ def cpu_run(n_proc: int, frames_each: int, threads_each: int, optimized: bool = 
     return total / wall, wall, time.perf_counter() - t0, stage_ms
 
 
-def _ref_compiled_worker(arg):
-    """One sequence through oracle/_ref/libref_frontend.so: the reference's own compiled
-    process() / track_features() / triangulate_stereo() / add_keyframe(), its OpenCV calls served
-    by cv2 through callbacks (oracle/ref_frontend.py)."""
-    seed, n_frames = arg
-    import cv2
-    from oracle import ref_frontend
-    from stereo_vo_b200 import synth
-    cv2.setNumThreads(1)
-    cv2.setUseOptimized(True)
-    frames = synth.sequence(seed, n_frames)
-    f, cx, cy, b = synth.KITTI00.f32()
-    ref = ref_frontend.RefPipeline(f, cx, cy, b, guess="as_stored")
-    t0 = time.perf_counter()
-    keyframes = 0
-    for t, (l, r) in enumerate(frames):
-        keyframes += int(ref.process(l, r, t / 11.0)["made_keyframe"])
-    dt = time.perf_counter() - t0
-    ref.close()
-    return dt, n_frames, keyframes
-
-
-def reference_compiled_sample(n_frames: int = 48):
-    """The compiled reference on one host core, beside the port (never raises: the library is
-    test infrastructure built in the container and may be absent)."""
+def reference_impl():
+    """("compiled", None) when oracle/_ref/libref_frontend.so is usable on this machine, else
+    ("port", why). Checked by running two frames through it in a child process."""
+    if os.environ.get("SVO_BENCH_REF_IMPL") == "port":
+        return "port", "SVO_BENCH_REF_IMPL=port"
     try:
-        import multiprocessing as mp
-        with mp.get_context("spawn").Pool(1) as pool:
-            # (a worker that dies would leave apply() waiting for ever: bounded wait instead)
-            dt, n, kf = pool.apply_async(_ref_compiled_worker, ((100, n_frames),)).get(timeout=180)
-        return {"value": n / dt, "unit": UNIT, "cores": 1, "kind": "reference",
-                "sample": f"1 process x {n} synthetic KITTI-shaped frames ({kf} keyframes) through "
-                          "oracle/_ref/libref_frontend.so: the reference's image_processor.cpp + "
-                          "feature_tracker.cpp + bundle_adjuster.cpp compiled where they lie, OpenCV "
-                          f"algorithms served by cv2 {_cv2_version()} through callbacks (one extra image "
-                          "copy per call, one Python call per matrix product: the stand-in's overhead is "
-                          "inside this number, so it is a lower bound on the reference's speed, not a "
-                          "tuned baseline), Ceres replaced by a recording stand-in (no solve)"}
+        fps, _, _, _ = cpu_run(1, 2, 1, True, impl="compiled")
+        return ("compiled", None) if fps > 0 else ("port", "no frames")
     except Exception as ex:                      # noqa: BLE001
-        return {"unavailable": repr(ex)[:200]}
+        return "port", repr(ex)[:160]
+
+
+_KIND = {"compiled": "reference", "port": "port"}
+_WHAT = {"compiled": "oracle/_ref/libref_frontend.so = the reference's own image_processor.cpp + "
+                     "feature_tracker.cpp + bundle_adjuster.cpp compiled where they lie (OpenCV's "
+                     "algorithms served by cv2 through callbacks, Ceres replaced by a recording "
+                     "stand-in: no solve)",
+         "port": "oracle/cv2_frontend.py = the reference restated call for call on cv2"}
 
 
 def cpu_baseline(sample_frames: int = 120):
     cores = len(os.sched_getaffinity(0))
     n_proc = max(1, min(cores, 32))
     each = max(8, sample_frames // n_proc) if n_proc > 1 else sample_frames
-    fps, wall, _, stage_ms = cpu_run(n_proc, each, 1)
+    impl, why_port = reference_impl()
+    try:
+        fps, wall, _, stage_ms = cpu_run(n_proc, each, 1, impl=impl)
+    except Exception as ex:                      # noqa: BLE001
+        if impl == "port":
+            raise
+        impl, why_port = "port", repr(ex)[:160]
+        fps, wall, _, stage_ms = cpu_run(n_proc, each, 1, impl=impl)
     # the canonical (setUseOptimized(False)) arithmetic the parity tests compare with, on a
     # quarter of the sample: SURVEY.md 8d asks for both modes
     c_each = max(8, each // 4)
-    c_fps, c_wall, _, c_stage_ms = cpu_run(n_proc, c_each, 1, optimized=False)
+    c_fps, c_wall, _, c_stage_ms = cpu_run(n_proc, c_each, 1, optimized=False, impl=impl)
     rnd = lambda d: {k: round(v, 3) for k, v in d.items()}
-    return {"value": fps, "unit": UNIT, "cores": n_proc, "kind": "port",
-            "sample": f"{n_proc} processes x {each} synthetic KITTI-shaped frames, cv2 "
-                      f"{_cv2_version()} oracle (oracle/cv2_frontend.py: the reference's own "
-                      "OpenCV calls), 1 OpenCV thread each, default optimized mode; "
-                      f"{wall:.1f} s wall = {wall * n_proc:.0f} core-seconds of CPU work",
-            "stage_ms_per_frame": rnd(stage_ms),
-            "stage_note": "mean wall ms per frame and core inside each OpenCV call of the "
-                          "reference (calcOpticalFlowPyrLK = forward + backward; StereoBM.compute "
-                          "and solvePnPRansac run on keyframes only, amortised over all frames)",
-            "reference_compiled": reference_compiled_sample(),
-            "canonical_mode": {"value": c_fps, "unit": UNIT,
-                               "sample": f"{n_proc} processes x {c_each} frames, "
-                                         f"cv2.setUseOptimized(False), {c_wall:.1f} s wall",
-                               "stage_ms_per_frame": rnd(c_stage_ms)}}
+    out = {"value": fps, "unit": UNIT, "cores": n_proc, "kind": _KIND[impl],
+           "sample": f"{n_proc} processes x {each} synthetic KITTI-shaped frames, {_WHAT[impl]}; cv2 "
+                     f"{_cv2_version()}, 1 OpenCV thread each, default optimized mode; "
+                     f"{wall:.1f} s wall = {wall * n_proc:.0f} core-seconds of CPU work",
+           "stage_ms_per_frame": rnd(stage_ms),
+           "stage_note": "mean wall ms per frame and core inside each OpenCV call of the "
+                         "reference (calcOpticalFlowPyrLK = forward + backward; StereoBM.compute "
+                         "and solvePnPRansac run on keyframes only, amortised over all frames)",
+           "canonical_mode": {"value": c_fps, "unit": UNIT,
+                              "sample": f"{n_proc} processes x {c_each} frames, "
+                                        f"cv2.setUseOptimized(False), {c_wall:.1f} s wall",
+                              "stage_ms_per_frame": rnd(c_stage_ms)}}
+    if impl == "compiled":
+        # the Python restatement beside it (the oracle of the parity tests), a quarter of the sample
+        p_fps, p_wall, _, _ = cpu_run(n_proc, c_each, 1, impl="port")
+        out["port"] = {"value": p_fps, "unit": UNIT, "kind": "port",
+                       "sample": f"{n_proc} processes x {c_each} frames, {_WHAT['port']}, {p_wall:.1f} s wall"}
+    else:
+        out["compiled_reference_unavailable"] = why_port
+    return out
 
 
 def _cv2_version():
@@ -790,19 +801,29 @@ def run_reference(args, rank, world):
     cores = len(os.sched_getaffinity(0))
     n_proc = max(1, min(cores, 64))
     each = args.ref_frames
-    for _ in range(args.warmup if args.warmup < 2 else 1):
-        cpu_run(n_proc, max(4, each // 2), 1)
-    t_total = 0.0
-    frames_total = 0
+    impl, why_port = reference_impl()
+
+    def timed_steps(which):
+        for _ in range(args.warmup if args.warmup < 2 else 1):
+            cpu_run(n_proc, max(4, each // 2), 1, impl=which)
+        t_sum, n_sum = 0.0, 0
+        for _ in range(K):
+            _fps, wall, _, _stages = cpu_run(n_proc, each, 1, impl=which)
+            t_sum += wall
+            n_sum += n_proc * each
+        return t_sum, n_sum
+
     K = max(1, min(args.steps, 3))
-    for _ in range(K):
-        fps, wall, _, _stages = cpu_run(n_proc, each, 1)
-        t_total += wall
-        frames_total += n_proc * each
+    try:
+        t_total, frames_total = timed_steps(impl)
+    except Exception as ex:                      # noqa: BLE001
+        if impl == "port":
+            raise
+        impl, why_port = "port", repr(ex)[:160]
+        t_total, frames_total = timed_steps(impl)
     value = frames_total / t_total
-    sample = (f"{n_proc} processes x {each} synthetic KITTI-shaped frames per step, cv2 "
-              f"{_cv2_version()} oracle restatement of src/image_processor.cpp + "
-              "src/feature_tracker.cpp (reference not buildable here: ROS/OpenCV SDK/Ceres absent)")
+    sample = (f"{n_proc} processes x {each} synthetic KITTI-shaped frames per step, {_WHAT[impl]}; cv2 "
+              f"{_cv2_version()}" + ("" if impl == "compiled" else f" (compiled reference not usable here: {why_port})"))
     return {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world,
         "steps": K, "warmup": args.warmup, "ms_per_step": t_total / K * 1e3,
@@ -814,7 +835,7 @@ def run_reference(args, rank, world):
                            f"{each} frames per step, at most 3 steps (the CPU path needs ~25 ms "
                            "per frame and core); frames/s is aggregate over all cores and "
                            "compares directly with the GPU arm's frames/s"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": n_proc, "kind": "port",
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": n_proc, "kind": _KIND[impl],
                          "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,

@@ -27,8 +27,10 @@ import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-REF_SRC = "/root/reference/src"
-OUT_DIR = os.path.join(HERE, "_ref")
+# (both overridable so that the tests can play a machine without the reference and without the
+# built libraries)
+REF_SRC = os.environ.get("ORACLE_REF_SRC", "/root/reference/src")
+OUT_DIR = os.environ.get("ORACLE_REF_OUT", os.path.join(HERE, "_ref"))
 LIB = os.path.join(OUT_DIR, "libref_ba.so")
 SOURCES = [os.path.join(REF_SRC, "bundle_adjuster.cpp"), os.path.join(REF_SRC, "reprojection_factor.cpp"),
            os.path.join(HERE, "ref_harness.cpp")]

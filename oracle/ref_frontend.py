@@ -38,7 +38,9 @@ class _Callbacks(C.Structure):
 
 
 def _img(ptr, rows, cols, step):
-    return np.ctypeslib.as_array(ptr, (rows, step))[:, :cols].copy()
+    """a view of the caller's pixels (the stand-in Mats are continuous: no copy needed)"""
+    a = np.ctypeslib.as_array(ptr, (rows, step))
+    return a if step == cols else np.ascontiguousarray(a[:, :cols])
 
 
 class RefPipeline:
@@ -47,8 +49,10 @@ class RefPipeline:
     what it answered."""
 
     def __init__(self, focal, cx, cy, baseline, min_feature_distance=30.0, parallax_thresh=20.0, window=5,
-                 guess="carried"):
-        """guess: how the extrinsic guess reaches cv2.solvePnPRansac. "as_stored": the values the
+                 guess="carried", record=True):
+        """record: keep, per frame, the arguments and results of every OpenCV call in `calls`
+        (the tests read them; the timing legs of bench.py switch it off).
+        guess: how the extrinsic guess reaches cv2.solvePnPRansac. "as_stored": the values the
         reference's CV_32F rvec / tvec Mats hold (OpenCV 3.x keeps them in that type between
         keyframes). "carried": the float64 vectors the previous call returned whenever the stored
         ones are exactly their float32 rounding - how oracle/cv2_frontend.py carries them (cv2
@@ -56,6 +60,7 @@ class RefPipeline:
         borderline inlier; the control flow under test is the same."""
         assert guess in ("carried", "as_stored")
         self.guess = guess
+        self.record = record
         self._last_pnp = None
         # built from the reference tree when it is here; elsewhere (the GPU box) the library
         # built in the container travels with the repository snapshot
@@ -90,8 +95,9 @@ class RefPipeline:
         pts = np.zeros((0, 2), np.float32) if pts is None else pts.reshape(-1, 2)
         n = min(pts.shape[0], cap)
         np.ctypeslib.as_array(out, (2 * max(cap, 1),))[:2 * n] = pts[:n].reshape(-1)
-        self.calls.append(("goodFeaturesToTrack", dict(max_corners=max_corners, quality=quality,
-                                                       min_distance=min_distance, corners=pts[:n].copy())))
+        if self.record:
+            self.calls.append(("goodFeaturesToTrack", dict(max_corners=max_corners, quality=quality,
+                                                           min_distance=min_distance, corners=pts[:n].copy())))
         return n
 
     def _lk(self, prev, pstep, nxt, nstep, rows, cols, pts, n, out_pts, status, err, win_w, win_h,
@@ -104,15 +110,17 @@ class RefPipeline:
         np.ctypeslib.as_array(out_pts, (n, 2))[:] = p1.reshape(-1, 2)
         np.ctypeslib.as_array(status, (n,))[:] = st.reshape(-1)
         np.ctypeslib.as_array(err, (n,))[:] = er.reshape(-1)
-        self.calls.append(("calcOpticalFlowPyrLK", dict(win=(win_w, win_h), max_level=max_level,
-                                                        criteria=(crit_type, crit_count, crit_eps), flags=flags,
-                                                        min_eig=min_eig, pts=p0.reshape(-1, 2).copy(),
-                                                        out=p1.reshape(-1, 2).copy(), status=st.reshape(-1).copy())))
+        if self.record:
+            self.calls.append(("calcOpticalFlowPyrLK", dict(win=(win_w, win_h), max_level=max_level,
+                                                            criteria=(crit_type, crit_count, crit_eps), flags=flags,
+                                                            min_eig=min_eig, pts=p0.reshape(-1, 2).copy(),
+                                                            out=p1.reshape(-1, 2).copy(), status=st.reshape(-1).copy())))
 
     def _sbm(self, left, lstep, right, rstep, rows, cols, ndisp, block, out):
         disp = cv2.StereoBM_create(ndisp, block).compute(_img(left, rows, cols, lstep), _img(right, rows, cols, rstep))
         np.ctypeslib.as_array(out, (rows, cols))[:] = disp
-        self.calls.append(("StereoBM", dict(ndisp=ndisp, block=block, disp16=disp.copy())))
+        if self.record:
+            self.calls.append(("StereoBM", dict(ndisp=ndisp, block=block, disp16=disp.copy())))
 
     def _pnp(self, world, image, n, k9, rvec, tvec, depth, use_guess, iterations, reproj, confidence, inliers, cap):
         w = np.ctypeslib.as_array(world, (n, 3)).copy()
@@ -138,7 +146,8 @@ class RefPipeline:
         inl = np.zeros(0, np.int32) if inl is None else inl.reshape(-1).astype(np.int32)
         m = min(inl.shape[0], cap)
         np.ctypeslib.as_array(inliers, (max(cap, 1),))[:m] = inl[:m]
-        self.calls.append(("solvePnPRansac", dict(n=n, K=K, depth=depth, use_guess=use_guess,
+        if self.record:
+            self.calls.append(("solvePnPRansac", dict(n=n, K=K, depth=depth, use_guess=use_guess,
                                                   iterations=iterations, reproj=reproj, confidence=confidence,
                                                   world=w, image=im, inliers=inl[:m].copy(),
                                                   rvec=rv.copy(), tvec=tv.copy())))
@@ -148,7 +157,8 @@ class RefPipeline:
         rv = np.ctypeslib.as_array(rvec, (3,)).astype(_DEPTH[depth]).reshape(3, 1)
         R, _ = cv2.Rodrigues(rv)
         np.ctypeslib.as_array(rmat, (9,))[:] = np.asarray(R, np.float64).reshape(9)
-        self.calls.append(("Rodrigues", dict(depth=depth)))
+        if self.record:
+            self.calls.append(("Rodrigues", dict(depth=depth)))
 
     def _gemm(self, a, b, depth, m, k, n, alpha, out):
         A = np.ctypeslib.as_array(a, (m, k)).astype(_DEPTH[depth])
@@ -165,6 +175,8 @@ class RefPipeline:
         if rc < 0:
             raise RuntimeError("the reference threw: " + self.lib.ref_vo_last_error().decode(errors="replace"))
         rec = dict(made_keyframe=bool(rc), calls=self.calls)
+        if not self.record:                      # timing runs: no read-back, no log
+            return rec
         cap = 4096
         xy, ids = np.zeros((cap, 2), np.float32), np.zeros(cap, np.uint64)
         n = self.lib.ref_vo_tracker(self.h, xy.ctypes.data, ids.ctypes.data, cap)

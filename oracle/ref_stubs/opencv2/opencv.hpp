@@ -186,8 +186,16 @@ class Mat {
     // reference performs (CV_16S disparity -> CV_32F, exact for alpha = 1/16)
     void convertTo(Mat& dst, int rtype, double alpha = 1.0) const {
         Mat out(rows, cols, rtype);
-        for (int r = 0; r < rows; ++r)
-            for (int c = 0; c < cols; ++c) out.set(r, c, get(r, c) * alpha);
+        if (type_ == CV_16S && rtype == CV_32F) {          // the disparity map: a whole image
+            for (int r = 0; r < rows; ++r) {
+                const short* s = reinterpret_cast<const short*>(ptr(r));
+                float* d = reinterpret_cast<float*>(out.ptr(r));
+                for (int c = 0; c < cols; ++c) d[c] = (float)(s[c] * alpha);
+            }
+        } else {
+            for (int r = 0; r < rows; ++r)
+                for (int c = 0; c < cols; ++c) out.set(r, c, get(r, c) * alpha);
+        }
         dst = out;
     }
     Mat t() const {

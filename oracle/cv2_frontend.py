@@ -6,7 +6,7 @@ import this module. The product path (stereo_vo_b200/ + libsvo.so) never does.
 
 Why cv2: every arithmetic step of the hot path lives in OpenCV, which the reference links but
 does not vendor (CMakeLists.txt:27 `find_package(OpenCV REQUIRED)`, version unpinned; the code
-is of the OpenCV 3.x era). The reference itself cannot be built here (needs catkin/roscpp,
+is of the OpenCV 3.x era). The reference cannot be built as it stands here (needs catkin/roscpp,
 OpenCV C++ SDK, Eigen, Ceres - none present). Python cv2 4.13.0 exports the same functions, so
 this file follows src/image_processor.cpp:18-208 and src/feature_tracker.cpp:3-72 line by line
 and calls them with the reference's literal arguments. BundleAdjuster is reduced to its
@@ -14,11 +14,17 @@ bookkeeping (ids and the world-point store, src/bundle_adjuster.cpp:60-135,159-1
 bundle_adjust() is a no-op because Ceres is absent (world points fed to PnP are un-refined on
 both sides of every comparison).
 
-Parity status: the reference has no tests, fixtures or golden vectors, so
-parity is UNPINNED by the reference itself. What pins this oracle: (1) it calls the very OpenCV
-entry points the reference calls; (2) oracle/restate.py re-derives each of them from published
-arithmetic and is checked against cv2 bit for bit in tests/test_oracle_restate.py; (3) golden
-vectors generated from this file are committed under tests/golden/.
+Parity status: the reference has no tests, fixtures or golden vectors.
+What pins this oracle: (0) the reference's OWN sources, compiled where they lie against stand-in
+headers with OpenCV's algorithms served by cv2 (oracle/build_ref.py, oracle/ref_frontend.py),
+do frame by frame what this file does - decisions, tracker ids and positions, LK / PnP inputs,
+new features, ids, 3-D points to 1e-5, the literal arguments of every OpenCV call
+(tests/test_reference_frontend.py; bookkeeping and reprojection factors:
+tests/test_reference_ba.py); (1) it calls the very OpenCV entry points the reference calls;
+(2) oracle/restate.py re-derives each of them from published arithmetic and is checked against
+cv2 bit for bit in tests/test_oracle_restate.py; (3) golden vectors generated from this file are
+committed under tests/golden/ and reproduced by the compiled reference. Still UNPINNED: OpenCV
+4.13 here against the un-versioned 3.x the reference was written for.
 
 Canonical arithmetic mode is cv2.setUseOptimized(False): the optimized cornerMinEigenVal uses
 position-dependent FMA contraction.
